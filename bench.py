@@ -1,0 +1,410 @@
+#!/usr/bin/env python
+"""Benchmark of the learner hot path (BASELINE.json metric: learner env-frames/s).
+
+    python bench.py --gpus 1 --steps 20 --warmup 5                 # our arm, one JSON line
+    python bench.py --impl reference --steps 3 --warmup 1          # reference CPU arm (oracle port)
+    torchrun --nnodes=1 --nproc-per-node N ... bench.py --gpus N   # data-parallel, weak scaling
+    python bench.py --sweep vtrace | --sweep head                  # kernel-only tables (profiles/)
+
+A "step" is one learner update (reference libs/utils.py:223-342: policy evaluation on the
+batch, V-trace targets, the three losses, backward, Adam) on one synthetic batch
+(SURVEY.md 8d).  Workload at N GPUs: BASELINE config 2 per GPU -- 16x16 map, T=80, 256 rows
+per rank (N=4 is config 3's global batch of 1024 rows).  frames/step = rows*T as the
+reference counts them (microbeast.py:230).
+
+value   = whole-job frames/s with the batch already resident in HBM.
+e2e     = the same step through the public call PPO_learn(...) with the batch in pinned HOST
+          memory: host->device copies of that step's inputs and the device->host read of the
+          four losses are inside the timed region.
+roofline= the dominant kernel of ours (head_eval_bwd, 758 B/cell), timed live with CUDA events
+          on the launching stream inside the timed region, against MEASURED_PEAKS.json.
+cpu_baseline = the oracle port of the reference's CPU path (oracle/learner.py) timed on the
+          host cores on a bounded sample of the same workload (rank 0, N=1 only).
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+METRIC = "learner_env_frames_per_sec"
+UNIT = "frames/s"
+FALLBACK_HBM_GBS = 6650.0          # B200_PROFILING.md fallback when MEASURED_PEAKS.json is absent
+
+WORKLOADS = {
+    # name: (h, w, T, rows per GPU)
+    "c1": (8, 8, 80, 32),
+    "c2": (16, 16, 80, 256),
+    "c4": (32, 32, 128, 64),
+}
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default="c2", choices=sorted(WORKLOADS))
+    ap.add_argument("--rows", type=int, default=0, help="rows per GPU (default: the workload's)")
+    ap.add_argument("--preset", default="dense")
+    ap.add_argument("--cpu-rows", type=int, default=32, help="rows of the CPU-baseline sample")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--sweep", default="", choices=["", "vtrace", "head"])
+    ap.add_argument("--out", default="", help="also append the JSON line(s) to this file")
+    return ap.parse_args()
+
+
+def hbm_peak():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    except Exception:
+        return FALLBACK_HBM_GBS, "fallback (B200_PROFILING.md)"
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled DURING the timed region."""
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index: int):
+        self.index, self.proc = index, None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                 "-lms", "100"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+        except Exception:
+            self.proc = None
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        try:
+            out, _ = self.proc.communicate(timeout=5)
+        except Exception:
+            self.proc.kill()
+            out = ""
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for line in out.strip().splitlines():
+            f = [x.strip() for x in line.split(",")]
+            if len(f) < 6:
+                continue
+            try:
+                sm.append(float(f[0])); mx.append(float(f[1]))
+            except ValueError:
+                continue
+            for name, val in zip(names, f[2:6]):
+                if val.lower().startswith("active"):
+                    reasons.add(name)
+        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "samples": len(sm), "reasons": sorted(reasons)}
+
+
+# ------------------------------------------------------------------------------------------
+# reference arm / cpu baseline: the oracle port of the reference's CPU learner step
+# ------------------------------------------------------------------------------------------
+def time_cpu_reference(h, w, T, rows, steps, warmup, preset):
+    import torch
+    from microbeast_b200 import synth
+    from oracle import NVEC_CELL
+    from oracle.learner import RefAgent, ref_learn_step
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    torch.manual_seed(1234)
+    agent = RefAgent((h, w, 27), list(NVEC_CELL) * (h * w), h * w)
+    with torch.no_grad():
+        agent.actor.weight.normal_(0, 0.01)          # reference init is all-zero
+    opt = torch.optim.Adam(agent.parameters(), lr=2.5e-4, eps=1e-5)        # microbeast.py:200
+    batch = synth.make_rollout_batch(h, w, T, rows, seed=1234, preset=preset)
+    with torch.no_grad():
+        o, _ = agent.get_action(batch, learning=True)
+    batch["logprobs"] = o["logprobs"] + 0.3 * torch.randn(o["logprobs"].shape)
+    times = []
+    for i in range(warmup + steps):
+        t0 = time.perf_counter()
+        ref_learn_step(agent, {k: v.clone() for k, v in batch.items()}, opt, rows, T, 1)
+        if i >= warmup:
+            times.append(time.perf_counter() - t0)
+    sec = sum(times) / max(len(times), 1)
+    return rows * T / sec, sec, cores
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    h, w, T, _ = WORKLOADS[args.workload]
+    rows = args.cpu_rows
+    fps, sec, cores = time_cpu_reference(h, w, T, rows, args.steps, args.warmup, args.preset)
+    sample = (f"{rows} of {args.rows or WORKLOADS[args.workload][3]} rows per step ({rows * (T + 1)} frames), "
+              f"full reference learner step (oracle port of libs/utils.py:223-342 + model.py:165-216), "
+              f"torch CPU, {cores} threads")
+    line = {
+        "impl": "reference", "metric": METRIC, "value": fps, "unit": UNIT, "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": sec * 1e3, "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": workload_config(args),
+        "cpu_baseline": {"value": fps, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
+        "e2e": {"value": fps, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    emit(line, args)
+
+
+def workload_config(args, rows_override=None):
+    h, w, T, rows = WORKLOADS[args.workload]
+    rows = rows_override or args.rows or rows
+    return {"workload": f"{args.workload}: {h}x{w} basesWorkers-shaped synthetic rollouts, T={T}, "
+                        f"{rows} rows per GPU, full learner step",
+            "map": f"{h}x{w}", "T": T, "rows_per_gpu": rows, "frames_per_step_per_gpu": rows * T,
+            "mask_preset": args.preset, "l2_policy": "inputs larger than L2 (logits alone are "
+            f"{rows * (T + 1) * h * w * 78 * 4 / 1e6:.0f} MB per GPU vs 126 MB L2)",
+            "parallelism": f"dp{args.gpus}"}
+
+
+def emit(line, args):
+    text = json.dumps(line)
+    print(text, flush=True)
+    if args.out:
+        with open(args.out, "a") as f:
+            f.write(text + "\n")
+
+
+# ------------------------------------------------------------------------------------------
+# our arm
+# ------------------------------------------------------------------------------------------
+def run_ours(args):
+    import torch
+    import torch.distributed as dist
+    from microbeast_b200 import ops, synth
+    from microbeast_b200.learner import LEARNER_KEYS, PPO_learn
+    from microbeast_b200.model import Agent
+    from microbeast_b200.parallel import GradAllReducer
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; the product path has no CPU fallback")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    torch.backends.cudnn.allow_tf32 = False          # dtype f32 means f32: no TF32 anywhere
+    torch.backends.cuda.matmul.allow_tf32 = False
+    torch.backends.cudnn.benchmark = True
+
+    h, w, T, rows = WORKLOADS[args.workload]
+    rows = args.rows or rows
+    cells = h * w
+    n = rows * (T + 1)
+    nvec = [6, 4, 4, 4, 4, 7, 49] * cells
+    torch.manual_seed(1234)                          # identical replica on every rank
+    model = Agent((h, w, 27), nvec, cells).to(dev)
+    with torch.no_grad():
+        model.actor.weight.normal_(0, 0.01)
+    model = model.to(memory_format=torch.channels_last)
+    opt = torch.optim.Adam(model.parameters(), lr=2.5e-4, eps=1e-5, fused=True)
+    reducer = GradAllReducer() if world > 1 else None
+
+    batch = synth.make_rollout_batch(h, w, T, rows, seed=1234 + rank, device=dev, preset=args.preset,
+                                     obs_dtype=torch.uint8, full_keys=False)
+    with torch.no_grad():
+        o, _ = model.get_action(batch, learning=True)
+        batch["logprobs"] = o["logprobs"] + 0.3 * torch.randn_like(o["logprobs"])
+        del o
+    dev_batch = {k: batch[k] for k in LEARNER_KEYS}
+
+    def step(b, sync):
+        return PPO_learn(model, model, "bench", b, opt, rows, T, 1, reducer=reducer, sync=sync)
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed(fn, steps, warmup, sample_clocks=False, kernel_timing=False):
+        for _ in range(warmup):
+            fn()
+        barrier()
+        sampler = ClockSampler(local) if sample_clocks else None
+        if sampler:
+            sampler.start()
+        launches0 = ops.total_launches()
+        if kernel_timing:
+            ops.start_kernel_timing()
+        t0, t1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        t0.record()
+        for _ in range(steps):
+            fn()
+        t1.record()
+        barrier()
+        ms = t0.elapsed_time(t1)
+        kt = ops.stop_kernel_timing() if kernel_timing else {}
+        clocks = sampler.stop() if sampler else None
+        if world > 1:
+            tt = torch.tensor([ms], device=dev)
+            dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+            ms = float(tt.item())
+        return ms / steps, ops.total_launches() - launches0, kt, clocks
+
+    # ---- value: batch resident in HBM -------------------------------------------------
+    ms_step, launches, ktimes, clocks = timed(lambda: step(dev_batch, False), args.steps, max(args.warmup, 3),
+                                              sample_clocks=True, kernel_timing=True)
+    frames = rows * T * world
+    value = frames / (ms_step * 1e-3)
+
+    # ---- roofline of the dominant kernel (live CUDA events from the timed region) -------
+    peak, peak_src = hbm_peak()
+    alg = {
+        "head_eval_fwd": 446 * cells * n + 8 * n,
+        "head_eval_bwd": 758 * cells * n + 8 * n,
+        "vtrace_loss": 37 * rows * T + 4 * rows,
+    }
+    kernels = {}
+    for name, ts in ktimes.items():
+        avg = sum(ts) / len(ts)
+        gbs = alg[name] / (avg * 1e-3) / 1e9 if name in alg else None
+        kernels[name] = {"launches": len(ts), "avg_ms": avg, "alg_bytes": alg.get(name),
+                         "gbs": gbs, "frac_of_peak": (gbs / peak if gbs else None)}
+    dom = "head_eval_bwd"
+    roof = None
+    if dom in kernels:
+        roof = {"kernel": dom, "bound": "hbm", "achieved": kernels[dom]["gbs"], "peak": peak, "unit": "GB/s",
+                "frac": kernels[dom]["gbs"] / peak, "traffic": None, "peak_source": peak_src,
+                "alg_bytes_per_launch": alg[dom], "avg_launch_ms": kernels[dom]["avg_ms"],
+                "kernel_share_of_step": kernels[dom]["avg_ms"] / ms_step}
+        tr = os.path.join(ROOT, "profiles", "traffic.json")       # dram bytes per launch from ncu --set full
+        if os.path.isfile(tr):
+            try:
+                roof["traffic"] = json.load(open(tr)).get(dom, {}).get(args.workload)
+            except Exception:
+                pass
+
+    # ---- e2e: host batch through the public call ---------------------------------------
+    e2e = None
+    if not args.no_e2e:
+        host = {k: torch.empty(v.shape, dtype=v.dtype, pin_memory=True).copy_(v) for k, v in dev_batch.items()}
+        h2d = sum(v.numel() * v.element_size() for v in host.values())
+        e2e_steps = max(3, min(args.steps, 10))
+        ms_e2e, _, _, _ = timed(lambda: step(host, True), e2e_steps, 3)
+        e2e = {"value": frames / (ms_e2e * 1e-3), "unit": UNIT, "h2d_bytes_per_step": h2d * world,
+               "d2h_bytes_per_step": 16 * world, "ms_per_step": ms_e2e, "steps": e2e_steps,
+               "call": "microbeast_b200.learner.PPO_learn(model, model, name, pinned_host_batch, adam, rows, T, 1)",
+               "wire_format": "obs u8, action_mask u8, action i64, reward/logprobs f32, done bool"}
+        del host
+
+    # ---- cpu baseline (rank 0, N=1) ------------------------------------------------------
+    cpu = None
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        crow = args.cpu_rows
+        fps, sec, cores = time_cpu_reference(h, w, T, crow, 2, 1, args.preset)
+        cpu = {"value": fps, "unit": UNIT, "cores": cores, "kind": "port",
+               "sample": f"{crow} of {rows} rows ({crow * (T + 1)} frames) per step, 2 timed steps after 1 "
+                         f"warm-up, full reference learner step on torch CPU ({sec:.2f} s/step)"}
+
+    if rank == 0:
+        line = {
+            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+            "warmup": max(args.warmup, 3), "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f32", "data": "synthetic", "config": workload_config(args),
+            "clocks": clocks, "e2e": e2e, "gpu_launches": launches, "roofline": roof, "cpu_baseline": cpu,
+            "kernels": kernels,
+        }
+        emit(line, args)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+# ------------------------------------------------------------------------------------------
+# kernel-only sweeps (profiles/): BASELINE config 5 and the head kernels at configs 1-4
+# ------------------------------------------------------------------------------------------
+def run_sweep(args):
+    import torch
+    from microbeast_b200 import ops, synth
+    dev = torch.device("cuda", 0)
+    peak, peak_src = hbm_peak()
+    g = torch.Generator(device=dev).manual_seed(1)
+    flush = torch.empty(512 << 20, dtype=torch.uint8, device=dev)        # > 126 MB L2
+
+    def bench(fn, iters):
+        ts = []
+        for i in range(3 + iters):
+            flush.zero_()
+            s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            s.record(); fn(); e.record()
+            torch.cuda.synchronize()
+            if i >= 3:
+                ts.append(s.elapsed_time(e))
+        ts.sort()
+        return ts[len(ts) // 2], ts[max(0, len(ts) // 10)], ts[min(len(ts) - 1, (9 * len(ts)) // 10)]
+
+    rows_out = []
+    if args.sweep == "vtrace":
+        for T in (20, 80, 256, 512):
+            for R in (256, 1024, 4096, 16384, 65536):
+                t = synth.make_vtrace_inputs(R, T, gen=g, device=dev)
+                fn = lambda: ops.vtrace_loss(t["lp_old"], t["lp_new"], t["values"], t["bootstrap"], t["rewards"],
+                                             t["done"], t["entropy"])
+                med, p10, p90 = bench(fn, 20)
+                nbytes = 37 * R * T + 4 * R
+                gbs = nbytes / (med * 1e-3) / 1e9
+                rows_out.append({"kernel": "vtrace_loss", "T": T, "rows": R, "elements": R * T, "median_us": med * 1e3,
+                                 "p10_us": p10 * 1e3, "p90_us": p90 * 1e3, "alg_bytes": nbytes, "gbs": gbs,
+                                 "frac_of_peak": gbs / peak,
+                                 "regime": "hbm" if R * T >= 8_000_000 else "latency-bound (L2 resident / launch)"})
+                del t
+    else:
+        for name, (h, w, T, rows) in WORKLOADS.items():
+            cells, n = h * w, rows * (T + 1)
+            logits = synth.make_logits(n, cells, gen=g, device=dev)
+            mask = synth.make_masks(n, cells, args.preset, gen=g, device=dev)
+            act = synth.make_valid_actions(mask, gen=g)
+            u = synth.make_uniforms(n, cells, gen=g, device=dev)
+            gl = torch.randn(n, generator=g, device=dev)
+            out = torch.empty_like(logits)
+            for kname, fn, per_cell, per_frame in (
+                    ("head_eval_fwd", lambda: ops.head_eval_fwd(logits, mask, act), 446, 8),
+                    ("head_eval_bwd", lambda: ops.head_eval_bwd(logits, mask, act, gl, gl, out=out), 758, 8),
+                    ("head_sample", lambda: ops.head_sample(logits, mask, u), 474, 8)):
+                med, p10, p90 = bench(fn, 10)
+                nbytes = per_cell * cells * n + per_frame * n
+                gbs = nbytes / (med * 1e-3) / 1e9
+                rows_out.append({"kernel": kname, "workload": name, "frames": n, "cells": cells,
+                                 "median_us": med * 1e3, "p10_us": p10 * 1e3, "p90_us": p90 * 1e3,
+                                 "alg_bytes": nbytes, "gbs": gbs, "frac_of_peak": gbs / peak})
+            del logits, mask, act, u, out
+    for r in rows_out:
+        r["peak_gbs"] = peak
+        r["peak_source"] = peak_src
+        emit(r, args)
+
+
+def main():
+    args = parse_args()
+    if args.sweep:
+        run_sweep(args)
+    elif args.impl == "reference":
+        run_reference(args)
+    else:
+        run_ours(args)
+
+
+if __name__ == "__main__":
+    main()

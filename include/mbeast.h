@@ -1,0 +1,113 @@
+/* microbeast_b200 -- C ABI of the B200 (sm_100a) learner hot path.
+ *
+ * The reference (Neos-codes/microbeast) has no FFI: its seam for this path is the Python call
+ * surface of model.py / libs/utils.py.  These entry points are what a binding for that seam
+ * calls; each comment names the reference code the entry point replaces.  Plain pointers and
+ * sizes only (no torch types).  See INTEGRATION.md for the ctypes binding a maintainer adds.
+ *
+ * Conventions
+ *  - every pointer is a DEVICE pointer unless stated; tensors are contiguous row-major;
+ *  - the library never allocates or frees device memory; callers own every buffer;
+ *  - every call is an asynchronous launch on `stream` (a cudaStream_t passed as void*; NULL =
+ *    the legacy default stream); no call synchronises or reads device results on the host;
+ *  - return value 0 = ok; otherwise an MB_ERR_* code and mb_last_error() holds a message
+ *    (thread-local string, valid until the next failing call on the same thread);
+ *  - `status` (optional, may be NULL) is a device int32 the kernels OR bits into:
+ *      MB_STATUS_BAD_ACTION  an action index outside [0, n_k) was seen (clamped; torch's
+ *                            Categorical(validate_args=True) raises ValueError there)
+ *      MB_STATUS_TIMEOUT     an internal pipeline wait gave up (kernel bug guard)
+ *    callers zero it once and check it whenever they synchronise anyway.
+ *
+ * Geometry: a map of `cells` = h*w cells; 78 logits / mask bytes and 7 components per cell,
+ * split 6/4/4/4/4/7/49 (reference microbeast.py:145, libs/utils.py:40-44).
+ */
+#ifndef MBEAST_H_
+#define MBEAST_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#if defined(__GNUC__)
+#define MB_API __attribute__((visibility("default")))
+#else
+#define MB_API
+#endif
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define MB_OK 0
+#define MB_ERR_INVALID 1
+#define MB_ERR_CUDA 2
+#define MB_ERR_UNSUPPORTED 3
+
+#define MB_STATUS_BAD_ACTION 1
+#define MB_STATUS_TIMEOUT 2
+
+/* Library ABI version (major*100 + minor). */
+MB_API int mb_version(void);
+
+/* Message of the last failing call on this thread ("" if none). */
+MB_API const char* mb_last_error(void);
+
+/* Learner branch of Agent.get_action after the actor Linear: reference model.py:180-214
+ * (torch.split -> 7*cells CategoricalMasked objects, model.py:33-52 -> log_prob / entropy ->
+ * sums over the 7*cells components of a frame).
+ *   logits [n_frames, 78*cells] f32, mask [n_frames, 78*cells] u8 (non-zero = valid),
+ *   action [n_frames, 7*cells] i64  ->  logp_out [n_frames] f32, ent_out [n_frames] f32. */
+MB_API int mb_head_eval_fwd(const float* logits, const uint8_t* mask, const int64_t* action, float* logp_out,
+                     float* ent_out, int64_t n_frames, int32_t cells, int32_t* status, void* stream);
+
+/* Autograd of the above (reference: total_loss.backward(), libs/utils.py:334, through the
+ * ~10*7*cells graph nodes built by model.py:190-196).  g_logp / g_ent [n_frames] are the
+ * upstream gradients of logp_out / ent_out; dlogits_out [n_frames, 78*cells] f32 is written in
+ * full (masked entries and fully masked components get exactly 0). */
+MB_API int mb_head_eval_bwd(const float* logits, const uint8_t* mask, const int64_t* action, const float* g_logp,
+                     const float* g_ent, float* dlogits_out, int64_t n_frames, int32_t cells, int32_t* status,
+                     void* stream);
+
+/* Actor branch of Agent.get_action: reference model.py:171-177,194-210 (Categorical.sample ->
+ * torch.multinomial on the global RNG).  Sampling here is inverse-CDF from caller-supplied
+ * uniforms [n_frames, 7*cells] f32 in [0,1) as defined in oracle/head.py:sample_invcdf
+ * (a = #{k < n-1 : u >= cdf_k}, fp64-exact decision).  action_out [n_frames, 7*cells] i64,
+ * logp_out [n_frames] f32 (log-prob of the sampled action), ent_out [n_frames] f32 or NULL. */
+MB_API int mb_head_sample(const float* logits, const uint8_t* mask, const float* uniforms, int64_t* action_out,
+                   float* logp_out, float* ent_out, int64_t n_frames, int32_t cells, int32_t* status,
+                   void* stream);
+
+/* Bytes of scratch mb_vtrace_loss needs for `rows` rows (ticket word + per-CTA partial sums). */
+MB_API size_t mb_vtrace_workspace_bytes(int64_t rows);
+
+/* V-trace + losses: the inline block of PPO_learn, reference libs/utils.py:277-329, and the
+ * gradients autograd derives from utils.py:320-329.
+ *   inputs  [rows, T], time contiguous, `in_row_stride` elements between rows:
+ *           lp_old (behaviour log-prob), lp_new (learner log-prob), values, rewards, entropy f32,
+ *           done u8/bool;  bootstrap [rows] f32 (= V at slot T, utils.py:258)
+ *   outputs [rows, T], `out_row_stride` elements between rows: vs_out, adv_out f32 and, when both
+ *           are non-NULL, dlp_out = adv * inv_n and dV_out = -(vs - V) * inv_n
+ *           (d total / d entropy is the constant -ent_coef * inv_n);
+ *           loss4_out [4] f32 = {pg, value, entropy, total} with means taken as sum * inv_n.
+ *   gamma, rho_bar, c_bar, pg_rho_bar, ent_coef: the reference hard-codes 0.99, 1, 1, 1, 0.01.
+ *   inv_n: 1 / (global rows * T) for data-parallel shards; <= 0 means 1 / (rows * T).
+ *   workspace: >= mb_vtrace_workspace_bytes(rows) bytes, 8-byte aligned; its first 4 bytes must
+ *           be zero before the FIRST call (the kernel restores the zero itself), and two calls
+ *           that may overlap on the GPU must not share a workspace.
+ * Uses TMA tiles when pointers are 16-byte aligned, in_row_stride % 16 == 0 and
+ * out_row_stride % 4 == 0; any other layout takes a slower generic kernel with equal results. */
+MB_API int mb_vtrace_loss(const float* lp_old, const float* lp_new, const float* values, const float* bootstrap,
+                   const float* rewards, const uint8_t* done, const float* entropy, int64_t rows, int32_t T,
+                   int64_t in_row_stride, int64_t out_row_stride, float gamma, float rho_bar, float c_bar,
+                   float pg_rho_bar, float ent_coef, float inv_n, float* vs_out, float* adv_out, float* loss4_out,
+                   float* dlp_out, float* dV_out, void* workspace, size_t workspace_bytes, void* stream);
+
+/* Tuning knobs for benchmarking (not part of the reference surface).  Keys:
+ *   "head_ctas_per_sm" (default 2), "head_grid" (0 = auto),
+ *   "vtrace_force_generic" (0/1), "vtrace_stages" (2, 3 or 4).
+ * Returns MB_ERR_INVALID for an unknown key. */
+MB_API int mb_set_tuning(const char* key, int32_t value);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* MBEAST_H_ */

@@ -1,0 +1,98 @@
+// extern "C" surface of libmbeast_sm100.so (declared in include/mbeast.h) and host plumbing.
+#include "common.cuh"
+
+#include <stdarg.h>
+#include <stdio.h>
+#include <string.h>
+
+#include "../../include/mbeast.h"
+
+namespace mb {
+
+static thread_local char g_err[512] = "";
+
+void set_error(const char* fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof(g_err), fmt, ap);
+    va_end(ap);
+}
+
+int cuda_fail(cudaError_t e, const char* what) {
+    set_error("CUDA error %d (%s) in %s", int(e), cudaGetErrorString(e), what);
+    return MB_ERR_CUDA;
+}
+
+int sm_count(int device) {
+    static int cached[64] = {};
+    if (device >= 0 && device < 64 && cached[device] > 0) return cached[device];
+    int n = 0;
+    if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, device) != cudaSuccess || n <= 0) n = 148;
+    if (device >= 0 && device < 64) cached[device] = n;
+    return n;
+}
+
+// implemented in head.cu / vtrace.cu
+int head_eval_fwd(const float*, const uint8_t*, const int64_t*, float*, float*, long long, int, int*, cudaStream_t);
+int head_eval_bwd(const float*, const uint8_t*, const int64_t*, const float*, const float*, float*, long long, int,
+                  int*, cudaStream_t);
+int head_sample(const float*, const uint8_t*, const float*, int64_t*, float*, float*, long long, int, int*,
+                cudaStream_t);
+void head_set_tuning(int ctas_per_sm, int grid_override);
+void vtrace_set_tuning(int force_generic, int stages);
+size_t vtrace_workspace_bytes(long long rows);
+
+struct VtParams;
+}  // namespace mb
+
+// VtParams is defined in vtrace.cu; the C entry point lives there too (mb_vtrace_loss) so the
+// struct stays private to that translation unit.
+
+extern "C" {
+
+int mb_version(void) { return 100; }
+
+const char* mb_last_error(void) { return mb::g_err; }
+
+int mb_head_eval_fwd(const float* logits, const uint8_t* mask, const int64_t* action, float* logp_out,
+                     float* ent_out, int64_t n_frames, int32_t cells, int32_t* status, void* stream) {
+    return mb::head_eval_fwd(logits, mask, action, logp_out, ent_out, n_frames, cells, status,
+                             static_cast<cudaStream_t>(stream));
+}
+
+int mb_head_eval_bwd(const float* logits, const uint8_t* mask, const int64_t* action, const float* g_logp,
+                     const float* g_ent, float* dlogits_out, int64_t n_frames, int32_t cells, int32_t* status,
+                     void* stream) {
+    return mb::head_eval_bwd(logits, mask, action, g_logp, g_ent, dlogits_out, n_frames, cells, status,
+                             static_cast<cudaStream_t>(stream));
+}
+
+int mb_head_sample(const float* logits, const uint8_t* mask, const float* uniforms, int64_t* action_out,
+                   float* logp_out, float* ent_out, int64_t n_frames, int32_t cells, int32_t* status,
+                   void* stream) {
+    return mb::head_sample(logits, mask, uniforms, action_out, logp_out, ent_out, n_frames, cells, status,
+                           static_cast<cudaStream_t>(stream));
+}
+
+size_t mb_vtrace_workspace_bytes(int64_t rows) { return mb::vtrace_workspace_bytes(rows); }
+
+int mb_set_tuning(const char* key, int32_t value) {
+    static int head_ctas = 2, head_grid = 0, vt_generic = 0, vt_stages = 3;
+    if (!key) {
+        mb::set_error("mb_set_tuning: null key");
+        return MB_ERR_INVALID;
+    }
+    if (!strcmp(key, "head_ctas_per_sm")) head_ctas = value;
+    else if (!strcmp(key, "head_grid")) head_grid = value;
+    else if (!strcmp(key, "vtrace_force_generic")) vt_generic = value;
+    else if (!strcmp(key, "vtrace_stages")) vt_stages = value;
+    else {
+        mb::set_error("mb_set_tuning: unknown key '%s'", key);
+        return MB_ERR_INVALID;
+    }
+    mb::head_set_tuning(head_ctas, head_grid);
+    mb::vtrace_set_tuning(vt_generic, vt_stages);
+    return MB_OK;
+}
+
+}  // extern "C"

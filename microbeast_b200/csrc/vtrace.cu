@@ -1,0 +1,464 @@
+// V-trace targets / advantages fused with the pg / baseline / entropy loss reduction and their
+// gradients, for sm_100a.
+//
+// Replaces the inline block of reference libs/utils.py:277-329 (PPO_learn): importance weights
+// rho = c = min(1, exp(lp_new - lp_old)), the reverse-time Python loop of utils.py:302-304, vs,
+// pg_advantages, and the three .mean() reductions + total (utils.py:320-329), plus the autograd
+// of those means (d/dlp_new = adv/n, d/dV = -(vs - V)/n, d/dentropy = -coef/n).
+//
+// Layout (reference D2): every input is [R, T] with TIME contiguous.  The recurrence is serial in
+// time and independent per row, so one thread owns one row.  A thread walking its row backwards
+// in time straight from global memory would touch 32 different 128-B lines per warp request;
+// instead each 32-thread CTA stages [32 rows x 32 steps] tiles of the six inputs through TMA
+// (cp.async.bulk.tensor.2d, SASS UTMALDG; 128-B swizzle so that per-thread float4 reads are bank
+// conflict free) into a multi-stage shared-memory ring, walks the time tiles from the end,
+// overwrites the tiles in place with vs / adv / d_logp / d_values and writes them back with TMA
+// stores (UTMASTG).  Loss sums are carried per thread (fp32 inside a tile, fp64 across tiles),
+// reduced by a fixed shuffle tree, written per CTA to a workspace and folded by the last CTA to
+// arrive (ticket counter) in a fixed order: deterministic, one launch, no float atomics.
+//
+// Roofline: HBM-bound, 29 B per [r,t] element forward (+8 B with the two gradient outputs).
+// Shapes below ~1e7 elements are launch/latency bound and L2 resident.
+#include "common.cuh"
+
+#include <cuda.h>
+#include <math.h>
+#include <string.h>
+
+namespace mb {
+
+struct VtParams {
+    const float* lp_old;
+    const float* lp_new;
+    const float* values;
+    const float* rewards;
+    const float* entropy;
+    const uint8_t* done;
+    const float* bootstrap;
+    float* vs;
+    float* adv;
+    float* dlp;      // may be null
+    float* dv;       // may be null
+    float* loss4;    // [pg, value, entropy, total]
+    double* partials;        // [grid][3]
+    unsigned int* ticket;    // zero on entry, reset to zero by the last CTA
+    long long rows;
+    int T;
+    long long in_stride;     // elements between consecutive rows of the inputs
+    long long out_stride;    // elements between consecutive rows of the outputs
+    float gamma, rho_bar, c_bar, pg_rho_bar, ent_coef, inv_n;
+};
+
+struct VtMaps {
+    CUtensorMap lp_old, lp_new, values, rewards, entropy, done, vs, adv, dlp, dv;
+};
+
+struct VtCarry {
+    float acc;       // vs_{t+1} - V_{t+1}   (utils.py:300: starts at 0)
+    float v_next;    // V_{t+1}              (utils.py:296: bootstrap at the end)
+    float vs_next;   // vs_{t+1}             (utils.py:313-314)
+};
+
+struct VtStepOut {
+    float vs, adv;
+};
+
+// One time step of utils.py:277-318 for one row.  Every product and sum is rounded separately
+// (__fmul_rn / __fadd_rn: no FMA contraction), in the reference's left-to-right order, so the
+// only arithmetic difference to the CPU torch path is the last ulp of expf.
+__device__ __forceinline__ VtStepOut vt_step(const VtParams& p, float lp_old, float lp_new, float v, float rew,
+                                             bool done, VtCarry& c) {
+    const float disc = done ? 0.0f : p.gamma;                                   // utils.py:277
+    const float ratio_exp = expf(__fsub_rn(lp_new, lp_old));                    // utils.py:285,290
+    const float rho = fminf(ratio_exp, p.rho_bar);                              // utils.py:293
+    const float cs = fminf(ratio_exp, p.c_bar);                                 // utils.py:294
+    const float delta =
+        __fmul_rn(rho, __fsub_rn(__fadd_rn(rew, __fmul_rn(disc, c.v_next)), v));        // utils.py:298
+    c.acc = __fadd_rn(delta, __fmul_rn(__fmul_rn(disc, cs), c.acc));            // utils.py:303
+    VtStepOut o;
+    o.vs = __fadd_rn(c.acc, v);                                                 // utils.py:310
+    const float pg_rho = fminf(rho, p.pg_rho_bar);                              // utils.py:316
+    o.adv = __fmul_rn(pg_rho, __fsub_rn(__fadd_rn(rew, __fmul_rn(disc, c.vs_next)), v));  // utils.py:318
+    c.v_next = v;
+    c.vs_next = o.vs;
+    return o;
+}
+
+// Folds the per-CTA partial sums; executed by one warp of the last CTA to arrive.
+__device__ __forceinline__ void vt_finalize(const VtParams& p, int lane) {
+    double s[3] = {0.0, 0.0, 0.0};
+    for (unsigned int b = lane; b < gridDim.x; b += 32) {
+#pragma unroll
+        for (int i = 0; i < 3; ++i) s[i] += __ldcg(p.partials + size_t(b) * 3 + i);
+    }
+#pragma unroll
+    for (int i = 0; i < 3; ++i) s[i] = warp_sum(s[i]);
+    if (lane == 0) {
+        const double n_inv = double(p.inv_n);
+        const float pg = float(s[0] * n_inv);                    // utils.py:320
+        const float vl = float(0.5 * s[1] * n_inv);              // utils.py:323
+        const float en = float(s[2] * n_inv);                    // utils.py:326
+        p.loss4[0] = pg;
+        p.loss4[1] = vl;
+        p.loss4[2] = en;
+        p.loss4[3] = __fsub_rn(__fadd_rn(pg, vl), __fmul_rn(p.ent_coef, en));   // utils.py:329
+        *p.ticket = 0u;
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+// TMA kernel: one warp per CTA, 32 rows, time tiles of 32 steps walked from the end.
+// ---------------------------------------------------------------------------------------------
+constexpr int kVtRows = 32;
+constexpr int kVtSteps = 32;
+constexpr int kVtTileF32 = kVtRows * kVtSteps * 4;     // 4096 B, 128-B rows, SWIZZLE_128B
+constexpr int kVtTileU8 = kVtRows * kVtSteps;          // 1024 B, 32-B rows, no swizzle
+constexpr int kVtStageBytes = 5 * kVtTileF32 + kVtTileU8;   // 21504 B (multiple of 1024)
+
+template <int NSTAGE>
+__global__ void __launch_bounds__(32) vtrace_tma_kernel(const __grid_constant__ VtMaps maps, const VtParams p) {
+    extern __shared__ uint8_t smem_raw[];
+    __shared__ __align__(8) uint64_t full[NSTAGE];
+    // SWIZZLE_128B needs 1024-B aligned tiles
+    uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
+
+    const int lane = threadIdx.x;
+    const int row0 = blockIdx.x * kVtRows;
+    const long long row = (long long)row0 + lane;
+    const bool row_ok = row < p.rows;
+    const bool want_grads = (p.dlp != nullptr);
+
+    if (lane == 0) {
+        for (int s = 0; s < NSTAGE; ++s) mbar_init(&full[s], 1);
+        fence_mbar_init();
+        tma_prefetch_desc(&maps.lp_old);
+        tma_prefetch_desc(&maps.lp_new);
+        tma_prefetch_desc(&maps.values);
+        tma_prefetch_desc(&maps.rewards);
+        tma_prefetch_desc(&maps.entropy);
+        tma_prefetch_desc(&maps.done);
+    }
+    __syncwarp();
+
+    const int nt = (p.T + kVtSteps - 1) / kVtSteps;
+
+    auto issue_load = [&](int k) {        // lane 0 only; k counts tiles from the END of the rows
+        const int s = k % NSTAGE;
+        const int t0 = (nt - 1 - k) * kVtSteps;
+        uint8_t* st = smem + size_t(s) * kVtStageBytes;
+        mbar_arrive_expect_tx(&full[s], uint32_t(kVtStageBytes));
+        tma_load_2d(st + 0 * kVtTileF32, &maps.lp_old, t0, row0, &full[s]);
+        tma_load_2d(st + 1 * kVtTileF32, &maps.lp_new, t0, row0, &full[s]);
+        tma_load_2d(st + 2 * kVtTileF32, &maps.values, t0, row0, &full[s]);
+        tma_load_2d(st + 3 * kVtTileF32, &maps.rewards, t0, row0, &full[s]);
+        tma_load_2d(st + 4 * kVtTileF32, &maps.entropy, t0, row0, &full[s]);
+        tma_load_2d(st + 5 * kVtTileF32, &maps.done, t0, row0, &full[s]);
+    };
+
+    if (lane == 0) {
+        for (int k = 0; k < NSTAGE - 1 && k < nt; ++k) issue_load(k);
+    }
+
+    VtCarry carry;
+    carry.acc = 0.0f;
+    carry.v_next = row_ok ? __ldg(p.bootstrap + row) : 0.0f;
+    carry.vs_next = carry.v_next;
+    double s_pg = 0.0, s_v = 0.0, s_en = 0.0;
+
+    for (int k = 0; k < nt; ++k) {
+        const int s = k % NSTAGE;
+        mbar_wait(&full[s], uint32_t((k / NSTAGE) & 1), nullptr);
+
+        uint8_t* st = smem + size_t(s) * kVtStageBytes;
+        const int t0 = (nt - 1 - k) * kVtSteps;
+        float t_pg = 0.0f, t_v = 0.0f, t_en = 0.0f;
+#pragma unroll
+        for (int j = kVtSteps / 4 - 1; j >= 0; --j) {
+            const uint32_t off = uint32_t(lane) * 128u + (uint32_t(j ^ (lane & 7)) << 4);
+            float4 a_old = *reinterpret_cast<const float4*>(st + 0 * kVtTileF32 + off);
+            float4 a_new = *reinterpret_cast<const float4*>(st + 1 * kVtTileF32 + off);
+            float4 a_val = *reinterpret_cast<const float4*>(st + 2 * kVtTileF32 + off);
+            float4 a_rew = *reinterpret_cast<const float4*>(st + 3 * kVtTileF32 + off);
+            float4 a_ent = *reinterpret_cast<const float4*>(st + 4 * kVtTileF32 + off);
+            const uint32_t dn = *reinterpret_cast<const uint32_t*>(st + 5 * kVtTileF32 + lane * 32 + j * 4);
+            float lo[4] = {a_old.x, a_old.y, a_old.z, a_old.w};
+            float ln[4] = {a_new.x, a_new.y, a_new.z, a_new.w};
+            float vv[4] = {a_val.x, a_val.y, a_val.z, a_val.w};
+            float rw[4] = {a_rew.x, a_rew.y, a_rew.z, a_rew.w};
+            float en[4] = {a_ent.x, a_ent.y, a_ent.z, a_ent.w};
+            float o_vs[4], o_adv[4], o_dlp[4], o_dv[4];
+#pragma unroll
+            for (int i = 3; i >= 0; --i) {
+                const int t = t0 + 4 * j + i;
+                o_vs[i] = 0.f; o_adv[i] = 0.f; o_dlp[i] = 0.f; o_dv[i] = 0.f;
+                if (t < p.T && row_ok) {
+                    const bool dflag = ((dn >> (8 * i)) & 0xffu) != 0;
+                    const VtStepOut o = vt_step(p, lo[i], ln[i], vv[i], rw[i], dflag, carry);
+                    o_vs[i] = o.vs;
+                    o_adv[i] = o.adv;
+                    const float dvs = __fsub_rn(o.vs, vv[i]);
+                    o_dlp[i] = o.adv * p.inv_n;
+                    o_dv[i] = -dvs * p.inv_n;
+                    t_pg = __fadd_rn(t_pg, __fmul_rn(ln[i], o.adv));
+                    t_v = __fadd_rn(t_v, __fmul_rn(dvs, dvs));
+                    t_en = __fadd_rn(t_en, en[i]);
+                }
+            }
+            // in place: vs over rewards, adv over lp_old, d_logp over lp_new, d_values over entropy
+            *reinterpret_cast<float4*>(st + 3 * kVtTileF32 + off) = make_float4(o_vs[0], o_vs[1], o_vs[2], o_vs[3]);
+            *reinterpret_cast<float4*>(st + 0 * kVtTileF32 + off) = make_float4(o_adv[0], o_adv[1], o_adv[2], o_adv[3]);
+            if (want_grads) {
+                *reinterpret_cast<float4*>(st + 1 * kVtTileF32 + off) =
+                    make_float4(o_dlp[0], o_dlp[1], o_dlp[2], o_dlp[3]);
+                *reinterpret_cast<float4*>(st + 4 * kVtTileF32 + off) = make_float4(o_dv[0], o_dv[1], o_dv[2], o_dv[3]);
+            }
+        }
+        s_pg += double(t_pg);
+        s_v += double(t_v);
+        s_en += double(t_en);
+
+        fence_proxy_async_smem();
+        __syncwarp();
+        if (lane == 0) {
+            tma_store_2d(&maps.vs, t0, row0, st + 3 * kVtTileF32);
+            tma_store_2d(&maps.adv, t0, row0, st + 0 * kVtTileF32);
+            if (want_grads) {
+                tma_store_2d(&maps.dlp, t0, row0, st + 1 * kVtTileF32);
+                tma_store_2d(&maps.dv, t0, row0, st + 4 * kVtTileF32);
+            }
+            bulk_commit();
+            if (k + NSTAGE - 1 < nt) {
+                // tile k+NSTAGE-1 goes into the stage tile k-1 was stored from; its store group was
+                // committed one iteration ago, so this wait normally returns at once
+                if (k >= 1) bulk_wait_read<1>();
+                issue_load(k + NSTAGE - 1);
+            }
+        }
+    }
+
+    s_pg = warp_sum(s_pg);
+    s_v = warp_sum(s_v);
+    s_en = warp_sum(s_en);
+    unsigned int tk = 0;
+    if (lane == 0) {
+        bulk_wait_all<0>();     // output tiles are in global memory before the CTA retires
+        p.partials[size_t(blockIdx.x) * 3 + 0] = s_pg;
+        p.partials[size_t(blockIdx.x) * 3 + 1] = s_v;
+        p.partials[size_t(blockIdx.x) * 3 + 2] = s_en;
+        __threadfence();
+        tk = atomicAdd(p.ticket, 1u);
+    }
+    tk = __shfl_sync(0xffffffffu, tk, 0);
+    if (tk == gridDim.x - 1) {
+        __threadfence();
+        vt_finalize(p, lane);
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+// Generic kernel: any stride / alignment (e.g. T = 20, sliced [R, T+1] views).  One thread per
+// row reading global memory directly; correct everywhere, fast nowhere.
+// ---------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(128) vtrace_generic_kernel(const VtParams p) {
+    __shared__ double red[4][3];
+    __shared__ unsigned int tk_s;
+    const long long row = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    double s_pg = 0.0, s_v = 0.0, s_en = 0.0;
+    if (row < p.rows) {
+        const long long ib = row * p.in_stride, ob = row * p.out_stride;
+        VtCarry carry;
+        carry.acc = 0.0f;
+        carry.v_next = p.bootstrap[row];
+        carry.vs_next = carry.v_next;
+        float t_pg = 0.f, t_v = 0.f, t_en = 0.f;
+        for (int t = p.T - 1; t >= 0; --t) {
+            const float v = p.values[ib + t], ln = p.lp_new[ib + t];
+            const VtStepOut o = vt_step(p, p.lp_old[ib + t], ln, v, p.rewards[ib + t], p.done[ib + t] != 0, carry);
+            p.vs[ob + t] = o.vs;
+            p.adv[ob + t] = o.adv;
+            const float dvs = __fsub_rn(o.vs, v);
+            if (p.dlp) p.dlp[ob + t] = o.adv * p.inv_n;
+            if (p.dv) p.dv[ob + t] = -dvs * p.inv_n;
+            t_pg = __fadd_rn(t_pg, __fmul_rn(ln, o.adv));
+            t_v = __fadd_rn(t_v, __fmul_rn(dvs, dvs));
+            t_en = __fadd_rn(t_en, p.entropy[ib + t]);
+            if ((t & 31) == 0) {
+                s_pg += double(t_pg); s_v += double(t_v); s_en += double(t_en);
+                t_pg = t_v = t_en = 0.f;
+            }
+        }
+    }
+    s_pg = warp_sum(s_pg);
+    s_v = warp_sum(s_v);
+    s_en = warp_sum(s_en);
+    if (lane == 0) {
+        red[warp][0] = s_pg; red[warp][1] = s_v; red[warp][2] = s_en;
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        for (int i = 0; i < 3; ++i)
+            p.partials[size_t(blockIdx.x) * 3 + i] = red[0][i] + red[1][i] + red[2][i] + red[3][i];
+        __threadfence();
+        tk_s = atomicAdd(p.ticket, 1u);
+    }
+    __syncthreads();
+    if (tk_s == gridDim.x - 1 && warp == 0) {
+        __threadfence();
+        vt_finalize(p, lane);
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+// Host side
+// ---------------------------------------------------------------------------------------------
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static EncodeTiledFn get_encode_fn() {
+    static EncodeTiledFn fn = nullptr;
+    static bool tried = false;
+    if (!tried) {
+        tried = true;
+        void* ptr = nullptr;
+        cudaDriverEntryPointQueryResult qres;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &ptr, cudaEnableDefault, &qres) == cudaSuccess &&
+            qres == cudaDriverEntryPointSuccess)
+            fn = reinterpret_cast<EncodeTiledFn>(ptr);
+    }
+    return fn;
+}
+
+static bool make_map_2d(EncodeTiledFn enc, CUtensorMap* m, const void* base, bool is_u8, long long rows, int T,
+                        long long stride_elems) {
+    const cuuint64_t gdim[2] = {cuuint64_t(T), cuuint64_t(rows)};
+    const cuuint64_t gstride[1] = {cuuint64_t(stride_elems) * (is_u8 ? 1u : 4u)};
+    const cuuint32_t box[2] = {cuuint32_t(kVtSteps), cuuint32_t(kVtRows)};
+    const cuuint32_t estr[2] = {1, 1};
+    CUresult r = enc(m, is_u8 ? CU_TENSOR_MAP_DATA_TYPE_UINT8 : CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2,
+                     const_cast<void*>(base), gdim, gstride, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                     is_u8 ? CU_TENSOR_MAP_SWIZZLE_NONE : CU_TENSOR_MAP_SWIZZLE_128B,
+                     CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    return r == CUDA_SUCCESS;
+}
+
+static int g_vt_force_generic = 0;
+static int g_vt_stages = 3;
+void vtrace_set_tuning(int force_generic, int stages) {
+    g_vt_force_generic = force_generic;
+    if (stages == 2 || stages == 3 || stages == 4) g_vt_stages = stages;
+}
+
+size_t vtrace_workspace_bytes(long long rows) {
+    if (rows < 0) rows = 0;
+    const size_t ctas = size_t((rows + kVtRows - 1) / kVtRows);     // the generic kernel uses fewer
+    return 256 + (ctas + 1) * 3 * sizeof(double);
+}
+
+static inline bool al16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; }
+
+template <int NSTAGE>
+static int launch_vt_tma(const VtMaps& maps, const VtParams& p, cudaStream_t stream) {
+    constexpr size_t smem = size_t(NSTAGE) * kVtStageBytes + 1024;
+    static bool attr_set[64] = {};
+    int dev = 0;
+    MB_CUDA(cudaGetDevice(&dev));
+    if (dev < 64 && !attr_set[dev]) {
+        MB_CUDA(cudaFuncSetAttribute(vtrace_tma_kernel<NSTAGE>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                     int(smem)));
+        attr_set[dev] = true;
+    }
+    const unsigned grid = unsigned((p.rows + kVtRows - 1) / kVtRows);
+    vtrace_tma_kernel<NSTAGE><<<grid, 32, smem, stream>>>(maps, p);
+    MB_CUDA(cudaGetLastError());
+    return MB_OK;
+}
+
+// `scratch` holds the ticket word at offset 0 (must be zero on entry; the kernel leaves it zero)
+// and the per-CTA partial sums from offset 256.
+int vtrace_loss_launch(VtParams p, void* scratch, size_t scratch_bytes, cudaStream_t stream) {
+    if (p.rows < 0 || p.T <= 0) {
+        set_error("vtrace_loss: rows=%lld T=%d out of range", p.rows, p.T);
+        return MB_ERR_INVALID;
+    }
+    if (!p.loss4) {
+        set_error("vtrace_loss: null loss4_out pointer");
+        return MB_ERR_INVALID;
+    }
+    if (p.rows == 0) {
+        MB_CUDA(cudaMemsetAsync(p.loss4, 0, 4 * sizeof(float), stream));
+        return MB_OK;
+    }
+    if (!p.lp_old || !p.lp_new || !p.values || !p.rewards || !p.entropy || !p.done || !p.bootstrap || !p.vs ||
+        !p.adv) {
+        set_error("vtrace_loss: null input/output pointer");
+        return MB_ERR_INVALID;
+    }
+    if ((p.dlp == nullptr) != (p.dv == nullptr)) {
+        set_error("vtrace_loss: dlp_out and dV_out must both be given or both be null");
+        return MB_ERR_INVALID;
+    }
+    if (p.in_stride < p.T || p.out_stride < p.T) {
+        set_error("vtrace_loss: row stride smaller than T");
+        return MB_ERR_INVALID;
+    }
+    if (!scratch || scratch_bytes < vtrace_workspace_bytes(p.rows) || (reinterpret_cast<uintptr_t>(scratch) & 7)) {
+        set_error("vtrace_loss: workspace missing, misaligned or smaller than mb_vtrace_workspace_bytes(rows)=%zu",
+                  vtrace_workspace_bytes(p.rows));
+        return MB_ERR_INVALID;
+    }
+    p.ticket = reinterpret_cast<unsigned int*>(scratch);
+    p.partials = reinterpret_cast<double*>(reinterpret_cast<uint8_t*>(scratch) + 256);
+    if (p.inv_n <= 0.0f) p.inv_n = float(1.0 / (double(p.rows) * double(p.T)));
+
+    EncodeTiledFn enc = get_encode_fn();
+    bool tma_ok = enc && !g_vt_force_generic && (p.in_stride % 16 == 0) && (p.out_stride % 4 == 0) &&
+                  al16(p.lp_old) && al16(p.lp_new) && al16(p.values) && al16(p.rewards) && al16(p.entropy) &&
+                  al16(p.done) && al16(p.vs) && al16(p.adv) && (!p.dlp || (al16(p.dlp) && al16(p.dv)));
+    if (tma_ok) {
+        VtMaps maps;
+        memset(&maps, 0, sizeof(maps));
+        bool ok = make_map_2d(enc, &maps.lp_old, p.lp_old, false, p.rows, p.T, p.in_stride) &&
+                  make_map_2d(enc, &maps.lp_new, p.lp_new, false, p.rows, p.T, p.in_stride) &&
+                  make_map_2d(enc, &maps.values, p.values, false, p.rows, p.T, p.in_stride) &&
+                  make_map_2d(enc, &maps.rewards, p.rewards, false, p.rows, p.T, p.in_stride) &&
+                  make_map_2d(enc, &maps.entropy, p.entropy, false, p.rows, p.T, p.in_stride) &&
+                  make_map_2d(enc, &maps.done, p.done, true, p.rows, p.T, p.in_stride) &&
+                  make_map_2d(enc, &maps.vs, p.vs, false, p.rows, p.T, p.out_stride) &&
+                  make_map_2d(enc, &maps.adv, p.adv, false, p.rows, p.T, p.out_stride);
+        if (ok && p.dlp)
+            ok = make_map_2d(enc, &maps.dlp, p.dlp, false, p.rows, p.T, p.out_stride) &&
+                 make_map_2d(enc, &maps.dv, p.dv, false, p.rows, p.T, p.out_stride);
+        if (ok) {
+            if (g_vt_stages == 2) return launch_vt_tma<2>(maps, p, stream);
+            if (g_vt_stages == 4) return launch_vt_tma<4>(maps, p, stream);
+            return launch_vt_tma<3>(maps, p, stream);
+        }
+        // tensor-map encoding refused the shape: fall through to the generic kernel
+    }
+    const unsigned grid = unsigned((p.rows + 127) / 128);
+    vtrace_generic_kernel<<<grid, 128, 0, stream>>>(p);
+    MB_CUDA(cudaGetLastError());
+    return MB_OK;
+}
+
+}  // namespace mb
+
+#include "../../include/mbeast.h"
+
+extern "C" int mb_vtrace_loss(const float* lp_old, const float* lp_new, const float* values, const float* bootstrap,
+                              const float* rewards, const uint8_t* done, const float* entropy, int64_t rows,
+                              int32_t T, int64_t in_row_stride, int64_t out_row_stride, float gamma, float rho_bar,
+                              float c_bar, float pg_rho_bar, float ent_coef, float inv_n, float* vs_out,
+                              float* adv_out, float* loss4_out, float* dlp_out, float* dV_out, void* workspace,
+                              size_t workspace_bytes, void* stream) {
+    mb::VtParams p;
+    memset(&p, 0, sizeof(p));
+    p.lp_old = lp_old; p.lp_new = lp_new; p.values = values; p.rewards = rewards; p.entropy = entropy;
+    p.done = done; p.bootstrap = bootstrap; p.vs = vs_out; p.adv = adv_out; p.dlp = dlp_out; p.dv = dV_out;
+    p.loss4 = loss4_out; p.rows = rows; p.T = T; p.in_stride = in_row_stride; p.out_stride = out_row_stride;
+    p.gamma = gamma; p.rho_bar = rho_bar; p.c_bar = c_bar; p.pg_rho_bar = pg_rho_bar; p.ent_coef = ent_coef;
+    p.inv_n = inv_n;
+    return mb::vtrace_loss_launch(p, workspace, workspace_bytes, static_cast<cudaStream_t>(stream));
+}

@@ -1,0 +1,103 @@
+"""Drop-in learner step for reference ``libs/utils.py:223-342`` (``PPO_learn``).
+
+Same signature and return value; the per-component Python loops, the reverse-time
+V-trace loop and the autograd graph of ~10*7*C nodes are replaced by four kernel
+launches (head forward, V-trace + losses + their gradients, head backward) around the
+PyTorch encoder.  Hyper-parameters that are literals in the reference (``gamma=0.99``,
+``rho_bar = c_bar = pg_rho_bar = 1``, entropy coefficient ``0.01`` -- quirk Q10) are
+keyword arguments defaulting to those literals.
+"""
+from __future__ import annotations
+
+import threading
+from typing import Dict, Optional
+
+import torch
+import torch.nn as nn
+
+from . import ops
+from .parallel import GradAllReducer
+
+# keys of the rollout batch the learner reads (reference buffers carry 11, libs/utils.py:34-46)
+LEARNER_KEYS = ("obs", "action_mask", "action", "reward", "done", "logprobs")
+
+
+def batch_to_device(batch: Dict[str, torch.Tensor], device, keys=LEARNER_KEYS, non_blocking=True):
+    """Host -> device copy of the keys the learner needs (the ``.to(device)`` the reference
+    left commented out at ``libs/utils.py:216``).  Pinned host tensors copy asynchronously."""
+    out = {}
+    for k in keys:
+        t = batch[k]
+        out[k] = t if t.is_cuda else t.to(device, non_blocking=non_blocking)
+    return out
+
+
+def learner_losses(learner_model: nn.Module, batch: Dict[str, torch.Tensor], rows: int, T: int, *,
+                   gamma=0.99, rho_bar=1.0, c_bar=1.0, pg_rho_bar=1.0, entropy_coef=0.01,
+                   global_rows: Optional[int] = None, time_major: bool = False):
+    """Forward part of ``PPO_learn`` (``utils.py:234-329``): returns ``(loss4, aux)`` with
+    ``loss4 = [pg, value, entropy, total]`` (device tensor, differentiable) and ``aux``
+    holding ``vs``, ``pg_advantages``, ``logprobs``, ``baseline``.
+
+    ``global_rows``: total rows over all data-parallel ranks; the means of
+    ``utils.py:320-326`` are then taken over the global ``rows*T`` so that a plain
+    sum-allreduce of gradients reproduces the single-GPU step.
+    ``time_major=False`` keeps the reference's ``reshape((R, T+1))`` of a batch flattened in
+    ``(t, b, e)`` order (quirk Q7); ``True`` transposes so that a row really is one
+    trajectory.
+    """
+    out, _ = learner_model.get_action(batch, learning=True, inds=[], agent_state=())      # utils.py:234
+
+    def rt(x):                       # utils.py:237-253 (reshape) or the true transpose
+        if time_major:
+            return x.reshape((T + 1, rows) + tuple(x.shape[1:])).transpose(0, 1)
+        return x.reshape((rows, T + 1) + tuple(x.shape[1:]))
+
+    logp = rt(out["logprobs"])
+    base = rt(out["baseline"].flatten())
+    ent = rt(out["entropy"])
+    bootstrap = base[:, -1].detach()                                                       # utils.py:258
+    inv_n = 1.0 / float((global_rows or rows) * T)
+    loss4, vs, adv = ops.VTraceLoss.apply(
+        logp[:, :-1], base[:, :-1], ent[:, :-1],                                           # utils.py:265
+        rt(batch["logprobs"])[:, 1:], bootstrap, rt(batch["reward"])[:, 1:], rt(batch["done"])[:, 1:],  # :263
+        gamma, rho_bar, c_bar, pg_rho_bar, entropy_coef, inv_n)
+    return loss4, dict(vs=vs, pg_advantages=adv, logprobs=logp, baseline=base, entropy=ent)
+
+
+def PPO_learn(actor_model: nn.Module, learner_model, exp_name: str, batch, optimizer, B: int, T: int,
+              n_envs: int, lock=threading.Lock(), *, gamma=0.99, rho_bar=1.0, c_bar=1.0, pg_rho_bar=1.0,
+              entropy_coef=0.01, reducer: Optional[GradAllReducer] = None, time_major: bool = False,
+              sync: bool = True):
+    """Performs a learning (optimization) step -- reference ``libs/utils.py:223-342``.
+
+    ``batch``: flat ``[N, ...]`` tensors, ``N = B*n_envs*(T+1)``, on the host (copied to the
+    model's device here, pinned memory makes that asynchronous) or already on the device.
+    Returns ``[pg_loss, value_loss, entropy_loss, total_loss]`` as python floats
+    (``utils.py:342``); with ``sync=False`` the 4-element device tensor is returned instead
+    and nothing synchronises.  ``reducer`` sums gradients across data-parallel ranks; the
+    returned losses are then the global ones.
+    """
+    if not isinstance(lock, type(threading.Lock())):
+        lock = threading.Lock()      # reference quirk Q15: microbeast.py:251 passes exp_name here
+    device = next(learner_model.parameters()).device
+    rows = B * n_envs
+    with lock:
+        dev_batch = batch_to_device(batch, device)
+        world = reducer.world_size if reducer is not None else 1
+        loss4, _aux = learner_losses(learner_model, dev_batch, rows, T, gamma=gamma, rho_bar=rho_bar,
+                                     c_bar=c_bar, pg_rho_bar=pg_rho_bar, entropy_coef=entropy_coef,
+                                     global_rows=rows * world, time_major=time_major)
+        optimizer.zero_grad()                                                              # utils.py:333
+        loss4[3].backward()                                                                # utils.py:334
+        losses = loss4.detach()
+        if reducer is not None:
+            losses = reducer.allreduce(learner_model, losses)
+        optimizer.step()                                                                   # utils.py:335
+        if actor_model is not learner_model:
+            actor_model.load_state_dict(learner_model.state_dict())                        # utils.py:337
+        if not sync:
+            return losses
+        four = losses.cpu().tolist()                                                       # utils.py:342
+        ops.check_status(device)
+        return four

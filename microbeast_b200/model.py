@@ -1,0 +1,189 @@
+"""Drop-in ``Agent`` / ``CategoricalMasked`` for reference ``model.py``.
+
+The conv/linear encoder (reference ``model.py:56-137``) stays on PyTorch -- it is the
+only dense contraction on the path and runs on cuDNN / cuBLAS.  The action head
+(``model.py:165-216``: 7*C ``CategoricalMasked`` objects per call) is replaced by the
+fused CUDA kernels of ``csrc/head.cu``.  Parameter names equal the reference's, so a
+reference ``state_dict`` loads unchanged.
+"""
+from __future__ import annotations
+
+from typing import Optional
+
+import numpy as np
+import torch
+import torch.nn as nn
+import torch.nn.functional as F
+
+from . import ops
+
+NVEC_CELL = (6, 4, 4, 4, 4, 7, 49)
+LOGITS_PER_CELL = 78
+COMPONENTS_PER_CELL = 7
+
+
+def layer_init(layer, std=np.sqrt(2), bias_const=0.0):
+    """Orthogonal weight / constant bias init -- reference ``model.py:24-27``."""
+    torch.nn.init.orthogonal_(layer.weight, std)
+    torch.nn.init.constant_(layer.bias, bias_const)
+    return layer
+
+
+class CategoricalMasked:
+    """All ``7*C`` masked categoricals of a batch of frames as ONE object.
+
+    The reference builds one ``CategoricalMasked(logits=, masks=)`` per component
+    (``model.py:33-52,176,190``) and stacks / sums their ``log_prob`` and ``entropy``
+    over the frame (``model.py:194-214``).  This class takes the un-split tensors --
+    ``logits [N,78C]``, ``masks [N,78C]`` -- and returns the per-frame sums directly.
+    Differentiable wrt ``logits``.
+    """
+
+    def __init__(self, probs=None, logits=None, validate_args=None, masks=None):
+        if probs is not None:
+            raise ValueError("CategoricalMasked: only `logits=` is supported (as used by the reference)")
+        if logits is None or masks is None or len(masks) == 0:
+            raise ValueError("CategoricalMasked: `logits` and `masks` are required")
+        self.logits = logits
+        self.masks = masks
+        self.validate_args = validate_args
+        self._cache = None          # (action, logp, ent)
+
+    def _eval(self, action):
+        if self._cache is None or self._cache[0] is not action:
+            logp, ent = ops.HeadEval.apply(self.logits, self.masks, action)
+            self._cache = (action, logp, ent)
+        return self._cache
+
+    def sample(self, uniforms: Optional[torch.Tensor] = None) -> torch.Tensor:
+        """``action [N,7C]``; inverse-CDF from ``uniforms [N,7C]`` (``torch.rand`` when omitted)."""
+        if uniforms is None:
+            n, width = self.logits.shape
+            uniforms = torch.rand((n, width // LOGITS_PER_CELL * COMPONENTS_PER_CELL),
+                                  device=self.logits.device)
+        with torch.no_grad():
+            action, logp, ent = ops.head_sample(self.logits.detach(), self.masks, uniforms)
+        self._cache = (action, logp, ent)
+        return action
+
+    def log_prob(self, action: torch.Tensor) -> torch.Tensor:
+        """Per-frame sum of the component log-probs (``model.py:194,199,214``)."""
+        out = self._eval(action)[1]
+        if self.validate_args:
+            ops.check_status(self.logits.device)
+        return out
+
+    def entropy(self, action: Optional[torch.Tensor] = None) -> torch.Tensor:
+        """Per-frame sum of the masked component entropies (``model.py:46-52,196,214``)."""
+        if action is None:
+            if self._cache is None:
+                n, width = self.logits.shape
+                action = torch.zeros((n, width // LOGITS_PER_CELL * COMPONENTS_PER_CELL),
+                                     dtype=torch.int64, device=self.logits.device)
+            else:
+                action = self._cache[0]
+        return self._eval(action)[2]
+
+
+class Residual_Block(nn.Module):
+    """relu-conv-relu-conv + skip -- reference ``model.py:56-73``."""
+
+    def __init__(self, channels):
+        super().__init__()
+        self.channels = channels
+        self.conv0 = nn.Conv2d(channels, channels, kernel_size=3, padding=1)
+        self.conv1 = nn.Conv2d(channels, channels, kernel_size=3, padding=1)
+
+    def forward(self, x):
+        y = self.conv0(F.relu(x))
+        y = self.conv1(F.relu(y))
+        return y + x
+
+
+class ConvSequence(nn.Module):
+    """conv3x3 -> maxpool(3, s2, p1) -> 2 residual blocks -- reference ``model.py:77-109``."""
+
+    def __init__(self, input_shape, out_channels):
+        super().__init__()
+        self._input_shape = tuple(input_shape)
+        self._out_channels = out_channels
+        self.conv = nn.Conv2d(self._input_shape[0], out_channels, kernel_size=3, padding=1)
+        self.res_block0 = Residual_Block(out_channels)
+        self.res_block1 = Residual_Block(out_channels)
+
+    def get_output_shape(self):
+        _c, h, w = self._input_shape
+        return (self._out_channels, (h + 1) // 2, (w + 1) // 2)
+
+    def forward(self, x):
+        x = F.max_pool2d(self.conv(x), kernel_size=3, stride=2, padding=1)
+        return self.res_block1(self.res_block0(x))
+
+
+class Agent(nn.Module):
+    """Reference ``model.py:112-220`` with the same constructor and ``get_action`` contract.
+
+    ``nvec`` must be ``[6,4,4,4,4,7,49] * cells`` (``microbeast.py:145``), which is what the
+    kernels are specialised for.
+    """
+
+    def __init__(self, obs_space_shape: tuple, nvec: list, mapsize=8 * 8, device="cpu"):
+        super().__init__()
+        h, w, c = obs_space_shape
+        nvec = [int(v) for v in nvec]
+        if len(nvec) % COMPONENTS_PER_CELL or nvec != list(NVEC_CELL) * (len(nvec) // COMPONENTS_PER_CELL):
+            raise ValueError("Agent: nvec must be [6,4,4,4,4,7,49] repeated once per map cell")
+        self.mapsize = mapsize
+        self.nvec = nvec
+        self.cells = len(nvec) // COMPONENTS_PER_CELL
+        shape = (c, h, w)
+        layers = []
+        for out_channels in (16, 32, 32):
+            seq = ConvSequence(shape, out_channels)
+            shape = seq.get_output_shape()
+            layers.append(seq)
+        layers += [nn.Flatten(), nn.ReLU(), nn.Linear(shape[0] * shape[1] * shape[2], 256), nn.ReLU()]
+        self.network = nn.Sequential(*layers)
+        self.actor = layer_init(nn.Linear(256, sum(nvec)), std=0.0)
+        self.critic = layer_init(nn.Linear(256, 1), std=1)
+
+    def initial_state(self, batch_size):
+        return tuple()
+
+    def _obs(self, input_dict, learning):
+        obs = input_dict["obs"] if learning else input_dict["obs"][0, 0, ...]     # model.py:156-160
+        if obs.dtype != torch.float32:
+            obs = obs.float()            # uint8 wire format of the B200 rollout store
+        return obs.permute((0, 3, 1, 2))  # NHWC storage == channels-last view
+
+    def forward(self, input_dict: dict, agent_state=(), learning=False, inds=()):
+        return self.network(self._obs(input_dict, learning))
+
+    def get_value(self, input_dict: dict, agent_state=(), learning=False, inds=()):
+        return self.critic(self.forward(input_dict, agent_state, learning, inds))
+
+    def get_action(self, input_dict: dict, learning=False, inds=(), agent_state=(),
+                   uniforms: Optional[torch.Tensor] = None):
+        """Same outputs as reference ``model.py:165-216``.
+
+        acting:   ``dict(action [n,7C], policy_logits [n,78C], logprobs [n], baseline [1,n])``
+        learning: the same plus ``entropy [N]``; ``action`` is the batch's action.
+        One encoder pass feeds both heads (the reference runs the encoder twice, quirk
+        Q6; values and summed gradients are identical).
+        """
+        hidden = self.forward(input_dict, agent_state, learning, inds)
+        logits = self.actor(hidden)                                             # model.py:167
+        baseline = self.critic(hidden).view(1, -1)                              # model.py:205
+        if not learning:
+            action_mask = input_dict["action_mask"][0, ...]                     # model.py:173
+            if uniforms is None:
+                uniforms = torch.rand((logits.shape[0], self.cells * COMPONENTS_PER_CELL),
+                                      device=logits.device)
+            action, logprobs, _ = ops.head_sample(logits.detach(), action_mask, uniforms,
+                                                  want_entropy=False)
+            return (dict(action=action, policy_logits=logits, logprobs=logprobs, baseline=baseline), ())
+        action = input_dict["action"]                                           # model.py:182
+        action_mask = input_dict["action_mask"]                                 # model.py:188
+        logprobs, entropy = ops.HeadEval.apply(logits, action_mask, action)
+        return (dict(action=action, policy_logits=logits, logprobs=logprobs, baseline=baseline,
+                     entropy=entropy), ())

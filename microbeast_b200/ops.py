@@ -1,0 +1,321 @@
+"""Tensor-level wrappers of the C ABI and their autograd glue.
+
+Every function takes CUDA tensors, launches on ``torch.cuda.current_stream()`` and
+returns without synchronising.  CPU tensors are rejected: there is no fallback path.
+"""
+from __future__ import annotations
+
+import ctypes
+from typing import Dict, Optional, Tuple
+
+import torch
+
+from . import _lib
+from ._lib import lib
+
+LOGITS_PER_CELL = 78
+COMPONENTS_PER_CELL = 7
+STATUS_BAD_ACTION = 1
+STATUS_TIMEOUT = 2
+
+# launches issued through this module, by kernel name (bench.py reports the count)
+launch_counts: Dict[str, int] = {}
+
+_status_words: Dict[int, torch.Tensor] = {}
+_workspaces: Dict[Tuple[int, int], torch.Tensor] = {}
+
+
+_timing = None      # list of (name, start_event, end_event) while kernel timing is on
+
+
+def start_kernel_timing() -> None:
+    """Record a CUDA-event pair around every kernel launch (on the launching stream)."""
+    global _timing
+    _timing = []
+
+
+def stop_kernel_timing() -> Dict[str, list]:
+    """Stops recording and returns ``{kernel: [ms, ...]}`` (synchronises)."""
+    global _timing
+    rec, _timing = _timing or [], None
+    torch.cuda.synchronize()
+    out: Dict[str, list] = {}
+    for name, s, e in rec:
+        out.setdefault(name, []).append(s.elapsed_time(e))
+    return out
+
+
+class _Launch:
+    """Counts a launch and, when timing is on, brackets it with CUDA events."""
+
+    def __init__(self, name: str):
+        self.name = name
+
+    def __enter__(self):
+        if _timing is not None:
+            self.start = torch.cuda.Event(enable_timing=True)
+            self.start.record()
+        return self
+
+    def __exit__(self, exc_type, exc, tb):
+        if exc_type is None:
+            launch_counts[self.name] = launch_counts.get(self.name, 0) + 1
+            if _timing is not None:
+                end = torch.cuda.Event(enable_timing=True)
+                end.record()
+                _timing.append((self.name, self.start, end))
+        return False
+
+
+def total_launches() -> int:
+    return sum(launch_counts.values())
+
+
+def _ptr(t: Optional[torch.Tensor]):
+    return ctypes.c_void_p(0 if t is None else t.data_ptr())
+
+
+def _stream():
+    return ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+def _check(rc: int) -> None:
+    if rc == 0:
+        return
+    msg = _lib.last_error()
+    if rc == 1:
+        raise ValueError(msg)
+    raise RuntimeError(msg)
+
+
+def _need_cuda(**tensors) -> torch.device:
+    dev = None
+    for name, t in tensors.items():
+        if t is None:
+            continue
+        if not t.is_cuda:
+            raise RuntimeError(f"microbeast_b200: `{name}` is on {t.device}; the kernels are CUDA-only "
+                               "(sm_100a) and there is no CPU fallback")
+        if dev is None:
+            dev = t.device
+        elif t.device != dev:
+            raise RuntimeError(f"microbeast_b200: `{name}` is on {t.device}, expected {dev}")
+    return dev
+
+
+def _as(t: torch.Tensor, dtype, name: str) -> torch.Tensor:
+    if t.dtype != dtype:
+        raise TypeError(f"`{name}` must be {dtype}, got {t.dtype}")
+    return t if t.is_contiguous() else t.contiguous()
+
+
+def _mask_u8(mask: torch.Tensor) -> torch.Tensor:
+    if mask.dtype == torch.bool:
+        mask = mask.view(torch.uint8)
+    return _as(mask, torch.uint8, "mask")
+
+
+def status_word(device: torch.device) -> torch.Tensor:
+    """Per-device int32 word the kernels OR error bits into (zeroed at creation)."""
+    idx = device.index if device.index is not None else torch.cuda.current_device()
+    w = _status_words.get(idx)
+    if w is None:
+        w = torch.zeros(1, dtype=torch.int32, device=torch.device("cuda", idx))
+        _status_words[idx] = w
+    return w
+
+
+def check_status(device: Optional[torch.device] = None) -> None:
+    """Synchronising check of the status word; raises like torch's ``validate_args`` (Q13)."""
+    device = device or torch.device("cuda", torch.cuda.current_device())
+    w = status_word(device)
+    bits = int(w.item())
+    if bits:
+        w.zero_()
+    if bits & STATUS_TIMEOUT:
+        raise RuntimeError("microbeast_b200: a kernel pipeline wait timed out (internal error)")
+    if bits & STATUS_BAD_ACTION:
+        raise ValueError("microbeast_b200: action index outside the support of its categorical "
+                         "(reference: torch Categorical.log_prob validate_args)")
+
+
+def _cells(width: int, per_cell: int, name: str) -> int:
+    if width % per_cell:
+        raise ValueError(f"`{name}` last dim {width} is not a multiple of {per_cell}")
+    return width // per_cell
+
+
+def head_eval_fwd(logits: torch.Tensor, mask: torch.Tensor, action: torch.Tensor):
+    """``(logprobs [N], entropy [N])`` of the taken actions -- reference ``model.py:180-214``."""
+    dev = _need_cuda(logits=logits, mask=mask, action=action)
+    logits = _as(logits, torch.float32, "logits")
+    mask = _mask_u8(mask)
+    action = _as(action, torch.int64, "action")
+    n = logits.shape[0]
+    cells = _cells(logits.shape[1], LOGITS_PER_CELL, "logits")
+    if mask.shape != logits.shape or tuple(action.shape) != (n, cells * COMPONENTS_PER_CELL):
+        raise ValueError(f"shape mismatch: logits {tuple(logits.shape)} mask {tuple(mask.shape)} "
+                         f"action {tuple(action.shape)}")
+    logp = torch.empty(n, dtype=torch.float32, device=dev)
+    ent = torch.empty(n, dtype=torch.float32, device=dev)
+    with torch.cuda.device(dev), _Launch("head_eval_fwd"):
+        _check(lib.mb_head_eval_fwd(_ptr(logits), _ptr(mask), _ptr(action), _ptr(logp), _ptr(ent),
+                                    n, cells, _ptr(status_word(dev)), _stream()))
+    return logp, ent
+
+
+def head_eval_bwd(logits, mask, action, g_logp, g_ent, out: Optional[torch.Tensor] = None):
+    """``dlogits [N,78C]`` for upstream grads ``g_logp [N]``, ``g_ent [N]``."""
+    dev = _need_cuda(logits=logits, mask=mask, action=action, g_logp=g_logp, g_ent=g_ent, out=out)
+    logits = _as(logits, torch.float32, "logits")
+    mask = _mask_u8(mask)
+    action = _as(action, torch.int64, "action")
+    g_logp = _as(g_logp, torch.float32, "g_logp")
+    g_ent = _as(g_ent, torch.float32, "g_ent")
+    n = logits.shape[0]
+    cells = _cells(logits.shape[1], LOGITS_PER_CELL, "logits")
+    if g_logp.numel() != n or g_ent.numel() != n:
+        raise ValueError("g_logp / g_ent must have one entry per frame")
+    if out is None:
+        out = torch.empty_like(logits)
+    elif out.shape != logits.shape or out.dtype != torch.float32 or not out.is_contiguous():
+        raise ValueError("`out` must be a contiguous float32 tensor shaped like logits")
+    with torch.cuda.device(dev), _Launch("head_eval_bwd"):
+        _check(lib.mb_head_eval_bwd(_ptr(logits), _ptr(mask), _ptr(action), _ptr(g_logp), _ptr(g_ent),
+                                    _ptr(out), n, cells, _ptr(status_word(dev)), _stream()))
+    return out
+
+
+def head_sample(logits, mask, uniforms, want_entropy: bool = True):
+    """Inverse-CDF sampling from caller-supplied uniforms (definition: ``oracle/head.py``).
+
+    Returns ``(action [N,7C] i64, logprobs [N], entropy [N] or None)`` -- the actor branch
+    of reference ``model.py:171-177,194-210``.
+    """
+    dev = _need_cuda(logits=logits, mask=mask, uniforms=uniforms)
+    logits = _as(logits, torch.float32, "logits")
+    mask = _mask_u8(mask)
+    uniforms = _as(uniforms, torch.float32, "uniforms")
+    n = logits.shape[0]
+    cells = _cells(logits.shape[1], LOGITS_PER_CELL, "logits")
+    if mask.shape != logits.shape or tuple(uniforms.shape) != (n, cells * COMPONENTS_PER_CELL):
+        raise ValueError("shape mismatch between logits / mask / uniforms")
+    action = torch.empty((n, cells * COMPONENTS_PER_CELL), dtype=torch.int64, device=dev)
+    logp = torch.empty(n, dtype=torch.float32, device=dev)
+    ent = torch.empty(n, dtype=torch.float32, device=dev) if want_entropy else None
+    with torch.cuda.device(dev), _Launch("head_sample"):
+        _check(lib.mb_head_sample(_ptr(logits), _ptr(mask), _ptr(uniforms), _ptr(action), _ptr(logp),
+                                  _ptr(ent), n, cells, _ptr(status_word(dev)), _stream()))
+    return action, logp, ent
+
+
+def vtrace_workspace(device: torch.device, rows: int) -> torch.Tensor:
+    """Zero-initialised scratch for ``mb_vtrace_loss`` (cached per device; the kernel keeps
+    its ticket word at zero between calls).  Calls on different streams that may overlap
+    must not share it -- pass their own ``workspace=``."""
+    need = int(lib.mb_vtrace_workspace_bytes(int(rows)))
+    idx = device.index if device.index is not None else torch.cuda.current_device()
+    key = (idx, 0)
+    ws = _workspaces.get(key)
+    if ws is None or ws.numel() < need:
+        ws = torch.zeros(max(need, 1 << 16), dtype=torch.uint8, device=torch.device("cuda", idx))
+        _workspaces[key] = ws
+    return ws
+
+
+def vtrace_loss(lp_old, lp_new, values, bootstrap, rewards, done, entropy, *, gamma=0.99, rho_bar=1.0,
+                c_bar=1.0, pg_rho_bar=1.0, entropy_coef=0.01, inv_n: Optional[float] = None,
+                want_grads: bool = True, workspace: Optional[torch.Tensor] = None):
+    """V-trace + losses (+ gradients) -- reference ``libs/utils.py:277-329``.
+
+    All inputs ``[R,T]`` (time contiguous), ``bootstrap [R]``.  Returns a dict with
+    ``vs``, ``pg_advantages`` ``[R,T]``, ``loss4`` ``[4]`` = pg, value, entropy, total and,
+    with ``want_grads``, ``d_logp``, ``d_values`` ``[R,T]`` and the scalar ``d_entropy``.
+    """
+    dev = _need_cuda(lp_old=lp_old, lp_new=lp_new, values=values, bootstrap=bootstrap, rewards=rewards,
+                     done=done, entropy=entropy, workspace=workspace)
+    lp_old = _as(lp_old, torch.float32, "lp_old")
+    lp_new = _as(lp_new, torch.float32, "lp_new")
+    values = _as(values, torch.float32, "values")
+    rewards = _as(rewards, torch.float32, "rewards")
+    entropy = _as(entropy, torch.float32, "entropy")
+    bootstrap = _as(bootstrap, torch.float32, "bootstrap")
+    if done.dtype == torch.bool:
+        done = done.view(torch.uint8) if done.is_contiguous() else done.contiguous().view(torch.uint8)
+    done = _as(done, torch.uint8, "done")
+    if values.dim() != 2:
+        raise ValueError("values must be [R, T]")
+    rows, T = values.shape
+    for name, t in (("lp_old", lp_old), ("lp_new", lp_new), ("rewards", rewards), ("done", done),
+                    ("entropy", entropy)):
+        if tuple(t.shape) != (rows, T):
+            raise ValueError(f"`{name}` has shape {tuple(t.shape)}, expected {(rows, T)}")
+    if bootstrap.numel() != rows:
+        raise ValueError("bootstrap must have one entry per row")
+    if inv_n is None:
+        inv_n = 1.0 / float(max(rows * T, 1))
+    vs = torch.empty((rows, T), dtype=torch.float32, device=dev)
+    adv = torch.empty((rows, T), dtype=torch.float32, device=dev)
+    loss4 = torch.empty(4, dtype=torch.float32, device=dev)
+    dlp = torch.empty((rows, T), dtype=torch.float32, device=dev) if want_grads else None
+    dv = torch.empty((rows, T), dtype=torch.float32, device=dev) if want_grads else None
+    ws = workspace if workspace is not None else vtrace_workspace(dev, rows)
+    with torch.cuda.device(dev), _Launch("vtrace_loss"):
+        _check(lib.mb_vtrace_loss(_ptr(lp_old), _ptr(lp_new), _ptr(values), _ptr(bootstrap), _ptr(rewards),
+                                  _ptr(done), _ptr(entropy), rows, T, T, T,
+                                  float(gamma), float(rho_bar), float(c_bar), float(pg_rho_bar),
+                                  float(entropy_coef), float(inv_n),
+                                  _ptr(vs), _ptr(adv), _ptr(loss4), _ptr(dlp), _ptr(dv),
+                                  _ptr(ws), ws.numel(), _stream()))
+    out = dict(vs=vs, pg_advantages=adv, loss4=loss4)
+    if want_grads:
+        out.update(d_logp=dlp, d_values=dv, d_entropy=-float(entropy_coef) * float(inv_n))
+    return out
+
+
+class HeadEval(torch.autograd.Function):
+    """``(logits, mask, action) -> (logprobs, entropy)`` with the hand-written backward."""
+
+    @staticmethod
+    def forward(ctx, logits, mask, action):
+        logp, ent = head_eval_fwd(logits, mask, action)
+        ctx.save_for_backward(logits, mask, action)
+        return logp, ent
+
+    @staticmethod
+    def backward(ctx, g_logp, g_ent):
+        logits, mask, action = ctx.saved_tensors
+        n = logits.shape[0]
+        if g_logp is None:
+            g_logp = torch.zeros(n, dtype=torch.float32, device=logits.device)
+        if g_ent is None:
+            g_ent = torch.zeros(n, dtype=torch.float32, device=logits.device)
+        return head_eval_bwd(logits, mask, action, g_logp.contiguous(), g_ent.contiguous()), None, None
+
+
+class VTraceLoss(torch.autograd.Function):
+    """Differentiable wrt ``lp_new``, ``values``, ``entropy``; everything V-trace is
+    ``no_grad`` exactly as in the reference (``utils.py:289``).  Returns
+    ``(loss4, vs, pg_advantages)``; ``loss4 = [pg, value, entropy, total]``."""
+
+    @staticmethod
+    def forward(ctx, lp_new, values, entropy, lp_old, bootstrap, rewards, done, gamma, rho_bar, c_bar,
+                pg_rho_bar, entropy_coef, inv_n):
+        out = vtrace_loss(lp_old, lp_new, values, bootstrap, rewards, done, entropy, gamma=gamma,
+                          rho_bar=rho_bar, c_bar=c_bar, pg_rho_bar=pg_rho_bar, entropy_coef=entropy_coef,
+                          inv_n=inv_n, want_grads=True)
+        ctx.save_for_backward(out["d_logp"], out["d_values"])
+        ctx.entropy_coef = float(entropy_coef)
+        ctx.inv_n = float(inv_n) if inv_n is not None else 1.0 / float(max(values.numel(), 1))
+        ctx.mark_non_differentiable(out["vs"], out["pg_advantages"])
+        return out["loss4"], out["vs"], out["pg_advantages"]
+
+    @staticmethod
+    def backward(ctx, g_loss4, _g_vs, _g_adv):
+        d_logp, d_values = ctx.saved_tensors
+        # loss4 = [pg, value, entropy, total]; total = pg + value - coef * entropy
+        g_pg = g_loss4[0] + g_loss4[3]
+        g_v = g_loss4[1] + g_loss4[3]
+        g_en = (g_loss4[2] - ctx.entropy_coef * g_loss4[3]) * ctx.inv_n
+        return (d_logp * g_pg, d_values * g_v, g_en.expand_as(d_logp), None, None, None, None,
+                None, None, None, None, None, None)

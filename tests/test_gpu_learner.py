@@ -1,0 +1,106 @@
+"""The drop-in Agent.get_action / PPO_learn on the GPU against the oracle's CPU learner step."""
+import numpy as np
+import pytest
+import torch
+
+from conftest import close_rms
+from test_oracle_golden import _agent_batch, golden_agent_weights
+
+pytestmark = pytest.mark.gpu
+
+# End-to-end the encoder runs on cuDNN/cuBLAS fp32 while the oracle runs CPU MKL, so inputs to
+# the head already differ by ~1e-6 relative; 1e-4 covers that.  The kernels themselves are held
+# to 1e-5 on identical inputs in test_gpu_head.py / test_gpu_vtrace.py.
+E2E_RTOL = 1e-4
+
+
+@pytest.fixture(autouse=True)
+def _fp32_exact():
+    old = (torch.backends.cudnn.allow_tf32, torch.backends.cuda.matmul.allow_tf32)
+    torch.backends.cudnn.allow_tf32 = False
+    torch.backends.cuda.matmul.allow_tf32 = False
+    yield
+    torch.backends.cudnn.allow_tf32, torch.backends.cuda.matmul.allow_tf32 = old
+
+
+def _pair(h, w, seed):
+    from microbeast_b200.model import Agent
+    from oracle import NVEC_CELL
+    from oracle.learner import RefAgent
+    nvec = list(NVEC_CELL) * (h * w)
+    ref = RefAgent((h, w, 27), nvec, h * w)
+    ref.load_state_dict(golden_agent_weights(ref.state_dict(), seed))
+    mine = Agent((h, w, 27), nvec, h * w).cuda()
+    mine.load_state_dict(ref.state_dict())
+    return mine, ref
+
+
+def test_golden_agent_get_action_and_ppo_learn(golden):
+    from microbeast_b200.learner import PPO_learn
+    g = golden("agent_4x4")
+    mine, ref = _pair(int(g["h"]), int(g["w"]), int(g["weight_seed"]))
+    batch = _agent_batch(g)
+    dev_batch = {k: v.cuda() for k, v in batch.items()}
+    with torch.no_grad():
+        out, _ = mine.get_action(dev_batch, learning=True)
+    for key, want in (("logprobs", "out_logprobs"), ("entropy", "out_entropy"), ("baseline", "out_baseline")):
+        ok, worst = close_rms(out[key], g[want], E2E_RTOL)
+        assert ok, (key, worst)
+    assert out["baseline"].shape == (1, batch["obs"].shape[0]) and out["action"] is dev_batch["action"]
+    opt = torch.optim.SGD(mine.parameters(), lr=0.0)
+    four = PPO_learn(mine, mine, "golden", batch, opt, int(g["B"]), int(g["T"]), int(g["n_envs"]))
+    assert isinstance(four, list) and all(isinstance(x, float) for x in four)
+    np.testing.assert_allclose(four, g["four"], rtol=E2E_RTOL)
+    grads = dict(mine.named_parameters())
+    for name, key in (("actor.bias", "grad_actor_bias"), ("critic.weight", "grad_critic_weight"),
+                      ("critic.bias", "grad_critic_bias"), ("network.0.conv.bias", "grad_conv0_bias"),
+                      ("network.5.bias", "grad_fc_bias")):
+        ok, worst = close_rms(grads[name].grad, g[key], E2E_RTOL)
+        assert ok, (name, worst)
+    ok, worst = close_rms(grads["actor.weight"].grad.sum(1), g["grad_actor_weight_rowsum"], E2E_RTOL)
+    assert ok, worst
+    norms = np.array([float(p.grad.norm()) for p in mine.parameters()])
+    np.testing.assert_allclose(norms, g["grad_norms"], rtol=1e-3)
+
+
+def test_c1_shape_step_matches_oracle_and_adam_update():
+    """BASELINE config 1 geometry (8x8, T=80) at a row count the CPU oracle finishes in seconds."""
+    from microbeast_b200 import synth
+    from microbeast_b200.learner import PPO_learn
+    from oracle.learner import ref_learn_step
+    h = w = 8
+    T, rows = 80, 4
+    mine, ref = _pair(h, w, seed=99)
+    batch = synth.make_rollout_batch(h, w, T, rows, seed=1234, preset="dense")
+    with torch.no_grad():
+        o, _ = ref.get_action(batch, learning=True)
+    batch["logprobs"] = o["logprobs"] + 0.3 * torch.randn(o["logprobs"].shape, generator=torch.Generator().manual_seed(2))
+    opt_ref = torch.optim.Adam(ref.parameters(), lr=2.5e-4, eps=1e-5)         # microbeast.py:200
+    opt_mine = torch.optim.Adam(mine.parameters(), lr=2.5e-4, eps=1e-5)
+    want = ref_learn_step(ref, {k: v.clone() for k, v in batch.items()}, opt_ref, 2, T, 2)
+    got = PPO_learn(mine, mine, "c1", batch, opt_mine, 2, T, 2)
+    np.testing.assert_allclose(got, want, rtol=E2E_RTOL)
+    for (n1, p1), (n2, p2) in zip(mine.named_parameters(), ref.named_parameters()):
+        ok, worst = close_rms(p1.detach(), p2.detach(), 1e-4)
+        assert ok, (n1, worst)
+
+
+def test_acting_branch_contract_and_determinism():
+    from microbeast_b200 import synth
+    mine, _ = _pair(8, 8, seed=5)
+    n_envs = 6
+    g = torch.Generator().manual_seed(0)
+    env_out = dict(obs=synth.make_obs(n_envs, 8, 8, gen=g).view(1, 1, n_envs, 8, 8, 27).cuda(),
+                   action_mask=synth.make_masks(n_envs, 64, "dense", gen=g).view(1, n_envs, -1).cuda())
+    u = synth.make_uniforms(n_envs, 64, gen=g).cuda()
+    with torch.no_grad():
+        out, state = mine.get_action(env_out, uniforms=u)
+        out2, _ = mine.get_action(env_out, uniforms=u)
+    assert state == () and set(out) == {"action", "policy_logits", "logprobs", "baseline"}
+    assert out["action"].shape == (n_envs, 7 * 64) and out["action"].dtype == torch.int64
+    assert out["policy_logits"].shape == (n_envs, 78 * 64) and out["logprobs"].shape == (n_envs,)
+    assert out["baseline"].shape == (1, n_envs)
+    assert torch.equal(out["action"], out2["action"]) and torch.equal(out["logprobs"], out2["logprobs"])
+    from oracle import head as ohead
+    ref_act = ohead.sample_invcdf(out["policy_logits"].cpu(), env_out["action_mask"][0].cpu(), u.cpu())
+    assert torch.equal(out["action"].cpu(), ref_act)
