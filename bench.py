@@ -59,7 +59,7 @@ def parse_args():
     ap.add_argument("--cpu-rows", type=int, default=32, help="rows of the CPU-baseline sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
-    ap.add_argument("--sweep", default="", choices=["", "vtrace", "head"])
+    ap.add_argument("--sweep", default="", choices=["", "vtrace", "head", "variants"])
     ap.add_argument("--out", default="", help="also append the JSON line(s) to this file")
     return ap.parse_args()
 
@@ -370,6 +370,45 @@ def run_sweep(args):
                                  "frac_of_peak": gbs / peak,
                                  "regime": "hbm" if R * T >= 8_000_000 else "latency-bound (L2 resident / launch)"})
                 del t
+    elif args.sweep == "variants":
+        import microbeast_b200
+        h, w, T, rows = WORKLOADS["c2"]
+        cells, n = h * w, rows * (T + 1)
+        logits = synth.make_logits(n, cells, gen=g, device=dev)
+        mask = synth.make_masks(n, cells, args.preset, gen=g, device=dev)
+        act = synth.make_valid_actions(mask, gen=g)
+        u = synth.make_uniforms(n, cells, gen=g, device=dev)
+        gl = torch.randn(n, generator=g, device=dev)
+        out = torch.empty_like(logits)
+        names = {0: "64x3", 1: "64x2", 2: "64x4", 3: "32x3", 4: "32x5", 5: "128x3", 6: "128x2"}
+        for variant, vname in names.items():
+            for per_sm in (0, 1):
+                microbeast_b200.set_tuning("head_variant", variant)
+                microbeast_b200.set_tuning("head_ctas_per_sm", per_sm)
+                for kname, fn, per_cell in (
+                        ("head_eval_fwd", lambda: ops.head_eval_fwd(logits, mask, act), 446),
+                        ("head_eval_bwd", lambda: ops.head_eval_bwd(logits, mask, act, gl, gl, out=out), 758),
+                        ("head_sample", lambda: ops.head_sample(logits, mask, u), 474)):
+                    med, p10, p90 = bench(fn, 6)
+                    nbytes = per_cell * cells * n + 8 * n
+                    gbs = nbytes / (med * 1e-3) / 1e9
+                    rows_out.append({"kernel": kname, "variant": vname, "ctas_per_sm": per_sm or "max",
+                                     "median_us": med * 1e3, "gbs": gbs, "frac_of_peak": gbs / peak})
+        microbeast_b200.set_tuning("head_variant", 0)
+        microbeast_b200.set_tuning("head_ctas_per_sm", 0)
+        for st in (2, 3, 4):
+            microbeast_b200.set_tuning("vtrace_stages", st)
+            for T, R in ((512, 65536), (256, 65536), (80, 65536)):
+                t = synth.make_vtrace_inputs(R, T, gen=g, device=dev)
+                fn = lambda: ops.vtrace_loss(t["lp_old"], t["lp_new"], t["values"], t["bootstrap"], t["rewards"],
+                                             t["done"], t["entropy"])
+                med, p10, p90 = bench(fn, 10)
+                nbytes = 37 * R * T + 4 * R
+                gbs = nbytes / (med * 1e-3) / 1e9
+                rows_out.append({"kernel": "vtrace_loss", "variant": f"stages{st}", "T": T, "rows": R,
+                                 "median_us": med * 1e3, "gbs": gbs, "frac_of_peak": gbs / peak})
+                del t
+        microbeast_b200.set_tuning("vtrace_stages", 3)
     else:
         for name, (h, w, T, rows) in WORKLOADS.items():
             cells, n = h * w, rows * (T + 1)

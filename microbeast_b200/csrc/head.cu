@@ -54,8 +54,8 @@ struct HeadCfg {
     static constexpr int kOffMask = kLogitBytes;
     static constexpr int kOffAct = kOffMask + kMaskBytes;
     static constexpr int kOffUni = kOffAct + kActBytes;
-    static constexpr int kStageBytes = kOffUni + kUniBytes;
-    static_assert(kStageBytes % 128 == 0, "stage must stay 128-B aligned");
+    static constexpr int kStageBytes = (kOffUni + kUniBytes + 127) / 128 * 128;
+    static_assert(kOffMask % 16 == 0 && kOffAct % 16 == 0 && kOffUni % 16 == 0, "bulk copies need 16-B alignment");
     static_assert(TC % 32 == 0 && TC % 8 == 0, "tile granularity");
 };
 
@@ -106,117 +106,47 @@ __device__ __noinline__ int sample_component_fp64(const float* z, const uint8_t*
     return a;
 }
 
-// Statistics of one component held in registers: max, sum of exp, sum of exp * (z - max).
-template <int LEN>
-__device__ __forceinline__ void seg_stats(const float* zp, float* e, float& m, float& S, float& W) {
-    m = zp[0];
-#pragma unroll
-    for (int i = 1; i < LEN; ++i) m = fmaxf(m, zp[i]);
-    S = 0.f;
-    W = 0.f;
-#pragma unroll
-    for (int i = 0; i < LEN; ++i) {
-        const float d = zp[i] - m;
-        const float ei = ex2_approx(d * kLog2e);
-        e[i] = ei;
-        S += ei;
-        W = fmaf(ei, d, W);
-    }
-}
+// ---- per-component math --------------------------------------------------------------------
+// z' = mask ? z : -1e8 (model.py:43); m = max z'; e_i = exp(z'_i - m); S = sum e; W = sum e*(z'-m);
+// lse = m + log S (torch logsumexp); logp = z'_a - lse; H = log S - W/S (== -sum p*l over valid
+// entries, model.py:46-52).  All code below is branch-free straight-line code over register arrays
+// so that the independent chains of the seven components interleave (ILP); log / divide use the
+// SFU approximations (lg2.approx: abs err 2^-22; rcp.approx: 1 ulp), far inside the 1e-5 budget.
+
+__device__ __forceinline__ float fast_log(float x) { return lg2_approx(x) * kLn2; }
 
 struct SegScalars {
-    float lse;   // logsumexp of the masked logits (torch: max + log(sum exp(z - max)))
-    float ent;   // masked entropy (model.py:46-52)
+    float lse;   // logsumexp of the masked logits
+    float ent;   // masked entropy
     bool dead;   // every entry masked (quirk Q1): log_prob 0, entropy 0, gradient 0, uniform sample
 };
 
 __device__ __forceinline__ SegScalars seg_finish(float m, float S, float W) {
     SegScalars r;
-    const float logS = logf(S);
+    const float logS = fast_log(S);
     r.lse = m + logS;
     r.dead = (m < -5e7f);
     // fully masked: lse = fl(-1e8 + ln n) = -1e8 in fp32, so lse - m == 0 and W == 0  ->  0 (Q1)
     const float h0 = r.dead ? (r.lse - m) : logS;
-    r.ent = h0 - W / S;
+    r.ent = h0 - __fdividef(W, S);
     return r;
-}
-
-__device__ __forceinline__ int check_action(long long a, int len, int* status) {
-    if (a < 0 || a >= len) {
-        if (status) atomicOr(status, kStatusBadAction);
-        a = a < 0 ? 0 : len - 1;
-    }
-    return int(a);
-}
-
-// Sequential inverse-CDF count over e[0..CNT) starting from running sum c; returns the number of
-// k with t >= c_k and flags `near` when t is inside the guard band of any edge.
-template <int CNT>
-__device__ __forceinline__ int cdf_count(const float* e, float& c, float t, float guard, bool& near) {
-    int a = 0;
-#pragma unroll
-    for (int i = 0; i < CNT; ++i) {
-        c += e[i];
-        a += (t >= c) ? 1 : 0;
-        near = near || (fabsf(t - c) <= guard);
-    }
-    return a;
 }
 
 __device__ __forceinline__ float sample_guard(float S, float W, int len) {
     // fp32 error budget of the running CDF against the fp64 definition, with a 4x margin:
-    // ex2.approx (2 ulp) + argument rounding (|d| * 2^-24 each) + len sequential adds + u*S.
+    // ex2.approx (2 ulp) + argument rounding (|d| * 2^-24 each) + len adds in any order + u*S.
     return S * (9.5367431640625e-07f + float(len + 1) * 2.384185791015625e-07f) + 4.76837158203125e-07f * fabsf(W);
 }
 
 // ---------------------------------------------------------------------------------------------
 // A role: one thread per cell, the six small components (logit offsets 0..28).
 // ---------------------------------------------------------------------------------------------
-template <int MODE, int OFF, int LEN, int K>
-__device__ __forceinline__ void a_role_component(float* z, float* zc, const uint8_t* mc, const int64_t* ain,
-                                                 int64_t* aout, const float* uni, float g_lp, float g_h,
-                                                 int* status, float& lp_acc, float& en_acc, int& taken,
-                                                 bool& taken_valid) {
-    float e[LEN];
-    float m, S, W;
-    seg_stats<LEN>(z + OFF, e, m, S, W);
-    const SegScalars sc = seg_finish(m, S, W);
-    int a;
-    if (MODE == kSample) {
-        const float u = uni[K];
-        const float t = u * S;
-        float c = 0.f;
-        bool near = false;
-        a = cdf_count<LEN - 1>(e, c, t, sample_guard(S, W, LEN), near);
-        if (near) a = sample_component_fp64(zc + OFF, mc + OFF, LEN, u);
-        aout[K] = a;
-    } else {
-        a = check_action(ain[K], LEN, status);
-    }
-    // z'_a re-read from shared memory (dynamic index); sentinel when the taken entry is masked (Q2)
-    taken = OFF + a;
-    taken_valid = mc[OFF + a] != 0;
-    const float za = taken_valid ? zc[OFF + a] : kMaskFill;
-    lp_acc += za - sc.lse;
-    en_acc += sc.ent;
-    if (MODE == kEvalBwd) {
-        // d/dz_i [g_lp*logp + g_h*H] = p_i*(-g_lp - g_h*(l_i + H)) + g_lp*[i==a]; masked entries have
-        // p_i == 0; a fully masked component gets exactly 0 (SURVEY 7.2, verified vs autograd)
-        const float invS = sc.dead ? 0.f : 1.f / S;
-        const float c0 = -g_lp - g_h * sc.ent;
-#pragma unroll
-        for (int i = 0; i < LEN; ++i) {
-            const float l = z[OFF + i] - sc.lse;
-            z[OFF + i] = (e[i] * invS) * fmaf(-g_h, l, c0);
-        }
-    }
-}
-
 template <int MODE>
-__device__ __forceinline__ void a_role_cell(float* zc, const uint8_t* mc, const int64_t* ain, int64_t* aout,
-                                            const float* uni, float g_lp, float g_h, int* status, float& lp,
-                                            float& en) {
-    float z[29];
+__device__ __forceinline__ void a_role_cell(float* zc, const uint8_t* mc, int64_t* ac, const float* uni,
+                                            float g_lp, float g_h, int* status, float& lp, float& en) {
+    constexpr int OFF[6] = {0, 6, 10, 14, 18, 22};
+    constexpr int LEN[6] = {6, 4, 4, 4, 4, 7};
+    float z[29], e[29];
 #pragma unroll
     for (int j = 0; j < 14; ++j) {
         const float2 v = *reinterpret_cast<const float2*>(zc + 2 * j);
@@ -226,34 +156,108 @@ __device__ __forceinline__ void a_role_cell(float* zc, const uint8_t* mc, const 
     }
     z[28] = mc[28] ? zc[28] : kMaskFill;
 
-    int a_k[6];
-    bool v_k[6];
-    a_role_component<MODE, 0, 6, 0>(z, zc, mc, ain, aout, uni, g_lp, g_h, status, lp, en, a_k[0], v_k[0]);
-    a_role_component<MODE, 6, 4, 1>(z, zc, mc, ain, aout, uni, g_lp, g_h, status, lp, en, a_k[1], v_k[1]);
-    a_role_component<MODE, 10, 4, 2>(z, zc, mc, ain, aout, uni, g_lp, g_h, status, lp, en, a_k[2], v_k[2]);
-    a_role_component<MODE, 14, 4, 3>(z, zc, mc, ain, aout, uni, g_lp, g_h, status, lp, en, a_k[3], v_k[3]);
-    a_role_component<MODE, 18, 4, 4>(z, zc, mc, ain, aout, uni, g_lp, g_h, status, lp, en, a_k[4], v_k[4]);
-    a_role_component<MODE, 22, 7, 5>(z, zc, mc, ain, aout, uni, g_lp, g_h, status, lp, en, a_k[5], v_k[5]);
+    float m[6], S[6], W[6];
+#pragma unroll
+    for (int k = 0; k < 6; ++k) {
+        m[k] = z[OFF[k]];
+#pragma unroll
+        for (int i = 1; i < LEN[k]; ++i) m[k] = fmaxf(m[k], z[OFF[k] + i]);
+    }
+#pragma unroll
+    for (int k = 0; k < 6; ++k) {
+        S[k] = 0.f;
+        W[k] = 0.f;
+#pragma unroll
+        for (int i = 0; i < LEN[k]; ++i) {
+            const float d = z[OFF[k] + i] - m[k];
+            const float ei = ex2_approx(d * kLog2e);
+            e[OFF[k] + i] = ei;
+            S[k] += ei;
+            W[k] = fmaf(ei, d, W[k]);
+        }
+    }
+    SegScalars sc[6];
+#pragma unroll
+    for (int k = 0; k < 6; ++k) sc[k] = seg_finish(m[k], S[k], W[k]);
 
+    int a[6];
+    if (MODE == kSample) {
+        unsigned near_bits = 0;
+#pragma unroll
+        for (int k = 0; k < 6; ++k) {
+            const float t = uni[k] * S[k];
+            const float guard = sample_guard(S[k], W[k], LEN[k]);
+            float c = 0.f;
+            int cnt = 0;
+            bool near = false;
+#pragma unroll
+            for (int i = 0; i < LEN[k] - 1; ++i) {
+                c += e[OFF[k] + i];
+                cnt += (t >= c) ? 1 : 0;
+                near = near || (fabsf(t - c) <= guard);
+            }
+            a[k] = cnt;
+            near_bits |= near ? (1u << k) : 0u;
+        }
+        if (near_bits) {                       // rare: decide exactly as the fp64 definition does
+#pragma unroll
+            for (int k = 0; k < 6; ++k)
+                if (near_bits & (1u << k)) a[k] = sample_component_fp64(zc + OFF[k], mc + OFF[k], LEN[k], uni[k]);
+        }
+#pragma unroll
+        for (int k = 0; k < 6; ++k) ac[k] = a[k];
+    } else {
+        bool bad = false;
+#pragma unroll
+        for (int k = 0; k < 6; ++k) {
+            const long long v = ac[k];
+            bad = bad || (v < 0) || (v >= LEN[k]);
+            a[k] = int(v < 0 ? 0 : (v >= LEN[k] ? LEN[k] - 1 : v));
+        }
+        if (bad && status) atomicOr(status, kStatusBadAction);
+    }
+    bool taken_valid[6];
+#pragma unroll
+    for (int k = 0; k < 6; ++k) {
+        // z'_a re-read from shared memory (dynamic index); sentinel when the taken entry is masked (Q2)
+        taken_valid[k] = mc[OFF[k] + a[k]] != 0;
+        const float za = taken_valid[k] ? zc[OFF[k] + a[k]] : kMaskFill;
+        lp += za - sc[k].lse;
+        en += sc[k].ent;
+    }
     if (MODE == kEvalBwd) {
+        // d/dz_i [g_lp*logp + g_h*H] = p_i*(-g_lp - g_h*(l_i + H)) + g_lp*[i==a]; masked entries have
+        // p_i == 0; a fully masked component gets exactly 0 (SURVEY 7.2, verified vs autograd)
+#pragma unroll
+        for (int k = 0; k < 6; ++k) {
+            const float invS = sc[k].dead ? 0.f : __fdividef(1.f, S[k]);
+            const float c0 = -g_lp - g_h * sc[k].ent;
+#pragma unroll
+            for (int i = 0; i < LEN[k]; ++i) {
+                const float l = z[OFF[k] + i] - sc[k].lse;
+                z[OFF[k] + i] = (e[OFF[k] + i] * invS) * fmaf(-g_h, l, c0);
+            }
+        }
         // z[] now holds dlogits; write it over the logits in the stage, then add the one-hot term
 #pragma unroll
         for (int j = 0; j < 14; ++j) *reinterpret_cast<float2*>(zc + 2 * j) = make_float2(z[2 * j], z[2 * j + 1]);
         zc[28] = z[28];
 #pragma unroll
         for (int k = 0; k < 6; ++k)
-            if (v_k[k]) zc[a_k[k]] += g_lp;
+            if (taken_valid[k]) zc[OFF[k] + a[k]] += g_lp;
     }
 }
 
 // ---------------------------------------------------------------------------------------------
 // B role: a lane pair per cell, the 49-way component (logit offsets 29..77).
 // even lane: element 29 + pairs 30..53 (25 entries); odd lane: pairs 54..77 (24 entries).
+// The 24 paired entries are summed as four independent blocks of six (ILP); the sampling CDF is
+// base_of_block + running sum inside the block.
 // ---------------------------------------------------------------------------------------------
 template <int MODE>
-__device__ __forceinline__ void b_role_cell(bool active, int half, float* zc, const uint8_t* mc,
-                                            const int64_t* ain, int64_t* aout, const float* uni, float g_lp,
-                                            float g_h, int* status, float& lp, float& en) {
+__device__ __forceinline__ void b_role_cell(bool active, int half, float* zc, const uint8_t* mc, int64_t* ac,
+                                            const float* uni, float g_lp, float g_h, int* status, float& lp,
+                                            float& en) {
     constexpr int OFF = 29, LEN = 49;
     const int pb = 30 + 24 * half;
     const bool has_x = (half == 0);
@@ -272,31 +276,45 @@ __device__ __forceinline__ void b_role_cell(bool active, int half, float* zc, co
 #pragma unroll
         for (int j = 0; j < 24; ++j) z[j] = kMaskFill;
     }
-    float m = z[0];
+    float mb[4];
 #pragma unroll
-    for (int i = 1; i < 24; ++i) m = fmaxf(m, z[i]);
+    for (int b = 0; b < 4; ++b) {
+        mb[b] = z[6 * b];
+#pragma unroll
+        for (int i = 1; i < 6; ++i) mb[b] = fmaxf(mb[b], z[6 * b + i]);
+    }
+    float m = fmaxf(fmaxf(mb[0], mb[1]), fmaxf(mb[2], mb[3]));
     if (has_x) m = fmaxf(m, zx);
     m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, 1));
-    float S = 0.f, W = 0.f;
+
+    float Sb[4], Wb[4];
+#pragma unroll
+    for (int b = 0; b < 4; ++b) {
+        Sb[b] = 0.f;
+        Wb[b] = 0.f;
+#pragma unroll
+        for (int i = 0; i < 6; ++i) {
+            const float d = z[6 * b + i] - m;
+            const float ei = ex2_approx(d * kLog2e);
+            e[6 * b + i] = ei;
+            Sb[b] += ei;
+            Wb[b] = fmaf(ei, d, Wb[b]);
+        }
+    }
+    float Wx = 0.f;
     if (has_x) {
         const float d = zx - m;
         ex = ex2_approx(d * kLog2e);
-        S = ex;
-        W = ex * d;
+        Wx = ex * d;
     }
-#pragma unroll
-    for (int i = 0; i < 24; ++i) {
-        const float d = z[i] - m;
-        const float ei = ex2_approx(d * kLog2e);
-        e[i] = ei;
-        S += ei;
-        W = fmaf(ei, d, W);
-    }
-    const float S_own = S;
-    const float S_other = __shfl_xor_sync(0xffffffffu, S, 1);
-    S = has_x ? (S_own + S_other) : (S_other + S_own);     // same operand order on both lanes
-    const float W_other = __shfl_xor_sync(0xffffffffu, W, 1);
-    W = has_x ? (W + W_other) : (W_other + W);
+    // bases of the four blocks in this lane's part of the CDF (the odd lane's start is filled below)
+    const float own1 = ex + Sb[0], own2 = own1 + Sb[1], own3 = own2 + Sb[2];
+    const float S_own = own3 + Sb[3];
+    const float W_own = ((Wx + Wb[0]) + Wb[1]) + (Wb[2] + Wb[3]);
+    const float S_other = __shfl_xor_sync(0xffffffffu, S_own, 1);
+    const float W_other = __shfl_xor_sync(0xffffffffu, W_own, 1);
+    const float S = has_x ? (S_own + S_other) : (S_other + S_own);     // same operand order on both lanes
+    const float W = has_x ? (W_own + W_other) : (W_other + W_own);
     const SegScalars sc = seg_finish(m, S, W);
 
     int a = 0;
@@ -304,36 +322,48 @@ __device__ __forceinline__ void b_role_cell(bool active, int half, float* zc, co
         const float u = active ? uni[6] : 0.5f;
         const float t = u * S;
         const float guard = sample_guard(S, W, LEN);
+        const float start = has_x ? 0.f : S_other;     // even lane's 25 entries come first
         bool near = false;
-        int cnt;
+        int cnt = 0;
         if (has_x) {
-            float c = ex;
-            cnt = (t >= c) ? 1 : 0;
-            near = fabsf(t - c) <= guard;
-            cnt += cdf_count<24>(e, c, t, guard, near);
-        } else {
-            float c = S_other;                         // sum of the even lane's 25 entries
-            cnt = cdf_count<23>(e, c, t, guard, near);  // entry 48 (k = n-1) is not counted
+            cnt = (t >= ex) ? 1 : 0;
+            near = fabsf(t - ex) <= guard;
+        }
+        const float base[4] = {start + ex, start + own1, start + own2, start + own3};
+#pragma unroll
+        for (int b = 0; b < 4; ++b) {
+            float c = base[b];
+#pragma unroll
+            for (int i = 0; i < 6; ++i) {
+                c += e[6 * b + i];
+                // entry 48 (k = n-1: the odd lane's last one) is not an edge of the count
+                const bool edge = has_x || (6 * b + i < 23);
+                cnt += (edge && t >= c) ? 1 : 0;
+                near = near || (edge && fabsf(t - c) <= guard);
+            }
         }
         cnt += __shfl_xor_sync(0xffffffffu, cnt, 1);
-        near = __shfl_xor_sync(0xffffffffu, int(near), 1) || near;
+        near = (__shfl_xor_sync(0xffffffffu, int(near), 1) != 0) || near;
         a = cnt;
         if (near && has_x && active) a = sample_component_fp64(zc + OFF, mc + OFF, LEN, u);
         a = __shfl_sync(0xffffffffu, a, (threadIdx.x & 31) & ~1);
-        if (has_x && active) aout[6] = a;
+        if (has_x && active) ac[6] = a;
     } else if (active) {
-        a = check_action(ain[6], LEN, has_x ? status : nullptr);
+        const long long v = ac[6];
+        const bool bad = (v < 0) || (v >= LEN);
+        a = int(v < 0 ? 0 : (v >= LEN ? LEN - 1 : v));
+        if (bad && has_x && status) atomicOr(status, kStatusBadAction);
     }
+    const bool taken_valid = active && (mc[OFF + a] != 0);
     if (active && has_x) {
-        const float za = mc[OFF + a] ? zc[OFF + a] : kMaskFill;
+        const float za = taken_valid ? zc[OFF + a] : kMaskFill;
         lp += za - sc.lse;
         en += sc.ent;
     }
     if (MODE == kEvalBwd) {
-        const bool taken_valid = active && (mc[OFF + a] != 0);
         __syncwarp();       // the even lane has read z'_a (possibly in the odd lane's range) above
         if (active) {
-            const float invS = sc.dead ? 0.f : 1.f / S;
+            const float invS = sc.dead ? 0.f : __fdividef(1.f, S);
             const float c0 = -g_lp - g_h * sc.ent;
 #pragma unroll
             for (int j = 0; j < 12; ++j) {
@@ -544,9 +574,9 @@ __global__ void __launch_bounds__(HeadCfg<TC, MODE>::kThreads) head_kernel(const
             const float* uc = reinterpret_cast<const float*>(st + Cfg::kOffUni) + cell_in_tile * kCompsPerCell;
             float lp = 0.f, en = 0.f;
             if (role == 0) {
-                if (active) a_role_cell<MODE>(zc, mc, ac, ac, uc, g_lp, g_h, p.status, lp, en);
+                if (active) a_role_cell<MODE>(zc, mc, ac, uc, g_lp, g_h, p.status, lp, en);
             } else {
-                b_role_cell<MODE>(active, half, zc, mc, ac, ac, uc, g_lp, g_h, p.status, lp, en);
+                b_role_cell<MODE>(active, half, zc, mc, ac, uc, g_lp, g_h, p.status, lp, en);
             }
             if (MODE != kEvalBwd) {
                 lp = warp_sum(lp);
@@ -566,31 +596,53 @@ __global__ void __launch_bounds__(HeadCfg<TC, MODE>::kThreads) head_kernel(const
 // ---------------------------------------------------------------------------------------------
 // Host launchers
 // ---------------------------------------------------------------------------------------------
-static int g_head_ctas_per_sm = 2;
+static int g_head_ctas_per_sm = 0;      // 0 = as many as fit (occupancy query)
 static int g_head_grid_override = 0;
-void head_set_tuning(int ctas_per_sm, int grid_override) {
-    if (ctas_per_sm > 0) g_head_ctas_per_sm = ctas_per_sm;
+static int g_head_variant = 0;          // tile / pipeline shape, see dispatch_head
+void head_set_tuning(int ctas_per_sm, int grid_override, int variant) {
+    g_head_ctas_per_sm = ctas_per_sm;
     g_head_grid_override = grid_override;
+    g_head_variant = variant;
 }
 
 template <int TC, int MODE, int NSTAGE>
-static int launch_head(const HeadParams& p, cudaStream_t stream) {
+static int launch_head(HeadParams p, cudaStream_t stream) {
     using Cfg = HeadCfg<TC, MODE>;
     constexpr size_t smem = head_smem_bytes<TC, MODE, NSTAGE>();
-    static bool attr_set[64] = {};
+    static int occ[64] = {};
     int dev = 0;
     MB_CUDA(cudaGetDevice(&dev));
-    if (dev < 64 && !attr_set[dev]) {
+    if (dev >= 64) dev = 63;
+    if (occ[dev] == 0) {
         MB_CUDA(cudaFuncSetAttribute(head_kernel<TC, MODE, NSTAGE>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                      int(smem)));
-        attr_set[dev] = true;
+        int n = 0;
+        MB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, head_kernel<TC, MODE, NSTAGE>, Cfg::kThreads,
+                                                              smem));
+        occ[dev] = n > 0 ? n : 1;
     }
-    long long grid = (long long)sm_count(dev) * g_head_ctas_per_sm;
+    p.tiles_per_frame = (p.cells + TC - 1) / TC;
+    const int per_sm = (g_head_ctas_per_sm > 0 && g_head_ctas_per_sm < occ[dev]) ? g_head_ctas_per_sm : occ[dev];
+    long long grid = (long long)sm_count(dev) * per_sm;
     if (g_head_grid_override > 0) grid = g_head_grid_override;
     if (grid > p.n_frames) grid = p.n_frames;
     head_kernel<TC, MODE, NSTAGE><<<dim3((unsigned)grid), dim3(Cfg::kThreads), smem, stream>>>(p);
     MB_CUDA(cudaGetLastError());
     return MB_OK;
+}
+
+// Tile / pipeline shapes selectable with mb_set_tuning("head_variant", v) for benchmarking.
+template <int MODE>
+static int dispatch_head(const HeadParams& p, cudaStream_t stream) {
+    switch (g_head_variant) {
+        case 1: return launch_head<64, MODE, 2>(p, stream);
+        case 2: return launch_head<64, MODE, 4>(p, stream);
+        case 3: return launch_head<32, MODE, 3>(p, stream);
+        case 4: return launch_head<32, MODE, 5>(p, stream);
+        case 5: return launch_head<128, MODE, 3>(p, stream);
+        case 6: return launch_head<128, MODE, 2>(p, stream);
+        default: return launch_head<64, MODE, 3>(p, stream);
+    }
 }
 
 static int check_head_common(const void* logits, const void* mask, long long n_frames, int cells) {
@@ -619,8 +671,8 @@ int head_eval_fwd(const float* logits, const uint8_t* mask, const int64_t* actio
     }
     HeadParams p{};
     p.logits = logits; p.mask = mask; p.action_in = action; p.logp_out = logp_out; p.ent_out = ent_out;
-    p.status = status; p.n_frames = n_frames; p.cells = cells; p.tiles_per_frame = (cells + 63) / 64;
-    return launch_head<64, kEvalFwd, 3>(p, stream);
+    p.status = status; p.n_frames = n_frames; p.cells = cells; 
+    return dispatch_head<kEvalFwd>(p, stream);
 }
 
 int head_eval_bwd(const float* logits, const uint8_t* mask, const int64_t* action, const float* g_logp,
@@ -635,8 +687,7 @@ int head_eval_bwd(const float* logits, const uint8_t* mask, const int64_t* actio
     HeadParams p{};
     p.logits = logits; p.mask = mask; p.action_in = action; p.g_logp = g_logp; p.g_ent = g_ent;
     p.dlogits = dlogits; p.status = status; p.n_frames = n_frames; p.cells = cells;
-    p.tiles_per_frame = (cells + 63) / 64;
-    return launch_head<64, kEvalBwd, 3>(p, stream);
+    return dispatch_head<kEvalBwd>(p, stream);
 }
 
 int head_sample(const float* logits, const uint8_t* mask, const float* uniforms, int64_t* action_out,
@@ -650,8 +701,7 @@ int head_sample(const float* logits, const uint8_t* mask, const float* uniforms,
     HeadParams p{};
     p.logits = logits; p.mask = mask; p.uniforms = uniforms; p.action_out = action_out; p.logp_out = logp_out;
     p.ent_out = ent_out; p.status = status; p.n_frames = n_frames; p.cells = cells;
-    p.tiles_per_frame = (cells + 63) / 64;
-    return launch_head<64, kSample, 3>(p, stream);
+    return dispatch_head<kSample>(p, stream);
 }
 
 }  // namespace mb

@@ -31,13 +31,23 @@ def golden():
     return load
 
 
-def close_rms(x, ref, rtol=1e-5):
-    """Parity norm of SURVEY 7.3-2: |x-ref| <= rtol * max(|ref|, rms(ref))."""
+def close_rms(x, ref, rtol=1e-5, support=None):
+    """Parity norm of SURVEY 7.3-2: |x-ref| <= rtol * max(|ref|, rms(ref)).
+
+    ``support`` (bool tensor): the entries that carry signal, e.g. the unmasked logits of a
+    gradient.  rms is then taken over the support only (a tensor that is 95 % structural zeros
+    would otherwise shrink the rms term to nothing and turn the test into a pure relative one
+    on entries that are themselves differences of nearly equal fp32 numbers); entries outside
+    the support must be checked for exact zeros by the caller.
+    """
     x = torch.as_tensor(x).double().cpu()
     ref = torch.as_tensor(ref).double().cpu()
-    rms = ref.pow(2).mean().sqrt() if ref.numel() else torch.tensor(0.0)
+    if support is not None:
+        sel = torch.as_tensor(support).cpu().bool()
+        x, ref = x[sel], ref[sel]
+    if ref.numel() == 0:
+        return True, 0.0
+    rms = ref.pow(2).mean().sqrt()
     bound = rtol * torch.maximum(ref.abs(), rms.expand_as(ref)) + 1e-30
     err = (x - ref).abs()
-    ok = bool((err <= bound).all())
-    worst = float((err / bound).max()) if ref.numel() else 0.0
-    return ok, worst
+    return bool((err <= bound).all()), float((err / bound).max())
