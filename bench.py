@@ -382,7 +382,7 @@ def run_sweep(args):
         out = torch.empty_like(logits)
         names = {0: "64x3", 1: "64x2", 2: "64x4", 3: "32x3", 4: "32x5", 5: "128x3", 6: "128x2"}
         for variant, vname in names.items():
-            for per_sm in (0, 1):
+            for per_sm in (0,):
                 microbeast_b200.set_tuning("head_variant", variant)
                 microbeast_b200.set_tuning("head_ctas_per_sm", per_sm)
                 for kname, fn, per_cell in (
@@ -394,10 +394,11 @@ def run_sweep(args):
                     gbs = nbytes / (med * 1e-3) / 1e9
                     rows_out.append({"kernel": kname, "variant": vname, "ctas_per_sm": per_sm or "max",
                                      "median_us": med * 1e3, "gbs": gbs, "frac_of_peak": gbs / peak})
-        microbeast_b200.set_tuning("head_variant", 0)
+        microbeast_b200.set_tuning("head_variant", -1)
         microbeast_b200.set_tuning("head_ctas_per_sm", 0)
-        for st in (2, 3, 4):
+        for st, promo in ((2, 256), (2, 128), (3, 256), (3, 128)):
             microbeast_b200.set_tuning("vtrace_stages", st)
+            microbeast_b200.set_tuning("vtrace_l2_promo", promo)
             for T, R in ((512, 65536), (256, 65536), (80, 65536)):
                 t = synth.make_vtrace_inputs(R, T, gen=g, device=dev)
                 fn = lambda: ops.vtrace_loss(t["lp_old"], t["lp_new"], t["values"], t["bootstrap"], t["rewards"],
@@ -405,10 +406,11 @@ def run_sweep(args):
                 med, p10, p90 = bench(fn, 10)
                 nbytes = 37 * R * T + 4 * R
                 gbs = nbytes / (med * 1e-3) / 1e9
-                rows_out.append({"kernel": "vtrace_loss", "variant": f"stages{st}", "T": T, "rows": R,
+                rows_out.append({"kernel": "vtrace_loss", "variant": f"stages{st}/promo{promo}", "T": T, "rows": R,
                                  "median_us": med * 1e3, "gbs": gbs, "frac_of_peak": gbs / peak})
                 del t
-        microbeast_b200.set_tuning("vtrace_stages", 3)
+        microbeast_b200.set_tuning("vtrace_stages", 2)
+        microbeast_b200.set_tuning("vtrace_l2_promo", 256)
     else:
         for name, (h, w, T, rows) in WORKLOADS.items():
             cells, n = h * w, rows * (T + 1)

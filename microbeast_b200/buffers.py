@@ -1,0 +1,223 @@
+"""Rollout store and batcher on pinned / device memory.
+
+Drop-ins for reference ``libs/utils.py:29-55`` (``create_buffers``) and ``:166-218``
+(``get_batch``); the slot-write contract of ``microbeast.py:73-100`` is unchanged
+(``buffers[key][index][t, ...] = value``).
+
+What changes underneath:
+
+* every key lives in ONE slab ``[n_buffers, T+1, n_envs, ...]`` in shared memory
+  (actor processes keep writing into it) that the learner process page-locks with
+  ``cudaHostRegister``, so host->device copies are asynchronous DMA;
+* wire format: ``obs`` travels as uint8 (microRTS planes are 0/1; 4x fewer bytes than the
+  reference's float32) and is widened on the device; ``action_mask`` stays uint8,
+  ``action`` int64 (the dtypes of the C ABI);
+* keys the learner never reads (``policy_logits``: 80 KB/frame at 16x16, ``last_action``,
+  ``ep_return``, ``ep_step``) are backed by a write-discarding slot when ``lean=True``,
+  so an unmodified ``act()`` still runs but nothing is stored or copied;
+* ``get_batch`` blocks on the queue instead of spinning on ``qsize()``
+  (``libs/utils.py:183-188`` burns a core), copies each buffer straight into its column of a
+  device-contiguous ``[T+1, B, n_envs, ...]`` staging tensor on a copy stream (no host
+  ``torch.stack``), and recycles the indices only after the DMA has finished.
+
+The flattening order is the reference's ``(t, b, e)`` (``libs/utils.py:197-205``), so
+``PPO_learn``'s reshape semantics (quirk Q7) are preserved.
+"""
+from __future__ import annotations
+
+import queue
+import threading
+from typing import Dict, List, Optional
+
+import torch
+
+Buffers = Dict[str, List[torch.Tensor]]
+
+LEARNER_KEYS = ("obs", "reward", "done", "logprobs", "action", "action_mask", "baseline")
+DEAD_KEYS = ("ep_return", "ep_step", "policy_logits", "last_action")
+
+
+def buffer_specs(n_envs: int, T: int, obs_size: tuple, obs_dtype=torch.float32) -> Dict[str, dict]:
+    """Shapes / dtypes of one rollout buffer -- reference ``libs/utils.py:33-46``."""
+    h = w = obs_size[0]
+    return dict(
+        obs=dict(size=(T + 1, n_envs, *obs_size), dtype=obs_dtype),
+        reward=dict(size=(T + 1, n_envs), dtype=torch.float32),
+        done=dict(size=(T + 1, n_envs), dtype=torch.bool),
+        ep_return=dict(size=(T + 1, n_envs), dtype=torch.float32),
+        ep_step=dict(size=(T + 1, n_envs), dtype=torch.int32),
+        policy_logits=dict(size=(T + 1, n_envs, h * w * 78), dtype=torch.float32),
+        baseline=dict(size=(T + 1, n_envs), dtype=torch.float32),
+        last_action=dict(size=(T + 1, n_envs, h * w * 7), dtype=torch.int64),
+        action=dict(size=(T + 1, n_envs, h * w * 7), dtype=torch.int64),
+        action_mask=dict(size=(T + 1, n_envs, 78 * h * w), dtype=torch.uint8),
+        logprobs=dict(size=(T + 1, n_envs), dtype=torch.float32),
+    )
+
+
+class DiscardSlot:
+    """Stands in for a buffer nobody reads: accepts the actor's slot writes and drops them."""
+
+    def __init__(self, size, dtype):
+        self.shape = torch.Size(size)
+        self.dtype = dtype
+
+    def size(self):
+        return self.shape
+
+    def __setitem__(self, index, value):
+        pass
+
+    def __getitem__(self, index):
+        return self
+
+    def share_memory_(self):
+        return self
+
+
+class RolloutBuffers(dict):
+    """``Dict[str, List[Tensor]]`` like the reference's, plus the slabs behind the lists."""
+
+    def __init__(self):
+        super().__init__()
+        self.slabs: Dict[str, torch.Tensor] = {}
+        self.pinned = False
+        self.n_buffers = 0
+        self._lock = threading.Lock()
+        self._staging = {}           # device -> [set0, set1] of {key: tensor}
+        self._turn = {}
+        self._pending = []           # (event, indices, free_queue) waiting for their DMA
+        self._stream = {}
+
+    def live_keys(self):
+        return [k for k, v in self.items() if isinstance(v[0], torch.Tensor)]
+
+    def pin(self) -> bool:
+        """Page-lock the shared slabs in THIS process (call once in the learner process)."""
+        if self.pinned or not torch.cuda.is_available():
+            return self.pinned
+        rt = torch.cuda.cudart()
+        for slab in self.slabs.values():
+            err = rt.cudaHostRegister(slab.data_ptr(), slab.numel() * slab.element_size(), 0)
+            if int(err) != 0:
+                raise RuntimeError(f"cudaHostRegister failed with error {int(err)}")
+        self.pinned = True
+        return True
+
+
+def create_buffers(n_buffers: int, n_envs: int, B: int, T: int, obs_size: tuple, *, lean: bool = True,
+                   obs_dtype=torch.uint8, share: bool = True) -> Buffers:
+    """Creates ``n_buffers`` rollout buffers shared between processes -- reference
+    ``libs/utils.py:29-55``, same positional signature and the same 11 keys.
+
+    ``lean=False, obs_dtype=torch.float32`` reproduces the reference layout exactly.
+    """
+    specs = buffer_specs(n_envs, T, tuple(obs_size), obs_dtype)
+    buffers = RolloutBuffers()
+    buffers.n_buffers = n_buffers
+    for key, spec in specs.items():
+        if lean and key in DEAD_KEYS:
+            buffers[key] = [DiscardSlot(spec["size"], spec["dtype"]) for _ in range(n_buffers)]
+            continue
+        slab = torch.zeros((n_buffers,) + tuple(spec["size"]), dtype=spec["dtype"])
+        if share:
+            slab.share_memory_()
+        buffers.slabs[key] = slab
+        buffers[key] = [slab[i] for i in range(n_buffers)]
+    return buffers
+
+
+def _recycle(buffers: RolloutBuffers, block: bool) -> None:
+    still = []
+    for event, indices, free_queue in buffers._pending:
+        if event is not None and not block and not event.query():
+            still.append((event, indices, free_queue))
+            continue
+        if event is not None:
+            event.synchronize()
+        for m in indices:
+            free_queue.put(m)                                    # utils.py:211-213
+    buffers._pending = still
+
+
+def get_batch(batch_size: int, shapes: dict, gamma: float, device, free_queue, full_queue, buffers: Buffers,
+              lock=threading.Lock(), *, keys: Optional[tuple] = None) -> dict:
+    """Returns ``batch_size`` rollouts as one flat batch -- reference ``libs/utils.py:166-218``.
+
+    Output: ``{key: [ (T+1)*batch_size*n_envs, ... ]}`` in ``(t, b, e)`` order, on ``device``.
+    ``shapes`` and ``gamma`` are accepted and ignored like in the reference.  With a CUDA
+    ``device`` the copies run on a side stream and the current stream is made to wait for them;
+    buffer indices return to ``free_queue`` once their DMA is done (at the latest on the next
+    call).
+    """
+    if not isinstance(lock, type(threading.Lock())):
+        lock = threading.Lock()
+    dev = torch.device(device) if device is not None else torch.device("cpu")
+    rb = buffers if isinstance(buffers, RolloutBuffers) else None
+    with lock:                                                   # utils.py:191-192
+        indices = []
+        while len(indices) < batch_size:                         # blocking get; no qsize() spin
+            try:
+                indices.append(full_queue.get(timeout=0.05))
+            except queue.Empty:
+                if rb is not None and rb._pending:
+                    _recycle(rb, block=True)     # actors may be waiting for buffers whose DMA is pending
+    live = [k for k, v in buffers.items() if isinstance(v[0], torch.Tensor)]
+    if keys is not None:
+        live = [k for k in live if k in keys]
+
+    if dev.type != "cuda":
+        # host batch (reference semantics: stack dim=1, flatten) -- used by CPU tests and actors
+        batch = {}
+        for key in live:
+            x = torch.stack([buffers[key][m] for m in indices], dim=1)            # utils.py:197-199
+            batch[key] = x.reshape((-1,) + tuple(x.shape[3:]))                    # utils.py:203-205
+        for m in indices:
+            free_queue.put(m)
+        return batch
+
+    if rb is not None:
+        rb.pin()
+        _recycle(rb, block=False)
+        sets = rb._staging.get((dev, batch_size))
+        if sets is None:
+            sets = []
+            for _ in range(2):
+                sets.append({key: torch.empty((buffers[key][0].shape[0], batch_size) + tuple(buffers[key][0].shape[1:]),
+                                              dtype=buffers[key][0].dtype, device=dev) for key in live})
+            rb._staging[(dev, batch_size)] = sets
+            rb._turn[(dev, batch_size)] = 0
+            rb._stream[dev] = torch.cuda.Stream(device=dev)
+        turn = rb._turn[(dev, batch_size)]
+        rb._turn[(dev, batch_size)] = turn ^ 1
+        stage = sets[turn]
+        stream = rb._stream[dev]
+    else:
+        stage = {key: torch.empty((buffers[key][0].shape[0], batch_size) + tuple(buffers[key][0].shape[1:]),
+                                  dtype=buffers[key][0].dtype, device=dev) for key in live}
+        stream = torch.cuda.Stream(device=dev)
+
+    cur = torch.cuda.current_stream(dev)
+    stream.wait_stream(cur)          # the staging set may still be read by the step before last
+    with torch.cuda.stream(stream):
+        for key in live:
+            dst = stage[key]
+            for j, m in enumerate(indices):
+                dst[:, j].copy_(buffers[key][m], non_blocking=True)
+        done = torch.cuda.Event()
+        done.record(stream)
+    cur.wait_event(done)
+    batch = {key: stage[key].reshape((-1,) + tuple(stage[key].shape[3:])) for key in live}
+    if rb is not None:
+        rb._pending.append((done, indices, free_queue))
+    else:
+        done.synchronize()
+        for m in indices:
+            free_queue.put(m)
+    return batch
+
+
+def release(buffers: Buffers) -> None:
+    """Wait for outstanding DMA and hand every buffer index back (call before shutdown)."""
+    if isinstance(buffers, RolloutBuffers):
+        _recycle(buffers, block=True)

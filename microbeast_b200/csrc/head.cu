@@ -59,50 +59,77 @@ struct HeadCfg {
     static_assert(TC % 32 == 0 && TC % 8 == 0, "tile granularity");
 };
 
+constexpr int kUcdfEntries = 64;     // exact uniform-CDF tables for n = 4 (3 edges), 6 (5), 7 (6), 49 (48)
+
 template <int TC, int MODE, int NSTAGE>
 constexpr size_t head_smem_bytes() {
     using Cfg = HeadCfg<TC, MODE>;
     return size_t(NSTAGE) * Cfg::kStageBytes + size_t(NSTAGE) * Cfg::kConsWarps * 2 * sizeof(float) +
-           2 * NSTAGE * sizeof(uint64_t) + 128;
+           2 * NSTAGE * sizeof(uint64_t) + kUcdfEntries * sizeof(double) + 128;
 }
 
 // ---------------------------------------------------------------------------------------------
-// fp64 restatement of the sampler definition (oracle/head.py: sample_invcdf), used only when the
-// fp32 fast path cannot decide (u within the guard band of a CDF edge).
-//   p = softmax(l), l = z' - logsumexp(z')  in fp64;  cdf sequential;  a = #{k<n-1 : u >= cdf_k};
-//   if the component has a valid entry and mask[a]==0, a = last valid index.
+// Exact (fp64) sampler decisions, as the oracle defines them (oracle/head.py: sample_invcdf):
+//   p = CategoricalMasked(logits.double(), mask).probs;  cdf sequential in fp64;
+//   a = #{k < n-1 : double(u) >= cdf_k};  landing on a masked entry -> last valid index.
+// Two places need them: (1) fully masked components (the common case, p == 1/n exactly) use a
+// per-CTA table of the sequential fp64 sums of fl(1/n); (2) components whose fp32 running CDF
+// puts u*S inside the guard band of an edge are recomputed by the WHOLE warp (the lanes would
+// idle through a divergent single-thread fallback anyway).
 // ---------------------------------------------------------------------------------------------
-__device__ __noinline__ int sample_component_fp64(const float* z, const uint8_t* mk, int len, float u) {
-    double m1 = -1e300;
-    for (int i = 0; i < len; ++i) {
-        double zi = mk[i] ? double(z[i]) : -1e8;
-        m1 = fmax(m1, zi);
-    }
-    double s1 = 0.0;
-    for (int i = 0; i < len; ++i) {
-        double zi = mk[i] ? double(z[i]) : -1e8;
-        s1 += exp(zi - m1);
-    }
-    const double lse = m1 + log(s1);
-    // second normalisation (Categorical.probs = softmax(normalised logits)); max(l) = m1 - lse
-    const double m2 = m1 - lse;
-    double s2 = 0.0;
-    for (int i = 0; i < len; ++i) {
-        double zi = mk[i] ? double(z[i]) : -1e8;
-        s2 += exp((zi - lse) - m2);
-    }
-    const double ud = double(u);
-    double cdf = 0.0;
-    int a = 0, last_valid = -1;
-    for (int i = 0; i < len; ++i) {
-        double zi = mk[i] ? double(z[i]) : -1e8;
-        if (mk[i]) last_valid = i;
-        if (i < len - 1) {
-            cdf += exp((zi - lse) - m2) / s2;
-            a += (ud >= cdf) ? 1 : 0;
+__device__ __forceinline__ constexpr int ucdf_offset(int n) { return n == 4 ? 0 : (n == 6 ? 3 : (n == 7 ? 8 : 14)); }
+
+__device__ __forceinline__ void ucdf_fill(double* tab) {
+    const int ns[4] = {4, 6, 7, 49};
+    for (int j = 0; j < 4; ++j) {
+        const int n = ns[j];
+        const double p = 1.0 / double(n);          // softmax of n equal logits: exp(0) / n
+        double acc = 0.0;
+        for (int k = 0; k < n - 1; ++k) {
+            acc += p;                               // sequential, like numpy.cumsum
+            tab[ucdf_offset(n) + k] = acc;
         }
     }
-    if (last_valid >= 0 && mk[a] == 0) a = last_valid;
+}
+
+// Uniform (fully masked, quirk Q1) component: exact count from the table around floor(u*n).
+__device__ __forceinline__ int ucdf_pick(const double* tab, int n, float u) {
+    const double* t = tab + ucdf_offset(n);
+    const double ud = double(u);
+    int a = min(max(int(u * float(n)), 0), n - 1);
+    while (a > 0 && ud < t[a - 1]) --a;
+    while (a < n - 1 && ud >= t[a]) ++a;
+    return a;
+}
+
+// Warp-cooperative exact recompute of one component (all 32 lanes call it with the same args).
+// Single normalisation p_i = exp(z'_i - m) / sum: equal to the oracle's doubly normalised softmax
+// up to ~1e-16 relative, and bit-identical in the structured cases that can put a CDF edge exactly
+// on an fp32 uniform (equal logits / one valid entry / fully masked: exp(0) == 1, p == 1/k).
+__device__ __noinline__ int warp_sample_fp64(const float* z, const uint8_t* mk, int len, float u) {
+    const int lane = threadIdx.x & 31;
+    const bool in0 = lane < len, in1 = lane + 32 < len;
+    const bool v0 = in0 && mk[lane] != 0, v1 = in1 && mk[lane + 32] != 0;
+    const double ninf = -__longlong_as_double(0x7ff0000000000000ll);
+    const double z0 = in0 ? (v0 ? double(z[lane]) : -1e8) : ninf;
+    const double z1 = in1 ? (v1 ? double(z[lane + 32]) : -1e8) : ninf;
+    double m = fmax(z0, z1);
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) m = fmax(m, __shfl_xor_sync(0xffffffffu, m, o));
+    const double e0 = in0 ? exp(z0 - m) : 0.0, e1 = in1 ? exp(z1 - m) : 0.0;
+    const double s = warp_sum(e0 + e1);
+    const double p0 = e0 / s, p1 = e1 / s;
+    const double ud = double(u);
+    double cdf = 0.0;
+    int a = 0;
+    for (int i = 0; i < len - 1; ++i) {
+        const double pi = __shfl_sync(0xffffffffu, (i < 32) ? p0 : p1, i & 31);
+        cdf += pi;
+        a += (ud >= cdf) ? 1 : 0;
+    }
+    const unsigned vm0 = __ballot_sync(0xffffffffu, v0), vm1 = __ballot_sync(0xffffffffu, v1);
+    const bool landed = (a < 32) ? ((vm0 >> a) & 1u) : ((vm1 >> (a - 32)) & 1u);
+    if ((vm0 | vm1) && !landed) a = vm1 ? 63 - __clz(int(vm1)) : 31 - __clz(int(vm0));
     return a;
 }
 
@@ -133,9 +160,11 @@ __device__ __forceinline__ SegScalars seg_finish(float m, float S, float W) {
 }
 
 __device__ __forceinline__ float sample_guard(float S, float W, int len) {
-    // fp32 error budget of the running CDF against the fp64 definition, with a 4x margin:
-    // ex2.approx (2 ulp) + argument rounding (|d| * 2^-24 each) + len adds in any order + u*S.
-    return S * (9.5367431640625e-07f + float(len + 1) * 2.384185791015625e-07f) + 4.76837158203125e-07f * fabsf(W);
+    // Rigorous fp32 error bound of (u*S - c_k) against exact arithmetic on the same fp32 inputs,
+    // times 1.25: ex2.approx 2^-22 rel. + exponent-argument rounding 3*2^-24*|d| per term, n adds
+    // in any order n*2^-24*S, the same again for S inside t = fl(u*S), and 2^-24*S for the product:
+    //   S*(2^-21 + (2n+1)*2^-24) + 6*2^-24*|W|.
+    return 5.9604644775390625e-08f * (S * (12.f + 2.5f * float(len)) + 8.f * fabsf(W));
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -143,7 +172,8 @@ __device__ __forceinline__ float sample_guard(float S, float W, int len) {
 // ---------------------------------------------------------------------------------------------
 template <int MODE>
 __device__ __forceinline__ void a_role_cell(float* zc, const uint8_t* mc, int64_t* ac, const float* uni,
-                                            float g_lp, float g_h, int* status, float& lp, float& en) {
+                                            float g_lp, float g_h, int* status, const double* ucdf, bool active,
+                                            float& lp, float& en) {
     constexpr int OFF[6] = {0, 6, 10, 14, 18, 22};
     constexpr int LEN[6] = {6, 4, 4, 4, 4, 7};
     float z[29], e[29];
@@ -185,7 +215,8 @@ __device__ __forceinline__ void a_role_cell(float* zc, const uint8_t* mc, int64_
         unsigned near_bits = 0;
 #pragma unroll
         for (int k = 0; k < 6; ++k) {
-            const float t = uni[k] * S[k];
+            const float u = uni[k];
+            const float t = u * S[k];
             const float guard = sample_guard(S[k], W[k], LEN[k]);
             float c = 0.f;
             int cnt = 0;
@@ -196,16 +227,34 @@ __device__ __forceinline__ void a_role_cell(float* zc, const uint8_t* mc, int64_
                 cnt += (t >= c) ? 1 : 0;
                 near = near || (fabsf(t - c) <= guard);
             }
+            if (sc[k].dead) {                  // uniform over all n entries: exact table decision
+                cnt = ucdf_pick(ucdf, LEN[k], u);
+                near = false;
+            }
             a[k] = cnt;
-            near_bits |= near ? (1u << k) : 0u;
+            near_bits |= (near && active) ? (1u << k) : 0u;
         }
-        if (near_bits) {                       // rare: decide exactly as the fp64 definition does
+        // rare: decide exactly as the fp64 definition does, the whole warp on one component at a time
+        unsigned flagged = __ballot_sync(0xffffffffu, near_bits != 0);
+        while (flagged) {
+            const int src = __ffs(flagged) - 1;
+            flagged &= flagged - 1;
+            const unsigned nb = __shfl_sync(0xffffffffu, near_bits, src);
+            const int delta = (src - int(threadIdx.x & 31));          // cells are consecutive in the tile
 #pragma unroll
-            for (int k = 0; k < 6; ++k)
-                if (near_bits & (1u << k)) a[k] = sample_component_fp64(zc + OFF[k], mc + OFF[k], LEN[k], uni[k]);
+            for (int k = 0; k < 6; ++k) {
+                if (nb & (1u << k)) {
+                    const int r = warp_sample_fp64(zc + delta * kLogitsPerCell + OFF[k],
+                                                   mc + delta * kLogitsPerCell + OFF[k], LEN[k],
+                                                   uni[delta * kCompsPerCell + k]);
+                    if (delta == 0) a[k] = r;
+                }
+            }
         }
+        if (active) {
 #pragma unroll
-        for (int k = 0; k < 6; ++k) ac[k] = a[k];
+            for (int k = 0; k < 6; ++k) ac[k] = a[k];
+        }
     } else {
         bool bad = false;
 #pragma unroll
@@ -214,7 +263,7 @@ __device__ __forceinline__ void a_role_cell(float* zc, const uint8_t* mc, int64_
             bad = bad || (v < 0) || (v >= LEN[k]);
             a[k] = int(v < 0 ? 0 : (v >= LEN[k] ? LEN[k] - 1 : v));
         }
-        if (bad && status) atomicOr(status, kStatusBadAction);
+        if (bad && active && status) atomicOr(status, kStatusBadAction);
     }
     bool taken_valid[6];
 #pragma unroll
@@ -222,10 +271,10 @@ __device__ __forceinline__ void a_role_cell(float* zc, const uint8_t* mc, int64_
         // z'_a re-read from shared memory (dynamic index); sentinel when the taken entry is masked (Q2)
         taken_valid[k] = mc[OFF[k] + a[k]] != 0;
         const float za = taken_valid[k] ? zc[OFF[k] + a[k]] : kMaskFill;
-        lp += za - sc[k].lse;
-        en += sc[k].ent;
+        lp += active ? (za - sc[k].lse) : 0.f;
+        en += active ? sc[k].ent : 0.f;
     }
-    if (MODE == kEvalBwd) {
+    if (MODE == kEvalBwd && active) {
         // d/dz_i [g_lp*logp + g_h*H] = p_i*(-g_lp - g_h*(l_i + H)) + g_lp*[i==a]; masked entries have
         // p_i == 0; a fully masked component gets exactly 0 (verified vs autograd)
 #pragma unroll
@@ -256,8 +305,8 @@ __device__ __forceinline__ void a_role_cell(float* zc, const uint8_t* mc, int64_
 // ---------------------------------------------------------------------------------------------
 template <int MODE>
 __device__ __forceinline__ void b_role_cell(bool active, int half, float* zc, const uint8_t* mc, int64_t* ac,
-                                            const float* uni, float g_lp, float g_h, int* status, float& lp,
-                                            float& en) {
+                                            const float* uni, float g_lp, float g_h, int* status,
+                                            const double* ucdf, float& lp, float& en) {
     constexpr int OFF = 29, LEN = 49;
     const int pb = 30 + 24 * half;
     const bool has_x = (half == 0);
@@ -319,7 +368,7 @@ __device__ __forceinline__ void b_role_cell(bool active, int half, float* zc, co
 
     int a = 0;
     if (MODE == kSample) {
-        const float u = active ? uni[6] : 0.5f;
+        const float u = uni[6];
         const float t = u * S;
         const float guard = sample_guard(S, W, LEN);
         const float start = has_x ? 0.f : S_other;     // even lane's 25 entries come first
@@ -345,8 +394,19 @@ __device__ __forceinline__ void b_role_cell(bool active, int half, float* zc, co
         cnt += __shfl_xor_sync(0xffffffffu, cnt, 1);
         near = (__shfl_xor_sync(0xffffffffu, int(near), 1) != 0) || near;
         a = cnt;
-        if (near && has_x && active) a = sample_component_fp64(zc + OFF, mc + OFF, LEN, u);
-        a = __shfl_sync(0xffffffffu, a, (threadIdx.x & 31) & ~1);
+        if (sc.dead) {                         // uniform over all 49 entries: exact table decision
+            a = ucdf_pick(ucdf, LEN, u);
+            near = false;
+        }
+        unsigned flagged = __ballot_sync(0xffffffffu, near && has_x && active);
+        while (flagged) {
+            const int src = __ffs(flagged) - 1;
+            flagged &= flagged - 1;
+            const int delta = (src >> 1) - int((threadIdx.x & 31) >> 1);
+            const int r = warp_sample_fp64(zc + delta * kLogitsPerCell + OFF, mc + delta * kLogitsPerCell + OFF,
+                                           LEN, uni[delta * kCompsPerCell + 6]);
+            if (delta == 0) a = r;
+        }
         if (has_x && active) ac[6] = a;
     } else if (active) {
         const long long v = ac[6];
@@ -389,6 +449,7 @@ __global__ void __launch_bounds__(HeadCfg<TC, MODE>::kThreads) head_kernel(const
     float* part = reinterpret_cast<float*>(smem + size_t(NSTAGE) * Cfg::kStageBytes);   // [NSTAGE][kConsWarps][2]
     uint64_t* full = reinterpret_cast<uint64_t*>(part + NSTAGE * Cfg::kConsWarps * 2);
     uint64_t* done = full + NSTAGE;
+    double* ucdf = reinterpret_cast<double*>(done + NSTAGE);      // sample mode only
 
     const int warp = threadIdx.x >> 5;
     const int lane = threadIdx.x & 31;
@@ -399,6 +460,7 @@ __global__ void __launch_bounds__(HeadCfg<TC, MODE>::kThreads) head_kernel(const
             mbar_init(&done[s], Cfg::kConsWarps);
         }
         fence_mbar_init();
+        if (MODE == kSample) ucdf_fill(ucdf);
     }
     __syncthreads();
 
@@ -573,10 +635,11 @@ __global__ void __launch_bounds__(HeadCfg<TC, MODE>::kThreads) head_kernel(const
             int64_t* ac = reinterpret_cast<int64_t*>(st + Cfg::kOffAct) + cell_in_tile * kCompsPerCell;
             const float* uc = reinterpret_cast<const float*>(st + Cfg::kOffUni) + cell_in_tile * kCompsPerCell;
             float lp = 0.f, en = 0.f;
+            // lanes past the end of a ragged tile run on stale stage contents and discard the result
             if (role == 0) {
-                if (active) a_role_cell<MODE>(zc, mc, ac, uc, g_lp, g_h, p.status, lp, en);
+                a_role_cell<MODE>(zc, mc, ac, uc, g_lp, g_h, p.status, ucdf, active, lp, en);
             } else {
-                b_role_cell<MODE>(active, half, zc, mc, ac, uc, g_lp, g_h, p.status, lp, en);
+                b_role_cell<MODE>(active, half, zc, mc, ac, uc, g_lp, g_h, p.status, ucdf, lp, en);
             }
             if (MODE != kEvalBwd) {
                 lp = warp_sum(lp);
@@ -598,7 +661,7 @@ __global__ void __launch_bounds__(HeadCfg<TC, MODE>::kThreads) head_kernel(const
 // ---------------------------------------------------------------------------------------------
 static int g_head_ctas_per_sm = 0;      // 0 = as many as fit (occupancy query)
 static int g_head_grid_override = 0;
-static int g_head_variant = 0;          // tile / pipeline shape, see dispatch_head
+static int g_head_variant = -1;         // tile / pipeline shape, see dispatch_head; -1 = per-mode default
 void head_set_tuning(int ctas_per_sm, int grid_override, int variant) {
     g_head_ctas_per_sm = ctas_per_sm;
     g_head_grid_override = grid_override;
@@ -634,7 +697,9 @@ static int launch_head(HeadParams p, cudaStream_t stream) {
 // Tile / pipeline shapes selectable with mb_set_tuning("head_variant", v) for benchmarking.
 template <int MODE>
 static int dispatch_head(const HeadParams& p, cudaStream_t stream) {
-    switch (g_head_variant) {
+    int v = g_head_variant;
+    if (v < 0) v = (MODE == kEvalFwd) ? 1 : (MODE == kEvalBwd ? 0 : 3);   // measured best on B200 (profiles/)
+    switch (v) {
         case 1: return launch_head<64, MODE, 2>(p, stream);
         case 2: return launch_head<64, MODE, 4>(p, stream);
         case 3: return launch_head<32, MODE, 3>(p, stream);

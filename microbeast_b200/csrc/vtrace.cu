@@ -25,6 +25,8 @@
 #include <math.h>
 #include <string.h>
 
+#include <mutex>
+
 namespace mb {
 
 struct VtParams {
@@ -330,24 +332,70 @@ static EncodeTiledFn get_encode_fn() {
     return fn;
 }
 
-static bool make_map_2d(EncodeTiledFn enc, CUtensorMap* m, const void* base, bool is_u8, long long rows, int T,
-                        long long stride_elems) {
+static int g_vt_l2_promo = 256;      // bytes: 0 (none), 64, 128, 256
+
+static bool encode_map_2d(EncodeTiledFn enc, CUtensorMap* m, const void* base, bool is_u8, long long rows, int T,
+                          long long stride_elems) {
     const cuuint64_t gdim[2] = {cuuint64_t(T), cuuint64_t(rows)};
     const cuuint64_t gstride[1] = {cuuint64_t(stride_elems) * (is_u8 ? 1u : 4u)};
     const cuuint32_t box[2] = {cuuint32_t(kVtSteps), cuuint32_t(kVtRows)};
     const cuuint32_t estr[2] = {1, 1};
+    // 256-B L2 promotion: a row's next (earlier) time tile sits in the other half of the same
+    // 256-B block, so one DRAM page activation serves two consecutive tiles of the walk
+    const CUtensorMapL2promotion promo = g_vt_l2_promo >= 256  ? CU_TENSOR_MAP_L2_PROMOTION_L2_256B
+                                         : g_vt_l2_promo >= 128 ? CU_TENSOR_MAP_L2_PROMOTION_L2_128B
+                                         : g_vt_l2_promo >= 64  ? CU_TENSOR_MAP_L2_PROMOTION_L2_64B
+                                                                : CU_TENSOR_MAP_L2_PROMOTION_NONE;
     CUresult r = enc(m, is_u8 ? CU_TENSOR_MAP_DATA_TYPE_UINT8 : CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2,
                      const_cast<void*>(base), gdim, gstride, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
-                     is_u8 ? CU_TENSOR_MAP_SWIZZLE_NONE : CU_TENSOR_MAP_SWIZZLE_128B,
-                     CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+                     is_u8 ? CU_TENSOR_MAP_SWIZZLE_NONE : CU_TENSOR_MAP_SWIZZLE_128B, promo,
+                     CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     return r == CUDA_SUCCESS;
 }
 
+// Encoding a tensor map costs a driver call; the learner calls with the same buffers every step,
+// so descriptors are kept in a small direct-mapped cache keyed by (pointer, shape, stride).
+struct MapKey {
+    const void* base;
+    long long rows, stride;
+    int T, is_u8, promo;
+    bool operator==(const MapKey& o) const {
+        return base == o.base && rows == o.rows && stride == o.stride && T == o.T && is_u8 == o.is_u8 &&
+               promo == o.promo;
+    }
+};
+struct MapSlot {
+    MapKey key;
+    CUtensorMap map;
+    bool valid;
+};
+static MapSlot g_map_cache[256];
+static std::mutex g_map_mutex;
+
+static bool make_map_2d(EncodeTiledFn enc, CUtensorMap* m, const void* base, bool is_u8, long long rows, int T,
+                        long long stride_elems) {
+    const MapKey key{base, rows, stride_elems, T, is_u8 ? 1 : 0, g_vt_l2_promo};
+    size_t h = reinterpret_cast<uintptr_t>(base) >> 8;
+    h ^= size_t(rows) * 0x9E3779B97F4A7C15ull ^ size_t(T) * 0xC2B2AE3D27D4EB4Full ^ size_t(stride_elems) << 17;
+    MapSlot& slot = g_map_cache[(h ^ (h >> 29)) & 255];
+    std::lock_guard<std::mutex> lock(g_map_mutex);
+    if (slot.valid && slot.key == key) {
+        *m = slot.map;
+        return true;
+    }
+    if (!encode_map_2d(enc, m, base, is_u8, rows, T, stride_elems)) return false;
+    slot.key = key;
+    slot.map = *m;
+    slot.valid = true;
+    return true;
+}
+
 static int g_vt_force_generic = 0;
-static int g_vt_stages = 3;
-void vtrace_set_tuning(int force_generic, int stages) {
+static int g_vt_stages = 2;
+void vtrace_set_tuning(int force_generic, int stages, int l2_promo) {
     g_vt_force_generic = force_generic;
     if (stages == 2 || stages == 3 || stages == 4) g_vt_stages = stages;
+    g_vt_l2_promo = l2_promo;
 }
 
 size_t vtrace_workspace_bytes(long long rows) {
@@ -431,9 +479,9 @@ int vtrace_loss_launch(VtParams p, void* scratch, size_t scratch_bytes, cudaStre
             ok = make_map_2d(enc, &maps.dlp, p.dlp, false, p.rows, p.T, p.out_stride) &&
                  make_map_2d(enc, &maps.dv, p.dv, false, p.rows, p.T, p.out_stride);
         if (ok) {
-            if (g_vt_stages == 2) return launch_vt_tma<2>(maps, p, stream);
+            if (g_vt_stages == 3) return launch_vt_tma<3>(maps, p, stream);
             if (g_vt_stages == 4) return launch_vt_tma<4>(maps, p, stream);
-            return launch_vt_tma<3>(maps, p, stream);
+            return launch_vt_tma<2>(maps, p, stream);
         }
         // tensor-map encoding refused the shape: fall through to the generic kernel
     }

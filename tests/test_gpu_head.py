@@ -103,6 +103,30 @@ def test_autograd_function_matches_reference_autograd():
     _assert_close(zc.grad, z.grad, "autograd dlogits", support=mask != 0)
 
 
+@pytest.mark.parametrize("variant", [0, 1, 2, 3, 4, 5, 6])
+def test_tile_shapes_agree(variant):
+    """Every tile / pipeline shape of the head kernel gives the same bits (the per-frame reduction
+    order depends on the tile size, so log-prob / entropy may differ in the last ulp only)."""
+    import microbeast_b200
+    ops, synth, ohead = _mods()
+    logits, mask, action = _case(100, 23, "all_valid", seed=31)
+    g = torch.Generator().manual_seed(1)
+    u = synth.make_uniforms(23, 100, gen=g)
+    zc, mc, ac, uc = logits.cuda(), mask.cuda(), action.cuda(), u.cuda()
+    gl = torch.randn(23, generator=g).cuda()
+    base = (ops.head_eval_fwd(zc, mc, ac), ops.head_eval_bwd(zc, mc, ac, gl, gl), ops.head_sample(zc, mc, uc))
+    microbeast_b200.set_tuning("head_variant", variant)
+    try:
+        got = (ops.head_eval_fwd(zc, mc, ac), ops.head_eval_bwd(zc, mc, ac, gl, gl), ops.head_sample(zc, mc, uc))
+    finally:
+        microbeast_b200.set_tuning("head_variant", -1)
+    assert torch.allclose(got[0][0], base[0][0], rtol=2e-6, atol=1e-4)
+    assert torch.allclose(got[0][1], base[0][1], rtol=2e-6, atol=1e-4)
+    assert torch.equal(got[1], base[1])
+    assert torch.equal(got[2][0], base[2][0])
+    assert torch.equal(got[2][0].cpu(), ohead.sample_invcdf(logits, mask, u))
+
+
 def test_bad_action_sets_status_like_validate_args():
     ops, _, _ = _mods()
     logits, mask, action = _case(64, 4, "all_valid", seed=8)

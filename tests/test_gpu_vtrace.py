@@ -91,7 +91,14 @@ def test_pipeline_depths_agree(stages):
     try:
         out = _run(ops, t)
     finally:
-        mb.set_tuning("vtrace_stages", 3)
+        mb.set_tuning("vtrace_stages", 2)
+    for k in ("vs", "pg_advantages", "d_logp", "d_values", "loss4"):
+        assert torch.equal(base[k], out[k]), k
+    mb.set_tuning("vtrace_l2_promo", 128)
+    try:
+        out = _run(ops, t)
+    finally:
+        mb.set_tuning("vtrace_l2_promo", 256)
     for k in ("vs", "pg_advantages", "d_logp", "d_values", "loss4"):
         assert torch.equal(base[k], out[k]), k
 
