@@ -218,7 +218,6 @@ def run_ours(args):
     model = Agent((h, w, 27), nvec, cells).to(dev)
     with torch.no_grad():
         model.actor.weight.normal_(0, 0.01)
-    model = model.to(memory_format=torch.channels_last)
     opt = torch.optim.Adam(model.parameters(), lr=2.5e-4, eps=1e-5, fused=True)
     reducer = GradAllReducer() if world > 1 else None
 
@@ -396,21 +395,20 @@ def run_sweep(args):
                                      "median_us": med * 1e3, "gbs": gbs, "frac_of_peak": gbs / peak})
         microbeast_b200.set_tuning("head_variant", -1)
         microbeast_b200.set_tuning("head_ctas_per_sm", 0)
-        for st, promo in ((2, 256), (2, 128), (3, 256), (3, 128)):
-            microbeast_b200.set_tuning("vtrace_stages", st)
-            microbeast_b200.set_tuning("vtrace_l2_promo", promo)
-            for T, R in ((512, 65536), (256, 65536), (80, 65536)):
+        vnames = {0: "2x1", 1: "3x1", 2: "4x1", 3: "2x2", 4: "3x2", 5: "2x4"}
+        for variant, vname in vnames.items():
+            microbeast_b200.set_tuning("vtrace_variant", variant)
+            for T, R in ((512, 65536), (256, 65536), (80, 65536), (512, 4096), (80, 256)):
                 t = synth.make_vtrace_inputs(R, T, gen=g, device=dev)
                 fn = lambda: ops.vtrace_loss(t["lp_old"], t["lp_new"], t["values"], t["bootstrap"], t["rewards"],
                                              t["done"], t["entropy"])
                 med, p10, p90 = bench(fn, 10)
                 nbytes = 37 * R * T + 4 * R
                 gbs = nbytes / (med * 1e-3) / 1e9
-                rows_out.append({"kernel": "vtrace_loss", "variant": f"stages{st}/promo{promo}", "T": T, "rows": R,
+                rows_out.append({"kernel": "vtrace_loss", "variant": vname, "T": T, "rows": R,
                                  "median_us": med * 1e3, "gbs": gbs, "frac_of_peak": gbs / peak})
                 del t
-        microbeast_b200.set_tuning("vtrace_stages", 2)
-        microbeast_b200.set_tuning("vtrace_l2_promo", 256)
+        microbeast_b200.set_tuning("vtrace_variant", -1)
     else:
         for name, (h, w, T, rows) in WORKLOADS.items():
             cells, n = h * w, rows * (T + 1)

@@ -39,7 +39,7 @@ int head_eval_bwd(const float*, const uint8_t*, const int64_t*, const float*, co
 int head_sample(const float*, const uint8_t*, const float*, int64_t*, float*, float*, long long, int, int*,
                 cudaStream_t);
 void head_set_tuning(int ctas_per_sm, int grid_override, int variant);
-void vtrace_set_tuning(int force_generic, int stages, int l2_promo);
+void vtrace_set_tuning(int force_generic, int variant, int l2_promo);
 size_t vtrace_workspace_bytes(long long rows);
 
 struct VtParams;
@@ -77,7 +77,7 @@ int mb_head_sample(const float* logits, const uint8_t* mask, const float* unifor
 size_t mb_vtrace_workspace_bytes(int64_t rows) { return mb::vtrace_workspace_bytes(rows); }
 
 int mb_set_tuning(const char* key, int32_t value) {
-    static int head_ctas = 0, head_grid = 0, head_variant = -1, vt_generic = 0, vt_stages = 2, vt_promo = 256;
+    static int head_ctas = 0, head_grid = 0, head_variant = -1, vt_generic = 0, vt_variant = -1, vt_promo = 256;
     if (!key) {
         mb::set_error("mb_set_tuning: null key");
         return MB_ERR_INVALID;
@@ -86,14 +86,14 @@ int mb_set_tuning(const char* key, int32_t value) {
     else if (!strcmp(key, "head_grid")) head_grid = value;
     else if (!strcmp(key, "head_variant")) head_variant = value;
     else if (!strcmp(key, "vtrace_force_generic")) vt_generic = value;
-    else if (!strcmp(key, "vtrace_stages")) vt_stages = value;
+    else if (!strcmp(key, "vtrace_variant")) vt_variant = value;
     else if (!strcmp(key, "vtrace_l2_promo")) vt_promo = value;
     else {
         mb::set_error("mb_set_tuning: unknown key '%s'", key);
         return MB_ERR_INVALID;
     }
     mb::head_set_tuning(head_ctas, head_grid, head_variant);
-    mb::vtrace_set_tuning(vt_generic, vt_stages, vt_promo);
+    mb::vtrace_set_tuning(vt_generic, vt_variant, vt_promo);
     return MB_OK;
 }
 

@@ -52,7 +52,7 @@ struct VtParams {
 };
 
 struct VtMaps {
-    CUtensorMap lp_old, lp_new, values, rewards, entropy, done, vs, adv, dlp, dv;
+    CUtensorMap lp_old, lp_new, values, rewards, done, vs, adv, dlp, dv;
 };
 
 struct VtCarry {
@@ -109,16 +109,22 @@ __device__ __forceinline__ void vt_finalize(const VtParams& p, int lane) {
 }
 
 // ---------------------------------------------------------------------------------------------
-// TMA kernel: one warp per CTA, 32 rows, time tiles of 32 steps walked from the end.
+// TMA kernel: one warp per CTA, 32 rows, time tiles of 32*BPT steps walked from the end.
+// A tile is BPT boxes of [32 rows x 32 steps] per array, issued back to back so that a row's
+// consecutive 128-B pieces reach the memory controller together (DRAM page locality).
+// Entropy only feeds a mean, so it is not staged: the warp streams its rows' entropy with plain
+// coalesced float4 loads spread over the iterations of the tile loop.
 // ---------------------------------------------------------------------------------------------
 constexpr int kVtRows = 32;
 constexpr int kVtSteps = 32;
 constexpr int kVtTileF32 = kVtRows * kVtSteps * 4;     // 4096 B, 128-B rows, SWIZZLE_128B
 constexpr int kVtTileU8 = kVtRows * kVtSteps;          // 1024 B, 32-B rows, no swizzle
-constexpr int kVtStageBytes = 5 * kVtTileF32 + kVtTileU8;   // 21504 B (multiple of 1024)
+constexpr int kVtBoxBytes = 4 * kVtTileF32 + kVtTileU8;     // lp_old, lp_new, values, rewards, done = 17408 B
 
-template <int NSTAGE>
+template <int NSTAGE, int BPT>
 __global__ void __launch_bounds__(32) vtrace_tma_kernel(const __grid_constant__ VtMaps maps, const VtParams p) {
+    constexpr int kStageBytes = BPT * kVtBoxBytes;         // multiple of 1024
+    constexpr int kTileSteps = BPT * kVtSteps;
     extern __shared__ uint8_t smem_raw[];
     __shared__ __align__(8) uint64_t full[NSTAGE];
     // SWIZZLE_128B needs 1024-B aligned tiles
@@ -137,24 +143,30 @@ __global__ void __launch_bounds__(32) vtrace_tma_kernel(const __grid_constant__ 
         tma_prefetch_desc(&maps.lp_new);
         tma_prefetch_desc(&maps.values);
         tma_prefetch_desc(&maps.rewards);
-        tma_prefetch_desc(&maps.entropy);
         tma_prefetch_desc(&maps.done);
     }
     __syncwarp();
 
-    const int nt = (p.T + kVtSteps - 1) / kVtSteps;
+    const int nt = (p.T + kTileSteps - 1) / kTileSteps;
+
+    // stage layout: [array a][box b] f32 tiles, then BPT done tiles
+    auto f32_tile = [&](uint8_t* st, int a, int b) -> uint8_t* { return st + (a * BPT + b) * kVtTileF32; };
+    auto u8_tile = [&](uint8_t* st, int b) -> uint8_t* { return st + 4 * BPT * kVtTileF32 + b * kVtTileU8; };
 
     auto issue_load = [&](int k) {        // lane 0 only; k counts tiles from the END of the rows
         const int s = k % NSTAGE;
-        const int t0 = (nt - 1 - k) * kVtSteps;
-        uint8_t* st = smem + size_t(s) * kVtStageBytes;
-        mbar_arrive_expect_tx(&full[s], uint32_t(kVtStageBytes));
-        tma_load_2d(st + 0 * kVtTileF32, &maps.lp_old, t0, row0, &full[s]);
-        tma_load_2d(st + 1 * kVtTileF32, &maps.lp_new, t0, row0, &full[s]);
-        tma_load_2d(st + 2 * kVtTileF32, &maps.values, t0, row0, &full[s]);
-        tma_load_2d(st + 3 * kVtTileF32, &maps.rewards, t0, row0, &full[s]);
-        tma_load_2d(st + 4 * kVtTileF32, &maps.entropy, t0, row0, &full[s]);
-        tma_load_2d(st + 5 * kVtTileF32, &maps.done, t0, row0, &full[s]);
+        const int t0 = (nt - 1 - k) * kTileSteps;
+        uint8_t* st = smem + size_t(s) * kStageBytes;
+        mbar_arrive_expect_tx(&full[s], uint32_t(kStageBytes));
+#pragma unroll
+        for (int b = 0; b < BPT; ++b) {
+            const int tb = t0 + b * kVtSteps;
+            tma_load_2d(f32_tile(st, 0, b), &maps.lp_old, tb, row0, &full[s]);
+            tma_load_2d(f32_tile(st, 1, b), &maps.lp_new, tb, row0, &full[s]);
+            tma_load_2d(f32_tile(st, 2, b), &maps.values, tb, row0, &full[s]);
+            tma_load_2d(f32_tile(st, 3, b), &maps.rewards, tb, row0, &full[s]);
+            tma_load_2d(u8_tile(st, b), &maps.done, tb, row0, &full[s]);
+        }
     };
 
     if (lane == 0) {
@@ -165,68 +177,102 @@ __global__ void __launch_bounds__(32) vtrace_tma_kernel(const __grid_constant__ 
     carry.acc = 0.0f;
     carry.v_next = row_ok ? __ldg(p.bootstrap + row) : 0.0f;
     carry.vs_next = carry.v_next;
-    double s_pg = 0.0, s_v = 0.0, s_en = 0.0;
+    double s_pg = 0.0, s_v = 0.0;
+    float s_en = 0.0f;
+
+    // entropy: the CTA's rows are streamed row by row, rows_per_iter rows per tile iteration
+    const int rows_here = int(min((long long)kVtRows, p.rows - row0));
+    const int rows_per_iter = (kVtRows + nt - 1) / nt;
+    const bool ent_vec = ((reinterpret_cast<uintptr_t>(p.entropy) | (uintptr_t(p.in_stride) * 4)) & 15) == 0;
 
     for (int k = 0; k < nt; ++k) {
         const int s = k % NSTAGE;
-        mbar_wait(&full[s], uint32_t((k / NSTAGE) & 1), nullptr);
-
-        uint8_t* st = smem + size_t(s) * kVtStageBytes;
-        const int t0 = (nt - 1 - k) * kVtSteps;
-        float t_pg = 0.0f, t_v = 0.0f, t_en = 0.0f;
-#pragma unroll
-        for (int j = kVtSteps / 4 - 1; j >= 0; --j) {
-            const uint32_t off = uint32_t(lane) * 128u + (uint32_t(j ^ (lane & 7)) << 4);
-            float4 a_old = *reinterpret_cast<const float4*>(st + 0 * kVtTileF32 + off);
-            float4 a_new = *reinterpret_cast<const float4*>(st + 1 * kVtTileF32 + off);
-            float4 a_val = *reinterpret_cast<const float4*>(st + 2 * kVtTileF32 + off);
-            float4 a_rew = *reinterpret_cast<const float4*>(st + 3 * kVtTileF32 + off);
-            float4 a_ent = *reinterpret_cast<const float4*>(st + 4 * kVtTileF32 + off);
-            const uint32_t dn = *reinterpret_cast<const uint32_t*>(st + 5 * kVtTileF32 + lane * 32 + j * 4);
-            float lo[4] = {a_old.x, a_old.y, a_old.z, a_old.w};
-            float ln[4] = {a_new.x, a_new.y, a_new.z, a_new.w};
-            float vv[4] = {a_val.x, a_val.y, a_val.z, a_val.w};
-            float rw[4] = {a_rew.x, a_rew.y, a_rew.z, a_rew.w};
-            float en[4] = {a_ent.x, a_ent.y, a_ent.z, a_ent.w};
-            float o_vs[4], o_adv[4], o_dlp[4], o_dv[4];
-#pragma unroll
-            for (int i = 3; i >= 0; --i) {
-                const int t = t0 + 4 * j + i;
-                o_vs[i] = 0.f; o_adv[i] = 0.f; o_dlp[i] = 0.f; o_dv[i] = 0.f;
-                if (t < p.T && row_ok) {
-                    const bool dflag = ((dn >> (8 * i)) & 0xffu) != 0;
-                    const VtStepOut o = vt_step(p, lo[i], ln[i], vv[i], rw[i], dflag, carry);
-                    o_vs[i] = o.vs;
-                    o_adv[i] = o.adv;
-                    const float dvs = __fsub_rn(o.vs, vv[i]);
-                    o_dlp[i] = o.adv * p.inv_n;
-                    o_dv[i] = -dvs * p.inv_n;
-                    t_pg = __fadd_rn(t_pg, __fmul_rn(ln[i], o.adv));
-                    t_v = __fadd_rn(t_v, __fmul_rn(dvs, dvs));
-                    t_en = __fadd_rn(t_en, en[i]);
+        // issue this iteration's share of the entropy stream before blocking on the tile
+        float ent_acc = 0.0f;
+        {
+            const int r_lo = k * rows_per_iter, r_hi = min(rows_here, r_lo + rows_per_iter);
+            for (int r = r_lo; r < r_hi; ++r) {
+                const float* src = p.entropy + (long long)(row0 + r) * p.in_stride;
+                if (ent_vec) {
+                    for (int t = lane * 4; t + 3 < p.T; t += 128) {
+                        const float4 v = __ldg(reinterpret_cast<const float4*>(src + t));
+                        ent_acc += (v.x + v.y) + (v.z + v.w);
+                    }
+                    for (int t = (p.T & ~3) + lane; t < p.T; t += 32) ent_acc += __ldg(src + t);
+                } else {
+                    for (int t = lane; t < p.T; t += 32) ent_acc += __ldg(src + t);
                 }
             }
-            // in place: vs over rewards, adv over lp_old, d_logp over lp_new, d_values over entropy
-            *reinterpret_cast<float4*>(st + 3 * kVtTileF32 + off) = make_float4(o_vs[0], o_vs[1], o_vs[2], o_vs[3]);
-            *reinterpret_cast<float4*>(st + 0 * kVtTileF32 + off) = make_float4(o_adv[0], o_adv[1], o_adv[2], o_adv[3]);
-            if (want_grads) {
-                *reinterpret_cast<float4*>(st + 1 * kVtTileF32 + off) =
-                    make_float4(o_dlp[0], o_dlp[1], o_dlp[2], o_dlp[3]);
-                *reinterpret_cast<float4*>(st + 4 * kVtTileF32 + off) = make_float4(o_dv[0], o_dv[1], o_dv[2], o_dv[3]);
-            }
         }
-        s_pg += double(t_pg);
-        s_v += double(t_v);
-        s_en += double(t_en);
+        mbar_wait(&full[s], uint32_t((k / NSTAGE) & 1), nullptr);
+
+        uint8_t* st = smem + size_t(s) * kStageBytes;
+        const int t0 = (nt - 1 - k) * kTileSteps;
+        float t_pg = 0.0f, t_v = 0.0f;
+#pragma unroll
+        for (int b = BPT - 1; b >= 0; --b) {
+            uint8_t* q_old = f32_tile(st, 0, b);
+            uint8_t* q_new = f32_tile(st, 1, b);
+            uint8_t* q_val = f32_tile(st, 2, b);
+            uint8_t* q_rew = f32_tile(st, 3, b);
+            const uint8_t* q_dn = u8_tile(st, b);
+#pragma unroll
+            for (int j = kVtSteps / 4 - 1; j >= 0; --j) {
+                const uint32_t off = uint32_t(lane) * 128u + (uint32_t(j ^ (lane & 7)) << 4);
+                const float4 a_old = *reinterpret_cast<const float4*>(q_old + off);
+                const float4 a_new = *reinterpret_cast<const float4*>(q_new + off);
+                const float4 a_val = *reinterpret_cast<const float4*>(q_val + off);
+                const float4 a_rew = *reinterpret_cast<const float4*>(q_rew + off);
+                const uint32_t dn = *reinterpret_cast<const uint32_t*>(q_dn + lane * 32 + j * 4);
+                const float lo[4] = {a_old.x, a_old.y, a_old.z, a_old.w};
+                const float ln[4] = {a_new.x, a_new.y, a_new.z, a_new.w};
+                const float vv[4] = {a_val.x, a_val.y, a_val.z, a_val.w};
+                const float rw[4] = {a_rew.x, a_rew.y, a_rew.z, a_rew.w};
+                float o_vs[4], o_adv[4], o_dlp[4], o_dv[4];
+#pragma unroll
+                for (int i = 3; i >= 0; --i) {
+                    const int t = t0 + b * kVtSteps + 4 * j + i;
+                    o_vs[i] = 0.f; o_adv[i] = 0.f; o_dlp[i] = 0.f; o_dv[i] = 0.f;
+                    if (t < p.T && row_ok) {
+                        const bool dflag = ((dn >> (8 * i)) & 0xffu) != 0;
+                        const VtStepOut o = vt_step(p, lo[i], ln[i], vv[i], rw[i], dflag, carry);
+                        o_vs[i] = o.vs;
+                        o_adv[i] = o.adv;
+                        const float dvs = __fsub_rn(o.vs, vv[i]);
+                        o_dlp[i] = o.adv * p.inv_n;
+                        o_dv[i] = -dvs * p.inv_n;
+                        t_pg = __fadd_rn(t_pg, __fmul_rn(ln[i], o.adv));
+                        t_v = __fadd_rn(t_v, __fmul_rn(dvs, dvs));
+                    }
+                }
+                // in place: vs over rewards, adv over lp_old, d_logp over lp_new, d_values over values
+                *reinterpret_cast<float4*>(q_rew + off) = make_float4(o_vs[0], o_vs[1], o_vs[2], o_vs[3]);
+                *reinterpret_cast<float4*>(q_old + off) = make_float4(o_adv[0], o_adv[1], o_adv[2], o_adv[3]);
+                if (want_grads) {
+                    *reinterpret_cast<float4*>(q_new + off) = make_float4(o_dlp[0], o_dlp[1], o_dlp[2], o_dlp[3]);
+                    *reinterpret_cast<float4*>(q_val + off) = make_float4(o_dv[0], o_dv[1], o_dv[2], o_dv[3]);
+                }
+            }
+            // the pg / value sums are folded into fp64 once per 32 steps (same grouping as the generic kernel)
+            s_pg += double(t_pg);
+            s_v += double(t_v);
+            t_pg = 0.0f;
+            t_v = 0.0f;
+        }
+        s_en += ent_acc;
 
         fence_proxy_async_smem();
         __syncwarp();
         if (lane == 0) {
-            tma_store_2d(&maps.vs, t0, row0, st + 3 * kVtTileF32);
-            tma_store_2d(&maps.adv, t0, row0, st + 0 * kVtTileF32);
-            if (want_grads) {
-                tma_store_2d(&maps.dlp, t0, row0, st + 1 * kVtTileF32);
-                tma_store_2d(&maps.dv, t0, row0, st + 4 * kVtTileF32);
+#pragma unroll
+            for (int b = 0; b < BPT; ++b) {
+                const int tb = t0 + b * kVtSteps;
+                tma_store_2d(&maps.vs, tb, row0, f32_tile(st, 3, b));
+                tma_store_2d(&maps.adv, tb, row0, f32_tile(st, 0, b));
+                if (want_grads) {
+                    tma_store_2d(&maps.dlp, tb, row0, f32_tile(st, 1, b));
+                    tma_store_2d(&maps.dv, tb, row0, f32_tile(st, 2, b));
+                }
             }
             bulk_commit();
             if (k + NSTAGE - 1 < nt) {
@@ -240,13 +286,13 @@ __global__ void __launch_bounds__(32) vtrace_tma_kernel(const __grid_constant__ 
 
     s_pg = warp_sum(s_pg);
     s_v = warp_sum(s_v);
-    s_en = warp_sum(s_en);
+    const double s_en_w = warp_sum(double(s_en));
     unsigned int tk = 0;
     if (lane == 0) {
         bulk_wait_all<0>();     // output tiles are in global memory before the CTA retires
         p.partials[size_t(blockIdx.x) * 3 + 0] = s_pg;
         p.partials[size_t(blockIdx.x) * 3 + 1] = s_v;
-        p.partials[size_t(blockIdx.x) * 3 + 2] = s_en;
+        p.partials[size_t(blockIdx.x) * 3 + 2] = s_en_w;
         __threadfence();
         tk = atomicAdd(p.ticket, 1u);
     }
@@ -391,10 +437,10 @@ static bool make_map_2d(EncodeTiledFn enc, CUtensorMap* m, const void* base, boo
 }
 
 static int g_vt_force_generic = 0;
-static int g_vt_stages = 2;
-void vtrace_set_tuning(int force_generic, int stages, int l2_promo) {
+static int g_vt_variant = -1;        // -1 = by grid size; see the switch in vtrace_loss_launch
+void vtrace_set_tuning(int force_generic, int variant, int l2_promo) {
     g_vt_force_generic = force_generic;
-    if (stages == 2 || stages == 3 || stages == 4) g_vt_stages = stages;
+    g_vt_variant = variant;
     g_vt_l2_promo = l2_promo;
 }
 
@@ -406,19 +452,19 @@ size_t vtrace_workspace_bytes(long long rows) {
 
 static inline bool al16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; }
 
-template <int NSTAGE>
+template <int NSTAGE, int BPT>
 static int launch_vt_tma(const VtMaps& maps, const VtParams& p, cudaStream_t stream) {
-    constexpr size_t smem = size_t(NSTAGE) * kVtStageBytes + 1024;
+    constexpr size_t smem = size_t(NSTAGE) * BPT * kVtBoxBytes + 1024;
     static bool attr_set[64] = {};
     int dev = 0;
     MB_CUDA(cudaGetDevice(&dev));
     if (dev < 64 && !attr_set[dev]) {
-        MB_CUDA(cudaFuncSetAttribute(vtrace_tma_kernel<NSTAGE>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+        MB_CUDA(cudaFuncSetAttribute(vtrace_tma_kernel<NSTAGE, BPT>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                      int(smem)));
         attr_set[dev] = true;
     }
     const unsigned grid = unsigned((p.rows + kVtRows - 1) / kVtRows);
-    vtrace_tma_kernel<NSTAGE><<<grid, 32, smem, stream>>>(maps, p);
+    vtrace_tma_kernel<NSTAGE, BPT><<<grid, 32, smem, stream>>>(maps, p);
     MB_CUDA(cudaGetLastError());
     return MB_OK;
 }
@@ -471,7 +517,6 @@ int vtrace_loss_launch(VtParams p, void* scratch, size_t scratch_bytes, cudaStre
                   make_map_2d(enc, &maps.lp_new, p.lp_new, false, p.rows, p.T, p.in_stride) &&
                   make_map_2d(enc, &maps.values, p.values, false, p.rows, p.T, p.in_stride) &&
                   make_map_2d(enc, &maps.rewards, p.rewards, false, p.rows, p.T, p.in_stride) &&
-                  make_map_2d(enc, &maps.entropy, p.entropy, false, p.rows, p.T, p.in_stride) &&
                   make_map_2d(enc, &maps.done, p.done, true, p.rows, p.T, p.in_stride) &&
                   make_map_2d(enc, &maps.vs, p.vs, false, p.rows, p.T, p.out_stride) &&
                   make_map_2d(enc, &maps.adv, p.adv, false, p.rows, p.T, p.out_stride);
@@ -479,9 +524,18 @@ int vtrace_loss_launch(VtParams p, void* scratch, size_t scratch_bytes, cudaStre
             ok = make_map_2d(enc, &maps.dlp, p.dlp, false, p.rows, p.T, p.out_stride) &&
                  make_map_2d(enc, &maps.dv, p.dv, false, p.rows, p.T, p.out_stride);
         if (ok) {
-            if (g_vt_stages == 3) return launch_vt_tma<3>(maps, p, stream);
-            if (g_vt_stages == 4) return launch_vt_tma<4>(maps, p, stream);
-            return launch_vt_tma<2>(maps, p, stream);
+            // pipeline shape: stages x boxes-per-tile.  Few CTAs (latency bound) -> deep prefetch;
+            // many CTAs (bandwidth bound) -> more resident CTAs per SM.
+            int v = g_vt_variant;
+            if (v < 0) v = (p.rows + kVtRows - 1) / kVtRows >= 4 * sm_count(0) ? 0 : 2;
+            switch (v) {
+                case 1: return launch_vt_tma<3, 1>(maps, p, stream);
+                case 2: return launch_vt_tma<4, 1>(maps, p, stream);
+                case 3: return launch_vt_tma<2, 2>(maps, p, stream);
+                case 4: return launch_vt_tma<3, 2>(maps, p, stream);
+                case 5: return launch_vt_tma<2, 4>(maps, p, stream);
+                default: return launch_vt_tma<2, 1>(maps, p, stream);
+            }
         }
         // tensor-map encoding refused the shape: fall through to the generic kernel
     }

@@ -136,6 +136,7 @@ class Agent(nn.Module):
         self.mapsize = mapsize
         self.nvec = nvec
         self.cells = len(nvec) // COMPONENTS_PER_CELL
+        self.nchw_copy = True
         shape = (c, h, w)
         layers = []
         for out_channels in (16, 32, 32):
@@ -154,7 +155,10 @@ class Agent(nn.Module):
         obs = input_dict["obs"] if learning else input_dict["obs"][0, 0, ...]     # model.py:156-160
         if obs.dtype != torch.float32:
             obs = obs.float()            # uint8 wire format of the B200 rollout store
-        return obs.permute((0, 3, 1, 2))  # NHWC storage == channels-last view
+        x = obs.permute((0, 3, 1, 2))
+        # fp32 cuDNN convolutions run ~12 % faster from a dense NCHW copy than from the
+        # channels-last view on B200 (profiles/r01_encoder_formats.txt); values are identical
+        return x.contiguous() if (x.is_cuda and self.nchw_copy) else x
 
     def forward(self, input_dict: dict, agent_state=(), learning=False, inds=()):
         return self.network(self._obs(input_dict, learning))

@@ -5,10 +5,8 @@ for f in tests/test_gpu_vtrace.py tests/test_gpu_head.py tests/test_gpu_learner.
   echo "$f exit $?" >> gpurun_out/summary.txt
 done
 timeout 600 python -c "import __graft_entry__ as g; g.smoke()" > gpurun_out/smoke.log 2>&1; echo "smoke exit $?" >> gpurun_out/summary.txt
-timeout 600 python scripts/encoder_experiment.py > gpurun_out/encoder_experiment.log 2>&1; echo "encoder exit $?" >> gpurun_out/summary.txt
 timeout 900 python bench.py --sweep variants --out gpurun_out/sweep_variants.jsonl > gpurun_out/sweep_variants.log 2>&1; echo "variants exit $?" >> gpurun_out/summary.txt
-timeout 900 python bench.py --sweep head --out gpurun_out/sweep_head.jsonl > gpurun_out/sweep_head.log 2>&1; echo "sweep head exit $?" >> gpurun_out/summary.txt
+timeout 900 python bench.py --steps 10 --warmup 3 --out gpurun_out/bench.jsonl > gpurun_out/bench.log 2>&1; echo "bench exit $?" >> gpurun_out/summary.txt
 timeout 900 python bench.py --sweep vtrace --out gpurun_out/sweep_vtrace.jsonl > gpurun_out/sweep_vtrace.log 2>&1; echo "sweep vtrace exit $?" >> gpurun_out/summary.txt
 cat gpurun_out/summary.txt
 for f in gpurun_out/test_gpu_vtrace.log gpurun_out/test_gpu_head.log gpurun_out/test_gpu_learner.log gpurun_out/smoke.log; do tail -n 3 $f; done
-cat gpurun_out/encoder_experiment.log

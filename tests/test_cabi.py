@@ -51,7 +51,7 @@ def test_argument_validation_needs_no_gpu():
     assert lib.mb_vtrace_workspace_bytes(65536) >= 256 + 2048 * 24
     with pytest.raises(ValueError):
         _lib.set_tuning("no_such_knob", 1)
-    _lib.set_tuning("vtrace_stages", 3)
+    _lib.set_tuning("vtrace_variant", -1)
 
 
 def test_ops_refuse_cpu_tensors():
