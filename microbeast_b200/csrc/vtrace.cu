@@ -180,29 +180,34 @@ __global__ void __launch_bounds__(32) vtrace_tma_kernel(const __grid_constant__ 
     double s_pg = 0.0, s_v = 0.0;
     float s_en = 0.0f;
 
-    // entropy: the CTA's rows are streamed row by row, rows_per_iter rows per tile iteration
+    // entropy: the CTA's [rows_here x T] block is a list of float4 slots (nq per row); lane l owns
+    // slots l, l+32, ... and fetches its next kEntSlots of them at the top of every iteration, so
+    // the loads fly while the warp waits for / works on the TMA tile and are summed afterwards
+    constexpr int kEntSlots = 8 * BPT;                     // 32*32*BPT floats per iteration per array
     const int rows_here = int(min((long long)kVtRows, p.rows - row0));
-    const int rows_per_iter = (kVtRows + nt - 1) / nt;
-    const bool ent_vec = ((reinterpret_cast<uintptr_t>(p.entropy) | (uintptr_t(p.in_stride) * 4)) & 15) == 0;
+    const int nq = (p.T + 3) >> 2;
+    const int tail = p.T - 4 * (nq - 1);                   // valid floats in a row's last slot (1..4)
+    int ent_r = 0, ent_c = lane;                           // (row, slot) of this lane's next slot
+    while (ent_c >= nq) { ent_c -= nq; ++ent_r; }
 
     for (int k = 0; k < nt; ++k) {
         const int s = k % NSTAGE;
-        // issue this iteration's share of the entropy stream before blocking on the tile
-        float ent_acc = 0.0f;
-        {
-            const int r_lo = k * rows_per_iter, r_hi = min(rows_here, r_lo + rows_per_iter);
-            for (int r = r_lo; r < r_hi; ++r) {
-                const float* src = p.entropy + (long long)(row0 + r) * p.in_stride;
-                if (ent_vec) {
-                    for (int t = lane * 4; t + 3 < p.T; t += 128) {
-                        const float4 v = __ldg(reinterpret_cast<const float4*>(src + t));
-                        ent_acc += (v.x + v.y) + (v.z + v.w);
-                    }
-                    for (int t = (p.T & ~3) + lane; t < p.T; t += 32) ent_acc += __ldg(src + t);
+        float4 ebuf[kEntSlots];
+#pragma unroll
+        for (int i = 0; i < kEntSlots; ++i) {
+            ebuf[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (ent_r < rows_here) {
+                const float* src = p.entropy + (long long)(row0 + ent_r) * p.in_stride + 4 * ent_c;
+                float4 v;
+                if (ent_c == nq - 1 && tail < 4) {         // never read past T in a row's last slot
+                    v = make_float4(__ldg(src), tail > 1 ? __ldg(src + 1) : 0.f, tail > 2 ? __ldg(src + 2) : 0.f, 0.f);
                 } else {
-                    for (int t = lane; t < p.T; t += 32) ent_acc += __ldg(src + t);
+                    v = __ldg(reinterpret_cast<const float4*>(src));
                 }
+                ebuf[i] = v;
             }
+            ent_c += 32;
+            while (ent_c >= nq) { ent_c -= nq; ++ent_r; }
         }
         mbar_wait(&full[s], uint32_t((k / NSTAGE) & 1), nullptr);
 
@@ -259,7 +264,8 @@ __global__ void __launch_bounds__(32) vtrace_tma_kernel(const __grid_constant__ 
             t_pg = 0.0f;
             t_v = 0.0f;
         }
-        s_en += ent_acc;
+#pragma unroll
+        for (int i = 0; i < kEntSlots; ++i) s_en += (ebuf[i].x + ebuf[i].y) + (ebuf[i].z + ebuf[i].w);
 
         fence_proxy_async_smem();
         __syncwarp();
