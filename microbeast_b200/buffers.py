@@ -27,6 +27,7 @@ from __future__ import annotations
 
 import queue
 import threading
+import weakref
 from typing import Dict, List, Optional
 
 import torch
@@ -88,6 +89,8 @@ class RolloutBuffers(dict):
         self._turn = {}
         self._pending = []           # (event, indices, free_queue) waiting for their DMA
         self._stream = {}
+        self._registered = []
+        self._finalizer = None
 
     def live_keys(self):
         return [k for k, v in self.items() if isinstance(v[0], torch.Tensor)]
@@ -98,11 +101,34 @@ class RolloutBuffers(dict):
             return self.pinned
         rt = torch.cuda.cudart()
         for slab in self.slabs.values():
-            err = rt.cudaHostRegister(slab.data_ptr(), slab.numel() * slab.element_size(), 0)
-            if int(err) != 0:
-                raise RuntimeError(f"cudaHostRegister failed with error {int(err)}")
+            err = int(rt.cudaHostRegister(slab.data_ptr(), slab.numel() * slab.element_size(), 0))
+            if err == 712:          # cudaErrorHostMemoryAlreadyRegistered: a stale registration of a freed
+                rt.cudaHostUnregister(slab.data_ptr())       # mapping at the same address; replace it
+                err = int(rt.cudaHostRegister(slab.data_ptr(), slab.numel() * slab.element_size(), 0))
+            if err != 0:
+                raise RuntimeError(f"cudaHostRegister failed with error {err}")
+            self._registered.append(slab.data_ptr())
         self.pinned = True
+        self._finalizer = weakref.finalize(self, _unregister, list(self._registered))
         return True
+
+    def unpin(self) -> None:
+        """Undo :meth:`pin` (also runs when the buffers are garbage collected)."""
+        if self.pinned:
+            self._finalizer.detach()
+            _unregister(self._registered)
+            self._registered = []
+            self.pinned = False
+
+
+def _unregister(ptrs) -> None:
+    try:
+        rt = torch.cuda.cudart()
+        torch.cuda.synchronize()
+        for ptr in ptrs:
+            rt.cudaHostUnregister(ptr)
+    except Exception:
+        pass
 
 
 def create_buffers(n_buffers: int, n_envs: int, B: int, T: int, obs_size: tuple, *, lean: bool = True,
@@ -221,3 +247,4 @@ def release(buffers: Buffers) -> None:
     """Wait for outstanding DMA and hand every buffer index back (call before shutdown)."""
     if isinstance(buffers, RolloutBuffers):
         _recycle(buffers, block=True)
+        buffers.unpin()

@@ -67,22 +67,28 @@ struct VtStepOut {
 
 // One time step of utils.py:277-318 for one row.  Every product and sum is rounded separately
 // (__fmul_rn / __fadd_rn: no FMA contraction), in the reference's left-to-right order, so the
-// only arithmetic difference to the CPU torch path is the last ulp of expf.
-__device__ __forceinline__ VtStepOut vt_step(const VtParams& p, float lp_old, float lp_new, float v, float rew,
-                                             bool done, VtCarry& c) {
+// only arithmetic difference to the CPU torch path is exp (ex2.approx of the scaled log-ratio:
+// 2 ulp).  Branch-free: `ok` (step inside [0,T) and row inside [0,R)) only gates the carry, so the
+// four steps of a chunk form one basic block and their independent parts overlap.
+__device__ __forceinline__ float vt_ratio_exp(float lp_old, float lp_new) {
+    return ex2_approx(__fmul_rn(__fsub_rn(lp_new, lp_old), kLog2e));           // utils.py:285,290
+}
+
+__device__ __forceinline__ VtStepOut vt_step(const VtParams& p, float ratio_exp, float v, float rew, bool done,
+                                             bool ok, VtCarry& c) {
     const float disc = done ? 0.0f : p.gamma;                                   // utils.py:277
-    const float ratio_exp = expf(__fsub_rn(lp_new, lp_old));                    // utils.py:285,290
     const float rho = fminf(ratio_exp, p.rho_bar);                              // utils.py:293
     const float cs = fminf(ratio_exp, p.c_bar);                                 // utils.py:294
     const float delta =
         __fmul_rn(rho, __fsub_rn(__fadd_rn(rew, __fmul_rn(disc, c.v_next)), v));        // utils.py:298
-    c.acc = __fadd_rn(delta, __fmul_rn(__fmul_rn(disc, cs), c.acc));            // utils.py:303
+    const float acc = __fadd_rn(delta, __fmul_rn(__fmul_rn(disc, cs), c.acc));  // utils.py:303
     VtStepOut o;
-    o.vs = __fadd_rn(c.acc, v);                                                 // utils.py:310
+    o.vs = __fadd_rn(acc, v);                                                   // utils.py:310
     const float pg_rho = fminf(rho, p.pg_rho_bar);                              // utils.py:316
     o.adv = __fmul_rn(pg_rho, __fsub_rn(__fadd_rn(rew, __fmul_rn(disc, c.vs_next)), v));  // utils.py:318
-    c.v_next = v;
-    c.vs_next = o.vs;
+    c.acc = ok ? acc : c.acc;
+    c.v_next = ok ? v : c.v_next;
+    c.vs_next = ok ? o.vs : c.vs_next;
     return o;
 }
 
@@ -233,22 +239,21 @@ __global__ void __launch_bounds__(32) vtrace_tma_kernel(const __grid_constant__ 
                 const float ln[4] = {a_new.x, a_new.y, a_new.z, a_new.w};
                 const float vv[4] = {a_val.x, a_val.y, a_val.z, a_val.w};
                 const float rw[4] = {a_rew.x, a_rew.y, a_rew.z, a_rew.w};
-                float o_vs[4], o_adv[4], o_dlp[4], o_dv[4];
+                float o_vs[4], o_adv[4], o_dlp[4], o_dv[4], re[4];
+#pragma unroll
+                for (int i = 0; i < 4; ++i) re[i] = vt_ratio_exp(lo[i], ln[i]);
 #pragma unroll
                 for (int i = 3; i >= 0; --i) {
-                    const int t = t0 + b * kVtSteps + 4 * j + i;
-                    o_vs[i] = 0.f; o_adv[i] = 0.f; o_dlp[i] = 0.f; o_dv[i] = 0.f;
-                    if (t < p.T && row_ok) {
-                        const bool dflag = ((dn >> (8 * i)) & 0xffu) != 0;
-                        const VtStepOut o = vt_step(p, lo[i], ln[i], vv[i], rw[i], dflag, carry);
-                        o_vs[i] = o.vs;
-                        o_adv[i] = o.adv;
-                        const float dvs = __fsub_rn(o.vs, vv[i]);
-                        o_dlp[i] = o.adv * p.inv_n;
-                        o_dv[i] = -dvs * p.inv_n;
-                        t_pg = __fadd_rn(t_pg, __fmul_rn(ln[i], o.adv));
-                        t_v = __fadd_rn(t_v, __fmul_rn(dvs, dvs));
-                    }
+                    const bool ok = row_ok && (t0 + b * kVtSteps + 4 * j + i < p.T);
+                    const bool dflag = ((dn >> (8 * i)) & 0xffu) != 0;
+                    const VtStepOut o = vt_step(p, re[i], vv[i], rw[i], dflag, ok, carry);
+                    const float dvs = __fsub_rn(o.vs, vv[i]);
+                    o_vs[i] = o.vs;             // out-of-range rows / steps are clipped by the TMA store
+                    o_adv[i] = o.adv;
+                    o_dlp[i] = o.adv * p.inv_n;
+                    o_dv[i] = -dvs * p.inv_n;
+                    t_pg = __fadd_rn(t_pg, ok ? __fmul_rn(ln[i], o.adv) : 0.0f);
+                    t_v = __fadd_rn(t_v, ok ? __fmul_rn(dvs, dvs) : 0.0f);
                 }
                 // in place: vs over rewards, adv over lp_old, d_logp over lp_new, d_values over values
                 *reinterpret_cast<float4*>(q_rew + off) = make_float4(o_vs[0], o_vs[1], o_vs[2], o_vs[3]);
@@ -328,7 +333,8 @@ __global__ void __launch_bounds__(128) vtrace_generic_kernel(const VtParams p) {
         float t_pg = 0.f, t_v = 0.f, t_en = 0.f;
         for (int t = p.T - 1; t >= 0; --t) {
             const float v = p.values[ib + t], ln = p.lp_new[ib + t];
-            const VtStepOut o = vt_step(p, p.lp_old[ib + t], ln, v, p.rewards[ib + t], p.done[ib + t] != 0, carry);
+            const VtStepOut o = vt_step(p, vt_ratio_exp(p.lp_old[ib + t], ln), v, p.rewards[ib + t],
+                                        p.done[ib + t] != 0, true, carry);
             p.vs[ob + t] = o.vs;
             p.adv[ob + t] = o.adv;
             const float dvs = __fsub_rn(o.vs, v);

@@ -3,7 +3,7 @@ import numpy as np
 import pytest
 import torch
 
-from microbeast_b200 import buffers as mbuf
+from microbeast_b200 import buffers as mbuf, synth
 from microbeast_b200.env_packer import Env_Packer, SyntheticVecEnv, _format_action_masks, _format_obs
 from oracle import refload
 
@@ -28,7 +28,7 @@ def test_packer_outputs_fit_the_rollout_buffers(tmp_path):
     for key in out:
         bufs[key][0][0, ...] = out[key]                                     # microbeast.py:73-75
     for t in range(T):
-        action = torch.zeros(n_envs, 7 * 64, dtype=torch.int64)
+        action = synth.make_valid_actions(out["action_mask"][0], gen=torch.Generator().manual_seed(t))
         out = packer.step(action)
         assert out["obs"].shape == (1, 1, n_envs, 8, 8, 27) and out["reward"].shape == (1, n_envs)
         assert out["done"].shape == (1, n_envs) and out["action_mask"].shape == (1, n_envs, 78 * 64)
@@ -37,7 +37,7 @@ def test_packer_outputs_fit_the_rollout_buffers(tmp_path):
     assert torch.equal(bufs["obs"][0].sum(-1), torch.full((T + 1, n_envs, 8, 8), 5, dtype=torch.uint8))
     rows = (tmp_path / "exp.csv").read_text().strip().splitlines()
     assert rows and all(len(r.split(",")) == 3 for r in rows)               # env_packer.py:69-75
-    # NOOP-everywhere actions are valid in every active cell of the synthetic env
+    # actions drawn from the masks the env handed out are all accepted
     assert env.invalid_actions == 0
 
 
