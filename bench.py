@@ -395,7 +395,7 @@ def run_sweep(args):
                                      "median_us": med * 1e3, "gbs": gbs, "frac_of_peak": gbs / peak})
         microbeast_b200.set_tuning("head_variant", -1)
         microbeast_b200.set_tuning("head_ctas_per_sm", 0)
-        vnames = {0: "2x1", 1: "3x1", 2: "4x1", 3: "2x2", 4: "3x2", 5: "2x4"}
+        vnames = {0: "2x32", 1: "3x32", 2: "4x32", 3: "3x16", 4: "4x16", 5: "5x16", 6: "6x16", 7: "8x16"}
         for variant, vname in vnames.items():
             microbeast_b200.set_tuning("vtrace_variant", variant)
             for T, R in ((512, 65536), (256, 65536), (80, 65536), (512, 4096), (80, 256)):

@@ -115,25 +115,36 @@ __device__ __forceinline__ void vt_finalize(const VtParams& p, int lane) {
 }
 
 // ---------------------------------------------------------------------------------------------
-// TMA kernel: one warp per CTA, 32 rows, time tiles of 32*BPT steps walked from the end.
-// A tile is BPT boxes of [32 rows x 32 steps] per array, issued back to back so that a row's
-// consecutive 128-B pieces reach the memory controller together (DRAM page locality).
+// TMA kernel: one warp per CTA, 32 rows, time tiles of TS (32 or 16) steps walked from the end.
+// The recurrence makes every thread a long dependent chain, so throughput comes from many resident
+// CTAs per SM: a stage is 17 B x 32 rows x TS steps (17 KB / 8.5 KB), NSTAGE of them per CTA.
 // Entropy only feeds a mean, so it is not staged: the warp streams its rows' entropy with plain
-// coalesced float4 loads spread over the iterations of the tile loop.
+// coalesced float4 loads issued at the top of every iteration and summed at its end.
 // ---------------------------------------------------------------------------------------------
 constexpr int kVtRows = 32;
-constexpr int kVtSteps = 32;
-constexpr int kVtTileF32 = kVtRows * kVtSteps * 4;     // 4096 B, 128-B rows, SWIZZLE_128B
-constexpr int kVtTileU8 = kVtRows * kVtSteps;          // 1024 B, 32-B rows, no swizzle
-constexpr int kVtBoxBytes = 4 * kVtTileF32 + kVtTileU8;     // lp_old, lp_new, values, rewards, done = 17408 B
 
-template <int NSTAGE, int BPT>
+template <int TS>
+struct VtTile {
+    static_assert(TS == 32 || TS == 16, "tile steps");
+    static constexpr int kF32 = kVtRows * TS * 4;          // 4096 / 2048 B; rows of 128 / 64 B, swizzled
+    static constexpr int kU8 = kVtRows * TS;               // 1024 / 512 B; rows of 32 / 16 B, no swizzle
+    static constexpr int kStage = 4 * kF32 + 1024;         // lp_old, lp_new, values, rewards, done (padded)
+    static constexpr int kChunks = TS / 4;                 // float4 chunks per row
+    static constexpr int kRowPitch = TS * 4;
+    // byte offset of float4 chunk j of row `lane` under SWIZZLE_128B (TS=32) / SWIZZLE_64B (TS=16)
+    __device__ static __forceinline__ uint32_t off(int lane, int j) {
+        return TS == 32 ? uint32_t(lane) * 128u + (uint32_t(j ^ (lane & 7)) << 4)
+                        : uint32_t(lane) * 64u + (uint32_t(j ^ ((lane >> 1) & 3)) << 4);
+    }
+};
+
+template <int NSTAGE, int TS>
 __global__ void __launch_bounds__(32) vtrace_tma_kernel(const __grid_constant__ VtMaps maps, const VtParams p) {
-    constexpr int kStageBytes = BPT * kVtBoxBytes;         // multiple of 1024
-    constexpr int kTileSteps = BPT * kVtSteps;
+    using Tile = VtTile<TS>;
+    constexpr int kStageBytes = Tile::kStage;              // multiple of 1024
     extern __shared__ uint8_t smem_raw[];
     __shared__ __align__(8) uint64_t full[NSTAGE];
-    // SWIZZLE_128B needs 1024-B aligned tiles
+    // swizzled tiles need 1024-B alignment
     uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
 
     const int lane = threadIdx.x;
@@ -153,26 +164,18 @@ __global__ void __launch_bounds__(32) vtrace_tma_kernel(const __grid_constant__ 
     }
     __syncwarp();
 
-    const int nt = (p.T + kTileSteps - 1) / kTileSteps;
-
-    // stage layout: [array a][box b] f32 tiles, then BPT done tiles
-    auto f32_tile = [&](uint8_t* st, int a, int b) -> uint8_t* { return st + (a * BPT + b) * kVtTileF32; };
-    auto u8_tile = [&](uint8_t* st, int b) -> uint8_t* { return st + 4 * BPT * kVtTileF32 + b * kVtTileU8; };
+    const int nt = (p.T + TS - 1) / TS;
 
     auto issue_load = [&](int k) {        // lane 0 only; k counts tiles from the END of the rows
         const int s = k % NSTAGE;
-        const int t0 = (nt - 1 - k) * kTileSteps;
+        const int t0 = (nt - 1 - k) * TS;
         uint8_t* st = smem + size_t(s) * kStageBytes;
-        mbar_arrive_expect_tx(&full[s], uint32_t(kStageBytes));
-#pragma unroll
-        for (int b = 0; b < BPT; ++b) {
-            const int tb = t0 + b * kVtSteps;
-            tma_load_2d(f32_tile(st, 0, b), &maps.lp_old, tb, row0, &full[s]);
-            tma_load_2d(f32_tile(st, 1, b), &maps.lp_new, tb, row0, &full[s]);
-            tma_load_2d(f32_tile(st, 2, b), &maps.values, tb, row0, &full[s]);
-            tma_load_2d(f32_tile(st, 3, b), &maps.rewards, tb, row0, &full[s]);
-            tma_load_2d(u8_tile(st, b), &maps.done, tb, row0, &full[s]);
-        }
+        mbar_arrive_expect_tx(&full[s], uint32_t(4 * Tile::kF32 + Tile::kU8));
+        tma_load_2d(st + 0 * Tile::kF32, &maps.lp_old, t0, row0, &full[s]);
+        tma_load_2d(st + 1 * Tile::kF32, &maps.lp_new, t0, row0, &full[s]);
+        tma_load_2d(st + 2 * Tile::kF32, &maps.values, t0, row0, &full[s]);
+        tma_load_2d(st + 3 * Tile::kF32, &maps.rewards, t0, row0, &full[s]);
+        tma_load_2d(st + 4 * Tile::kF32, &maps.done, t0, row0, &full[s]);
     };
 
     if (lane == 0) {
@@ -185,11 +188,12 @@ __global__ void __launch_bounds__(32) vtrace_tma_kernel(const __grid_constant__ 
     carry.vs_next = carry.v_next;
     double s_pg = 0.0, s_v = 0.0;
     float s_en = 0.0f;
+    float t_pg = 0.0f, t_v = 0.0f;
 
     // entropy: the CTA's [rows_here x T] block is a list of float4 slots (nq per row); lane l owns
     // slots l, l+32, ... and fetches its next kEntSlots of them at the top of every iteration, so
     // the loads fly while the warp waits for / works on the TMA tile and are summed afterwards
-    constexpr int kEntSlots = 8 * BPT;                     // 32*32*BPT floats per iteration per array
+    constexpr int kEntSlots = TS / 4;                      // 32*TS floats per iteration per array
     const int rows_here = int(min((long long)kVtRows, p.rows - row0));
     const int nq = (p.T + 3) >> 2;
     const int tail = p.T - 4 * (nq - 1);                   // valid floats in a row's last slot (1..4)
@@ -218,52 +222,52 @@ __global__ void __launch_bounds__(32) vtrace_tma_kernel(const __grid_constant__ 
         mbar_wait(&full[s], uint32_t((k / NSTAGE) & 1), nullptr);
 
         uint8_t* st = smem + size_t(s) * kStageBytes;
-        const int t0 = (nt - 1 - k) * kTileSteps;
-        float t_pg = 0.0f, t_v = 0.0f;
+        const int t0 = (nt - 1 - k) * TS;
+        uint8_t* q_old = st + 0 * Tile::kF32;
+        uint8_t* q_new = st + 1 * Tile::kF32;
+        uint8_t* q_val = st + 2 * Tile::kF32;
+        uint8_t* q_rew = st + 3 * Tile::kF32;
+        const uint8_t* q_dn = st + 4 * Tile::kF32;
+        // only the first tile handled (the END of the rows) can reach past T; rows past R only in the last CTA
+        const bool guard = (k == 0) || !row_ok;
 #pragma unroll
-        for (int b = BPT - 1; b >= 0; --b) {
-            uint8_t* q_old = f32_tile(st, 0, b);
-            uint8_t* q_new = f32_tile(st, 1, b);
-            uint8_t* q_val = f32_tile(st, 2, b);
-            uint8_t* q_rew = f32_tile(st, 3, b);
-            const uint8_t* q_dn = u8_tile(st, b);
+        for (int j = Tile::kChunks - 1; j >= 0; --j) {
+            const uint32_t off = Tile::off(lane, j);
+            const float4 a_old = *reinterpret_cast<const float4*>(q_old + off);
+            const float4 a_new = *reinterpret_cast<const float4*>(q_new + off);
+            const float4 a_val = *reinterpret_cast<const float4*>(q_val + off);
+            const float4 a_rew = *reinterpret_cast<const float4*>(q_rew + off);
+            const uint32_t dn = *reinterpret_cast<const uint32_t*>(q_dn + lane * TS + j * 4);
+            const float lo[4] = {a_old.x, a_old.y, a_old.z, a_old.w};
+            const float ln[4] = {a_new.x, a_new.y, a_new.z, a_new.w};
+            const float vv[4] = {a_val.x, a_val.y, a_val.z, a_val.w};
+            const float rw[4] = {a_rew.x, a_rew.y, a_rew.z, a_rew.w};
+            float o_vs[4], o_adv[4], o_dlp[4], o_dv[4], re[4];
 #pragma unroll
-            for (int j = kVtSteps / 4 - 1; j >= 0; --j) {
-                const uint32_t off = uint32_t(lane) * 128u + (uint32_t(j ^ (lane & 7)) << 4);
-                const float4 a_old = *reinterpret_cast<const float4*>(q_old + off);
-                const float4 a_new = *reinterpret_cast<const float4*>(q_new + off);
-                const float4 a_val = *reinterpret_cast<const float4*>(q_val + off);
-                const float4 a_rew = *reinterpret_cast<const float4*>(q_rew + off);
-                const uint32_t dn = *reinterpret_cast<const uint32_t*>(q_dn + lane * 32 + j * 4);
-                const float lo[4] = {a_old.x, a_old.y, a_old.z, a_old.w};
-                const float ln[4] = {a_new.x, a_new.y, a_new.z, a_new.w};
-                const float vv[4] = {a_val.x, a_val.y, a_val.z, a_val.w};
-                const float rw[4] = {a_rew.x, a_rew.y, a_rew.z, a_rew.w};
-                float o_vs[4], o_adv[4], o_dlp[4], o_dv[4], re[4];
+            for (int i = 0; i < 4; ++i) re[i] = vt_ratio_exp(lo[i], ln[i]);
 #pragma unroll
-                for (int i = 0; i < 4; ++i) re[i] = vt_ratio_exp(lo[i], ln[i]);
-#pragma unroll
-                for (int i = 3; i >= 0; --i) {
-                    const bool ok = row_ok && (t0 + b * kVtSteps + 4 * j + i < p.T);
-                    const bool dflag = ((dn >> (8 * i)) & 0xffu) != 0;
-                    const VtStepOut o = vt_step(p, re[i], vv[i], rw[i], dflag, ok, carry);
-                    const float dvs = __fsub_rn(o.vs, vv[i]);
-                    o_vs[i] = o.vs;             // out-of-range rows / steps are clipped by the TMA store
-                    o_adv[i] = o.adv;
-                    o_dlp[i] = o.adv * p.inv_n;
-                    o_dv[i] = -dvs * p.inv_n;
-                    t_pg = __fadd_rn(t_pg, ok ? __fmul_rn(ln[i], o.adv) : 0.0f);
-                    t_v = __fadd_rn(t_v, ok ? __fmul_rn(dvs, dvs) : 0.0f);
-                }
-                // in place: vs over rewards, adv over lp_old, d_logp over lp_new, d_values over values
-                *reinterpret_cast<float4*>(q_rew + off) = make_float4(o_vs[0], o_vs[1], o_vs[2], o_vs[3]);
-                *reinterpret_cast<float4*>(q_old + off) = make_float4(o_adv[0], o_adv[1], o_adv[2], o_adv[3]);
-                if (want_grads) {
-                    *reinterpret_cast<float4*>(q_new + off) = make_float4(o_dlp[0], o_dlp[1], o_dlp[2], o_dlp[3]);
-                    *reinterpret_cast<float4*>(q_val + off) = make_float4(o_dv[0], o_dv[1], o_dv[2], o_dv[3]);
-                }
+            for (int i = 3; i >= 0; --i) {
+                const bool ok = !guard || (row_ok && (t0 + 4 * j + i < p.T));
+                const bool dflag = ((dn >> (8 * i)) & 0xffu) != 0;
+                const VtStepOut o = vt_step(p, re[i], vv[i], rw[i], dflag, ok, carry);
+                const float dvs = __fsub_rn(o.vs, vv[i]);
+                o_vs[i] = o.vs;                 // out-of-range rows / steps are clipped by the TMA store
+                o_adv[i] = o.adv;
+                o_dlp[i] = o.adv * p.inv_n;
+                o_dv[i] = -dvs * p.inv_n;
+                t_pg = __fadd_rn(t_pg, ok ? __fmul_rn(ln[i], o.adv) : 0.0f);
+                t_v = __fadd_rn(t_v, ok ? __fmul_rn(dvs, dvs) : 0.0f);
             }
-            // the pg / value sums are folded into fp64 once per 32 steps (same grouping as the generic kernel)
+            // in place: vs over rewards, adv over lp_old, d_logp over lp_new, d_values over values
+            *reinterpret_cast<float4*>(q_rew + off) = make_float4(o_vs[0], o_vs[1], o_vs[2], o_vs[3]);
+            *reinterpret_cast<float4*>(q_old + off) = make_float4(o_adv[0], o_adv[1], o_adv[2], o_adv[3]);
+            if (want_grads) {
+                *reinterpret_cast<float4*>(q_new + off) = make_float4(o_dlp[0], o_dlp[1], o_dlp[2], o_dlp[3]);
+                *reinterpret_cast<float4*>(q_val + off) = make_float4(o_dv[0], o_dv[1], o_dv[2], o_dv[3]);
+            }
+        }
+        // the pg / value sums are folded into fp64 once per 32 steps (same grouping as the generic kernel)
+        if (TS == 32 || ((nt - 1 - k) & 1) == 0) {
             s_pg += double(t_pg);
             s_v += double(t_v);
             t_pg = 0.0f;
@@ -275,15 +279,11 @@ __global__ void __launch_bounds__(32) vtrace_tma_kernel(const __grid_constant__ 
         fence_proxy_async_smem();
         __syncwarp();
         if (lane == 0) {
-#pragma unroll
-            for (int b = 0; b < BPT; ++b) {
-                const int tb = t0 + b * kVtSteps;
-                tma_store_2d(&maps.vs, tb, row0, f32_tile(st, 3, b));
-                tma_store_2d(&maps.adv, tb, row0, f32_tile(st, 0, b));
-                if (want_grads) {
-                    tma_store_2d(&maps.dlp, tb, row0, f32_tile(st, 1, b));
-                    tma_store_2d(&maps.dv, tb, row0, f32_tile(st, 2, b));
-                }
+            tma_store_2d(&maps.vs, t0, row0, q_rew);
+            tma_store_2d(&maps.adv, t0, row0, q_old);
+            if (want_grads) {
+                tma_store_2d(&maps.dlp, t0, row0, q_new);
+                tma_store_2d(&maps.dv, t0, row0, q_val);
             }
             bulk_commit();
             if (k + NSTAGE - 1 < nt) {
@@ -393,10 +393,10 @@ static EncodeTiledFn get_encode_fn() {
 static int g_vt_l2_promo = 256;      // bytes: 0 (none), 64, 128, 256
 
 static bool encode_map_2d(EncodeTiledFn enc, CUtensorMap* m, const void* base, bool is_u8, long long rows, int T,
-                          long long stride_elems) {
+                          long long stride_elems, int tile_steps) {
     const cuuint64_t gdim[2] = {cuuint64_t(T), cuuint64_t(rows)};
     const cuuint64_t gstride[1] = {cuuint64_t(stride_elems) * (is_u8 ? 1u : 4u)};
-    const cuuint32_t box[2] = {cuuint32_t(kVtSteps), cuuint32_t(kVtRows)};
+    const cuuint32_t box[2] = {cuuint32_t(tile_steps), cuuint32_t(kVtRows)};
     const cuuint32_t estr[2] = {1, 1};
     // 256-B L2 promotion: a row's next (earlier) time tile sits in the other half of the same
     // 256-B block, so one DRAM page activation serves two consecutive tiles of the walk
@@ -406,7 +406,9 @@ static bool encode_map_2d(EncodeTiledFn enc, CUtensorMap* m, const void* base, b
                                                                 : CU_TENSOR_MAP_L2_PROMOTION_NONE;
     CUresult r = enc(m, is_u8 ? CU_TENSOR_MAP_DATA_TYPE_UINT8 : CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2,
                      const_cast<void*>(base), gdim, gstride, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
-                     is_u8 ? CU_TENSOR_MAP_SWIZZLE_NONE : CU_TENSOR_MAP_SWIZZLE_128B, promo,
+                     is_u8 ? CU_TENSOR_MAP_SWIZZLE_NONE
+                           : (tile_steps == 32 ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_64B),
+                     promo,
                      CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     return r == CUDA_SUCCESS;
 }
@@ -416,10 +418,10 @@ static bool encode_map_2d(EncodeTiledFn enc, CUtensorMap* m, const void* base, b
 struct MapKey {
     const void* base;
     long long rows, stride;
-    int T, is_u8, promo;
+    int T, is_u8, promo, ts;
     bool operator==(const MapKey& o) const {
         return base == o.base && rows == o.rows && stride == o.stride && T == o.T && is_u8 == o.is_u8 &&
-               promo == o.promo;
+               promo == o.promo && ts == o.ts;
     }
 };
 struct MapSlot {
@@ -431,17 +433,18 @@ static MapSlot g_map_cache[256];
 static std::mutex g_map_mutex;
 
 static bool make_map_2d(EncodeTiledFn enc, CUtensorMap* m, const void* base, bool is_u8, long long rows, int T,
-                        long long stride_elems) {
-    const MapKey key{base, rows, stride_elems, T, is_u8 ? 1 : 0, g_vt_l2_promo};
+                        long long stride_elems, int tile_steps) {
+    const MapKey key{base, rows, stride_elems, T, is_u8 ? 1 : 0, g_vt_l2_promo, tile_steps};
     size_t h = reinterpret_cast<uintptr_t>(base) >> 8;
-    h ^= size_t(rows) * 0x9E3779B97F4A7C15ull ^ size_t(T) * 0xC2B2AE3D27D4EB4Full ^ size_t(stride_elems) << 17;
+    h ^= size_t(rows) * 0x9E3779B97F4A7C15ull ^ size_t(T) * 0xC2B2AE3D27D4EB4Full ^ size_t(stride_elems) << 17 ^
+         size_t(tile_steps) << 3;
     MapSlot& slot = g_map_cache[(h ^ (h >> 29)) & 255];
     std::lock_guard<std::mutex> lock(g_map_mutex);
     if (slot.valid && slot.key == key) {
         *m = slot.map;
         return true;
     }
-    if (!encode_map_2d(enc, m, base, is_u8, rows, T, stride_elems)) return false;
+    if (!encode_map_2d(enc, m, base, is_u8, rows, T, stride_elems, tile_steps)) return false;
     slot.key = key;
     slot.map = *m;
     slot.valid = true;
@@ -464,22 +467,25 @@ size_t vtrace_workspace_bytes(long long rows) {
 
 static inline bool al16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; }
 
-template <int NSTAGE, int BPT>
+template <int NSTAGE, int TS>
 static int launch_vt_tma(const VtMaps& maps, const VtParams& p, cudaStream_t stream) {
-    constexpr size_t smem = size_t(NSTAGE) * BPT * kVtBoxBytes + 1024;
+    constexpr size_t smem = size_t(NSTAGE) * VtTile<TS>::kStage + 1024;
     static bool attr_set[64] = {};
     int dev = 0;
     MB_CUDA(cudaGetDevice(&dev));
     if (dev < 64 && !attr_set[dev]) {
-        MB_CUDA(cudaFuncSetAttribute(vtrace_tma_kernel<NSTAGE, BPT>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+        MB_CUDA(cudaFuncSetAttribute(vtrace_tma_kernel<NSTAGE, TS>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                      int(smem)));
         attr_set[dev] = true;
     }
     const unsigned grid = unsigned((p.rows + kVtRows - 1) / kVtRows);
-    vtrace_tma_kernel<NSTAGE, BPT><<<grid, 32, smem, stream>>>(maps, p);
+    vtrace_tma_kernel<NSTAGE, TS><<<grid, 32, smem, stream>>>(maps, p);
     MB_CUDA(cudaGetLastError());
     return MB_OK;
 }
+
+// pipeline shapes (stages x steps per tile) selectable with mb_set_tuning("vtrace_variant", v)
+static const int kVtVariantSteps[8] = {32, 32, 32, 16, 16, 16, 16, 16};
 
 // `scratch` holds the ticket word at offset 0 (must be zero on entry; the kernel leaves it zero)
 // and the per-CTA partial sums from offset 256.
@@ -523,30 +529,32 @@ int vtrace_loss_launch(VtParams p, void* scratch, size_t scratch_bytes, cudaStre
                   al16(p.lp_old) && al16(p.lp_new) && al16(p.values) && al16(p.rewards) && al16(p.entropy) &&
                   al16(p.done) && al16(p.vs) && al16(p.adv) && (!p.dlp || (al16(p.dlp) && al16(p.dv)));
     if (tma_ok) {
+        // Few CTAs (latency bound) -> deep prefetch; many CTAs (bandwidth bound) -> more CTAs per SM.
+        int v = g_vt_variant;
+        if (v < 0 || v > 7) v = (p.rows + kVtRows - 1) / kVtRows >= 4 * sm_count(0) ? 1 : 2;
+        const int ts = kVtVariantSteps[v];
         VtMaps maps;
         memset(&maps, 0, sizeof(maps));
-        bool ok = make_map_2d(enc, &maps.lp_old, p.lp_old, false, p.rows, p.T, p.in_stride) &&
-                  make_map_2d(enc, &maps.lp_new, p.lp_new, false, p.rows, p.T, p.in_stride) &&
-                  make_map_2d(enc, &maps.values, p.values, false, p.rows, p.T, p.in_stride) &&
-                  make_map_2d(enc, &maps.rewards, p.rewards, false, p.rows, p.T, p.in_stride) &&
-                  make_map_2d(enc, &maps.done, p.done, true, p.rows, p.T, p.in_stride) &&
-                  make_map_2d(enc, &maps.vs, p.vs, false, p.rows, p.T, p.out_stride) &&
-                  make_map_2d(enc, &maps.adv, p.adv, false, p.rows, p.T, p.out_stride);
+        bool ok = make_map_2d(enc, &maps.lp_old, p.lp_old, false, p.rows, p.T, p.in_stride, ts) &&
+                  make_map_2d(enc, &maps.lp_new, p.lp_new, false, p.rows, p.T, p.in_stride, ts) &&
+                  make_map_2d(enc, &maps.values, p.values, false, p.rows, p.T, p.in_stride, ts) &&
+                  make_map_2d(enc, &maps.rewards, p.rewards, false, p.rows, p.T, p.in_stride, ts) &&
+                  make_map_2d(enc, &maps.done, p.done, true, p.rows, p.T, p.in_stride, ts) &&
+                  make_map_2d(enc, &maps.vs, p.vs, false, p.rows, p.T, p.out_stride, ts) &&
+                  make_map_2d(enc, &maps.adv, p.adv, false, p.rows, p.T, p.out_stride, ts);
         if (ok && p.dlp)
-            ok = make_map_2d(enc, &maps.dlp, p.dlp, false, p.rows, p.T, p.out_stride) &&
-                 make_map_2d(enc, &maps.dv, p.dv, false, p.rows, p.T, p.out_stride);
+            ok = make_map_2d(enc, &maps.dlp, p.dlp, false, p.rows, p.T, p.out_stride, ts) &&
+                 make_map_2d(enc, &maps.dv, p.dv, false, p.rows, p.T, p.out_stride, ts);
         if (ok) {
-            // pipeline shape: stages x boxes-per-tile.  Few CTAs (latency bound) -> deep prefetch;
-            // many CTAs (bandwidth bound) -> more resident CTAs per SM.
-            int v = g_vt_variant;
-            if (v < 0) v = (p.rows + kVtRows - 1) / kVtRows >= 4 * sm_count(0) ? 0 : 2;
             switch (v) {
-                case 1: return launch_vt_tma<3, 1>(maps, p, stream);
-                case 2: return launch_vt_tma<4, 1>(maps, p, stream);
-                case 3: return launch_vt_tma<2, 2>(maps, p, stream);
-                case 4: return launch_vt_tma<3, 2>(maps, p, stream);
-                case 5: return launch_vt_tma<2, 4>(maps, p, stream);
-                default: return launch_vt_tma<2, 1>(maps, p, stream);
+                case 0: return launch_vt_tma<2, 32>(maps, p, stream);
+                case 2: return launch_vt_tma<4, 32>(maps, p, stream);
+                case 3: return launch_vt_tma<3, 16>(maps, p, stream);
+                case 4: return launch_vt_tma<4, 16>(maps, p, stream);
+                case 5: return launch_vt_tma<5, 16>(maps, p, stream);
+                case 6: return launch_vt_tma<6, 16>(maps, p, stream);
+                case 7: return launch_vt_tma<8, 16>(maps, p, stream);
+                default: return launch_vt_tma<3, 32>(maps, p, stream);
             }
         }
         // tensor-map encoding refused the shape: fall through to the generic kernel

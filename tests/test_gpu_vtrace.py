@@ -81,9 +81,9 @@ def test_vs_oracle_shapes(rows, T):
     assert torch.equal(out["loss4"], out3["loss4"]) and torch.equal(out["vs"], out3["vs"])
 
 
-@pytest.mark.parametrize("variant", [0, 1, 2, 3, 4, 5])
+@pytest.mark.parametrize("variant", [0, 1, 2, 3, 4, 5, 6, 7])
 def test_pipeline_shapes_agree(variant):
-    """Every stages x boxes-per-tile shape of the TMA kernel gives the same targets, bit for bit."""
+    """Every stages x steps-per-tile shape of the TMA kernel gives the same targets, bit for bit."""
     mb, ops, synth, _ = _mods()
     g = torch.Generator().manual_seed(5)
     t = synth.make_vtrace_inputs(300, 160, gen=g)
