@@ -379,7 +379,7 @@ def run_sweep(args):
         u = synth.make_uniforms(n, cells, gen=g, device=dev)
         gl = torch.randn(n, generator=g, device=dev)
         out = torch.empty_like(logits)
-        names = {0: "64x3", 1: "64x2", 2: "64x4", 3: "32x3", 4: "32x5", 5: "128x3", 6: "128x2"}
+        names = {0: "64x3", 1: "64x2", 2: "64x4", 3: "32x3", 4: "32x5", 5: "128x3", 6: "128x2", 7: "32x2"}
         for variant, vname in names.items():
             for per_sm in (0,):
                 microbeast_b200.set_tuning("head_variant", variant)

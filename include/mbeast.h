@@ -103,7 +103,7 @@ MB_API int mb_vtrace_loss(const float* lp_old, const float* lp_new, const float*
 
 /* Tuning knobs for benchmarking (not part of the reference surface).  Keys:
  *   "head_ctas_per_sm" (0 = as many as fit), "head_grid" (0 = auto), "head_variant" (tile /
- *   pipeline shape: 0 = 64 cells x 3 stages, 1 = 64x2, 2 = 64x4, 3 = 32x3, 4 = 32x5, 5 = 128x3, 6 = 128x2),
+ *   pipeline shape: 0 = 64 cells x 3 stages, 1 = 64x2, 2 = 64x4, 3 = 32x3, 4 = 32x5, 5 = 128x3, 6 = 128x2, 7 = 32x2; -1 = per-kernel default),
  *   "vtrace_force_generic" (0/1), "vtrace_l2_promo" (0/64/128/256 bytes),
  *   "vtrace_variant" (stages x steps per tile: -1 = by grid size, 0 = 2x32, 1 = 3x32, 2 = 4x32,
  *   3 = 3x16, 4 = 4x16, 5 = 5x16, 6 = 6x16, 7 = 8x16).

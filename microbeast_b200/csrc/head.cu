@@ -49,7 +49,7 @@ struct HeadCfg {
     static constexpr int kThreads = 32 * (1 + kConsWarps);
     static constexpr int kLogitBytes = TC * kLogitsPerCell * 4;
     static constexpr int kMaskBytes = TC * kLogitsPerCell;
-    static constexpr int kActBytes = TC * kCompsPerCell * 8;
+    static constexpr int kActBytes = (MODE == kSample) ? 0 : TC * kCompsPerCell * 8;   // sample writes actions to global
     static constexpr int kUniBytes = (MODE == kSample) ? TC * kCompsPerCell * 4 : 0;
     static constexpr int kOffMask = kLogitBytes;
     static constexpr int kOffAct = kOffMask + kMaskBytes;
@@ -568,24 +568,10 @@ __global__ void __launch_bounds__(HeadCfg<TC, MODE>::kThreads) head_kernel(const
                     for (int i = lane; i < nc * kLogitsPerCell; i += 32) gd[i] = sl[i];
                     __syncwarp();
                 }
-            } else {
-                int64_t* ga = p.action_out + cell * kCompsPerCell;
-                const uint32_t bytes = uint32_t(nc) * kCompsPerCell * 8;
-                last_store_bulk = ((reinterpret_cast<uintptr_t>(ga) | bytes) & 15) == 0;
-                if (last_store_bulk) {
-                    if (lane == 0) {
-                        bulk_s2g(ga, st + Cfg::kOffAct, bytes);
-                        bulk_commit();
-                    }
-                } else {
-                    const int64_t* sa = reinterpret_cast<const int64_t*>(st + Cfg::kOffAct);
-                    for (int i = lane; i < nc * kCompsPerCell; i += 32) ga[i] = sa[i];
-                    __syncwarp();
-                }
             }
         };
 
-        if (MODE == kEvalFwd) {
+        if (MODE != kEvalBwd) {
             for (long long j = 0; j < n_tiles + NSTAGE; ++j) {
                 if (j >= NSTAGE) retire_tile(j - NSTAGE);
                 if (j < n_tiles) load_tile(j);
@@ -632,7 +618,10 @@ __global__ void __launch_bounds__(HeadCfg<TC, MODE>::kThreads) head_kernel(const
             const bool active = cell_in_tile < nc;
             float* zc = reinterpret_cast<float*>(st) + cell_in_tile * kLogitsPerCell;
             const uint8_t* mc = st + Cfg::kOffMask + cell_in_tile * kLogitsPerCell;
-            int64_t* ac = reinterpret_cast<int64_t*>(st + Cfg::kOffAct) + cell_in_tile * kCompsPerCell;
+            // eval: the taken actions staged in shared memory; sample: the global output row of this cell
+            int64_t* ac = (MODE == kSample)
+                              ? p.action_out + (tile_frame(j) * p.cells + tile_cell0(j) + cell_in_tile) * kCompsPerCell
+                              : reinterpret_cast<int64_t*>(st + Cfg::kOffAct) + cell_in_tile * kCompsPerCell;
             const float* uc = reinterpret_cast<const float*>(st + Cfg::kOffUni) + cell_in_tile * kCompsPerCell;
             float lp = 0.f, en = 0.f;
             // lanes past the end of a ragged tile run on stale stage contents and discard the result
@@ -649,7 +638,7 @@ __global__ void __launch_bounds__(HeadCfg<TC, MODE>::kThreads) head_kernel(const
                     part[(s * Cfg::kConsWarps + cw) * 2 + 1] = en;
                 }
             }
-            if (MODE != kEvalFwd) fence_proxy_async_smem();   // in-place outputs -> async-proxy bulk store
+            if (MODE == kEvalBwd) fence_proxy_async_smem();   // in-place dlogits -> async-proxy bulk store
             __syncwarp();
             if (lane == 0) mbar_arrive(&done[s]);
         }
@@ -706,6 +695,7 @@ static int dispatch_head(const HeadParams& p, cudaStream_t stream) {
         case 4: return launch_head<32, MODE, 5>(p, stream);
         case 5: return launch_head<128, MODE, 3>(p, stream);
         case 6: return launch_head<128, MODE, 2>(p, stream);
+        case 7: return launch_head<32, MODE, 2>(p, stream);
         default: return launch_head<64, MODE, 3>(p, stream);
     }
 }

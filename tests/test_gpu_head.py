@@ -103,7 +103,7 @@ def test_autograd_function_matches_reference_autograd():
     _assert_close(zc.grad, z.grad, "autograd dlogits", support=mask != 0)
 
 
-@pytest.mark.parametrize("variant", [0, 1, 2, 3, 4, 5, 6])
+@pytest.mark.parametrize("variant", [0, 1, 2, 3, 4, 5, 6, 7])
 def test_tile_shapes_agree(variant):
     """Every tile / pipeline shape of the head kernel gives the same bits (the per-frame reduction
     order depends on the tile size, so log-prob / entropy may differ in the last ulp only)."""
