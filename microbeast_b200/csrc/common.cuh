@@ -60,14 +60,16 @@ __device__ __forceinline__ void mbar_arrive_expect_tx(uint64_t* bar, uint32_t by
                  : "memory");
 }
 
+// try_wait suspends the warp in hardware until the phase completes or the time hint (ns) runs
+// out, so a waiting warp does not burn issue slots that computing warps need.
 __device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
     uint32_t ok;
     asm volatile(
         "{\n\t.reg .pred p;\n\t"
-        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2, %3;\n\t"
         "selp.u32 %0, 1, 0, p;\n\t}"
         : "=r"(ok)
-        : "r"(smem_u32(bar)), "r"(parity)
+        : "r"(smem_u32(bar)), "r"(parity), "r"(0x989680u)
         : "memory");
     return ok != 0;
 }
@@ -78,15 +80,20 @@ __device__ __forceinline__ uint64_t global_timer_ns() {
     return t;
 }
 
-// Bounded wait: a pipeline bug must trap instead of hanging the GPU (2 s of wall clock).
+// Bounded wait: a pipeline bug must trap instead of hanging the GPU (about 2 s of wall clock).
 __device__ __forceinline__ bool mbar_wait(uint64_t* bar, uint32_t parity, int* status) {
     if (mbar_try_wait(bar, parity)) return true;
-    const uint64_t t0 = global_timer_ns();
+    uint64_t t0 = 0;
+    uint32_t spins = 0;
 #pragma unroll 1
     while (!mbar_try_wait(bar, parity)) {
-        if (global_timer_ns() - t0 > 2000000000ull) {
-            if (status) atomicOr(status, kStatusTimeout);
-            __trap();
+        if ((++spins & 63u) == 0) {
+            const uint64_t now = global_timer_ns();
+            if (t0 == 0) t0 = now;
+            if (now - t0 > 2000000000ull) {
+                if (status) atomicOr(status, kStatusTimeout);
+                __trap();
+            }
         }
     }
     return true;

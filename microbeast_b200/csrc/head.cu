@@ -96,10 +96,12 @@ __device__ __forceinline__ void ucdf_fill(double* tab) {
 __device__ __forceinline__ int ucdf_pick(const double* tab, int n, float u) {
     const double* t = tab + ucdf_offset(n);
     const double ud = double(u);
-    int a = min(max(int(u * float(n)), 0), n - 1);
-    while (a > 0 && ud < t[a - 1]) --a;
-    while (a < n - 1 && ud >= t[a]) ++a;
-    return a;
+    // floor(fl32(u*n)) is within one of the exact count (table entries are (k+1)/n up to 1e-16 and the
+    // fp32 product is off by at most n*2^-24), so one look at the two neighbouring edges settles it
+    const int a = min(max(int(u * float(n)), 0), n - 1);
+    const int up = (a < n - 1 && ud >= t[min(a, n - 2)]) ? 1 : 0;
+    const int down = (a > 0 && ud < t[max(a - 1, 0)]) ? 1 : 0;
+    return a + up - down;
 }
 
 // Warp-cooperative exact recompute of one component (all 32 lanes call it with the same args).
