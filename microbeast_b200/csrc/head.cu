@@ -689,7 +689,7 @@ static int launch_head(HeadParams p, cudaStream_t stream) {
 template <int MODE>
 static int dispatch_head(const HeadParams& p, cudaStream_t stream) {
     int v = g_head_variant;
-    if (v < 0) v = (MODE == kEvalFwd) ? 1 : (MODE == kEvalBwd ? 0 : 3);   // measured best on B200 (profiles/)
+    if (v < 0) v = (MODE == kEvalFwd) ? 1 : (MODE == kEvalBwd ? 0 : 7);   // measured best on B200 (profiles/)
     switch (v) {
         case 1: return launch_head<64, MODE, 2>(p, stream);
         case 2: return launch_head<64, MODE, 4>(p, stream);

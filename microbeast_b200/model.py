@@ -186,6 +186,9 @@ class Agent(nn.Module):
             action, logprobs, _ = ops.head_sample(logits.detach(), action_mask, uniforms,
                                                   want_entropy=False)
             return (dict(action=action, policy_logits=logits, logprobs=logprobs, baseline=baseline), ())
+        ready = input_dict.get("_ready")      # set by learner.batch_to_device: side-stream H2D of mask / action
+        if ready is not None:
+            torch.cuda.current_stream().wait_event(ready)
         action = input_dict["action"]                                           # model.py:182
         action_mask = input_dict["action_mask"]                                 # model.py:188
         logprobs, entropy = ops.HeadEval.apply(logits, action_mask, action)

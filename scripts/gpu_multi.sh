@@ -1,0 +1,10 @@
+#!/bin/bash
+# usage: gpu_multi.sh N   (run under gpurun --gpus N)
+N=${1:-2}
+mkdir -p gpurun_out
+nvidia-smi --query-gpu=index,name --format=csv > gpurun_out/gpus_$N.txt 2>&1
+timeout 600 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29517 \
+  scripts/dp_check.py > gpurun_out/dp_check_$N.log 2>&1; echo "dp_check $N exit $?" | tee -a gpurun_out/summary_multi.txt
+timeout 900 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29518 \
+  bench.py --gpus $N --steps 10 --warmup 3 --out gpurun_out/bench_n$N.jsonl > gpurun_out/bench_n$N.log 2>&1; echo "bench $N exit $?" | tee -a gpurun_out/summary_multi.txt
+tail -n 3 gpurun_out/dp_check_$N.log; tail -c 600 gpurun_out/bench_n$N.log
