@@ -101,6 +101,27 @@ MB_API int mb_vtrace_loss(const float* lp_old, const float* lp_new, const float*
                    float pg_rho_bar, float ent_coef, float inv_n, float* vs_out, float* adv_out, float* loss4_out,
                    float* dlp_out, float* dV_out, void* workspace, size_t workspace_bytes, void* stream);
 
+/* mb_vtrace_loss without the workspace argument.  It has no counterpart in the reference: it exists
+ * for users of this library who cannot allocate device memory where they call it (a C / ctypes host
+ * with no allocator of its own, a step loop that must stay clear of cudaMalloc's device-wide
+ * synchronisation, a thread running while another stream of the process is under capture, when the
+ * runtime refuses cudaMalloc).  The scratch is a fixed 64 KiB array inside the library image, one
+ * per GPU that loads the library, kept until the process exits.
+ *   - rows <= 65536 per call; more is rejected with MB_ERR_INVALID (use mb_vtrace_loss then);
+ *   - the first call on each device looks the array's device address up (cudaGetSymbolAddress, with
+ *     that device current); make that first call outside any stream capture;
+ *   - the call never allocates or frees device memory; it clears the part of the scratch that must
+ *     start at zero on `stream` before the launch;
+ *   - every call on a GPU shares the one array: calls that may overlap on the GPU race with each
+ *     other -- keep them on one stream or order them with events.
+ * All other arguments, outputs and return codes are those of mb_vtrace_loss. */
+MB_API int mb_vtrace_loss_static(const float* lp_old, const float* lp_new, const float* values,
+                                 const float* bootstrap, const float* rewards, const uint8_t* done,
+                                 const float* entropy, int64_t rows, int32_t T, int64_t in_row_stride,
+                                 int64_t out_row_stride, float gamma, float rho_bar, float c_bar,
+                                 float pg_rho_bar, float ent_coef, float inv_n, float* vs_out, float* adv_out,
+                                 float* loss4_out, float* dlp_out, float* dV_out, void* stream);
+
 /* Tuning knobs for benchmarking (not part of the reference surface).  Keys:
  *   "head_ctas_per_sm" (0 = as many as fit), "head_grid" (0 = auto), "head_variant" (tile /
  *   pipeline shape: 0 = 64 cells x 3 stages, 1 = 64x2, 2 = 64x4, 3 = 32x3, 4 = 32x5, 5 = 128x3, 6 = 128x2, 7 = 32x2; -1 = per-kernel default),

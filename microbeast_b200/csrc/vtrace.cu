@@ -584,3 +584,81 @@ extern "C" int mb_vtrace_loss(const float* lp_old, const float* lp_new, const fl
     p.inv_n = inv_n;
     return mb::vtrace_loss_launch(p, workspace, workspace_bytes, static_cast<cudaStream_t>(stream));
 }
+
+// ---------------------------------------------------------------------------------------------
+// mb_vtrace_loss_static: the same computation for callers that cannot hand in a workspace.
+//
+// mb_vtrace_loss needs a few KB of scratch (a ticket word and three partial sums per CTA) and
+// leaves it to the caller to allocate them.  Some users of this library are not in a position to
+// allocate device memory where they call it: a plain C / ctypes host that links no allocator, a
+// step loop that must not run into cudaMalloc's device-wide synchronisation, or a thread that runs
+// while another part of the process has a stream under capture (the runtime refuses cudaMalloc
+// then).  For them the scratch lives in the library image itself: one fixed array per GPU that has
+// loaded the library, held until the process exits.
+//
+// The array's name is only a host-side handle; the kernel needs the device address behind it, which
+// cudaGetSymbolAddress returns for the device that is current at the time.  The first call on each
+// device does that look-up (and nothing else extra), so make the first call on a device outside any
+// stream capture.  No call allocates or frees device memory.
+//
+// All calls on one GPU share the array and it keeps whatever the previous call left there.  The only
+// part that has to start at zero, the ticket word, is cleared on the caller's stream before every
+// launch.  Two calls that may run on the GPU at the same time (different streams, no dependency
+// between them) would corrupt each other's sums: serialise them or use mb_vtrace_loss with separate
+// workspaces.
+// ---------------------------------------------------------------------------------------------
+namespace mb {
+
+constexpr long long kVtStaticMaxRows = 65536;            // 2048 CTAs x 24 B of partial sums + header
+constexpr size_t kVtStaticScratchBytes = 64 * 1024;
+
+static __device__ __align__(256) unsigned char g_vt_static_scratch[kVtStaticScratchBytes];
+
+static int vt_static_scratch(void** out) {
+    static std::mutex mu;
+    static void* ptrs[64] = {};
+    int dev = -1;
+    MB_CUDA(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= 64) {
+        set_error("mb_vtrace_loss_static: device index %d not supported (0..63)", dev);
+        return MB_ERR_UNSUPPORTED;
+    }
+    std::lock_guard<std::mutex> lock(mu);
+    if (!ptrs[dev]) {
+        void* p = nullptr;
+        MB_CUDA(cudaGetSymbolAddress(&p, g_vt_static_scratch));      // device address on the CURRENT device
+        ptrs[dev] = p;
+    }
+    *out = ptrs[dev];
+    return MB_OK;
+}
+
+}  // namespace mb
+
+extern "C" int mb_vtrace_loss_static(const float* lp_old, const float* lp_new, const float* values,
+                                     const float* bootstrap, const float* rewards, const uint8_t* done,
+                                     const float* entropy, int64_t rows, int32_t T, int64_t in_row_stride,
+                                     int64_t out_row_stride, float gamma, float rho_bar, float c_bar,
+                                     float pg_rho_bar, float ent_coef, float inv_n, float* vs_out, float* adv_out,
+                                     float* loss4_out, float* dlp_out, float* dV_out, void* stream) {
+    if (rows > mb::kVtStaticMaxRows) {
+        mb::set_error("mb_vtrace_loss_static: rows=%lld exceeds the built-in scratch (at most %lld rows per call); "
+                      "use mb_vtrace_loss with a caller-owned workspace",
+                      (long long)rows, mb::kVtStaticMaxRows);
+        return MB_ERR_INVALID;
+    }
+    static_assert(mb::kVtStaticScratchBytes >= 256 + (mb::kVtStaticMaxRows / mb::kVtRows + 1) * 3 * sizeof(double),
+                  "static scratch too small for the advertised row limit");
+    void* scratch = nullptr;
+    if (int rc = mb::vt_static_scratch(&scratch)) return rc;
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    if (rows > 0) MB_CUDA(cudaMemsetAsync(scratch, 0, 256, st));      // ticket word (and its padding) start at zero
+    mb::VtParams p;
+    memset(&p, 0, sizeof(p));
+    p.lp_old = lp_old; p.lp_new = lp_new; p.values = values; p.rewards = rewards; p.entropy = entropy;
+    p.done = done; p.bootstrap = bootstrap; p.vs = vs_out; p.adv = adv_out; p.dlp = dlp_out; p.dv = dV_out;
+    p.loss4 = loss4_out; p.rows = rows; p.T = T; p.in_stride = in_row_stride; p.out_stride = out_row_stride;
+    p.gamma = gamma; p.rho_bar = rho_bar; p.c_bar = c_bar; p.pg_rho_bar = pg_rho_bar; p.ent_coef = ent_coef;
+    p.inv_n = inv_n;
+    return mb::vtrace_loss_launch(p, scratch, mb::kVtStaticScratchBytes, st);
+}
