@@ -59,6 +59,8 @@ def parse_args():
     ap.add_argument("--cpu-rows", type=int, default=32, help="rows of the CPU-baseline sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--wire", default="compact", choices=["compact", "plain"],
+                    help="host batch format of the e2e leg (compact = the rollout store's wire format)")
     ap.add_argument("--sweep", default="", choices=["", "vtrace", "head", "variants"])
     ap.add_argument("--out", default="", help="also append the JSON line(s) to this file")
     return ap.parse_args()
@@ -299,14 +301,20 @@ def run_ours(args):
     # ---- e2e: host batch through the public call ---------------------------------------
     e2e = None
     if not args.no_e2e:
-        host = {k: torch.empty(v.shape, dtype=v.dtype, pin_memory=True).copy_(v) for k, v in dev_batch.items()}
+        from microbeast_b200 import buffers as mbuf
+        wire = {k: v.cpu() for k, v in dev_batch.items()}
+        if args.wire == "compact":
+            wire = mbuf.pack_batch(wire)        # rollout-store wire format: mask bits, u8 actions, u8 obs
+        host = {k: torch.empty(v.shape, dtype=v.dtype, pin_memory=True).copy_(v) for k, v in wire.items()}
         h2d = sum(v.numel() * v.element_size() for v in host.values())
         e2e_steps = max(3, min(args.steps, 10))
         ms_e2e, _, _, _ = timed(lambda: step(host, True), e2e_steps, 3)
         e2e = {"value": frames / (ms_e2e * 1e-3), "unit": UNIT, "h2d_bytes_per_step": h2d * world,
                "d2h_bytes_per_step": 16 * world, "ms_per_step": ms_e2e, "steps": e2e_steps,
                "call": "microbeast_b200.learner.PPO_learn(model, model, name, pinned_host_batch, adam, rows, T, 1)",
-               "wire_format": "obs u8, action_mask u8, action i64, reward/logprobs f32, done bool"}
+               "wire_format": ("obs u8, action_mask bit-packed, action u8 (widened on the device by "
+                               "mb_unpack_rollout), reward/logprobs f32, done bool") if args.wire == "compact"
+               else "obs u8, action_mask u8, action i64, reward/logprobs f32, done bool"}
         del host
 
     # ---- cpu baseline (rank 0, N=1) ------------------------------------------------------

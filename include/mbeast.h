@@ -122,6 +122,15 @@ MB_API int mb_vtrace_loss_static(const float* lp_old, const float* lp_new, const
                                  float pg_rho_bar, float ent_coef, float inv_n, float* vs_out, float* adv_out,
                                  float* loss4_out, float* dlp_out, float* dV_out, void* stream);
 
+/* Wire-format expansion of the rollout store (no reference counterpart; it restores the dtypes of
+ * reference libs/utils.py:43-44 on the device after a compact host->device copy).
+ *   mask_bits [n_frames, ceil(78*cells/8)] u8, bit i of byte j = mask entry 8j+i of the frame
+ *        ->  mask_out [n_frames, 78*cells] u8 (0/1);
+ *   action_u8 [n_frames, 7*cells] u8  ->  action_out [n_frames, 7*cells] i64.
+ * Either pair may be NULL/NULL to skip it. */
+MB_API int mb_unpack_rollout(const uint8_t* mask_bits, const uint8_t* action_u8, uint8_t* mask_out,
+                             int64_t* action_out, int64_t n_frames, int32_t cells, void* stream);
+
 /* Tuning knobs for benchmarking (not part of the reference surface).  Keys:
  *   "head_ctas_per_sm" (0 = as many as fit), "head_grid" (0 = auto), "head_variant" (tile /
  *   pipeline shape: 0 = 64 cells x 3 stages, 1 = 64x2, 2 = 64x4, 3 = 32x3, 4 = 32x5, 5 = 128x3, 6 = 128x2, 7 = 32x2; -1 = per-kernel default),

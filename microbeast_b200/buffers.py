@@ -76,6 +76,48 @@ class DiscardSlot:
         return self
 
 
+def pack_mask(mask: torch.Tensor) -> torch.Tensor:
+    """``[..., W]`` u8/bool mask -> ``[..., ceil(W/8)]`` u8, bit i of byte j = entry 8j+i (host side)."""
+    import numpy as np
+    arr = (mask.cpu().numpy() != 0)
+    return torch.from_numpy(np.packbits(arr, axis=-1, bitorder="little"))
+
+
+def pack_batch(batch: dict) -> dict:
+    """Reference-format host batch -> the compact wire format ``PPO_learn`` also accepts:
+    ``action_mask`` becomes ``action_mask_bits`` (8x smaller) and ``action`` uint8 (8x smaller;
+    indices are < 49).  ``obs`` becomes uint8 (planes are 0/1)."""
+    out = {k: v for k, v in batch.items() if k not in ("action_mask", "action", "obs")}
+    out["action_mask_bits"] = pack_mask(batch["action_mask"])
+    out["action"] = batch["action"].to(torch.uint8)
+    out["obs"] = batch["obs"].to(torch.uint8)
+    return out
+
+
+class PackedMaskSlot:
+    """Rollout-buffer slot that keeps the action mask bit-packed: the actor's slot write
+    ``buffers["action_mask"][i][t, ...] = mask`` (``microbeast.py:75,96``) packs on the way in."""
+
+    def __init__(self, packed: torch.Tensor, width: int):
+        self.packed = packed               # [T+1, n_envs, ceil(width/8)] u8 view of the slab
+        self.width = width
+        self.shape = torch.Size(tuple(packed.shape[:-1]) + (width,))
+        self.dtype = torch.uint8
+
+    def size(self):
+        return self.shape
+
+    def __setitem__(self, index, value):
+        value = torch.as_tensor(value)
+        self.packed[index] = pack_mask(value.reshape(tuple(value.shape[:-1]) + (self.width,))).reshape(
+            self.packed[index].shape)
+
+    def unpacked(self) -> torch.Tensor:
+        import numpy as np
+        bits = np.unpackbits(self.packed.numpy(), axis=-1, bitorder="little")[..., :self.width]
+        return torch.from_numpy(bits)
+
+
 class RolloutBuffers(dict):
     """``Dict[str, List[Tensor]]`` like the reference's, plus the slabs behind the lists."""
 
@@ -90,6 +132,8 @@ class RolloutBuffers(dict):
         self._pending = []           # (event, indices, free_queue) waiting for their DMA
         self._stream = {}
         self._registered = []
+        self.compact = False
+        self.cells = 0
         self._finalizer = None
 
     def live_keys(self):
@@ -132,11 +176,14 @@ def _unregister(ptrs) -> None:
 
 
 def create_buffers(n_buffers: int, n_envs: int, B: int, T: int, obs_size: tuple, *, lean: bool = True,
-                   obs_dtype=torch.uint8, share: bool = True) -> Buffers:
+                   obs_dtype=torch.uint8, share: bool = True, compact: bool = False) -> Buffers:
     """Creates ``n_buffers`` rollout buffers shared between processes -- reference
     ``libs/utils.py:29-55``, same positional signature and the same 11 keys.
 
     ``lean=False, obs_dtype=torch.float32`` reproduces the reference layout exactly.
+    ``compact=True`` additionally keeps ``action_mask`` bit-packed and ``action`` as uint8 in the
+    slabs (8x less host->device traffic for both); ``get_batch`` widens them on the device
+    (``mb_unpack_rollout``) so the learner still sees u8 masks and i64 actions.
     """
     specs = buffer_specs(n_envs, T, tuple(obs_size), obs_dtype)
     buffers = RolloutBuffers()
@@ -145,11 +192,21 @@ def create_buffers(n_buffers: int, n_envs: int, B: int, T: int, obs_size: tuple,
         if lean and key in DEAD_KEYS:
             buffers[key] = [DiscardSlot(spec["size"], spec["dtype"]) for _ in range(n_buffers)]
             continue
-        slab = torch.zeros((n_buffers,) + tuple(spec["size"]), dtype=spec["dtype"])
+        size, dtype = tuple(spec["size"]), spec["dtype"]
+        if compact and key == "action_mask":            # bits on the wire, widened on the device
+            size = size[:-1] + ((size[-1] + 7) // 8,)
+        if compact and key == "action":                 # indices < 49 fit a byte
+            dtype = torch.uint8
+        slab = torch.zeros((n_buffers,) + size, dtype=dtype)
         if share:
             slab.share_memory_()
         buffers.slabs[key] = slab
-        buffers[key] = [slab[i] for i in range(n_buffers)]
+        if compact and key == "action_mask":
+            buffers[key] = [PackedMaskSlot(slab[i], spec["size"][-1]) for i in range(n_buffers)]
+        else:
+            buffers[key] = [slab[i] for i in range(n_buffers)]
+    buffers.compact = compact
+    buffers.cells = obs_size[0] * obs_size[1]
     return buffers
 
 
@@ -188,7 +245,7 @@ def get_batch(batch_size: int, shapes: dict, gamma: float, device, free_queue, f
             except queue.Empty:
                 if rb is not None and rb._pending:
                     _recycle(rb, block=True)     # actors may be waiting for buffers whose DMA is pending
-    live = [k for k, v in buffers.items() if isinstance(v[0], torch.Tensor)]
+    live = [k for k, v in buffers.items() if isinstance(v[0], (torch.Tensor, PackedMaskSlot))]
     if keys is not None:
         live = [k for k in live if k in keys]
 
@@ -196,21 +253,30 @@ def get_batch(batch_size: int, shapes: dict, gamma: float, device, free_queue, f
         # host batch (reference semantics: stack dim=1, flatten) -- used by CPU tests and actors
         batch = {}
         for key in live:
-            x = torch.stack([buffers[key][m] for m in indices], dim=1)            # utils.py:197-199
+            slots = [buffers[key][m] for m in indices]
+            slots = [sl.unpacked() if isinstance(sl, PackedMaskSlot) else sl for sl in slots]
+            if key == "action" and slots[0].dtype == torch.uint8:
+                slots = [sl.long() for sl in slots]
+            x = torch.stack(slots, dim=1)                                         # utils.py:197-199
             batch[key] = x.reshape((-1,) + tuple(x.shape[3:]))                    # utils.py:203-205
         for m in indices:
             free_queue.put(m)
         return batch
+
+    def raw(key, m):                 # the tensor actually stored in the slab for slot (key, m)
+        sl = buffers[key][m]
+        return sl.packed if isinstance(sl, PackedMaskSlot) else sl
+
+    def alloc():
+        return {key: torch.empty((raw(key, 0).shape[0], batch_size) + tuple(raw(key, 0).shape[1:]),
+                                 dtype=raw(key, 0).dtype, device=dev) for key in live}
 
     if rb is not None:
         rb.pin()
         _recycle(rb, block=False)
         sets = rb._staging.get((dev, batch_size))
         if sets is None:
-            sets = []
-            for _ in range(2):
-                sets.append({key: torch.empty((buffers[key][0].shape[0], batch_size) + tuple(buffers[key][0].shape[1:]),
-                                              dtype=buffers[key][0].dtype, device=dev) for key in live})
+            sets = [alloc(), alloc()]
             rb._staging[(dev, batch_size)] = sets
             rb._turn[(dev, batch_size)] = 0
             rb._stream[dev] = torch.cuda.Stream(device=dev)
@@ -219,8 +285,7 @@ def get_batch(batch_size: int, shapes: dict, gamma: float, device, free_queue, f
         stage = sets[turn]
         stream = rb._stream[dev]
     else:
-        stage = {key: torch.empty((buffers[key][0].shape[0], batch_size) + tuple(buffers[key][0].shape[1:]),
-                                  dtype=buffers[key][0].dtype, device=dev) for key in live}
+        stage = alloc()
         stream = torch.cuda.Stream(device=dev)
 
     cur = torch.cuda.current_stream(dev)
@@ -229,11 +294,21 @@ def get_batch(batch_size: int, shapes: dict, gamma: float, device, free_queue, f
         for key in live:
             dst = stage[key]
             for j, m in enumerate(indices):
-                dst[:, j].copy_(buffers[key][m], non_blocking=True)
+                dst[:, j].copy_(raw(key, m), non_blocking=True)
+        batch = {key: stage[key].reshape((-1,) + tuple(stage[key].shape[3:])) for key in live}
+        if rb is not None and rb.compact:
+            # widen the wire format on the device: bits -> u8 mask, u8 -> i64 action
+            from . import ops
+            wide = stage.setdefault("_wide", {})
+            n = batch["action"].shape[0]
+            if "mask" not in wide:
+                wide["mask"] = torch.empty((n, rb.cells * 78), dtype=torch.uint8, device=dev)
+                wide["action"] = torch.empty((n, rb.cells * 7), dtype=torch.int64, device=dev)
+            ops.unpack_rollout(batch["action_mask"], batch["action"], rb.cells, wide["mask"], wide["action"])
+            batch["action_mask"], batch["action"] = wide["mask"], wide["action"]
         done = torch.cuda.Event()
         done.record(stream)
     cur.wait_event(done)
-    batch = {key: stage[key].reshape((-1,) + tuple(stage[key].shape[3:])) for key in live}
     if rb is not None:
         rb._pending.append((done, indices, free_queue))
     else:

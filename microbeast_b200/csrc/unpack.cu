@@ -1,0 +1,77 @@
+// Wire-format expansion of the rollout store: the store ships action masks as bits
+// (78*C bits per frame, bit i of byte j = entry 8j+i) and actions as uint8; the policy-head kernels
+// take the reference's dtypes (u8 mask, i64 action: libs/utils.py:43-44), so one streaming kernel
+// widens both on the device.  9.75 + 7 B read and 78 + 56 B written per cell: HBM-bound and small
+// next to the 446 B/cell the head forward reads; the point is the 8x smaller host->device copy.
+#include "common.cuh"
+
+#include "../../include/mbeast.h"
+
+namespace mb {
+
+__global__ void __launch_bounds__(256) unpack_mask_kernel(const uint8_t* __restrict__ bits, uint8_t* __restrict__ mask,
+                                                          long long n_frames, int width, int bytes_per_frame) {
+    const long long total = n_frames * bytes_per_frame;
+    const bool vec = (width % 8 == 0) && ((reinterpret_cast<uintptr_t>(mask) & 7) == 0);
+    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total;
+         i += (long long)gridDim.x * blockDim.x) {
+        const long long f = i / bytes_per_frame;
+        const int j = int(i - f * bytes_per_frame);
+        const uint32_t b = bits[i];
+        uint8_t* out = mask + f * width + 8 * j;
+        if (vec) {
+            uint64_t v = 0;
+#pragma unroll
+            for (int k = 0; k < 8; ++k) v |= uint64_t((b >> k) & 1u) << (8 * k);
+            *reinterpret_cast<uint64_t*>(out) = v;
+        } else {
+            const int cnt = min(8, width - 8 * j);
+            for (int k = 0; k < cnt; ++k) out[k] = uint8_t((b >> k) & 1u);
+        }
+    }
+}
+
+__global__ void __launch_bounds__(256) widen_action_kernel(const uint8_t* __restrict__ a8, int64_t* __restrict__ a64,
+                                                           long long total) {
+    const bool vec = ((reinterpret_cast<uintptr_t>(a8) & 7) == 0) && ((reinterpret_cast<uintptr_t>(a64) & 15) == 0);
+    const long long groups = vec ? total / 8 : 0;
+    const long long tid = blockIdx.x * (long long)blockDim.x + threadIdx.x, stride = (long long)gridDim.x * blockDim.x;
+    for (long long g = tid; g < groups; g += stride) {
+        const uint64_t v = *reinterpret_cast<const uint64_t*>(a8 + 8 * g);
+        longlong2* out = reinterpret_cast<longlong2*>(a64 + 8 * g);
+#pragma unroll
+        for (int k = 0; k < 4; ++k)
+            out[k] = make_longlong2((long long)((v >> (16 * k)) & 0xffu), (long long)((v >> (16 * k + 8)) & 0xffu));
+    }
+    for (long long i = groups * 8 + tid; i < total; i += stride) a64[i] = a8[i];
+}
+
+}  // namespace mb
+
+extern "C" int mb_unpack_rollout(const uint8_t* mask_bits, const uint8_t* action_u8, uint8_t* mask_out,
+                                 int64_t* action_out, int64_t n_frames, int32_t cells, void* stream) {
+    if (n_frames < 0 || cells <= 0) {
+        mb::set_error("mb_unpack_rollout: n_frames=%lld cells=%d out of range", (long long)n_frames, cells);
+        return MB_ERR_INVALID;
+    }
+    if ((mask_bits == nullptr) != (mask_out == nullptr) || (action_u8 == nullptr) != (action_out == nullptr)) {
+        mb::set_error("mb_unpack_rollout: give both pointers of a pair (packed input and output) or neither");
+        return MB_ERR_INVALID;
+    }
+    if (n_frames == 0) return MB_OK;
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    int dev = 0;
+    MB_CUDA(cudaGetDevice(&dev));
+    const int grid = mb::sm_count(dev) * 8;
+    if (mask_bits) {
+        const int width = cells * mb::kLogitsPerCell;
+        mb::unpack_mask_kernel<<<grid, 256, 0, st>>>(mask_bits, mask_out, n_frames, width, (width + 7) / 8);
+        MB_CUDA(cudaGetLastError());
+    }
+    if (action_u8) {
+        mb::widen_action_kernel<<<grid, 256, 0, st>>>(action_u8, action_out,
+                                                      (long long)n_frames * cells * mb::kCompsPerCell);
+        MB_CUDA(cudaGetLastError());
+    }
+    return MB_OK;
+}

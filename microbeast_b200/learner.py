@@ -35,8 +35,17 @@ class _Stager:
         self.buffers = {}
         self.streams = {}
 
+    def _buf(self, name, shape, dtype, device):
+        key = (name, tuple(shape), dtype, device)
+        buf = self.buffers.get(key)
+        if buf is None:
+            buf = self.buffers[key] = torch.empty(tuple(shape), dtype=dtype, device=device)
+        return buf
+
     def stage(self, batch, device, keys):
-        if all(batch[k].is_cuda for k in keys):
+        compact = "action_mask_bits" in batch        # wire format of buffers.pack_batch / compact store
+        keys = [("action_mask_bits" if (k == "action_mask" and compact) else k) for k in keys]
+        if all(batch[k].is_cuda for k in keys) and not compact and batch["action"].dtype == torch.int64:
             return {k: batch[k] for k in keys}, None
         side = self.streams.get(device)
         if side is None:
@@ -49,16 +58,28 @@ class _Stager:
             if t.is_cuda:
                 out[k] = t
                 continue
-            key = (k, tuple(t.shape), t.dtype, device)
-            buf = self.buffers.get(key)
-            if buf is None:
-                buf = self.buffers[key] = torch.empty(t.shape, dtype=t.dtype, device=device)
+            buf = self._buf(k, t.shape, t.dtype, device)
             if k == "obs":
                 buf.copy_(t, non_blocking=True)
             else:
                 with torch.cuda.stream(side):
                     buf.copy_(t, non_blocking=True)
             out[k] = buf
+        if compact or out["action"].dtype == torch.uint8:
+            # widen bit-packed masks / uint8 actions on the side stream, still off the critical path
+            n = out["action"].shape[0]
+            cells = out["action"].shape[1] // 7
+            bits = out.pop("action_mask_bits", None)
+            a8 = out["action"] if out["action"].dtype == torch.uint8 else None
+            with torch.cuda.stream(side):
+                mask, act = ops.unpack_rollout(
+                    bits, a8, cells,
+                    self._buf("wide_mask", (n, cells * 78), torch.uint8, device) if bits is not None else None,
+                    self._buf("wide_action", (n, cells * 7), torch.int64, device) if a8 is not None else None)
+            if bits is not None:
+                out["action_mask"] = mask
+            if a8 is not None:
+                out["action"] = act
         ready = torch.cuda.Event()
         ready.record(side)
         return out, ready

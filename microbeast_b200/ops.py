@@ -209,6 +209,31 @@ def head_sample(logits, mask, uniforms, want_entropy: bool = True):
     return action, logp, ent
 
 
+def unpack_rollout(mask_bits: Optional[torch.Tensor], action_u8: Optional[torch.Tensor], cells: int,
+                   mask_out: Optional[torch.Tensor] = None, action_out: Optional[torch.Tensor] = None):
+    """Device-side expansion of the rollout store's wire format: bit-packed masks
+    ``[N, ceil(78C/8)]`` -> ``[N,78C]`` u8 and uint8 actions ``[N,7C]`` -> i64 (the dtypes of
+    reference ``libs/utils.py:43-44``).  Either input may be ``None``."""
+    dev = _need_cuda(mask_bits=mask_bits, action_u8=action_u8, mask_out=mask_out, action_out=action_out)
+    n = (mask_bits if mask_bits is not None else action_u8).shape[0]
+    if mask_bits is not None:
+        mask_bits = _as(mask_bits, torch.uint8, "mask_bits")
+        if mask_bits.shape[1] != (cells * LOGITS_PER_CELL + 7) // 8:
+            raise ValueError("mask_bits must be [N, ceil(78*cells/8)]")
+        if mask_out is None:
+            mask_out = torch.empty((n, cells * LOGITS_PER_CELL), dtype=torch.uint8, device=dev)
+    if action_u8 is not None:
+        action_u8 = _as(action_u8, torch.uint8, "action_u8")
+        if tuple(action_u8.shape) != (n, cells * COMPONENTS_PER_CELL):
+            raise ValueError("action_u8 must be [N, 7*cells]")
+        if action_out is None:
+            action_out = torch.empty((n, cells * COMPONENTS_PER_CELL), dtype=torch.int64, device=dev)
+    with torch.cuda.device(dev), _Launch("unpack_rollout"):
+        _check(lib.mb_unpack_rollout(_ptr(mask_bits), _ptr(action_u8), _ptr(mask_out if mask_bits is not None else None),
+                                     _ptr(action_out if action_u8 is not None else None), n, cells, _stream()))
+    return mask_out, action_out
+
+
 def vtrace_workspace(device: torch.device, rows: int) -> torch.Tensor:
     """Zero-initialised scratch for ``mb_vtrace_loss`` (cached per device; the kernel keeps
     its ticket word at zero between calls).  Calls on different streams that may overlap

@@ -93,3 +93,31 @@ def test_get_batch_equals_the_reference_implementation():
     assert sorted(got) == sorted(want)
     for key in want:
         assert torch.equal(got[key], want[key]), key
+
+
+def test_compact_store_round_trips_masks_and_actions():
+    """compact=True keeps masks as bits and actions as uint8 in the slabs; slot writes pack on the way
+    in and the host path of get_batch returns exactly what a plain store returns."""
+    from microbeast_b200 import synth
+    n_buffers, n_envs, B, T = 3, 2, 2, 4
+    plain = mbuf.create_buffers(n_buffers, n_envs, B, T, (8, 8, 27), share=False)
+    comp = mbuf.create_buffers(n_buffers, n_envs, B, T, (8, 8, 27), share=False, compact=True)
+    assert comp.slabs["action_mask"].shape[-1] == (78 * 64 + 7) // 8 and comp.slabs["action"].dtype == torch.uint8
+    src = synth.make_rollout_batch(8, 8, T, n_buffers * n_envs, seed=3, obs_dtype=torch.uint8, full_keys=False)
+    for key in ("obs", "action_mask", "action", "reward", "done", "logprobs", "baseline"):
+        x = src[key].view((n_buffers, T + 1, n_envs) + tuple(src[key].shape[1:]))
+        for i in range(n_buffers):
+            for t in range(T + 1):
+                plain[key][i][t, ...] = x[i, t]               # per-step slot writes, microbeast.py:95-100
+                comp[key][i][t, ...] = x[i, t]
+    q = [queue.Queue() for _ in range(4)]
+    for m in (2, 0):
+        q[1].put(m); q[3].put(m)
+    a = mbuf.get_batch(B, {}, 0.99, "cpu", q[0], q[1], plain)
+    b = mbuf.get_batch(B, {}, 0.99, "cpu", q[2], q[3], comp)
+    assert sorted(a) == sorted(b)
+    for key in a:
+        assert torch.equal(a[key], b[key]) and a[key].dtype == b[key].dtype, key
+    packed = mbuf.pack_batch(src)
+    assert packed["action_mask_bits"].shape == (src["action"].shape[0], 624) and packed["action"].dtype == torch.uint8
+    assert torch.equal(mbuf.PackedMaskSlot(packed["action_mask_bits"], 78 * 64).unpacked(), src["action_mask"])

@@ -169,3 +169,52 @@ def test_actor_loop_fills_buffers_that_the_learner_consumes():
     assert all(np.isfinite(four))
     # on-policy data (same weights, slot t+1 holds the action of obs_t: quirk Q8) -> finite, modest ratios
     mbuf.release(bufs)
+
+
+@pytest.mark.parametrize("cells,n", [(64, 33), (256, 5), (9, 7), (100, 3)])
+def test_unpack_rollout_kernel(cells, n):
+    """mb_unpack_rollout: bit-packed masks and uint8 actions widened on the device, bit for bit."""
+    from microbeast_b200 import buffers as mbuf, ops, synth
+    g = torch.Generator().manual_seed(cells)
+    mask = synth.make_masks(n, cells, "all_valid", gen=g) * (torch.rand(n, 78 * cells, generator=g) < 0.4)
+    action = synth.make_valid_actions(mask, gen=g)
+    bits = mbuf.pack_mask(mask)
+    m2, a2 = ops.unpack_rollout(bits.cuda(), action.to(torch.uint8).cuda(), cells)
+    assert torch.equal(m2.cpu(), mask) and torch.equal(a2.cpu(), action)
+    m3, none = ops.unpack_rollout(bits.cuda(), None, cells)
+    assert none is None and torch.equal(m3.cpu(), mask)
+
+
+def test_ppo_learn_accepts_the_compact_wire_format():
+    from microbeast_b200 import buffers as mbuf, synth
+    from microbeast_b200.learner import PPO_learn
+    mine, _ = _pair(8, 8, seed=21)
+    batch = synth.make_rollout_batch(8, 8, 10, 6, seed=8, full_keys=False)
+    batch["logprobs"] = -torch.rand(batch["reward"].shape) * 30
+    a = PPO_learn(mine, mine, "plain", batch, torch.optim.SGD(mine.parameters(), lr=0.0), 3, 10, 2)
+    ga = [p.grad.clone() for p in mine.parameters()]
+    b = PPO_learn(mine, mine, "compact", mbuf.pack_batch(batch), torch.optim.SGD(mine.parameters(), lr=0.0), 3, 10, 2)
+    assert a == b
+    assert all(torch.equal(x, p.grad) for x, p in zip(ga, mine.parameters()))
+
+
+def test_compact_rollout_store_on_device():
+    import queue
+    from microbeast_b200 import buffers as mbuf, synth
+    n_buffers, n_envs, B, T = 4, 2, 2, 6
+    bufs = mbuf.create_buffers(n_buffers, n_envs, B, T, (8, 8, 27), compact=True)
+    src = synth.make_rollout_batch(8, 8, T, n_buffers * n_envs, seed=5, obs_dtype=torch.uint8, full_keys=False)
+    for key in ("obs", "action_mask", "action", "reward", "done", "logprobs", "baseline"):
+        x = src[key].view((n_buffers, T + 1, n_envs) + tuple(src[key].shape[1:]))
+        for i in range(n_buffers):
+            bufs[key][i][...] = x[i]
+    free_q, full_q = queue.Queue(), queue.Queue()
+    for m in (3, 1):
+        full_q.put(m)
+    got = mbuf.get_batch(B, {}, 0.99, torch.device("cuda", 0), free_q, full_q, bufs)
+    assert got["action_mask"].dtype == torch.uint8 and got["action"].dtype == torch.int64
+    for key in ("action_mask", "action", "reward", "obs"):
+        x = src[key].view((n_buffers, T + 1, n_envs) + tuple(src[key].shape[1:]))
+        want = torch.stack([x[3], x[1]], dim=1).reshape((-1,) + tuple(x.shape[3:]))
+        assert torch.equal(got[key].cpu(), want), key
+    mbuf.release(bufs)
