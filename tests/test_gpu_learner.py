@@ -194,8 +194,10 @@ def test_ppo_learn_accepts_the_compact_wire_format():
     a = PPO_learn(mine, mine, "plain", batch, torch.optim.SGD(mine.parameters(), lr=0.0), 3, 10, 2)
     ga = [p.grad.clone() for p in mine.parameters()]
     b = PPO_learn(mine, mine, "compact", mbuf.pack_batch(batch), torch.optim.SGD(mine.parameters(), lr=0.0), 3, 10, 2)
-    assert a == b
-    assert all(torch.equal(x, p.grad) for x, p in zip(ga, mine.parameters()))
+    assert a == b                     # forward path is deterministic: identical losses
+    for x, p in zip(ga, mine.parameters()):          # cuDNN weight gradients are not run-to-run deterministic
+        ok, worst = close_rms(p.grad, x, 1e-4)
+        assert ok, worst
 
 
 def test_compact_rollout_store_on_device():
