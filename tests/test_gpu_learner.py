@@ -220,3 +220,15 @@ def test_compact_rollout_store_on_device():
         want = torch.stack([x[3], x[1]], dim=1).reshape((-1,) + tuple(x.shape[3:]))
         assert torch.equal(got[key].cpu(), want), key
     mbuf.release(bufs)
+
+
+def test_train_driver_runs_actors_and_learner(tmp_path):
+    """train() (microbeast.py:109-264 structure): threads of act() on a synthetic env feed the
+    learner loop; the loss CSV has the reference's columns and one row per update."""
+    from microbeast_b200.train import train
+    name = str(tmp_path / "exp")
+    rows = train(name, n_actors=2, n_envs=2, env_size=8, T=8, B=2, total_steps=3 * 2 * 2 * 8, seed=1)
+    assert len(rows) == 3 and all(len(r) == 6 and np.isfinite(r[1:5]).all() for r in rows)
+    lines = open(name + "Losses.csv").read().strip().splitlines()
+    assert lines[0] == "update,pg_loss,value_loss,entropy_loss,total_loss,update time" and len(lines) == 4
+    assert open(name + ".csv").read().splitlines()[0] == "Return,steps"
