@@ -148,10 +148,11 @@ __global__ void __launch_bounds__(32) vtrace_tma_kernel(const __grid_constant__ 
     uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
 
     const int lane = threadIdx.x;
-    const int row0 = blockIdx.x * kVtRows;
-    const long long row = (long long)row0 + lane;
-    const bool row_ok = row < p.rows;
     const bool want_grads = (p.dlp != nullptr);
+    // persistent: this CTA owns the 32-row groups blockIdx.x, blockIdx.x + gridDim.x, ... and runs
+    // their time tiles as ONE stream through the ring, so the pipeline never drains between groups
+    const int n_groups = int((p.rows + kVtRows - 1) / kVtRows);
+    const int my_groups = (n_groups - int(blockIdx.x) + int(gridDim.x) - 1) / int(gridDim.x);
 
     if (lane == 0) {
         for (int s = 0; s < NSTAGE; ++s) mbar_init(&full[s], 1);
@@ -166,9 +167,14 @@ __global__ void __launch_bounds__(32) vtrace_tma_kernel(const __grid_constant__ 
 
     const int nt = (p.T + TS - 1) / TS;
 
-    auto issue_load = [&](int k) {        // lane 0 only; k counts tiles from the END of the rows
-        const int s = k % NSTAGE;
-        const int t0 = (nt - 1 - k) * TS;
+    const long long total_q = (long long)my_groups * nt;
+    // producer-side cursor (lane 0): tile lq = (group lg, tile lk counted from the END of the rows)
+    long long lq = 0;
+    int lg = 0, lk = 0;
+    auto issue_load = [&]() {             // lane 0 only: loads tile lq and advances the cursor
+        const int s = int(lq % NSTAGE);
+        const int t0 = (nt - 1 - lk) * TS;
+        const int row0 = (int(blockIdx.x) + lg * int(gridDim.x)) * kVtRows;
         uint8_t* st = smem + size_t(s) * kStageBytes;
         mbar_arrive_expect_tx(&full[s], uint32_t(4 * Tile::kF32 + Tile::kU8));
         tma_load_2d(st + 0 * Tile::kF32, &maps.lp_old, t0, row0, &full[s]);
@@ -176,32 +182,56 @@ __global__ void __launch_bounds__(32) vtrace_tma_kernel(const __grid_constant__ 
         tma_load_2d(st + 2 * Tile::kF32, &maps.values, t0, row0, &full[s]);
         tma_load_2d(st + 3 * Tile::kF32, &maps.rewards, t0, row0, &full[s]);
         tma_load_2d(st + 4 * Tile::kF32, &maps.done, t0, row0, &full[s]);
+        ++lq;
+        if (++lk == nt) { lk = 0; ++lg; }
     };
 
     if (lane == 0) {
-        for (int k = 0; k < NSTAGE - 1 && k < nt; ++k) issue_load(k);
+        for (int i = 0; i < NSTAGE - 1 && lq < total_q; ++i) issue_load();
     }
 
     VtCarry carry;
     carry.acc = 0.0f;
-    carry.v_next = row_ok ? __ldg(p.bootstrap + row) : 0.0f;
-    carry.vs_next = carry.v_next;
-    double s_pg = 0.0, s_v = 0.0;
+    carry.v_next = 0.0f;
+    carry.vs_next = 0.0f;
+    double s_pg = 0.0, s_v = 0.0, s_en_d = 0.0;
     float s_en = 0.0f;
     float t_pg = 0.0f, t_v = 0.0f;
+    // bootstrap of the NEXT group is fetched one group ahead so its latency is never exposed
+    float boot_next = 0.0f;
+    {
+        const long long r = (long long)blockIdx.x * kVtRows + lane;
+        if (r < p.rows) boot_next = __ldg(p.bootstrap + r);
+    }
+    int row0 = 0, rows_here = 0;
+    bool row_ok = false;
 
     // entropy: the CTA's [rows_here x T] block is a list of float4 slots (nq per row); lane l owns
     // slots l, l+32, ... and fetches its next kEntSlots of them at the top of every iteration, so
     // the loads fly while the warp waits for / works on the TMA tile and are summed afterwards
     constexpr int kEntSlots = TS / 4;                      // 32*TS floats per iteration per array
-    const int rows_here = int(min((long long)kVtRows, p.rows - row0));
     const int nq = (p.T + 3) >> 2;
     const int tail = p.T - 4 * (nq - 1);                   // valid floats in a row's last slot (1..4)
-    int ent_r = 0, ent_c = lane;                           // (row, slot) of this lane's next slot
-    while (ent_c >= nq) { ent_c -= nq; ++ent_r; }
+    int ent_r = 0, ent_c = 0;                              // (row, slot) of this lane's next slot
 
-    for (int k = 0; k < nt; ++k) {
-        const int s = k % NSTAGE;
+    int k = 0, g = 0;                                      // consumer-side cursor: tile k of group g
+    for (long long q = 0; q < total_q; ++q) {
+        const int s = int(q % NSTAGE);
+        if (k == 0) {                                      // a new group of 32 rows starts
+            row0 = (int(blockIdx.x) + g * int(gridDim.x)) * kVtRows;
+            rows_here = int(min((long long)kVtRows, p.rows - row0));
+            row_ok = lane < rows_here;
+            carry.acc = 0.0f;                              // utils.py:300
+            carry.v_next = boot_next;                      // utils.py:296: V_T = bootstrap
+            carry.vs_next = boot_next;                     // utils.py:313-314
+            const long long rn = (long long)(row0 + int(gridDim.x) * kVtRows) + lane;
+            boot_next = (g + 1 < my_groups && rn < p.rows) ? __ldg(p.bootstrap + rn) : 0.0f;
+            ent_r = 0;
+            ent_c = lane;
+            while (ent_c >= nq) { ent_c -= nq; ++ent_r; }
+            s_en_d += double(s_en);
+            s_en = 0.0f;
+        }
         float4 ebuf[kEntSlots];
 #pragma unroll
         for (int i = 0; i < kEntSlots; ++i) {
@@ -219,7 +249,7 @@ __global__ void __launch_bounds__(32) vtrace_tma_kernel(const __grid_constant__ 
             ent_c += 32;
             while (ent_c >= nq) { ent_c -= nq; ++ent_r; }
         }
-        mbar_wait(&full[s], uint32_t((k / NSTAGE) & 1), nullptr);
+        mbar_wait(&full[s], uint32_t((q / NSTAGE) & 1), nullptr);
 
         uint8_t* st = smem + size_t(s) * kStageBytes;
         const int t0 = (nt - 1 - k) * TS;
@@ -228,7 +258,7 @@ __global__ void __launch_bounds__(32) vtrace_tma_kernel(const __grid_constant__ 
         uint8_t* q_val = st + 2 * Tile::kF32;
         uint8_t* q_rew = st + 3 * Tile::kF32;
         const uint8_t* q_dn = st + 4 * Tile::kF32;
-        // only the first tile handled (the END of the rows) can reach past T; rows past R only in the last CTA
+        // only the first tile of a group (the END of its rows) can reach past T; rows past R only in the last group
         const bool guard = (k == 0) || !row_ok;
 #pragma unroll
         for (int j = Tile::kChunks - 1; j >= 0; --j) {
@@ -286,18 +316,19 @@ __global__ void __launch_bounds__(32) vtrace_tma_kernel(const __grid_constant__ 
                 tma_store_2d(&maps.dv, t0, row0, q_val);
             }
             bulk_commit();
-            if (k + NSTAGE - 1 < nt) {
-                // tile k+NSTAGE-1 goes into the stage tile k-1 was stored from; its store group was
+            if (lq < total_q) {
+                // tile q+NSTAGE-1 goes into the stage tile q-1 was stored from; its store group was
                 // committed one iteration ago, so this wait normally returns at once
-                if (k >= 1) bulk_wait_read<1>();
-                issue_load(k + NSTAGE - 1);
+                if (q >= 1) bulk_wait_read<1>();
+                issue_load();
             }
         }
+        if (++k == nt) { k = 0; ++g; }
     }
 
     s_pg = warp_sum(s_pg);
     s_v = warp_sum(s_v);
-    const double s_en_w = warp_sum(double(s_en));
+    const double s_en_w = warp_sum(s_en_d + double(s_en));
     unsigned int tk = 0;
     if (lane == 0) {
         bulk_wait_all<0>();     // output tiles are in global memory before the CTA retires
@@ -478,7 +509,15 @@ static int launch_vt_tma(const VtMaps& maps, const VtParams& p, cudaStream_t str
                                      int(smem)));
         attr_set[dev] = true;
     }
-    const unsigned grid = unsigned((p.rows + kVtRows - 1) / kVtRows);
+    static int per_sm[64] = {};
+    if (dev < 64 && per_sm[dev] == 0) {
+        int n = 0;
+        MB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, vtrace_tma_kernel<NSTAGE, TS>, 32, smem));
+        per_sm[dev] = n > 0 ? n : 1;
+    }
+    const long long groups = (p.rows + kVtRows - 1) / kVtRows;
+    const long long resident = (long long)sm_count(dev) * (dev < 64 ? per_sm[dev] : 1);
+    const unsigned grid = unsigned(groups < resident ? groups : resident);
     vtrace_tma_kernel<NSTAGE, TS><<<grid, 32, smem, stream>>>(maps, p);
     MB_CUDA(cudaGetLastError());
     return MB_OK;

@@ -95,8 +95,8 @@ def test_pipeline_shapes_agree(variant):
         mb.set_tuning("vtrace_variant", -1)
     for k in ("vs", "pg_advantages", "d_logp", "d_values"):
         assert torch.equal(base[k], out[k]), k
-    assert torch.equal(base["loss4"][:2], out["loss4"][:2])
-    assert torch.allclose(base["loss4"], out["loss4"], rtol=1e-6, atol=0)     # entropy mean: other sum order
+    # loss sums: the persistent grid (CTAs per SM) depends on the shape, so the fp64 fold order does too
+    assert torch.allclose(base["loss4"], out["loss4"], rtol=1e-6, atol=0)
     mb.set_tuning("vtrace_l2_promo", 128)
     try:
         out = _run(ops, t)
@@ -104,6 +104,19 @@ def test_pipeline_shapes_agree(variant):
         mb.set_tuning("vtrace_l2_promo", 256)
     for k in ("vs", "pg_advantages", "d_logp", "d_values", "loss4"):
         assert torch.equal(base[k], out[k]), k
+
+
+def test_persistent_groups_more_rows_than_resident_ctas():
+    """More 32-row groups than resident CTAs: every CTA walks several groups through one pipeline."""
+    _, ops, synth, ovt = _mods()
+    g = torch.Generator().manual_seed(9)
+    rows, T = 32 * 1500 + 5, 48
+    t = synth.make_vtrace_inputs(rows, T, gen=g)
+    t["done"] = torch.rand((rows, T), generator=g) < 0.05
+    ref = ovt.vtrace_losses_and_grads(t["lp_old"], t["lp_new"], t["values"], t["bootstrap"], t["rewards"],
+                                      t["done"], t["entropy"])
+    ref["lp_new_in"] = t["lp_new"]
+    _compare(_run(ops, t), ref)
 
 
 def test_non_default_constants_and_global_normalisation():
