@@ -374,24 +374,25 @@ __device__ __forceinline__ void b_role_cell(bool active, int half, float* zc, co
         const float t = u * S;
         const float guard = sample_guard(S, W, LEN);
         const float start = has_x ? 0.f : S_other;     // even lane's 25 entries come first
-        bool near = false;
-        int cnt = 0;
-        if (has_x) {
-            cnt = (t >= ex) ? 1 : 0;
-            near = fabsf(t - ex) <= guard;
-        }
-        const float base[4] = {start + ex, start + own1, start + own2, start + own3};
+        // Two-level count.  The running CDF is monotone, so every edge of a block that ends at or
+        // below t is counted and none of a block that starts above t; only the block that straddles
+        // t is scanned entry by entry (its six entries are picked out of the register array with
+        // selects), and an edge can be within `guard` of t only if it is in that block or is one of
+        // its two boundaries.
+        const float base[5] = {start + ex, start + own1, start + own2, start + own3, start + S_own};
+        const int bsel = ((t >= base[1]) ? 1 : 0) + ((t >= base[2]) ? 1 : 0) + ((t >= base[3]) ? 1 : 0);
+        float c = (bsel & 2) ? ((bsel & 1) ? base[3] : base[2]) : ((bsel & 1) ? base[1] : base[0]);
+        int cnt = 6 * bsel + ((has_x && t >= ex) ? 1 : 0);
+        bool near = fabsf(t - c) <= guard;
 #pragma unroll
-        for (int b = 0; b < 4; ++b) {
-            float c = base[b];
-#pragma unroll
-            for (int i = 0; i < 6; ++i) {
-                c += e[6 * b + i];
-                // entry 48 (k = n-1: the odd lane's last one) is not an edge of the count
-                const bool edge = has_x || (6 * b + i < 23);
-                cnt += (edge && t >= c) ? 1 : 0;
-                near = near || (edge && fabsf(t - c) <= guard);
-            }
+        for (int i = 0; i < 6; ++i) {
+            const float lo = (bsel & 1) ? e[6 + i] : e[i];
+            const float hi = (bsel & 1) ? e[18 + i] : e[12 + i];
+            c += (bsel & 2) ? hi : lo;
+            // entry 48 (k = n-1: the odd lane's last one) is not an edge of the count
+            const bool edge = has_x || i < 5 || bsel < 3;
+            cnt += (edge && t >= c) ? 1 : 0;
+            near = near || (edge && fabsf(t - c) <= guard);
         }
         cnt += __shfl_xor_sync(0xffffffffu, cnt, 1);
         near = (__shfl_xor_sync(0xffffffffu, int(near), 1) != 0) || near;
