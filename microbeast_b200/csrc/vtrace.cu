@@ -139,23 +139,30 @@ struct VtTile {
 };
 
 template <int NSTAGE, int TS>
-__global__ void __launch_bounds__(32) vtrace_tma_kernel(const __grid_constant__ VtMaps maps, const VtParams p) {
+__global__ void __launch_bounds__(64) vtrace_tma_kernel(const __grid_constant__ VtMaps maps, const VtParams p) {
     using Tile = VtTile<TS>;
     constexpr int kStageBytes = Tile::kStage;              // multiple of 1024
     extern __shared__ uint8_t smem_raw[];
-    __shared__ __align__(8) uint64_t full[NSTAGE];
+    __shared__ __align__(8) uint64_t full[NSTAGE];     // TMA loads of a stage have landed
+    __shared__ __align__(8) uint64_t done[NSTAGE];     // the compute warp has overwritten the stage with outputs
     // swizzled tiles need 1024-B alignment
     uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
 
-    const int lane = threadIdx.x;
+    // warp 0 computes (one thread per row); warp 1 is the TMA warp: its lane 0 issues every load and
+    // store, so descriptor issue, store drain and refill never sit on the compute warp's critical path
+    const int lane = threadIdx.x & 31;
+    const int warp = threadIdx.x >> 5;
     const bool want_grads = (p.dlp != nullptr);
     // persistent: this CTA owns the 32-row groups blockIdx.x, blockIdx.x + gridDim.x, ... and runs
     // their time tiles as ONE stream through the ring, so the pipeline never drains between groups
     const int n_groups = int((p.rows + kVtRows - 1) / kVtRows);
     const int my_groups = (n_groups - int(blockIdx.x) + int(gridDim.x) - 1) / int(gridDim.x);
 
-    if (lane == 0) {
-        for (int s = 0; s < NSTAGE; ++s) mbar_init(&full[s], 1);
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < NSTAGE; ++s) {
+            mbar_init(&full[s], 1);
+            mbar_init(&done[s], 1);
+        }
         fence_mbar_init();
         tma_prefetch_desc(&maps.lp_old);
         tma_prefetch_desc(&maps.lp_new);
@@ -163,7 +170,7 @@ __global__ void __launch_bounds__(32) vtrace_tma_kernel(const __grid_constant__ 
         tma_prefetch_desc(&maps.rewards);
         tma_prefetch_desc(&maps.done);
     }
-    __syncwarp();
+    __syncthreads();
 
     const int nt = (p.T + TS - 1) / TS;
 
@@ -186,9 +193,37 @@ __global__ void __launch_bounds__(32) vtrace_tma_kernel(const __grid_constant__ 
         if (++lk == nt) { lk = 0; ++lg; }
     };
 
-    if (lane == 0) {
-        for (int i = 0; i < NSTAGE - 1 && lq < total_q; ++i) issue_load();
+    if (warp == 1) {
+        // ===================== TMA warp =====================
+        if (lane == 0) {
+            for (int i = 0; i < NSTAGE && lq < total_q; ++i) issue_load();
+            int sg = 0, sk = 0;                            // store cursor: tile sk of group sg
+            for (long long q = 0; q < total_q; ++q) {
+                const int s = int(q % NSTAGE);
+                mbar_wait(&done[s], uint32_t((q / NSTAGE) & 1), nullptr);
+                uint8_t* st = smem + size_t(s) * kStageBytes;
+                const int t0 = (nt - 1 - sk) * TS;
+                const int row0 = (int(blockIdx.x) + sg * int(gridDim.x)) * kVtRows;
+                // in place: vs over rewards, adv over lp_old, d_logp over lp_new, d_values over values
+                tma_store_2d(&maps.vs, t0, row0, st + 3 * Tile::kF32);
+                tma_store_2d(&maps.adv, t0, row0, st + 0 * Tile::kF32);
+                if (want_grads) {
+                    tma_store_2d(&maps.dlp, t0, row0, st + 1 * Tile::kF32);
+                    tma_store_2d(&maps.dv, t0, row0, st + 2 * Tile::kF32);
+                }
+                bulk_commit();
+                if (q >= 1 && lq < total_q) {
+                    // tile q-1+NSTAGE goes into the stage tile q-1 was stored from one iteration ago
+                    bulk_wait_read<1>();
+                    issue_load();
+                }
+                if (++sk == nt) { sk = 0; ++sg; }
+            }
+            bulk_wait_all<0>();     // output tiles are in global memory before the CTA retires
+        }
+        return;
     }
+    // ===================== compute warp =====================
 
     VtCarry carry;
     carry.acc = 0.0f;
@@ -306,23 +341,9 @@ __global__ void __launch_bounds__(32) vtrace_tma_kernel(const __grid_constant__ 
 #pragma unroll
         for (int i = 0; i < kEntSlots; ++i) s_en += (ebuf[i].x + ebuf[i].y) + (ebuf[i].z + ebuf[i].w);
 
-        fence_proxy_async_smem();
+        fence_proxy_async_smem();       // generic-proxy writes -> visible to the TMA store
         __syncwarp();
-        if (lane == 0) {
-            tma_store_2d(&maps.vs, t0, row0, q_rew);
-            tma_store_2d(&maps.adv, t0, row0, q_old);
-            if (want_grads) {
-                tma_store_2d(&maps.dlp, t0, row0, q_new);
-                tma_store_2d(&maps.dv, t0, row0, q_val);
-            }
-            bulk_commit();
-            if (lq < total_q) {
-                // tile q+NSTAGE-1 goes into the stage tile q-1 was stored from; its store group was
-                // committed one iteration ago, so this wait normally returns at once
-                if (q >= 1) bulk_wait_read<1>();
-                issue_load();
-            }
-        }
+        if (lane == 0) mbar_arrive(&done[s]);
         if (++k == nt) { k = 0; ++g; }
     }
 
@@ -331,7 +352,6 @@ __global__ void __launch_bounds__(32) vtrace_tma_kernel(const __grid_constant__ 
     const double s_en_w = warp_sum(s_en_d + double(s_en));
     unsigned int tk = 0;
     if (lane == 0) {
-        bulk_wait_all<0>();     // output tiles are in global memory before the CTA retires
         p.partials[size_t(blockIdx.x) * 3 + 0] = s_pg;
         p.partials[size_t(blockIdx.x) * 3 + 1] = s_v;
         p.partials[size_t(blockIdx.x) * 3 + 2] = s_en_w;
@@ -512,13 +532,13 @@ static int launch_vt_tma(const VtMaps& maps, const VtParams& p, cudaStream_t str
     static int per_sm[64] = {};
     if (dev < 64 && per_sm[dev] == 0) {
         int n = 0;
-        MB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, vtrace_tma_kernel<NSTAGE, TS>, 32, smem));
+        MB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, vtrace_tma_kernel<NSTAGE, TS>, 64, smem));
         per_sm[dev] = n > 0 ? n : 1;
     }
     const long long groups = (p.rows + kVtRows - 1) / kVtRows;
     const long long resident = (long long)sm_count(dev) * (dev < 64 ? per_sm[dev] : 1);
     const unsigned grid = unsigned(groups < resident ? groups : resident);
-    vtrace_tma_kernel<NSTAGE, TS><<<grid, 32, smem, stream>>>(maps, p);
+    vtrace_tma_kernel<NSTAGE, TS><<<grid, 64, smem, stream>>>(maps, p);
     MB_CUDA(cudaGetLastError());
     return MB_OK;
 }
