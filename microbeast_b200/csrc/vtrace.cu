@@ -26,6 +26,7 @@
 #include <string.h>
 
 #include <mutex>
+#include <type_traits>
 
 namespace mb {
 
@@ -277,7 +278,11 @@ __global__ void __launch_bounds__(64) vtrace_tma_kernel(const __grid_constant__ 
                 if (ent_c == nq - 1 && tail < 4) {         // never read past T in a row's last slot
                     v = make_float4(__ldg(src), tail > 1 ? __ldg(src + 1) : 0.f, tail > 2 ? __ldg(src + 2) : 0.f, 0.f);
                 } else {
-                    v = __ldg(reinterpret_cast<const float4*>(src));
+                    // volatile asm: stays ahead of the mbarrier wait below (the compiler would otherwise
+                    // sink the load to its use after the tile and expose its latency there)
+                    asm volatile("ld.global.nc.v4.f32 {%0, %1, %2, %3}, [%4];"
+                                 : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w)
+                                 : "l"(src));
                 }
                 ebuf[i] = v;
             }
@@ -293,44 +298,51 @@ __global__ void __launch_bounds__(64) vtrace_tma_kernel(const __grid_constant__ 
         uint8_t* q_val = st + 2 * Tile::kF32;
         uint8_t* q_rew = st + 3 * Tile::kF32;
         const uint8_t* q_dn = st + 4 * Tile::kF32;
-        // only the first tile of a group (the END of its rows) can reach past T; rows past R only in the last group
-        const bool guard = (k == 0) || !row_ok;
+        // Only the first tile of a group (the END of its rows) can reach past T, and rows past R exist
+        // only in the last group: every other tile runs the body without any range checks.
+        auto tile_body = [&](auto guard_tag) {
+            constexpr bool kGuard = decltype(guard_tag)::value;
 #pragma unroll
-        for (int j = Tile::kChunks - 1; j >= 0; --j) {
-            const uint32_t off = Tile::off(lane, j);
-            const float4 a_old = *reinterpret_cast<const float4*>(q_old + off);
-            const float4 a_new = *reinterpret_cast<const float4*>(q_new + off);
-            const float4 a_val = *reinterpret_cast<const float4*>(q_val + off);
-            const float4 a_rew = *reinterpret_cast<const float4*>(q_rew + off);
-            const uint32_t dn = *reinterpret_cast<const uint32_t*>(q_dn + lane * TS + j * 4);
-            const float lo[4] = {a_old.x, a_old.y, a_old.z, a_old.w};
-            const float ln[4] = {a_new.x, a_new.y, a_new.z, a_new.w};
-            const float vv[4] = {a_val.x, a_val.y, a_val.z, a_val.w};
-            const float rw[4] = {a_rew.x, a_rew.y, a_rew.z, a_rew.w};
-            float o_vs[4], o_adv[4], o_dlp[4], o_dv[4], re[4];
+            for (int j = Tile::kChunks - 1; j >= 0; --j) {
+                const uint32_t off = Tile::off(lane, j);
+                const float4 a_old = *reinterpret_cast<const float4*>(q_old + off);
+                const float4 a_new = *reinterpret_cast<const float4*>(q_new + off);
+                const float4 a_val = *reinterpret_cast<const float4*>(q_val + off);
+                const float4 a_rew = *reinterpret_cast<const float4*>(q_rew + off);
+                const uint32_t dn = *reinterpret_cast<const uint32_t*>(q_dn + lane * TS + j * 4);
+                const float lo[4] = {a_old.x, a_old.y, a_old.z, a_old.w};
+                const float ln[4] = {a_new.x, a_new.y, a_new.z, a_new.w};
+                const float vv[4] = {a_val.x, a_val.y, a_val.z, a_val.w};
+                const float rw[4] = {a_rew.x, a_rew.y, a_rew.z, a_rew.w};
+                float o_vs[4], o_adv[4], o_dlp[4], o_dv[4], re[4];
 #pragma unroll
-            for (int i = 0; i < 4; ++i) re[i] = vt_ratio_exp(lo[i], ln[i]);
+                for (int i = 0; i < 4; ++i) re[i] = vt_ratio_exp(lo[i], ln[i]);
 #pragma unroll
-            for (int i = 3; i >= 0; --i) {
-                const bool ok = !guard || (row_ok && (t0 + 4 * j + i < p.T));
-                const bool dflag = ((dn >> (8 * i)) & 0xffu) != 0;
-                const VtStepOut o = vt_step(p, re[i], vv[i], rw[i], dflag, ok, carry);
-                const float dvs = __fsub_rn(o.vs, vv[i]);
-                o_vs[i] = o.vs;                 // out-of-range rows / steps are clipped by the TMA store
-                o_adv[i] = o.adv;
-                o_dlp[i] = o.adv * p.inv_n;
-                o_dv[i] = -dvs * p.inv_n;
-                t_pg = __fadd_rn(t_pg, ok ? __fmul_rn(ln[i], o.adv) : 0.0f);
-                t_v = __fadd_rn(t_v, ok ? __fmul_rn(dvs, dvs) : 0.0f);
+                for (int i = 3; i >= 0; --i) {
+                    const bool ok = !kGuard || (row_ok && (t0 + 4 * j + i < p.T));
+                    const bool dflag = ((dn >> (8 * i)) & 0xffu) != 0;
+                    const VtStepOut o = vt_step(p, re[i], vv[i], rw[i], dflag, ok, carry);
+                    const float dvs = __fsub_rn(o.vs, vv[i]);
+                    o_vs[i] = o.vs;             // out-of-range rows / steps are clipped by the TMA store
+                    o_adv[i] = o.adv;
+                    o_dlp[i] = o.adv * p.inv_n;
+                    o_dv[i] = -dvs * p.inv_n;
+                    t_pg = __fadd_rn(t_pg, ok ? __fmul_rn(ln[i], o.adv) : 0.0f);
+                    t_v = __fadd_rn(t_v, ok ? __fmul_rn(dvs, dvs) : 0.0f);
+                }
+                // in place: vs over rewards, adv over lp_old, d_logp over lp_new, d_values over values
+                *reinterpret_cast<float4*>(q_rew + off) = make_float4(o_vs[0], o_vs[1], o_vs[2], o_vs[3]);
+                *reinterpret_cast<float4*>(q_old + off) = make_float4(o_adv[0], o_adv[1], o_adv[2], o_adv[3]);
+                if (want_grads) {
+                    *reinterpret_cast<float4*>(q_new + off) = make_float4(o_dlp[0], o_dlp[1], o_dlp[2], o_dlp[3]);
+                    *reinterpret_cast<float4*>(q_val + off) = make_float4(o_dv[0], o_dv[1], o_dv[2], o_dv[3]);
+                }
             }
-            // in place: vs over rewards, adv over lp_old, d_logp over lp_new, d_values over values
-            *reinterpret_cast<float4*>(q_rew + off) = make_float4(o_vs[0], o_vs[1], o_vs[2], o_vs[3]);
-            *reinterpret_cast<float4*>(q_old + off) = make_float4(o_adv[0], o_adv[1], o_adv[2], o_adv[3]);
-            if (want_grads) {
-                *reinterpret_cast<float4*>(q_new + off) = make_float4(o_dlp[0], o_dlp[1], o_dlp[2], o_dlp[3]);
-                *reinterpret_cast<float4*>(q_val + off) = make_float4(o_dv[0], o_dv[1], o_dv[2], o_dv[3]);
-            }
-        }
+        };
+        if ((k == 0) || !row_ok)
+            tile_body(std::true_type{});
+        else
+            tile_body(std::false_type{});
         // the pg / value sums are folded into fp64 once per 32 steps (same grouping as the generic kernel)
         if (TS == 32 || ((nt - 1 - k) & 1) == 0) {
             s_pg += double(t_pg);
