@@ -59,6 +59,8 @@ def parse_args():
     ap.add_argument("--cpu-rows", type=int, default=32, help="rows of the CPU-baseline sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--tf32-info", action="store_true",
+                    help="also time the step with TF32 allowed in the PyTorch encoder (reported under info)")
     ap.add_argument("--wire", default="compact", choices=["compact", "plain"],
                     help="host batch format of the e2e leg (compact = the rollout store's wire format)")
     ap.add_argument("--sweep", default="", choices=["", "vtrace", "head", "variants"])
@@ -304,7 +306,7 @@ def run_ours(args):
         from microbeast_b200 import buffers as mbuf
         wire = {k: v.cpu() for k, v in dev_batch.items()}
         if args.wire == "compact":
-            wire = mbuf.pack_batch(wire)        # rollout-store wire format: mask bits, u8 actions, u8 obs
+            wire = mbuf.pack_batch(wire)        # rollout-store wire format: bit-packed obs / masks, u8 actions
         host = {k: torch.empty(v.shape, dtype=v.dtype, pin_memory=True).copy_(v) for k, v in wire.items()}
         h2d = sum(v.numel() * v.element_size() for v in host.values())
         e2e_steps = max(3, min(args.steps, 10))
@@ -312,10 +314,23 @@ def run_ours(args):
         e2e = {"value": frames / (ms_e2e * 1e-3), "unit": UNIT, "h2d_bytes_per_step": h2d * world,
                "d2h_bytes_per_step": 16 * world, "ms_per_step": ms_e2e, "steps": e2e_steps,
                "call": "microbeast_b200.learner.PPO_learn(model, model, name, pinned_host_batch, adam, rows, T, 1)",
-               "wire_format": ("obs u8, action_mask bit-packed, action u8 (widened on the device by "
-                               "mb_unpack_rollout), reward/logprobs f32, done bool") if args.wire == "compact"
+               "wire_format": ("obs one int32 per cell (27 binary planes), action_mask bit-packed, action u8 -- widened "
+                               "on the device by mb_unpack_obs / mb_unpack_rollout; reward/logprobs f32, done bool") if args.wire == "compact"
                else "obs u8, action_mask u8, action i64, reward/logprobs f32, done bool"}
         del host
+
+    # ---- informational only: the same step with PyTorch's TF32 convolutions / matmuls allowed ----
+    # (the encoder is PyTorch's; `value` above keeps it in strict fp32 so that "dtype": "f32" holds)
+    info = None
+    if args.tf32_info:
+        torch.backends.cudnn.allow_tf32 = True
+        torch.backends.cuda.matmul.allow_tf32 = True
+        ms_tf32, _, _, _ = timed(lambda: step(dev_batch, False), max(3, min(args.steps, 5)), 3)
+        torch.backends.cudnn.allow_tf32 = False
+        torch.backends.cuda.matmul.allow_tf32 = False
+        info = {"encoder_tf32": {"value": frames / (ms_tf32 * 1e-3), "unit": UNIT, "ms_per_step": ms_tf32,
+                                 "note": "not the headline: TF32 tensor-core math in the PyTorch encoder only; "
+                                         "the policy-head and V-trace kernels are unchanged (fp32)"}}
 
     # ---- cpu baseline (rank 0, N=1) ------------------------------------------------------
     cpu = None
@@ -332,7 +347,7 @@ def run_ours(args):
             "warmup": max(args.warmup, 3), "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "f32", "data": "synthetic", "config": workload_config(args),
             "clocks": clocks, "e2e": e2e, "gpu_launches": launches, "roofline": roof, "cpu_baseline": cpu,
-            "kernels": kernels,
+            "kernels": kernels, "info": info,
         }
         emit(line, args)
     if world > 1:

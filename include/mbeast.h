@@ -131,6 +131,13 @@ MB_API int mb_vtrace_loss_static(const float* lp_old, const float* lp_new, const
 MB_API int mb_unpack_rollout(const uint8_t* mask_bits, const uint8_t* action_u8, uint8_t* mask_out,
                              int64_t* action_out, int64_t n_frames, int32_t cells, void* stream);
 
+/* Observation planes on the wire (no reference counterpart; replaces the float cast of reference
+ * env_packer.py:8-10 and the permute of model.py:156-160 after a 27x smaller copy than float32):
+ *   obs_bits [n_frames, cells] u32, bit c = feature plane c of the cell (planes are 0/1)
+ *        ->  obs_out [n_frames, planes, cells] f32, i.e. NCHW with cells = h*w. */
+MB_API int mb_unpack_obs(const uint32_t* obs_bits, float* obs_out, int64_t n_frames, int32_t cells,
+                         int32_t planes, void* stream);
+
 /* Tuning knobs for benchmarking (not part of the reference surface).  Keys:
  *   "head_ctas_per_sm" (0 = as many as fit), "head_grid" (0 = auto), "head_variant" (tile /
  *   pipeline shape: 0 = 64 cells x 3 stages, 1 = 64x2, 2 = 64x4, 3 = 32x3, 4 = 32x5, 5 = 128x3, 6 = 128x2, 7 = 32x2; -1 = per-kernel default),

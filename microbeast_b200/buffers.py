@@ -83,14 +83,30 @@ def pack_mask(mask: torch.Tensor) -> torch.Tensor:
     return torch.from_numpy(np.packbits(arr, axis=-1, bitorder="little"))
 
 
+def pack_obs(obs: torch.Tensor) -> torch.Tensor:
+    """``[..., P]`` 0/1 feature planes (P <= 32) -> ``[...]`` int32 with bit c = plane c (host side)."""
+    import numpy as np
+    arr = (obs.cpu().numpy() != 0)
+    weights = (np.uint32(1) << np.arange(arr.shape[-1], dtype=np.uint32))
+    return torch.from_numpy((arr * weights).sum(axis=-1, dtype=np.uint32).astype(np.int32))
+
+
+def unpack_obs_host(bits: torch.Tensor, planes: int = 27) -> torch.Tensor:
+    """Inverse of :func:`pack_obs` on the host (uint8 planes); the device path is ``ops.unpack_obs``."""
+    import numpy as np
+    b = bits.numpy().astype(np.uint32)[..., None]
+    return torch.from_numpy(((b >> np.arange(planes, dtype=np.uint32)) & 1).astype(np.uint8))
+
+
 def pack_batch(batch: dict) -> dict:
     """Reference-format host batch -> the compact wire format ``PPO_learn`` also accepts:
     ``action_mask`` becomes ``action_mask_bits`` (8x smaller) and ``action`` uint8 (8x smaller;
-    indices are < 49).  ``obs`` becomes uint8 (planes are 0/1)."""
+    indices are < 49).  ``obs`` becomes one int32 per cell (the 27 planes are 0/1: 27x smaller than
+    the reference's float32)."""
     out = {k: v for k, v in batch.items() if k not in ("action_mask", "action", "obs")}
     out["action_mask_bits"] = pack_mask(batch["action_mask"])
     out["action"] = batch["action"].to(torch.uint8)
-    out["obs"] = batch["obs"].to(torch.uint8)
+    out["obs"] = pack_obs(batch["obs"])      # one int32 per cell; widened to NCHW fp32 on the device
     return out
 
 
@@ -116,6 +132,26 @@ class PackedMaskSlot:
         import numpy as np
         bits = np.unpackbits(self.packed.numpy(), axis=-1, bitorder="little")[..., :self.width]
         return torch.from_numpy(bits)
+
+
+class PackedObsSlot:
+    """Rollout-buffer slot that keeps observations as one int32 per cell (bit c = plane c)."""
+
+    def __init__(self, packed: torch.Tensor, planes: int):
+        self.packed = packed               # [T+1, n_envs, h, w] int32 view of the slab
+        self.planes = planes
+        self.shape = torch.Size(tuple(packed.shape) + (planes,))
+        self.dtype = torch.uint8
+
+    def size(self):
+        return self.shape
+
+    def __setitem__(self, index, value):
+        value = torch.as_tensor(value)
+        self.packed[index] = pack_obs(value).reshape(self.packed[index].shape)
+
+    def unpacked(self) -> torch.Tensor:
+        return unpack_obs_host(self.packed, self.planes)
 
 
 class RolloutBuffers(dict):
@@ -181,9 +217,10 @@ def create_buffers(n_buffers: int, n_envs: int, B: int, T: int, obs_size: tuple,
     ``libs/utils.py:29-55``, same positional signature and the same 11 keys.
 
     ``lean=False, obs_dtype=torch.float32`` reproduces the reference layout exactly.
-    ``compact=True`` additionally keeps ``action_mask`` bit-packed and ``action`` as uint8 in the
-    slabs (8x less host->device traffic for both); ``get_batch`` widens them on the device
-    (``mb_unpack_rollout``) so the learner still sees u8 masks and i64 actions.
+    ``compact=True`` additionally keeps ``action_mask`` bit-packed, ``action`` as uint8 and ``obs``
+    as one int32 per cell in the slabs; ``get_batch`` widens masks and actions on the device
+    (``mb_unpack_rollout``) so the learner still sees u8 masks and i64 actions, and hands the
+    packed observations to ``Agent``, which expands them straight to NCHW fp32 (``mb_unpack_obs``).
     """
     specs = buffer_specs(n_envs, T, tuple(obs_size), obs_dtype)
     buffers = RolloutBuffers()
@@ -197,12 +234,16 @@ def create_buffers(n_buffers: int, n_envs: int, B: int, T: int, obs_size: tuple,
             size = size[:-1] + ((size[-1] + 7) // 8,)
         if compact and key == "action":                 # indices < 49 fit a byte
             dtype = torch.uint8
+        if compact and key == "obs":                    # 27 binary planes -> one int32 per cell
+            size, dtype = size[:-1], torch.int32
         slab = torch.zeros((n_buffers,) + size, dtype=dtype)
         if share:
             slab.share_memory_()
         buffers.slabs[key] = slab
         if compact and key == "action_mask":
             buffers[key] = [PackedMaskSlot(slab[i], spec["size"][-1]) for i in range(n_buffers)]
+        elif compact and key == "obs":
+            buffers[key] = [PackedObsSlot(slab[i], spec["size"][-1]) for i in range(n_buffers)]
         else:
             buffers[key] = [slab[i] for i in range(n_buffers)]
     buffers.compact = compact
@@ -245,7 +286,7 @@ def get_batch(batch_size: int, shapes: dict, gamma: float, device, free_queue, f
             except queue.Empty:
                 if rb is not None and rb._pending:
                     _recycle(rb, block=True)     # actors may be waiting for buffers whose DMA is pending
-    live = [k for k, v in buffers.items() if isinstance(v[0], (torch.Tensor, PackedMaskSlot))]
+    live = [k for k, v in buffers.items() if isinstance(v[0], (torch.Tensor, PackedMaskSlot, PackedObsSlot))]
     if keys is not None:
         live = [k for k in live if k in keys]
 
@@ -254,7 +295,7 @@ def get_batch(batch_size: int, shapes: dict, gamma: float, device, free_queue, f
         batch = {}
         for key in live:
             slots = [buffers[key][m] for m in indices]
-            slots = [sl.unpacked() if isinstance(sl, PackedMaskSlot) else sl for sl in slots]
+            slots = [sl.unpacked() if isinstance(sl, (PackedMaskSlot, PackedObsSlot)) else sl for sl in slots]
             if key == "action" and slots[0].dtype == torch.uint8:
                 slots = [sl.long() for sl in slots]
             x = torch.stack(slots, dim=1)                                         # utils.py:197-199
@@ -265,7 +306,7 @@ def get_batch(batch_size: int, shapes: dict, gamma: float, device, free_queue, f
 
     def raw(key, m):                 # the tensor actually stored in the slab for slot (key, m)
         sl = buffers[key][m]
-        return sl.packed if isinstance(sl, PackedMaskSlot) else sl
+        return sl.packed if isinstance(sl, (PackedMaskSlot, PackedObsSlot)) else sl
 
     def alloc():
         return {key: torch.empty((raw(key, 0).shape[0], batch_size) + tuple(raw(key, 0).shape[1:]),

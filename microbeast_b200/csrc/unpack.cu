@@ -46,7 +46,43 @@ __global__ void __launch_bounds__(256) widen_action_kernel(const uint8_t* __rest
     for (long long i = groups * 8 + tid; i < total; i += stride) a64[i] = a8[i];
 }
 
+// obs: the 27 feature planes of a cell are 0/1 (five one-hot groups), so a cell travels as one
+// uint32 (bit c = plane c) and is expanded straight into the NCHW fp32 tensor the cuDNN
+// convolutions consume -- replacing the uint8->float cast and the NHWC->NCHW copy on the device.
+__global__ void __launch_bounds__(256) unpack_obs_kernel(const uint32_t* __restrict__ bits, float* __restrict__ out,
+                                                         long long n_frames, int cells, int planes) {
+    const long long total = n_frames * cells;
+    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total;
+         i += (long long)gridDim.x * blockDim.x) {
+        const long long f = i / cells;
+        const int c = int(i - f * cells);
+        const uint32_t b = bits[i];
+        float* o = out + f * (long long)planes * cells + c;
+        for (int k = 0; k < planes; ++k) o[(long long)k * cells] = float((b >> k) & 1u);
+    }
+}
+
 }  // namespace mb
+
+extern "C" int mb_unpack_obs(const uint32_t* obs_bits, float* obs_out, int64_t n_frames, int32_t cells,
+                             int32_t planes, void* stream) {
+    if (n_frames < 0 || cells <= 0 || planes <= 0 || planes > 32) {
+        mb::set_error("mb_unpack_obs: n_frames=%lld cells=%d planes=%d out of range (planes <= 32)",
+                      (long long)n_frames, cells, planes);
+        return MB_ERR_INVALID;
+    }
+    if (n_frames == 0) return MB_OK;
+    if (!obs_bits || !obs_out) {
+        mb::set_error("mb_unpack_obs: null pointer");
+        return MB_ERR_INVALID;
+    }
+    int dev = 0;
+    MB_CUDA(cudaGetDevice(&dev));
+    mb::unpack_obs_kernel<<<mb::sm_count(dev) * 8, 256, 0, static_cast<cudaStream_t>(stream)>>>(
+        obs_bits, obs_out, n_frames, cells, planes);
+    MB_CUDA(cudaGetLastError());
+    return MB_OK;
+}
 
 extern "C" int mb_unpack_rollout(const uint8_t* mask_bits, const uint8_t* action_u8, uint8_t* mask_out,
                                  int64_t* action_out, int64_t n_frames, int32_t cells, void* stream) {

@@ -137,6 +137,7 @@ class Agent(nn.Module):
         self.nvec = nvec
         self.cells = len(nvec) // COMPONENTS_PER_CELL
         self.nchw_copy = True
+        self.obs_planes = c
         shape = (c, h, w)
         layers = []
         for out_channels in (16, 32, 32):
@@ -153,6 +154,8 @@ class Agent(nn.Module):
 
     def _obs(self, input_dict, learning):
         obs = input_dict["obs"] if learning else input_dict["obs"][0, 0, ...]     # model.py:156-160
+        if obs.dtype == torch.int32:     # bit-packed planes from the compact rollout store: [N,h,w] -> NCHW fp32
+            return ops.unpack_obs(obs, planes=self.obs_planes)
         if obs.dtype != torch.float32:
             obs = obs.float()            # uint8 wire format of the B200 rollout store
         x = obs.permute((0, 3, 1, 2))

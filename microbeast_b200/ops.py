@@ -234,6 +234,21 @@ def unpack_rollout(mask_bits: Optional[torch.Tensor], action_u8: Optional[torch.
     return mask_out, action_out
 
 
+def unpack_obs(obs_bits: torch.Tensor, planes: int = 27, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """Bit-packed observations ``[N,h,w]`` int32 (bit c = plane c) -> ``[N,planes,h,w]`` fp32 NCHW,
+    the layout the encoder's convolutions read."""
+    dev = _need_cuda(obs_bits=obs_bits, out=out)
+    obs_bits = _as(obs_bits, torch.int32, "obs_bits")
+    if obs_bits.dim() != 3:
+        raise ValueError("obs_bits must be [N, h, w]")
+    n, h, w = obs_bits.shape
+    if out is None:
+        out = torch.empty((n, planes, h, w), dtype=torch.float32, device=dev)
+    with torch.cuda.device(dev), _Launch("unpack_obs"):
+        _check(lib.mb_unpack_obs(_ptr(obs_bits), _ptr(out), n, h * w, planes, _stream()))
+    return out
+
+
 def vtrace_workspace(device: torch.device, rows: int) -> torch.Tensor:
     """Zero-initialised scratch for ``mb_vtrace_loss`` (cached per device; the kernel keeps
     its ticket word at zero between calls).  Calls on different streams that may overlap

@@ -218,8 +218,33 @@ def test_compact_rollout_store_on_device():
     for key in ("action_mask", "action", "reward", "obs"):
         x = src[key].view((n_buffers, T + 1, n_envs) + tuple(src[key].shape[1:]))
         want = torch.stack([x[3], x[1]], dim=1).reshape((-1,) + tuple(x.shape[3:]))
-        assert torch.equal(got[key].cpu(), want), key
+        have = got[key].cpu()
+        if key == "obs":                      # stays bit-packed until the Agent expands it to NCHW fp32
+            assert have.dtype == torch.int32
+            have = mbuf.unpack_obs_host(have)
+        assert torch.equal(have, want), key
     mbuf.release(bufs)
+
+
+def test_packed_observations_feed_the_encoder_unchanged():
+    """mb_unpack_obs: int32-per-cell observations -> NCHW fp32; the Agent gives the same outputs as
+    with the uint8 / float32 observation tensors of the reference layout."""
+    from microbeast_b200 import buffers as mbuf, ops, synth
+    g = torch.Generator().manual_seed(3)
+    obs = synth.make_obs(10, 8, 8, gen=g, dtype=torch.uint8)
+    bits = mbuf.pack_obs(obs)
+    nchw = ops.unpack_obs(bits.cuda())
+    assert nchw.shape == (10, 27, 8, 8)
+    assert torch.equal(nchw.cpu(), obs.permute(0, 3, 1, 2).float())
+    mine, _ = _pair(8, 8, seed=13)
+    batch = synth.make_rollout_batch(8, 8, 4, 2, seed=9, full_keys=False)
+    dev = {k: v.cuda() for k, v in batch.items()}
+    with torch.no_grad():
+        a, _ = mine.get_action(dev, learning=True)
+        dev["obs"] = mbuf.pack_obs(batch["obs"]).cuda()
+        b, _ = mine.get_action(dev, learning=True)
+    for k in ("policy_logits", "logprobs", "entropy", "baseline"):
+        assert torch.equal(a[k], b[k]), k
 
 
 def test_train_driver_runs_actors_and_learner(tmp_path):
