@@ -232,6 +232,11 @@ def run_ours(args):
         batch["logprobs"] = o["logprobs"] + 0.3 * torch.randn_like(o["logprobs"])
         del o
     dev_batch = {k: batch[k] for k in LEARNER_KEYS}
+    if args.wire == "compact":
+        # resident batch in the rollout store's observation format: one int32 per cell (bit c = plane c),
+        # expanded to NCHW fp32 by mb_unpack_obs inside the step
+        shifts = torch.arange(27, device=dev, dtype=torch.int32)
+        dev_batch["obs"] = (batch["obs"].to(torch.int32) << shifts).sum(-1, dtype=torch.int32)
 
     def step(b, sync):
         return PPO_learn(model, model, "bench", b, opt, rows, T, 1, reducer=reducer, sync=sync)
@@ -305,6 +310,7 @@ def run_ours(args):
     if not args.no_e2e:
         from microbeast_b200 import buffers as mbuf
         wire = {k: v.cpu() for k, v in dev_batch.items()}
+        wire["obs"] = batch["obs"].cpu()
         if args.wire == "compact":
             wire = mbuf.pack_batch(wire)        # rollout-store wire format: bit-packed obs / masks, u8 actions
         host = {k: torch.empty(v.shape, dtype=v.dtype, pin_memory=True).copy_(v) for k, v in wire.items()}
