@@ -11,7 +11,9 @@ h = w = 16; T = 80; rows = 256; cells = h * w; n = rows * (T + 1)
 g = torch.Generator(device=dev).manual_seed(0)
 obs = synth.make_obs(n, h, w, gen=g, device=dev, dtype=torch.uint8)
 
-def run(name, channels_last, tf32, benchmark=True, nchw_copy=False):
+def run(name, channels_last, tf32, benchmark=True, nchw_copy=False, cudnn=True, deterministic=False):
+    torch.backends.cudnn.enabled = cudnn
+    torch.backends.cudnn.deterministic = deterministic
     torch.backends.cudnn.allow_tf32 = tf32
     torch.backends.cuda.matmul.allow_tf32 = tf32
     torch.backends.cudnn.benchmark = benchmark
@@ -38,6 +40,8 @@ def run(name, channels_last, tf32, benchmark=True, nchw_copy=False):
     e.record(); torch.cuda.synchronize()
     print(f"{name:40s} {s.elapsed_time(e) / 5:8.2f} ms/iter", flush=True)
 
+run("nchw-copy fp32 cudnn OFF (native conv)", False, False, nchw_copy=True, cudnn=False)
+run("nchw-copy fp32 cudnn deterministic", False, False, nchw_copy=True, deterministic=True)
 run("channels_last fp32", True, False)
 run("nchw-copy + nchw weights fp32", False, False, nchw_copy=True)
 run("nhwc view + nchw weights fp32", False, False)
