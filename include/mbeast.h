@@ -93,8 +93,9 @@ MB_API size_t mb_vtrace_workspace_bytes(int64_t rows);
  *   workspace: >= mb_vtrace_workspace_bytes(rows) bytes, 8-byte aligned; its first 4 bytes must
  *           be zero before the FIRST call (the kernel restores the zero itself), and two calls
  *           that may overlap on the GPU must not share a workspace.
- * Uses TMA tiles when pointers are 16-byte aligned, in_row_stride % 16 == 0 and
- * out_row_stride % 4 == 0; any other layout takes a slower generic kernel with equal results. */
+ * Uses TMA tiles when the f32 pointers are 16-byte aligned and both row strides are multiples of 4
+ * (`done` rides along as a TMA tile when in_row_stride % 16 == 0, else it is read directly); any
+ * other layout takes a slower generic kernel with equal results. */
 MB_API int mb_vtrace_loss(const float* lp_old, const float* lp_new, const float* values, const float* bootstrap,
                    const float* rewards, const uint8_t* done, const float* entropy, int64_t rows, int32_t T,
                    int64_t in_row_stride, int64_t out_row_stride, float gamma, float rho_bar, float c_bar,

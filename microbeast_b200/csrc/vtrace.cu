@@ -139,7 +139,9 @@ struct VtTile {
     }
 };
 
-template <int NSTAGE, int TS>
+// DONE_TMA = false: the rows' byte pitch is not a multiple of 16 (e.g. T = 20), which a tensor map
+// cannot describe for the u8 `done` array; each thread then reads its row's done bytes directly.
+template <int NSTAGE, int TS, bool DONE_TMA = true>
 __global__ void __launch_bounds__(64) vtrace_tma_kernel(const __grid_constant__ VtMaps maps, const VtParams p) {
     using Tile = VtTile<TS>;
     constexpr int kStageBytes = Tile::kStage;              // multiple of 1024
@@ -169,7 +171,7 @@ __global__ void __launch_bounds__(64) vtrace_tma_kernel(const __grid_constant__ 
         tma_prefetch_desc(&maps.lp_new);
         tma_prefetch_desc(&maps.values);
         tma_prefetch_desc(&maps.rewards);
-        tma_prefetch_desc(&maps.done);
+        if (DONE_TMA) tma_prefetch_desc(&maps.done);
     }
     __syncthreads();
 
@@ -184,12 +186,12 @@ __global__ void __launch_bounds__(64) vtrace_tma_kernel(const __grid_constant__ 
         const int t0 = (nt - 1 - lk) * TS;
         const int row0 = (int(blockIdx.x) + lg * int(gridDim.x)) * kVtRows;
         uint8_t* st = smem + size_t(s) * kStageBytes;
-        mbar_arrive_expect_tx(&full[s], uint32_t(4 * Tile::kF32 + Tile::kU8));
+        mbar_arrive_expect_tx(&full[s], uint32_t(4 * Tile::kF32 + (DONE_TMA ? Tile::kU8 : 0)));
         tma_load_2d(st + 0 * Tile::kF32, &maps.lp_old, t0, row0, &full[s]);
         tma_load_2d(st + 1 * Tile::kF32, &maps.lp_new, t0, row0, &full[s]);
         tma_load_2d(st + 2 * Tile::kF32, &maps.values, t0, row0, &full[s]);
         tma_load_2d(st + 3 * Tile::kF32, &maps.rewards, t0, row0, &full[s]);
-        tma_load_2d(st + 4 * Tile::kF32, &maps.done, t0, row0, &full[s]);
+        if (DONE_TMA) tma_load_2d(st + 4 * Tile::kF32, &maps.done, t0, row0, &full[s]);
         ++lq;
         if (++lk == nt) { lk = 0; ++lg; }
     };
@@ -309,7 +311,16 @@ __global__ void __launch_bounds__(64) vtrace_tma_kernel(const __grid_constant__ 
                 const float4 a_new = *reinterpret_cast<const float4*>(q_new + off);
                 const float4 a_val = *reinterpret_cast<const float4*>(q_val + off);
                 const float4 a_rew = *reinterpret_cast<const float4*>(q_rew + off);
-                const uint32_t dn = *reinterpret_cast<const uint32_t*>(q_dn + lane * TS + j * 4);
+                uint32_t dn;
+                if (DONE_TMA) {
+                    dn = *reinterpret_cast<const uint32_t*>(q_dn + lane * TS + j * 4);
+                } else {
+                    dn = 0;
+                    const uint8_t* drow = p.done + (long long)(row0 + lane) * p.in_stride + t0 + 4 * j;
+#pragma unroll
+                    for (int i = 0; i < 4; ++i)
+                        if (row_ok && t0 + 4 * j + i < p.T) dn |= uint32_t(__ldg(drow + i) != 0) << (8 * i);
+                }
                 const float lo[4] = {a_old.x, a_old.y, a_old.z, a_old.w};
                 const float ln[4] = {a_new.x, a_new.y, a_new.z, a_new.w};
                 const float vv[4] = {a_val.x, a_val.y, a_val.z, a_val.w};
@@ -530,27 +541,27 @@ size_t vtrace_workspace_bytes(long long rows) {
 
 static inline bool al16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; }
 
-template <int NSTAGE, int TS>
+template <int NSTAGE, int TS, bool DONE_TMA = true>
 static int launch_vt_tma(const VtMaps& maps, const VtParams& p, cudaStream_t stream) {
     constexpr size_t smem = size_t(NSTAGE) * VtTile<TS>::kStage + 1024;
     static bool attr_set[64] = {};
     int dev = 0;
     MB_CUDA(cudaGetDevice(&dev));
     if (dev < 64 && !attr_set[dev]) {
-        MB_CUDA(cudaFuncSetAttribute(vtrace_tma_kernel<NSTAGE, TS>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+        MB_CUDA(cudaFuncSetAttribute(vtrace_tma_kernel<NSTAGE, TS, DONE_TMA>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                      int(smem)));
         attr_set[dev] = true;
     }
     static int per_sm[64] = {};
     if (dev < 64 && per_sm[dev] == 0) {
         int n = 0;
-        MB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, vtrace_tma_kernel<NSTAGE, TS>, 64, smem));
+        MB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, vtrace_tma_kernel<NSTAGE, TS, DONE_TMA>, 64, smem));
         per_sm[dev] = n > 0 ? n : 1;
     }
     const long long groups = (p.rows + kVtRows - 1) / kVtRows;
     const long long resident = (long long)sm_count(dev) * (dev < 64 ? per_sm[dev] : 1);
     const unsigned grid = unsigned(groups < resident ? groups : resident);
-    vtrace_tma_kernel<NSTAGE, TS><<<grid, 64, smem, stream>>>(maps, p);
+    vtrace_tma_kernel<NSTAGE, TS, DONE_TMA><<<grid, 64, smem, stream>>>(maps, p);
     MB_CUDA(cudaGetLastError());
     return MB_OK;
 }
@@ -596,9 +607,10 @@ int vtrace_loss_launch(VtParams p, void* scratch, size_t scratch_bytes, cudaStre
     if (p.inv_n <= 0.0f) p.inv_n = float(1.0 / (double(p.rows) * double(p.T)));
 
     EncodeTiledFn enc = get_encode_fn();
-    bool tma_ok = enc && !g_vt_force_generic && (p.in_stride % 16 == 0) && (p.out_stride % 4 == 0) &&
+    bool tma_ok = enc && !g_vt_force_generic && (p.in_stride % 4 == 0) && (p.out_stride % 4 == 0) &&
                   al16(p.lp_old) && al16(p.lp_new) && al16(p.values) && al16(p.rewards) && al16(p.entropy) &&
-                  al16(p.done) && al16(p.vs) && al16(p.adv) && (!p.dlp || (al16(p.dlp) && al16(p.dv)));
+                  al16(p.vs) && al16(p.adv) && (!p.dlp || (al16(p.dlp) && al16(p.dv)));
+    const bool done_tma = (p.in_stride % 16 == 0) && al16(p.done);
     if (tma_ok) {
         // Few CTAs (latency bound) -> deep prefetch; many CTAs (bandwidth bound) -> more CTAs per SM.
         int v = g_vt_variant;
@@ -611,12 +623,16 @@ int vtrace_loss_launch(VtParams p, void* scratch, size_t scratch_bytes, cudaStre
                   make_map_2d(enc, &maps.lp_new, p.lp_new, false, p.rows, p.T, p.in_stride, ts) &&
                   make_map_2d(enc, &maps.values, p.values, false, p.rows, p.T, p.in_stride, ts) &&
                   make_map_2d(enc, &maps.rewards, p.rewards, false, p.rows, p.T, p.in_stride, ts) &&
-                  make_map_2d(enc, &maps.done, p.done, true, p.rows, p.T, p.in_stride, ts) &&
+                  (!done_tma || make_map_2d(enc, &maps.done, p.done, true, p.rows, p.T, p.in_stride, ts)) &&
                   make_map_2d(enc, &maps.vs, p.vs, false, p.rows, p.T, p.out_stride, ts) &&
                   make_map_2d(enc, &maps.adv, p.adv, false, p.rows, p.T, p.out_stride, ts);
         if (ok && p.dlp)
             ok = make_map_2d(enc, &maps.dlp, p.dlp, false, p.rows, p.T, p.out_stride, ts) &&
                  make_map_2d(enc, &maps.dv, p.dv, false, p.rows, p.T, p.out_stride, ts);
+        if (ok && !done_tma) {
+            if (ts == 16) return launch_vt_tma<4, 16, false>(maps, p, stream);
+            return launch_vt_tma<4, 32, false>(maps, p, stream);
+        }
         if (ok) {
             switch (v) {
                 case 0: return launch_vt_tma<2, 32>(maps, p, stream);

@@ -55,7 +55,7 @@ def test_golden_small(golden):
 
 
 @pytest.mark.parametrize("rows,T", [(256, 80), (32, 64), (33, 80), (7, 16), (100, 20), (64, 33), (5, 1),
-                                    (1024, 80), (96, 256), (40, 512), (3, 48)])
+                                    (1024, 80), (96, 256), (40, 512), (3, 48), (1000, 44), (300, 12), (70, 100)])
 def test_vs_oracle_shapes(rows, T):
     """TMA path (T % 16 == 0) and generic path (other T) against the reference arithmetic."""
     mb, ops, synth, ovt = _mods()
