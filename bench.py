@@ -122,12 +122,12 @@ class ClockSampler:
 # ------------------------------------------------------------------------------------------
 # reference arm / cpu baseline: the oracle port of the reference's CPU learner step
 # ------------------------------------------------------------------------------------------
-def time_cpu_reference(h, w, T, rows, steps, warmup, preset):
+def time_cpu_reference(h, w, T, rows, steps, warmup, preset, threads=None):
     import torch
     from microbeast_b200 import synth
     from oracle import NVEC_CELL
     from oracle.learner import RefAgent, ref_learn_step
-    cores = os.cpu_count() or 1
+    cores = threads or os.cpu_count() or 1
     torch.set_num_threads(cores)
     torch.manual_seed(1234)
     agent = RefAgent((h, w, 27), list(NVEC_CELL) * (h * w), h * w)
@@ -346,6 +346,11 @@ def run_ours(args):
         cpu = {"value": fps, "unit": UNIT, "cores": cores, "kind": "port",
                "sample": f"{crow} of {rows} rows ({crow * (T + 1)} frames) per step, 2 timed steps after 1 "
                          f"warm-up, full reference learner step on torch CPU ({sec:.2f} s/step)"}
+        # the reference's nominal setting is OMP_NUM_THREADS=1 (microbeast.py:16): one timed step on a quarter sample
+        fps1, sec1, _ = time_cpu_reference(h, w, T, max(crow // 4, 1), 1, 1, args.preset, threads=1)
+        cpu["single_thread"] = {"value": fps1, "unit": UNIT, "cores": 1,
+                                "sample": f"{max(crow // 4, 1)} rows per step, 1 timed step ({sec1:.2f} s/step)"}
+        torch.set_num_threads(os.cpu_count() or 1)
 
     if rank == 0:
         line = {
@@ -393,7 +398,16 @@ def run_sweep(args):
                 med, p10, p90 = bench(fn, 20)
                 nbytes = 37 * R * T + 4 * R
                 gbs = nbytes / (med * 1e-3) / 1e9
+                cpu_ms = None
+                if R * T <= (1 << 21):
+                    from oracle import vtrace as ovt
+                    c = {k: v.cpu() for k, v in t.items()}
+                    t0 = time.perf_counter()
+                    ovt.vtrace_losses(c["lp_old"], c["lp_new"], c["values"], c["bootstrap"], c["rewards"], c["done"],
+                                      c["entropy"])
+                    cpu_ms = (time.perf_counter() - t0) * 1e3
                 rows_out.append({"kernel": "vtrace_loss", "T": T, "rows": R, "elements": R * T, "median_us": med * 1e3,
+                                 "cpu_reference_ms": cpu_ms,
                                  "p10_us": p10 * 1e3, "p90_us": p90 * 1e3, "alg_bytes": nbytes, "gbs": gbs,
                                  "frac_of_peak": gbs / peak,
                                  "regime": "hbm" if R * T >= 8_000_000 else "latency-bound (L2 resident / launch)"})
