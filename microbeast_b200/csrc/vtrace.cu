@@ -304,22 +304,40 @@ __global__ void __launch_bounds__(64) vtrace_tma_kernel(const __grid_constant__ 
         // only in the last group: every other tile runs the body without any range checks.
         auto tile_body = [&](auto guard_tag) {
             constexpr bool kGuard = decltype(guard_tag)::value;
+            // software pipeline over the chunks of the tile: the four LDS.128 (and the done word) of
+            // chunk j-1 are issued before chunk j is computed, so shared-memory latency and the next
+            // chunk's exp() overlap the serial part of the recurrence
+            auto load_dn = [&](int j) -> uint32_t {
+                if (DONE_TMA) return *reinterpret_cast<const uint32_t*>(q_dn + lane * TS + j * 4);
+                uint32_t d = 0;
+                const uint8_t* drow = p.done + (long long)(row0 + lane) * p.in_stride + t0 + 4 * j;
+#pragma unroll
+                for (int i = 0; i < 4; ++i)
+                    if (row_ok && t0 + 4 * j + i < p.T) d |= uint32_t(__ldg(drow + i) != 0) << (8 * i);
+                return d;
+            };
+            float4 n_old, n_new, n_val, n_rew;
+            uint32_t n_dn;
+            {
+                const uint32_t off0 = Tile::off(lane, Tile::kChunks - 1);
+                n_old = *reinterpret_cast<const float4*>(q_old + off0);
+                n_new = *reinterpret_cast<const float4*>(q_new + off0);
+                n_val = *reinterpret_cast<const float4*>(q_val + off0);
+                n_rew = *reinterpret_cast<const float4*>(q_rew + off0);
+                n_dn = load_dn(Tile::kChunks - 1);
+            }
 #pragma unroll
             for (int j = Tile::kChunks - 1; j >= 0; --j) {
                 const uint32_t off = Tile::off(lane, j);
-                const float4 a_old = *reinterpret_cast<const float4*>(q_old + off);
-                const float4 a_new = *reinterpret_cast<const float4*>(q_new + off);
-                const float4 a_val = *reinterpret_cast<const float4*>(q_val + off);
-                const float4 a_rew = *reinterpret_cast<const float4*>(q_rew + off);
-                uint32_t dn;
-                if (DONE_TMA) {
-                    dn = *reinterpret_cast<const uint32_t*>(q_dn + lane * TS + j * 4);
-                } else {
-                    dn = 0;
-                    const uint8_t* drow = p.done + (long long)(row0 + lane) * p.in_stride + t0 + 4 * j;
-#pragma unroll
-                    for (int i = 0; i < 4; ++i)
-                        if (row_ok && t0 + 4 * j + i < p.T) dn |= uint32_t(__ldg(drow + i) != 0) << (8 * i);
+                const float4 a_old = n_old, a_new = n_new, a_val = n_val, a_rew = n_rew;
+                const uint32_t dn = n_dn;
+                if (j > 0) {
+                    const uint32_t offn = Tile::off(lane, j - 1);
+                    n_old = *reinterpret_cast<const float4*>(q_old + offn);
+                    n_new = *reinterpret_cast<const float4*>(q_new + offn);
+                    n_val = *reinterpret_cast<const float4*>(q_val + offn);
+                    n_rew = *reinterpret_cast<const float4*>(q_rew + offn);
+                    n_dn = load_dn(j - 1);
                 }
                 const float lo[4] = {a_old.x, a_old.y, a_old.z, a_old.w};
                 const float ln[4] = {a_new.x, a_new.y, a_new.z, a_new.w};
