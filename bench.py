@@ -406,6 +406,16 @@ def run_sweep(args):
                     ovt.vtrace_losses(c["lp_old"], c["lp_new"], c["values"], c["bootstrap"], c["rewards"], c["done"],
                                       c["entropy"])
                     cpu_ms = (time.perf_counter() - t0) * 1e3
+                tt = {k: (v.t().contiguous() if v.dim() == 2 else v) for k, v in t.items()}
+                fn_tm = lambda: ops.vtrace_loss(tt["lp_old"], tt["lp_new"], tt["values"], tt["bootstrap"], tt["rewards"],
+                                                tt["done"], tt["entropy"], time_major=True)
+                med_tm, p10_tm, p90_tm = bench(fn_tm, 20)
+                gbs_tm = nbytes / (med_tm * 1e-3) / 1e9
+                rows_out.append({"kernel": "vtrace_loss_tmajor", "T": T, "rows": R, "elements": R * T,
+                                 "median_us": med_tm * 1e3, "p10_us": p10_tm * 1e3, "p90_us": p90_tm * 1e3,
+                                 "alg_bytes": nbytes, "gbs": gbs_tm, "frac_of_peak": gbs_tm / peak,
+                                 "regime": "hbm" if R * T >= 8_000_000 else "latency-bound (L2 resident / launch)"})
+                del tt
                 rows_out.append({"kernel": "vtrace_loss", "T": T, "rows": R, "elements": R * T, "median_us": med * 1e3,
                                  "cpu_reference_ms": cpu_ms,
                                  "p10_us": p10 * 1e3, "p90_us": p90 * 1e3, "alg_bytes": nbytes, "gbs": gbs,

@@ -102,6 +102,20 @@ MB_API int mb_vtrace_loss(const float* lp_old, const float* lp_new, const float*
                    float pg_rho_bar, float ent_coef, float inv_n, float* vs_out, float* adv_out, float* loss4_out,
                    float* dlp_out, float* dV_out, void* workspace, size_t workspace_bytes, void* stream);
 
+/* mb_vtrace_loss on TIME-MAJOR arrays: every [rows, T] tensor of mb_vtrace_loss is given as [T, rows]
+ * (rows contiguous, `in_t_stride` / `out_t_stride` elements between consecutive time steps).  This is
+ * the order the reference's rollout buffers are written in and get_batch flattens them in
+ * (libs/utils.py:35-45,197-205: [T+1, n_envs, ...]); the reference reshapes that to [R, T+1]
+ * (utils.py:245,253), which this entry point makes unnecessary when a row is meant to be one
+ * trajectory.  Same arithmetic, arguments, outputs (time-major) and workspace rules otherwise. */
+MB_API int mb_vtrace_loss_tmajor(const float* lp_old, const float* lp_new, const float* values,
+                                 const float* bootstrap, const float* rewards, const uint8_t* done,
+                                 const float* entropy, int64_t rows, int32_t T, int64_t in_t_stride,
+                                 int64_t out_t_stride, float gamma, float rho_bar, float c_bar,
+                                 float pg_rho_bar, float ent_coef, float inv_n, float* vs_out, float* adv_out,
+                                 float* loss4_out, float* dlp_out, float* dV_out, void* workspace,
+                                 size_t workspace_bytes, void* stream);
+
 /* mb_vtrace_loss without the workspace argument.  It has no counterpart in the reference: it exists
  * for users of this library who cannot allocate device memory where they call it (a C / ctypes host
  * with no allocator of its own, a step loop that must stay clear of cudaMalloc's device-wide

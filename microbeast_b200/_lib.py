@@ -26,6 +26,11 @@ SIGNATURES = {
                                       ctypes.c_float, ctypes.c_float, ctypes.c_float, ctypes.c_float,
                                       ctypes.c_float, ctypes.c_float,
                                       _P, _P, _P, _P, _P, _P, ctypes.c_size_t, _P]),
+    "mb_vtrace_loss_tmajor": (ctypes.c_int, [_P, _P, _P, _P, _P, _P, _P, ctypes.c_int64, ctypes.c_int32,
+                                             ctypes.c_int64, ctypes.c_int64,
+                                             ctypes.c_float, ctypes.c_float, ctypes.c_float, ctypes.c_float,
+                                             ctypes.c_float, ctypes.c_float,
+                                             _P, _P, _P, _P, _P, _P, ctypes.c_size_t, _P]),
     "mb_vtrace_loss_static": (ctypes.c_int, [_P, _P, _P, _P, _P, _P, _P, ctypes.c_int64, ctypes.c_int32,
                                              ctypes.c_int64, ctypes.c_int64,
                                              ctypes.c_float, ctypes.c_float, ctypes.c_float, ctypes.c_float,

@@ -462,6 +462,98 @@ __global__ void __launch_bounds__(128) vtrace_generic_kernel(const VtParams p) {
 }
 
 // ---------------------------------------------------------------------------------------------
+// Time-major kernel: arrays laid out [T, R] (rows contiguous), which is the order the rollout
+// buffers are written in (libs/utils.py:35-45: [T+1, n_envs, ...]) and the order get_batch
+// flattens them (utils.py:197-205).  With one thread per row a warp's 32 loads of one time step
+// are then a single 128-B line: perfectly coalesced, no shared-memory staging needed.  Each thread
+// keeps the next block of kTmU time steps in flight in registers while it computes the current one.
+// Same arithmetic (vt_step) and the same 32-step fp64 folding as the other two kernels.
+// ---------------------------------------------------------------------------------------------
+constexpr int kTmU = 8;
+
+struct TmBlock {
+    float lo[kTmU], ln[kTmU], v[kTmU], rw[kTmU], en[kTmU];
+    uint32_t dn[kTmU];
+};
+
+__device__ __forceinline__ void tm_load(const VtParams& p, long long row, int t_hi, bool row_ok, TmBlock& b) {
+#pragma unroll
+    for (int i = 0; i < kTmU; ++i) {
+        const int t = t_hi - 1 - i;
+        const bool ok = row_ok && t >= 0;
+        const long long idx = ok ? (long long)t * p.in_stride + row : 0;
+        b.lo[i] = ok ? __ldg(p.lp_old + idx) : 0.f;
+        b.ln[i] = ok ? __ldg(p.lp_new + idx) : 0.f;
+        b.v[i] = ok ? __ldg(p.values + idx) : 0.f;
+        b.rw[i] = ok ? __ldg(p.rewards + idx) : 0.f;
+        b.en[i] = ok ? __ldg(p.entropy + idx) : 0.f;
+        b.dn[i] = ok ? uint32_t(__ldg(p.done + idx)) : 0u;
+    }
+}
+
+__global__ void __launch_bounds__(128) vtrace_tmajor_kernel(const VtParams p) {
+    __shared__ double red[4][3];
+    __shared__ unsigned int tk_s;
+    const long long row = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const bool row_ok = row < p.rows;
+    double s_pg = 0.0, s_v = 0.0, s_en = 0.0;
+    VtCarry carry;
+    carry.acc = 0.0f;
+    carry.v_next = row_ok ? __ldg(p.bootstrap + row) : 0.f;
+    carry.vs_next = carry.v_next;
+    float t_pg = 0.f, t_v = 0.f, t_en = 0.f;
+    TmBlock cur, nxt;
+    tm_load(p, row, p.T, row_ok, cur);
+    for (int t_hi = p.T; t_hi > 0; t_hi -= kTmU) {
+        if (t_hi - kTmU > 0) tm_load(p, row, t_hi - kTmU, row_ok, nxt);
+#pragma unroll
+        for (int i = 0; i < kTmU; ++i) {
+            const int t = t_hi - 1 - i;
+            const bool ok = row_ok && t >= 0;
+            const VtStepOut o = vt_step(p, vt_ratio_exp(cur.lo[i], cur.ln[i]), cur.v[i], cur.rw[i], cur.dn[i] != 0, ok,
+                                        carry);
+            const float dvs = __fsub_rn(o.vs, cur.v[i]);
+            if (ok) {
+                const long long od = (long long)t * p.out_stride + row;
+                p.vs[od] = o.vs;
+                p.adv[od] = o.adv;
+                if (p.dlp) {
+                    p.dlp[od] = o.adv * p.inv_n;
+                    p.dv[od] = -dvs * p.inv_n;
+                }
+            }
+            t_pg = __fadd_rn(t_pg, ok ? __fmul_rn(cur.ln[i], o.adv) : 0.f);
+            t_v = __fadd_rn(t_v, ok ? __fmul_rn(dvs, dvs) : 0.f);
+            t_en = __fadd_rn(t_en, ok ? cur.en[i] : 0.f);
+            if (ok && (t & 31) == 0) {
+                s_pg += double(t_pg); s_v += double(t_v); s_en += double(t_en);
+                t_pg = t_v = t_en = 0.f;
+            }
+        }
+        cur = nxt;
+    }
+    s_pg = warp_sum(s_pg);
+    s_v = warp_sum(s_v);
+    s_en = warp_sum(s_en);
+    if (lane == 0) {
+        red[warp][0] = s_pg; red[warp][1] = s_v; red[warp][2] = s_en;
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        for (int i = 0; i < 3; ++i)
+            p.partials[size_t(blockIdx.x) * 3 + i] = red[0][i] + red[1][i] + red[2][i] + red[3][i];
+        __threadfence();
+        tk_s = atomicAdd(p.ticket, 1u);
+    }
+    __syncthreads();
+    if (tk_s == gridDim.x - 1 && warp == 0) {
+        __threadfence();
+        vt_finalize(p, lane);
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
 // Host side
 // ---------------------------------------------------------------------------------------------
 typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
@@ -767,4 +859,61 @@ extern "C" int mb_vtrace_loss_static(const float* lp_old, const float* lp_new, c
     p.gamma = gamma; p.rho_bar = rho_bar; p.c_bar = c_bar; p.pg_rho_bar = pg_rho_bar; p.ent_coef = ent_coef;
     p.inv_n = inv_n;
     return mb::vtrace_loss_launch(p, scratch, mb::kVtStaticScratchBytes, st);
+}
+
+
+// ---------------------------------------------------------------------------------------------
+// mb_vtrace_loss_tmajor: the same computation on TIME-MAJOR arrays [T, rows].
+// ---------------------------------------------------------------------------------------------
+extern "C" int mb_vtrace_loss_tmajor(const float* lp_old, const float* lp_new, const float* values,
+                                     const float* bootstrap, const float* rewards, const uint8_t* done,
+                                     const float* entropy, int64_t rows, int32_t T, int64_t in_t_stride,
+                                     int64_t out_t_stride, float gamma, float rho_bar, float c_bar,
+                                     float pg_rho_bar, float ent_coef, float inv_n, float* vs_out, float* adv_out,
+                                     float* loss4_out, float* dlp_out, float* dV_out, void* workspace,
+                                     size_t workspace_bytes, void* stream) {
+    using namespace mb;
+    if (rows < 0 || T <= 0) {
+        set_error("vtrace_loss_tmajor: rows=%lld T=%d out of range", (long long)rows, T);
+        return MB_ERR_INVALID;
+    }
+    if (!loss4_out) {
+        set_error("vtrace_loss_tmajor: null loss4_out pointer");
+        return MB_ERR_INVALID;
+    }
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    if (rows == 0) {
+        MB_CUDA(cudaMemsetAsync(loss4_out, 0, 4 * sizeof(float), st));
+        return MB_OK;
+    }
+    if (!lp_old || !lp_new || !values || !rewards || !entropy || !done || !bootstrap || !vs_out || !adv_out) {
+        set_error("vtrace_loss_tmajor: null input/output pointer");
+        return MB_ERR_INVALID;
+    }
+    if ((dlp_out == nullptr) != (dV_out == nullptr)) {
+        set_error("vtrace_loss_tmajor: dlp_out and dV_out must both be given or both be null");
+        return MB_ERR_INVALID;
+    }
+    if (in_t_stride < rows || out_t_stride < rows) {
+        set_error("vtrace_loss_tmajor: time stride smaller than rows");
+        return MB_ERR_INVALID;
+    }
+    if (!workspace || workspace_bytes < vtrace_workspace_bytes(rows) || (reinterpret_cast<uintptr_t>(workspace) & 7)) {
+        set_error("vtrace_loss_tmajor: workspace missing, misaligned or smaller than mb_vtrace_workspace_bytes(rows)=%zu",
+                  vtrace_workspace_bytes(rows));
+        return MB_ERR_INVALID;
+    }
+    VtParams p;
+    memset(&p, 0, sizeof(p));
+    p.lp_old = lp_old; p.lp_new = lp_new; p.values = values; p.rewards = rewards; p.entropy = entropy;
+    p.done = done; p.bootstrap = bootstrap; p.vs = vs_out; p.adv = adv_out; p.dlp = dlp_out; p.dv = dV_out;
+    p.loss4 = loss4_out; p.rows = rows; p.T = T; p.in_stride = in_t_stride; p.out_stride = out_t_stride;
+    p.gamma = gamma; p.rho_bar = rho_bar; p.c_bar = c_bar; p.pg_rho_bar = pg_rho_bar; p.ent_coef = ent_coef;
+    p.inv_n = inv_n > 0.0f ? inv_n : float(1.0 / (double(rows) * double(T)));
+    p.ticket = reinterpret_cast<unsigned int*>(workspace);
+    p.partials = reinterpret_cast<double*>(reinterpret_cast<uint8_t*>(workspace) + 256);
+    const unsigned grid = unsigned((rows + 127) / 128);
+    vtrace_tmajor_kernel<<<grid, 128, 0, st>>>(p);
+    MB_CUDA(cudaGetLastError());
+    return MB_OK;
 }

@@ -108,24 +108,35 @@ def learner_losses(learner_model: nn.Module, batch: Dict[str, torch.Tensor], row
     ``utils.py:320-326`` are then taken over the global ``rows*T`` so that a plain
     sum-allreduce of gradients reproduces the single-GPU step.
     ``time_major=False`` keeps the reference's ``reshape((R, T+1))`` of a batch flattened in
-    ``(t, b, e)`` order (quirk Q7); ``True`` transposes so that a row really is one
-    trajectory.
+    ``(t, b, e)`` order (quirk Q7); ``True`` treats the flat batch as what it is, ``[T+1, rows]``,
+    so that a row really is one trajectory, and runs the time-major V-trace kernel on it in place.
     """
     out, _ = learner_model.get_action(batch, learning=True, inds=[], agent_state=())      # utils.py:234
-
-    def rt(x):                       # utils.py:237-253 (reshape) or the true transpose
-        if time_major:
-            return x.reshape((T + 1, rows) + tuple(x.shape[1:])).transpose(0, 1)
-        return x.reshape((rows, T + 1) + tuple(x.shape[1:]))
 
     ready = batch.get("_ready")
     if ready is not None:
         torch.cuda.current_stream().wait_event(ready)     # reward / done / logprobs staged on the side stream
+    inv_n = 1.0 / float((global_rows or rows) * T)
+    if time_major:
+        # the flat batch is (t, row): views [T+1, rows]; slot T is the bootstrap, batch keys shift by one
+        # slot (utils.py:258-265).  No transpose, no copy: mb_vtrace_loss_tmajor reads this layout.
+        def tm(x):
+            return x.reshape((T + 1, rows) + tuple(x.shape[1:]))
+        logp, base, ent = tm(out["logprobs"]), tm(out["baseline"].flatten()), tm(out["entropy"])
+        bootstrap = base[-1].detach()
+        loss4, vs, adv = ops.VTraceLoss.apply(
+            logp[:-1], base[:-1], ent[:-1], tm(batch["logprobs"])[1:], bootstrap, tm(batch["reward"])[1:],
+            tm(batch["done"])[1:], gamma, rho_bar, c_bar, pg_rho_bar, entropy_coef, inv_n, True)
+        return loss4, dict(vs=vs.transpose(0, 1), pg_advantages=adv.transpose(0, 1), logprobs=logp.transpose(0, 1),
+                           baseline=base.transpose(0, 1), entropy=ent.transpose(0, 1))
+
+    def rt(x):                       # utils.py:237-253: the reference's reshape (quirk Q7)
+        return x.reshape((rows, T + 1) + tuple(x.shape[1:]))
+
     logp = rt(out["logprobs"])
     base = rt(out["baseline"].flatten())
     ent = rt(out["entropy"])
     bootstrap = base[:, -1].detach()                                                       # utils.py:258
-    inv_n = 1.0 / float((global_rows or rows) * T)
     loss4, vs, adv = ops.VTraceLoss.apply(
         logp[:, :-1], base[:, :-1], ent[:, :-1],                                           # utils.py:265
         rt(batch["logprobs"])[:, 1:], bootstrap, rt(batch["reward"])[:, 1:], rt(batch["done"])[:, 1:],  # :263

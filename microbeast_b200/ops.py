@@ -265,10 +265,12 @@ def vtrace_workspace(device: torch.device, rows: int) -> torch.Tensor:
 
 def vtrace_loss(lp_old, lp_new, values, bootstrap, rewards, done, entropy, *, gamma=0.99, rho_bar=1.0,
                 c_bar=1.0, pg_rho_bar=1.0, entropy_coef=0.01, inv_n: Optional[float] = None,
-                want_grads: bool = True, workspace: Optional[torch.Tensor] = None):
+                want_grads: bool = True, workspace: Optional[torch.Tensor] = None, time_major: bool = False):
     """V-trace + losses (+ gradients) -- reference ``libs/utils.py:277-329``.
 
-    All inputs ``[R,T]`` (time contiguous), ``bootstrap [R]``.  Returns a dict with
+    All inputs ``[R,T]`` (time contiguous, the reference's layout) or, with ``time_major=True``,
+    ``[T,R]`` (rows contiguous, the layout the rollout buffers are written in; outputs are then
+    ``[T,R]`` too); ``bootstrap [R]``.  Returns a dict with
     ``vs``, ``pg_advantages`` ``[R,T]``, ``loss4`` ``[4]`` = pg, value, entropy, total and,
     with ``want_grads``, ``d_logp``, ``d_values`` ``[R,T]`` and the scalar ``d_entropy``.
     """
@@ -284,25 +286,27 @@ def vtrace_loss(lp_old, lp_new, values, bootstrap, rewards, done, entropy, *, ga
         done = done.view(torch.uint8) if done.is_contiguous() else done.contiguous().view(torch.uint8)
     done = _as(done, torch.uint8, "done")
     if values.dim() != 2:
-        raise ValueError("values must be [R, T]")
-    rows, T = values.shape
+        raise ValueError("values must be [R, T] (or [T, R] with time_major)")
+    rows, T = (values.shape[1], values.shape[0]) if time_major else values.shape
+    shape = tuple(values.shape)
     for name, t in (("lp_old", lp_old), ("lp_new", lp_new), ("rewards", rewards), ("done", done),
                     ("entropy", entropy)):
-        if tuple(t.shape) != (rows, T):
-            raise ValueError(f"`{name}` has shape {tuple(t.shape)}, expected {(rows, T)}")
+        if tuple(t.shape) != shape:
+            raise ValueError(f"`{name}` has shape {tuple(t.shape)}, expected {shape}")
     if bootstrap.numel() != rows:
         raise ValueError("bootstrap must have one entry per row")
     if inv_n is None:
         inv_n = 1.0 / float(max(rows * T, 1))
-    vs = torch.empty((rows, T), dtype=torch.float32, device=dev)
-    adv = torch.empty((rows, T), dtype=torch.float32, device=dev)
+    vs = torch.empty(shape, dtype=torch.float32, device=dev)
+    adv = torch.empty(shape, dtype=torch.float32, device=dev)
     loss4 = torch.empty(4, dtype=torch.float32, device=dev)
-    dlp = torch.empty((rows, T), dtype=torch.float32, device=dev) if want_grads else None
-    dv = torch.empty((rows, T), dtype=torch.float32, device=dev) if want_grads else None
+    dlp = torch.empty(shape, dtype=torch.float32, device=dev) if want_grads else None
+    dv = torch.empty(shape, dtype=torch.float32, device=dev) if want_grads else None
     ws = workspace if workspace is not None else vtrace_workspace(dev, rows)
-    with torch.cuda.device(dev), _Launch("vtrace_loss"):
-        _check(lib.mb_vtrace_loss(_ptr(lp_old), _ptr(lp_new), _ptr(values), _ptr(bootstrap), _ptr(rewards),
-                                  _ptr(done), _ptr(entropy), rows, T, T, T,
+    entry, pitch = (lib.mb_vtrace_loss_tmajor, rows) if time_major else (lib.mb_vtrace_loss, T)
+    with torch.cuda.device(dev), _Launch("vtrace_loss_tmajor" if time_major else "vtrace_loss"):
+        _check(entry(_ptr(lp_old), _ptr(lp_new), _ptr(values), _ptr(bootstrap), _ptr(rewards),
+                                  _ptr(done), _ptr(entropy), rows, T, pitch, pitch,
                                   float(gamma), float(rho_bar), float(c_bar), float(pg_rho_bar),
                                   float(entropy_coef), float(inv_n),
                                   _ptr(vs), _ptr(adv), _ptr(loss4), _ptr(dlp), _ptr(dv),
@@ -340,10 +344,10 @@ class VTraceLoss(torch.autograd.Function):
 
     @staticmethod
     def forward(ctx, lp_new, values, entropy, lp_old, bootstrap, rewards, done, gamma, rho_bar, c_bar,
-                pg_rho_bar, entropy_coef, inv_n):
+                pg_rho_bar, entropy_coef, inv_n, time_major=False):
         out = vtrace_loss(lp_old, lp_new, values, bootstrap, rewards, done, entropy, gamma=gamma,
                           rho_bar=rho_bar, c_bar=c_bar, pg_rho_bar=pg_rho_bar, entropy_coef=entropy_coef,
-                          inv_n=inv_n, want_grads=True)
+                          inv_n=inv_n, want_grads=True, time_major=time_major)
         ctx.save_for_backward(out["d_logp"], out["d_values"])
         ctx.entropy_coef = float(entropy_coef)
         ctx.inv_n = float(inv_n) if inv_n is not None else 1.0 / float(max(values.numel(), 1))
@@ -358,4 +362,4 @@ class VTraceLoss(torch.autograd.Function):
         g_v = g_loss4[1] + g_loss4[3]
         g_en = (g_loss4[2] - ctx.entropy_coef * g_loss4[3]) * ctx.inv_n
         return (d_logp * g_pg, d_values * g_v, g_en.expand_as(d_logp), None, None, None, None,
-                None, None, None, None, None, None)
+                None, None, None, None, None, None, None)

@@ -257,3 +257,29 @@ def test_train_driver_runs_actors_and_learner(tmp_path):
     lines = open(name + "Losses.csv").read().strip().splitlines()
     assert lines[0] == "update,pg_loss,value_loss,entropy_loss,total_loss,update time" and len(lines) == 4
     assert open(name + ".csv").read().splitlines()[0] == "Return,steps"
+
+
+def test_time_major_learner_step_matches_oracle_on_transposed_batch():
+    """PPO_learn(time_major=True): rows are real trajectories.  The oracle gets the same data
+    re-ordered to (row, t), which is what its reshape((R, T+1)) assumes."""
+    from microbeast_b200 import synth
+    from microbeast_b200.learner import PPO_learn
+    from oracle.learner import ref_learn_step
+    h = w = 8
+    T, rows = 12, 6
+    mine, ref = _pair(h, w, seed=77)
+    batch = synth.make_rollout_batch(h, w, T, rows, seed=4, preset="dense")          # flat order (t, row)
+    with torch.no_grad():
+        o, _ = ref.get_action(batch, learning=True)
+    batch["logprobs"] = o["logprobs"] + 0.3 * torch.randn(o["logprobs"].shape, generator=torch.Generator().manual_seed(2))
+
+    def to_row_major(x):
+        return x.reshape((T + 1, rows) + tuple(x.shape[1:])).transpose(0, 1).reshape(x.shape)
+
+    want = ref_learn_step(ref, {k: to_row_major(v) for k, v in batch.items()},
+                          torch.optim.SGD(ref.parameters(), lr=0.0), 3, T, 2)
+    got = PPO_learn(mine, mine, "tm", batch, torch.optim.SGD(mine.parameters(), lr=0.0), 3, T, 2, time_major=True)
+    np.testing.assert_allclose(got, want, rtol=E2E_RTOL)
+    for (n1, p1), (n2, p2) in zip(mine.named_parameters(), ref.named_parameters()):
+        ok, worst = close_rms(p1.grad, p2.grad, 20 * E2E_RTOL)
+        assert ok, (n1, worst)

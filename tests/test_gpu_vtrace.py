@@ -175,3 +175,26 @@ def test_autograd_function():
     _assert_close(lp.grad, ref["d_logp"], "autograd d_logp")
     _assert_close(v.grad, ref["d_values"], "autograd d_values")
     _assert_close(e.grad, ref["d_entropy"], "autograd d_entropy")
+
+
+@pytest.mark.parametrize("rows,T", [(256, 80), (33, 7), (1000, 44), (5, 1), (4096, 129), (130, 512)])
+def test_time_major_kernel(rows, T):
+    """mb_vtrace_loss_tmajor on [T, R] arrays: the oracle on the transposed inputs, and the row-major
+    kernel bit for bit."""
+    _, ops, synth, ovt = _mods()
+    g = torch.Generator().manual_seed(rows + 31 * T)
+    t = synth.make_vtrace_inputs(rows, T, gen=g)
+    t["done"] = torch.rand((rows, T), generator=g) < 0.05
+    ref = ovt.vtrace_losses_and_grads(t["lp_old"], t["lp_new"], t["values"], t["bootstrap"], t["rewards"],
+                                      t["done"], t["entropy"])
+    ref["lp_new_in"] = t["lp_new"]
+    c = {k: (v.t().contiguous() if v.dim() == 2 else v).cuda() for k, v in t.items()}
+    out = ops.vtrace_loss(c["lp_old"], c["lp_new"], c["values"], c["bootstrap"], c["rewards"], c["done"],
+                          c["entropy"], time_major=True)
+    assert out["vs"].shape == (T, rows)
+    back = {k: (v.t() if torch.is_tensor(v) and v.dim() == 2 else v) for k, v in out.items()}
+    _compare(back, ref)
+    rm = _run(ops, t)
+    for k in ("vs", "pg_advantages", "d_logp", "d_values"):
+        assert torch.equal(back[k], rm[k]), k
+    assert torch.allclose(out["loss4"], rm["loss4"], rtol=1e-6, atol=0)
