@@ -279,7 +279,18 @@ def test_time_major_learner_step_matches_oracle_on_transposed_batch():
     want = ref_learn_step(ref, {k: to_row_major(v) for k, v in batch.items()},
                           torch.optim.SGD(ref.parameters(), lr=0.0), 3, T, 2)
     got = PPO_learn(mine, mine, "tm", batch, torch.optim.SGD(mine.parameters(), lr=0.0), 3, T, 2, time_major=True)
-    np.testing.assert_allclose(got, want, rtol=E2E_RTOL)
+    g_tm = [p.grad.clone() for p in mine.parameters()]
+    # same device, same encoder: the time-major path on (t,row) data equals the row-major path on (row,t) data
+    rowm = PPO_learn(mine, mine, "rm", {k: to_row_major(v) for k, v in batch.items()},
+                     torch.optim.SGD(mine.parameters(), lr=0.0), 3, T, 2)
+    np.testing.assert_allclose(got, rowm, rtol=2e-5)
+    for a, p in zip(g_tm, mine.parameters()):
+        ok, worst = close_rms(p.grad, a, 1e-4)
+        assert ok, worst
+    # against the CPU oracle: pg (and total) are means of signed terms |logp * adv| ~ 100x their mean here,
+    # so the fp32 encoder difference (cuDNN vs MKL) shows at 1e-4..1e-3 relative; value / entropy at 1e-4
+    np.testing.assert_allclose(got[1:3], want[1:3], rtol=E2E_RTOL)
+    np.testing.assert_allclose(got, want, rtol=1e-3)
     for (n1, p1), (n2, p2) in zip(mine.named_parameters(), ref.named_parameters()):
-        ok, worst = close_rms(p1.grad, p2.grad, 20 * E2E_RTOL)
+        ok, worst = close_rms(g_tm[[n for n, _ in mine.named_parameters()].index(n1)], p2.grad, 20 * E2E_RTOL)
         assert ok, (n1, worst)
