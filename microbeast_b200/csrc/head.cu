@@ -6,14 +6,15 @@
 //
 // Data layout.  logits [N, 78*C] f32, mask [N, 78*C] u8, action [N, 7*C] i64 and uniforms
 // [N, 7*C] f32 are all contiguous, i.e. arrays of *cells*: 312 B + 78 B + 56 B (+ 28 B) per cell.
-// A CTA streams tiles of TC=64 consecutive cells of one frame through a 3-stage shared-memory
-// ring: one elected producer thread issues 1-D bulk copies (cp.async.bulk -> SASS UBLKCP) that
-// complete on an mbarrier; six consumer warps read the tile out of shared memory with
-// thread-per-cell (29 small-component logits) and lane-pair-per-cell (the 49-way component)
-// mappings, so every global byte is fetched exactly once, fully coalesced, with no register
-// staging.  Backward / sampling outputs are written in place into the stage and leave through
-// bulk stores.  Per-frame sums are reduced in a fixed order (lane shuffle tree -> per-warp
-// partial -> producer thread), so results are run-to-run deterministic and need no atomics.
+// A CTA streams tiles of TC (32/64/128) consecutive cells of one frame through an NSTAGE-deep
+// shared-memory ring: one elected producer thread issues 1-D bulk copies (cp.async.bulk -> SASS
+// UBLKCP) that complete on an mbarrier; three consumer warps per 32 cells read the tile out of
+// shared memory with thread-per-cell (29 small-component logits) and lane-pair-per-cell (the
+// 49-way component) mappings, so every global byte is fetched exactly once, fully coalesced, with
+// no register staging.  The backward writes dlogits in place into the stage and ships it with a
+// bulk store; sampled actions go straight to global memory.  Per-frame sums are reduced in a fixed
+// order (lane shuffle tree -> per-warp partial -> producer thread), so results are run-to-run
+// deterministic and need no atomics and no scratch memory.
 //
 // Roofline: HBM-bound.  Algorithmic bytes per cell: eval fwd 446, eval bwd 758, sample 474
 // (+8 / +8 / +4..8 per frame) -- SURVEY.md section 8(d).

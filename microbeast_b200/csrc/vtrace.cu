@@ -9,13 +9,15 @@
 // Layout (reference D2): every input is [R, T] with TIME contiguous.  The recurrence is serial in
 // time and independent per row, so one thread owns one row.  A thread walking its row backwards
 // in time straight from global memory would touch 32 different 128-B lines per warp request;
-// instead each 32-thread CTA stages [32 rows x 32 steps] tiles of the six inputs through TMA
-// (cp.async.bulk.tensor.2d, SASS UTMALDG; 128-B swizzle so that per-thread float4 reads are bank
-// conflict free) into a multi-stage shared-memory ring, walks the time tiles from the end,
+// instead a CTA (compute warp + TMA warp) stages [32 rows x 32|16 steps] tiles of the inputs through
+// TMA (cp.async.bulk.tensor.2d, SASS UTMALDG; 128-B / 64-B swizzle so that per-thread float4 reads
+// are bank conflict free) into a multi-stage shared-memory ring, walks the time tiles from the end,
 // overwrites the tiles in place with vs / adv / d_logp / d_values and writes them back with TMA
-// stores (UTMASTG).  Loss sums are carried per thread (fp32 inside a tile, fp64 across tiles),
+// stores (UTMASTG).  Loss sums are carried per thread (fp32 inside 32 steps, fp64 across),
 // reduced by a fixed shuffle tree, written per CTA to a workspace and folded by the last CTA to
 // arrive (ticket counter) in a fixed order: deterministic, one launch, no float atomics.
+// Three kernels share the arithmetic (vt_step): the TMA kernel, a generic thread-per-row kernel
+// for layouts TMA cannot describe, and a time-major kernel for [T, R] arrays.
 //
 // Roofline: HBM-bound, 29 B per [r,t] element forward (+8 B with the two gradient outputs).
 // Shapes below ~1e7 elements are launch/latency bound and L2 resident.
