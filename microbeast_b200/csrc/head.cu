@@ -80,7 +80,9 @@ constexpr size_t head_smem_bytes() {
 // ---------------------------------------------------------------------------------------------
 __device__ __forceinline__ constexpr int ucdf_offset(int n) { return n == 4 ? 0 : (n == 6 ? 3 : (n == 7 ? 8 : 14)); }
 
-__device__ __forceinline__ void ucdf_fill(double* tab) {
+// The table holds, per edge, the smallest fp32 value that is >= the fp64 edge: for an fp32 uniform u,
+// u >= edge_fp64  <=>  u >= that fp32 value, so the exact decision needs no fp64 at run time.
+__device__ __forceinline__ void ucdf_fill(float* tab) {
     const int ns[4] = {4, 6, 7, 49};
     for (int j = 0; j < 4; ++j) {
         const int n = ns[j];
@@ -88,15 +90,15 @@ __device__ __forceinline__ void ucdf_fill(double* tab) {
         double acc = 0.0;
         for (int k = 0; k < n - 1; ++k) {
             acc += p;                               // sequential, like numpy.cumsum
-            tab[ucdf_offset(n) + k] = acc;
+            tab[ucdf_offset(n) + k] = __double2float_ru(acc);
         }
     }
 }
 
 // Uniform (fully masked, quirk Q1) component: exact count from the table around floor(u*n).
-__device__ __forceinline__ int ucdf_pick(const double* tab, int n, float u) {
-    const double* t = tab + ucdf_offset(n);
-    const double ud = double(u);
+__device__ __forceinline__ int ucdf_pick(const float* tab, int n, float u) {
+    const float* t = tab + ucdf_offset(n);
+    const float ud = u;
     // floor(fl32(u*n)) is within one of the exact count (table entries are (k+1)/n up to 1e-16 and the
     // fp32 product is off by at most n*2^-24), so one look at the two neighbouring edges settles it
     const int a = min(max(int(u * float(n)), 0), n - 1);
@@ -175,7 +177,7 @@ __device__ __forceinline__ float sample_guard(float S, float W, int len) {
 // ---------------------------------------------------------------------------------------------
 template <int MODE>
 __device__ __forceinline__ void a_role_cell(float* zc, const uint8_t* mc, int64_t* ac, const float* uni,
-                                            float g_lp, float g_h, int* status, const double* ucdf, bool active,
+                                            float g_lp, float g_h, int* status, const float* ucdf, bool active,
                                             float& lp, float& en) {
     constexpr int OFF[6] = {0, 6, 10, 14, 18, 22};
     constexpr int LEN[6] = {6, 4, 4, 4, 4, 7};
@@ -230,10 +232,10 @@ __device__ __forceinline__ void a_role_cell(float* zc, const uint8_t* mc, int64_
                 cnt += (t >= c) ? 1 : 0;
                 near = near || (fabsf(t - c) <= guard);
             }
-            if (sc[k].dead) {                  // uniform over all n entries: exact table decision
-                cnt = ucdf_pick(ucdf, LEN[k], u);
-                near = false;
-            }
+            // uniform over all n entries when fully masked: exact table decision (branch-free select)
+            const int cnt_dead = ucdf_pick(ucdf, LEN[k], u);
+            cnt = sc[k].dead ? cnt_dead : cnt;
+            near = near && !sc[k].dead;
             a[k] = cnt;
             near_bits |= (near && active) ? (1u << k) : 0u;
         }
@@ -309,7 +311,7 @@ __device__ __forceinline__ void a_role_cell(float* zc, const uint8_t* mc, int64_
 template <int MODE>
 __device__ __forceinline__ void b_role_cell(bool active, int half, float* zc, const uint8_t* mc, int64_t* ac,
                                             const float* uni, float g_lp, float g_h, int* status,
-                                            const double* ucdf, float& lp, float& en) {
+                                            const float* ucdf, float& lp, float& en) {
     constexpr int OFF = 29, LEN = 49;
     const int pb = 30 + 24 * half;
     const bool has_x = (half == 0);
@@ -398,10 +400,10 @@ __device__ __forceinline__ void b_role_cell(bool active, int half, float* zc, co
         cnt += __shfl_xor_sync(0xffffffffu, cnt, 1);
         near = (__shfl_xor_sync(0xffffffffu, int(near), 1) != 0) || near;
         a = cnt;
-        if (sc.dead) {                         // uniform over all 49 entries: exact table decision
-            a = ucdf_pick(ucdf, LEN, u);
-            near = false;
-        }
+        // uniform over all 49 entries when fully masked: exact table decision (branch-free select)
+        const int a_dead = ucdf_pick(ucdf, LEN, u);
+        a = sc.dead ? a_dead : a;
+        near = near && !sc.dead;
         unsigned flagged = __ballot_sync(0xffffffffu, near && has_x && active);
         while (flagged) {
             const int src = __ffs(flagged) - 1;
@@ -453,7 +455,7 @@ __global__ void __launch_bounds__(HeadCfg<TC, MODE>::kThreads) head_kernel(const
     float* part = reinterpret_cast<float*>(smem + size_t(NSTAGE) * Cfg::kStageBytes);   // [NSTAGE][kConsWarps][2]
     uint64_t* full = reinterpret_cast<uint64_t*>(part + NSTAGE * Cfg::kConsWarps * 2);
     uint64_t* done = full + NSTAGE;
-    double* ucdf = reinterpret_cast<double*>(done + NSTAGE);      // sample mode only
+    float* ucdf = reinterpret_cast<float*>(done + NSTAGE);        // sample mode only
 
     const int warp = threadIdx.x >> 5;
     const int lane = threadIdx.x & 31;
