@@ -59,8 +59,8 @@ def parse_args():
     ap.add_argument("--cpu-rows", type=int, default=32, help="rows of the CPU-baseline sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
-    ap.add_argument("--tf32-info", action="store_true",
-                    help="also time the step with TF32 allowed in the PyTorch encoder (reported under info)")
+    ap.add_argument("--no-tf32-info", dest="tf32_info", action="store_false",
+                    help="skip the informational leg that times the step with TF32 allowed in the PyTorch encoder")
     ap.add_argument("--wire", default="compact", choices=["compact", "plain"],
                     help="host batch format of the e2e leg (compact = the rollout store's wire format)")
     ap.add_argument("--sweep", default="", choices=["", "vtrace", "head", "variants"])

@@ -11,6 +11,6 @@ timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 2500 --
 echo "ncu launches exit $?" >> gpurun_out/summary.txt
 timeout 900 python bench.py --sweep head --out gpurun_out/sweep_head.jsonl > gpurun_out/sweep_head.log 2>&1; echo "sweep head exit $?" >> gpurun_out/summary.txt
 timeout 900 python bench.py --sweep vtrace --out gpurun_out/sweep_vtrace.jsonl > gpurun_out/sweep_vtrace.log 2>&1; echo "sweep vtrace exit $?" >> gpurun_out/summary.txt
-timeout 900 python bench.py --steps 20 --warmup 5 --tf32-info --out gpurun_out/bench.jsonl > gpurun_out/bench.log 2>&1; echo "bench exit $?" >> gpurun_out/summary.txt
+timeout 900 python bench.py --steps 20 --warmup 5 --out gpurun_out/bench.jsonl > gpurun_out/bench.log 2>&1; echo "bench exit $?" >> gpurun_out/summary.txt
 timeout 600 python bench.py --impl reference --steps 3 --warmup 1 --out gpurun_out/bench_ref.jsonl > gpurun_out/bench_ref.log 2>&1; echo "bench ref exit $?" >> gpurun_out/summary.txt
 cat gpurun_out/summary.txt
