@@ -24,8 +24,11 @@ def _to_device(env_output: dict, device) -> dict:
 
 
 def act(agent, n_envs: int, T: int, buffers, a_id: int, free_queue, full_queue, unroll_length: int,
-        exp_name: str, envs=None, max_unrolls: Optional[int] = None, seed: Optional[int] = None):
-    """Fills rollout buffers until ``None`` arrives on ``free_queue`` (or ``max_unrolls``)."""
+        exp_name: str, envs=None, max_unrolls: Optional[int] = None, seed: Optional[int] = None, server=None):
+    """Fills rollout buffers until ``None`` arrives on ``free_queue`` (or ``max_unrolls``).
+
+    ``server``: an ``inference.InferenceServer``; the actor then sends its ``get_action`` requests
+    there (batched with the other actors') instead of running the model itself."""
     if envs is None:
         raise RuntimeError("act(): pass envs= (gym-microRTS is unavailable here; see env_packer.SyntheticVecEnv)")
     packer = envs if isinstance(envs, Env_Packer) else Env_Packer(envs, a_id, exp_name)
@@ -37,6 +40,8 @@ def act(agent, n_envs: int, T: int, buffers, a_id: int, free_queue, full_queue, 
     cells = agent.cells
 
     def policy(env_output):
+        if server is not None:
+            return server.infer(env_output)
         dev = _to_device({k: env_output[k] for k in ("obs", "action_mask")}, device)
         u = torch.rand((n_envs, 7 * cells), device=device, generator=gen)
         with torch.no_grad():

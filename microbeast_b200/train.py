@@ -35,7 +35,8 @@ from .parallel import GradAllReducer
 def train(exp_name: str, *, env_factory: Optional[Callable[[int, int, int], object]] = None, n_actors: int = 10,
           n_envs: int = 6, env_size: int = 8, T: int = 64, B: int = 2, total_steps: int = 10_000_000,
           device: Optional[str] = None, lr: float = 2.5e-4, eps: float = 1e-5, seed: int = 0,
-          reducer: Optional[GradAllReducer] = None, compact: bool = True, log: bool = False) -> List[list]:
+          reducer: Optional[GradAllReducer] = None, compact: bool = True, log: bool = False,
+          batched_inference: bool = True) -> List[list]:
     """Runs actors + learner until ``total_steps`` env-frames have been learned from
     (``step += n_envs*B*T`` per update, ``microbeast.py:230``).  Returns the loss rows that were
     also appended to ``<exp_name>Losses.csv``.
@@ -66,11 +67,15 @@ def train(exp_name: str, *, env_factory: Optional[Callable[[int, int, int], obje
         free_queue.put(index)                                                # microbeast.py:174-175
 
     model_lock = threading.Lock()         # actors read the weights the learner updates in place
+    server = None
+    if batched_inference:                 # one batched get_action for all actors (inference.py)
+        from .inference import InferenceServer
+        server = InferenceServer(model, max_batch_envs=n_actors * n_envs, seed=seed).start()
     threads = []
     for i in range(n_actors):                                                # microbeast.py:179-191
         th = threading.Thread(target=act, daemon=True,
                               args=(model, n_envs, T, buffers, i, free_queue, full_queue, T, exp_name),
-                              kwargs=dict(envs=env_factory(i, n_envs, env_size), seed=seed * 7919 + i))
+                              kwargs=dict(envs=env_factory(i, n_envs, env_size), seed=seed * 7919 + i, server=server))
         th.start()
         threads.append(th)
 
@@ -93,5 +98,7 @@ def train(exp_name: str, *, env_factory: Optional[Callable[[int, int, int], obje
         free_queue.put(None)              # the sentinel act() stops on (microbeast.py:67-68)
     for th in threads:
         th.join(timeout=30)
+    if server is not None:
+        server.stop()
     mbuf.release(buffers)
     return rows

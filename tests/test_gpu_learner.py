@@ -294,3 +294,41 @@ def test_time_major_learner_step_matches_oracle_on_transposed_batch():
     for (n1, p1), (n2, p2) in zip(mine.named_parameters(), ref.named_parameters()):
         ok, worst = close_rms(g_tm[[n for n, _ in mine.named_parameters()].index(n1)], p2.grad, 20 * E2E_RTOL)
         assert ok, (n1, worst)
+
+
+def test_inference_server_batches_actors_and_keeps_their_actions():
+    """InferenceServer: requests of several actor threads are evaluated as one batch; every actor
+    gets exactly the actions it would get alone (the policy head is independent per frame)."""
+    import threading
+    from microbeast_b200 import synth
+    from microbeast_b200.inference import InferenceServer
+    mine, _ = _pair(8, 8, seed=5)
+    n_actors, n_envs = 4, 3
+    g = torch.Generator().manual_seed(0)
+    reqs = []
+    for a in range(n_actors):
+        env_out = dict(obs=synth.make_obs(n_envs, 8, 8, gen=g).view(1, 1, n_envs, 8, 8, 27),
+                       action_mask=synth.make_masks(n_envs, 64, "dense", gen=g).view(1, n_envs, -1))
+        reqs.append((env_out, synth.make_uniforms(n_envs, 64, gen=g)))
+    alone = []
+    for env_out, u in reqs:
+        with torch.no_grad():
+            out, _ = mine.get_action({k: v.cuda() for k, v in env_out.items()}, uniforms=u.cuda())
+        alone.append({k: out[k].cpu() for k in ("action", "logprobs", "baseline")})
+    server = InferenceServer(mine, max_batch_envs=n_actors * n_envs, max_wait_ms=200.0).start()
+    got = [None] * n_actors
+
+    def worker(i):
+        got[i] = server.infer(reqs[i][0], uniforms=reqs[i][1])
+
+    threads = [threading.Thread(target=worker, args=(i,)) for i in range(n_actors)]
+    for t in threads:
+        t.start()
+    for t in threads:
+        t.join(timeout=60)
+    server.stop()
+    assert server.served == n_actors and server.max_seen >= 2          # requests really were batched
+    for i in range(n_actors):
+        assert torch.equal(got[i]["action"], alone[i]["action"])
+        assert got[i]["baseline"].shape == (1, n_envs) and got[i]["policy_logits"].shape == (n_envs, 78 * 64)
+        assert torch.allclose(got[i]["logprobs"], alone[i]["logprobs"], rtol=1e-5, atol=1e-5)
