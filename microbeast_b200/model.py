@@ -85,6 +85,40 @@ class CategoricalMasked:
         return self._eval(action)[2]
 
 
+class _Conv3x3(torch.autograd.Function):
+    """3x3 / stride 1 / pad 1 convolution whose backward-data pass is itself a forward convolution
+    (with the kernel flipped and its channel axes swapped).  Same mathematics as autograd's
+    ``conv2d`` backward; the point is which cuDNN kernel runs: for these small-channel fp32 shapes
+    cuDNN's data-gradient kernel (``dgrad2d_grouped_direct``) is ~3x slower than its forward
+    implicit-GEMM kernel (``profiles/r01_step_launches_c2.csv``), and it was 37 % of the step."""
+
+    @staticmethod
+    def forward(ctx, x, weight, bias):
+        ctx.save_for_backward(x, weight)
+        return F.conv2d(x, weight, bias, padding=1)
+
+    @staticmethod
+    def backward(ctx, g):
+        x, weight = ctx.saved_tensors
+        g = g.contiguous()
+        gx = None
+        if ctx.needs_input_grad[0]:
+            gx = F.conv2d(g, weight.flip(2, 3).transpose(0, 1).contiguous(), None, padding=1)
+        _, gw, gb = torch.ops.aten.convolution_backward(
+            g, x, weight, [weight.shape[0]], [1, 1], [1, 1], [1, 1], False, [0, 0], 1, [False, True, True])
+        return gx, gw, gb
+
+
+def conv3x3(conv: nn.Conv2d, x: torch.Tensor) -> torch.Tensor:
+    """``conv(x)`` for the encoder's 3x3 convolutions; on CUDA it goes through :class:`_Conv3x3`."""
+    if x.is_cuda and FAST_CONV_BACKWARD and torch.is_grad_enabled():
+        return _Conv3x3.apply(x, conv.weight, conv.bias)
+    return conv(x)
+
+
+FAST_CONV_BACKWARD = True
+
+
 class Residual_Block(nn.Module):
     """relu-conv-relu-conv + skip -- reference ``model.py:56-73``."""
 
@@ -95,8 +129,8 @@ class Residual_Block(nn.Module):
         self.conv1 = nn.Conv2d(channels, channels, kernel_size=3, padding=1)
 
     def forward(self, x):
-        y = self.conv0(F.relu(x))
-        y = self.conv1(F.relu(y))
+        y = conv3x3(self.conv0, F.relu(x))
+        y = conv3x3(self.conv1, F.relu(y))
         return y + x
 
 
@@ -116,7 +150,7 @@ class ConvSequence(nn.Module):
         return (self._out_channels, (h + 1) // 2, (w + 1) // 2)
 
     def forward(self, x):
-        x = F.max_pool2d(self.conv(x), kernel_size=3, stride=2, padding=1)
+        x = F.max_pool2d(conv3x3(self.conv, x), kernel_size=3, stride=2, padding=1)
         return self.res_block1(self.res_block0(x))
 
 

@@ -11,7 +11,9 @@ h = w = 16; T = 80; rows = 256; cells = h * w; n = rows * (T + 1)
 g = torch.Generator(device=dev).manual_seed(0)
 obs = synth.make_obs(n, h, w, gen=g, device=dev, dtype=torch.uint8)
 
-def run(name, channels_last, tf32, benchmark=True, nchw_copy=False, cudnn=True, deterministic=False):
+def run(name, channels_last, tf32, benchmark=True, nchw_copy=False, cudnn=True, deterministic=False, fast_bwd=False):
+    import microbeast_b200.model as mm
+    mm.FAST_CONV_BACKWARD = fast_bwd
     torch.backends.cudnn.enabled = cudnn
     torch.backends.cudnn.deterministic = deterministic
     torch.backends.cudnn.allow_tf32 = tf32
@@ -40,8 +42,8 @@ def run(name, channels_last, tf32, benchmark=True, nchw_copy=False, cudnn=True, 
     e.record(); torch.cuda.synchronize()
     print(f"{name:40s} {s.elapsed_time(e) / 5:8.2f} ms/iter", flush=True)
 
-run("nchw-copy fp32 cudnn OFF (native conv)", False, False, nchw_copy=True, cudnn=False)
-run("nchw-copy fp32 cudnn deterministic", False, False, nchw_copy=True, deterministic=True)
+run("nchw-copy fp32, dgrad as forward conv", False, False, nchw_copy=True, fast_bwd=True)
+run("channels_last fp32, dgrad as forward conv", True, False, fast_bwd=True)
 run("channels_last fp32", True, False)
 run("nchw-copy + nchw weights fp32", False, False, nchw_copy=True)
 run("nhwc view + nchw weights fp32", False, False)
