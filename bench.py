@@ -59,6 +59,8 @@ def parse_args():
     ap.add_argument("--cpu-rows", type=int, default=32, help="rows of the CPU-baseline sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--sparse-head", action="store_true",
+                    help="headline with Agent.sparse_head (actor logits only for cells with a valid action)")
     ap.add_argument("--no-tf32-info", dest="tf32_info", action="store_false",
                     help="skip the informational leg that times the step with TF32 allowed in the PyTorch encoder")
     ap.add_argument("--wire", default="compact", choices=["compact", "plain"],
@@ -222,6 +224,7 @@ def run_ours(args):
     model = Agent((h, w, 27), nvec, cells).to(dev)
     with torch.no_grad():
         model.actor.weight.normal_(0, 0.01)
+    model.sparse_head = bool(args.sparse_head)
     opt = torch.optim.Adam(model.parameters(), lr=2.5e-4, eps=1e-5, fused=True)
     reducer = GradAllReducer() if world > 1 else None
 
@@ -337,6 +340,16 @@ def run_ours(args):
         info = {"encoder_tf32": {"value": frames / (ms_tf32 * 1e-3), "unit": UNIT, "ms_per_step": ms_tf32,
                                  "note": "not the headline: TF32 tensor-core math in the PyTorch encoder only; "
                                          "the policy-head and V-trace kernels are unchanged (fp32)"}}
+
+    if not args.sparse_head:
+        # informational: the same step with the sparse actor head (logits only for active cells)
+        model.sparse_head = True
+        ms_sp, _, _, _ = timed(lambda: step(dev_batch, False), max(3, min(args.steps, 5)), 3)
+        model.sparse_head = False
+        info = dict(info or {})
+        info["sparse_head"] = {"value": frames / (ms_sp * 1e-3), "unit": UNIT, "ms_per_step": ms_sp,
+                               "note": "opt-in Agent.sparse_head: fp32, same losses and gradients; policy_logits "
+                                       "is not produced for fully masked cells"}
 
     # ---- cpu baseline (rank 0, N=1) ------------------------------------------------------
     cpu = None

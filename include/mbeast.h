@@ -76,6 +76,19 @@ MB_API int mb_head_sample(const float* logits, const uint8_t* mask, const float*
                    float* logp_out, float* ent_out, int64_t n_frames, int32_t cells, int32_t* status,
                    void* stream);
 
+/* Cell-list forms of the two eval entry points, for a sparse actor head that computes logits only for
+ * cells with at least one valid action (a fully masked cell contributes exactly 0 to log-prob, entropy
+ * and gradients whatever its logits are: reference model.py:43 + fp32 absorption, quirk Q1).
+ *   logits / mask [n_cells, 78], action [n_cells, 7]; n_cells a multiple of 64 (pad with masked cells);
+ *   cell_out4 [4, n_cells] f32 = log-prob of the six small components, their entropy, log-prob of the
+ *   49-way component, its entropy (the caller adds the pairs and scatters them to frames);
+ *   g_logp_cell / g_ent_cell [n_cells] upstream gradients per cell; dlogits_out [n_cells, 78]. */
+MB_API int mb_head_eval_cells_fwd(const float* logits, const uint8_t* mask, const int64_t* action,
+                                  float* cell_out4, int64_t n_cells, int32_t* status, void* stream);
+MB_API int mb_head_eval_cells_bwd(const float* logits, const uint8_t* mask, const int64_t* action,
+                                  const float* g_logp_cell, const float* g_ent_cell, float* dlogits_out,
+                                  int64_t n_cells, int32_t* status, void* stream);
+
 /* Bytes of scratch mb_vtrace_loss needs for `rows` rows (ticket word + per-CTA partial sums). */
 MB_API size_t mb_vtrace_workspace_bytes(int64_t rows);
 

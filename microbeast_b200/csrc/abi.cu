@@ -38,6 +38,9 @@ int head_eval_bwd(const float*, const uint8_t*, const int64_t*, const float*, co
                   int*, cudaStream_t);
 int head_sample(const float*, const uint8_t*, const float*, int64_t*, float*, float*, long long, int, int*,
                 cudaStream_t);
+int head_eval_cells_fwd(const float*, const uint8_t*, const int64_t*, float*, long long, int*, cudaStream_t);
+int head_eval_cells_bwd(const float*, const uint8_t*, const int64_t*, const float*, const float*, float*, long long, int*,
+                        cudaStream_t);
 void head_set_tuning(int ctas_per_sm, int grid_override, int variant);
 void vtrace_set_tuning(int force_generic, int variant, int l2_promo);
 size_t vtrace_workspace_bytes(long long rows);
@@ -72,6 +75,18 @@ int mb_head_sample(const float* logits, const uint8_t* mask, const float* unifor
                    void* stream) {
     return mb::head_sample(logits, mask, uniforms, action_out, logp_out, ent_out, n_frames, cells, status,
                            static_cast<cudaStream_t>(stream));
+}
+
+int mb_head_eval_cells_fwd(const float* logits, const uint8_t* mask, const int64_t* action, float* cell_out4,
+                           int64_t n_cells, int32_t* status, void* stream) {
+    return mb::head_eval_cells_fwd(logits, mask, action, cell_out4, n_cells, status, static_cast<cudaStream_t>(stream));
+}
+
+int mb_head_eval_cells_bwd(const float* logits, const uint8_t* mask, const int64_t* action, const float* g_logp_cell,
+                           const float* g_ent_cell, float* dlogits_out, int64_t n_cells, int32_t* status,
+                           void* stream) {
+    return mb::head_eval_cells_bwd(logits, mask, action, g_logp_cell, g_ent_cell, dlogits_out, n_cells, status,
+                                   static_cast<cudaStream_t>(stream));
 }
 
 size_t mb_vtrace_workspace_bytes(int64_t rows) { return mb::vtrace_workspace_bytes(rows); }

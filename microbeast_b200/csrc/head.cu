@@ -37,6 +37,9 @@ struct HeadParams {
     float* ent_out;            // [N] (may be null in sample mode)
     float* dlogits;            // [N, 78C]   bwd
     int64_t* action_out;       // [N, 7C]    sample
+    float* cell_out;           // per-cell mode (eval fwd): [4][n_frames*cells] = logp of the six small
+                               // components, their entropy, logp of the 49-way component, its entropy
+    int per_cell;              // 1: outputs / upstream gradients are per CELL, not per frame
     int* status;               // optional device status word
     long long n_frames;
     int cells;
@@ -543,7 +546,7 @@ __global__ void __launch_bounds__(HeadCfg<TC, MODE>::kThreads) head_kernel(const
                     acc_lp += ps[2 * w];
                     acc_en += ps[2 * w + 1];
                 }
-                if ((j % tpf) == tpf - 1) {
+                if ((j % tpf) == tpf - 1 && !p.per_cell) {
                     const long long frame = tile_frame(j);
                     p.logp_out[frame] = acc_lp;
                     if (p.ent_out) p.ent_out[frame] = acc_en;
@@ -613,15 +616,17 @@ __global__ void __launch_bounds__(HeadCfg<TC, MODE>::kThreads) head_kernel(const
             const int s = int(j % NSTAGE);
             uint8_t* st = stages + size_t(s) * Cfg::kStageBytes;
             const int nc = min(TC, p.cells - tile_cell0(j));
+            const bool active = cell_in_tile < nc;
+            const long long cell_global = tile_frame(j) * p.cells + tile_cell0(j) + cell_in_tile;
             float g_lp = 0.f, g_h = 0.f;
             if (MODE == kEvalBwd) {
-                const long long frame = tile_frame(j);
-                g_lp = __ldg(p.g_logp + frame);
-                g_h = __ldg(p.g_ent + frame);
+                // upstream gradients: one pair per frame, or (cell-list mode) one pair per cell
+                const long long gi = p.per_cell ? (active ? cell_global : 0) : tile_frame(j);
+                g_lp = __ldg(p.g_logp + gi);
+                g_h = __ldg(p.g_ent + gi);
             }
             mbar_wait(&full[s], uint32_t((j / NSTAGE) & 1), p.status);
 
-            const bool active = cell_in_tile < nc;
             float* zc = reinterpret_cast<float*>(st) + cell_in_tile * kLogitsPerCell;
             const uint8_t* mc = st + Cfg::kOffMask + cell_in_tile * kLogitsPerCell;
             // eval: the taken actions staged in shared memory; sample: the global output row of this cell
@@ -636,7 +641,15 @@ __global__ void __launch_bounds__(HeadCfg<TC, MODE>::kThreads) head_kernel(const
             } else {
                 b_role_cell<MODE>(active, half, zc, mc, ac, uc, g_lp, g_h, p.status, ucdf, lp, en);
             }
-            if (MODE != kEvalBwd) {
+            if (MODE == kEvalFwd && p.per_cell) {
+                // cell-list mode: no per-frame sum; each cell's two partial results go out as they are
+                const long long total = p.n_frames * p.cells;
+                if (active && (role == 0 || half == 0)) {
+                    float* o = p.cell_out + (role == 0 ? 0 : 2) * total + cell_global;
+                    o[0] = lp;
+                    o[total] = en;
+                }
+            } else if (MODE != kEvalBwd) {
                 lp = warp_sum(lp);
                 en = warp_sum(en);
                 if (lane == 0) {
@@ -763,6 +776,46 @@ int head_sample(const float* logits, const uint8_t* mask, const float* uniforms,
     p.logits = logits; p.mask = mask; p.uniforms = uniforms; p.action_out = action_out; p.logp_out = logp_out;
     p.ent_out = ent_out; p.status = status; p.n_frames = n_frames; p.cells = cells;
     return dispatch_head<kSample>(p, stream);
+}
+
+// Cell-list mode: the inputs are an arbitrary list of cells ([n_cells, 78] logits / mask, [n_cells, 7]
+// actions) instead of whole frames -- what a sparse actor head produces when it computes logits only
+// for cells that have a valid action.  Results are per cell; the caller scatters them to frames.
+int head_eval_cells_fwd(const float* logits, const uint8_t* mask, const int64_t* action, float* cell_out4,
+                        long long n_cells, int* status, cudaStream_t stream) {
+    if (n_cells < 0 || n_cells % 64 != 0) {
+        set_error("head_eval_cells_fwd: n_cells=%lld must be a non-negative multiple of 64 (pad with masked cells)",
+                  n_cells);
+        return MB_ERR_INVALID;
+    }
+    if (n_cells == 0) return MB_OK;
+    if (!logits || !mask || !action || !cell_out4) {
+        set_error("head_eval_cells_fwd: null pointer");
+        return MB_ERR_INVALID;
+    }
+    HeadParams p{};
+    p.logits = logits; p.mask = mask; p.action_in = action; p.cell_out = cell_out4; p.per_cell = 1;
+    p.status = status; p.n_frames = n_cells / 64; p.cells = 64;
+    return dispatch_head<kEvalFwd>(p, stream);
+}
+
+int head_eval_cells_bwd(const float* logits, const uint8_t* mask, const int64_t* action, const float* g_logp_cell,
+                        const float* g_ent_cell, float* dlogits, long long n_cells, int* status,
+                        cudaStream_t stream) {
+    if (n_cells < 0 || n_cells % 64 != 0) {
+        set_error("head_eval_cells_bwd: n_cells=%lld must be a non-negative multiple of 64 (pad with masked cells)",
+                  n_cells);
+        return MB_ERR_INVALID;
+    }
+    if (n_cells == 0) return MB_OK;
+    if (!logits || !mask || !action || !g_logp_cell || !g_ent_cell || !dlogits) {
+        set_error("head_eval_cells_bwd: null pointer");
+        return MB_ERR_INVALID;
+    }
+    HeadParams p{};
+    p.logits = logits; p.mask = mask; p.action_in = action; p.g_logp = g_logp_cell; p.g_ent = g_ent_cell;
+    p.dlogits = dlogits; p.per_cell = 1; p.status = status; p.n_frames = n_cells / 64; p.cells = 64;
+    return dispatch_head<kEvalBwd>(p, stream);
 }
 
 }  // namespace mb

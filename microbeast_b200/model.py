@@ -171,6 +171,7 @@ class Agent(nn.Module):
         self.nvec = nvec
         self.cells = len(nvec) // COMPONENTS_PER_CELL
         self.nchw_copy = True
+        self.sparse_head = False
         self.obs_planes = c
         shape = (c, h, w)
         layers = []
@@ -197,6 +198,44 @@ class Agent(nn.Module):
         # channels-last view on B200 (profiles/r01_encoder_formats.txt); values are identical
         return x.contiguous() if (x.is_cuda and self.nchw_copy) else x
 
+    def _sparse_head(self, hidden, action_mask, action):
+        """Learner-mode head on the ACTIVE cells only (opt-in, ``self.sparse_head = True``).
+
+        A cell whose 78 mask bytes are all zero contributes exactly 0 to the frame's log-prob and
+        entropy and gets zero gradient whatever its logits are (quirk Q1), so the actor Linear is
+        evaluated only for (frame, cell) pairs with a valid action: pairs are grouped by cell, each
+        group padded to the longest one, ``logits = hidden[frames] @ W_cell^T + b_cell`` as one batched
+        matmul, the cell list goes through the cell-list head kernels and per-cell results are
+        scattered back to their frames.  Same values as the dense path up to fp32 summation order;
+        ``policy_logits`` is not produced."""
+        n, cells = hidden.shape[0], self.cells
+        mask3 = action_mask.view(n, cells, LOGITS_PER_CELL)
+        active = (mask3 != 0).any(dim=2)                                   # [N, C]
+        counts = active.sum(dim=0)                                         # active frames per cell
+        pairs = active.t().nonzero()                                       # [P, 2] = (cell, frame), grouped by cell
+        lmax = int(counts.max().item()) if pairs.shape[0] else 0           # host syncs: nonzero + this
+        lmax = max(-(-max(lmax, 1) // 64) * 64, 64)                        # groups of 64 cells for the kernel
+        # frame indices of the active pairs, one row per cell, padded with frame n (a zero row of `hid`)
+        starts = torch.cumsum(counts, 0) - counts
+        pos = torch.arange(pairs.shape[0], device=hidden.device) - starts[pairs[:, 0]]
+        fidx = torch.full((cells, lmax), n, dtype=torch.int64, device=hidden.device)
+        fidx[pairs[:, 0], pos] = pairs[:, 1]
+        valid = fidx < n
+        hid = torch.cat([hidden, hidden.new_zeros(1, hidden.shape[1])])[fidx]                    # [C, lmax, 256]
+        w = self.actor.weight.view(cells, LOGITS_PER_CELL, -1)
+        b = self.actor.bias.view(cells, 1, LOGITS_PER_CELL)
+        logits_c = torch.baddbmm(b, hid, w.transpose(1, 2)).reshape(-1, LOGITS_PER_CELL)      # [C*lmax, 78]
+        cidx = torch.arange(cells, device=hidden.device).unsqueeze(1).expand(cells, lmax)
+        safe = fidx.clamp(max=n - 1)
+        mask_c = torch.where(valid.unsqueeze(2), mask3[safe, cidx], torch.zeros((), dtype=mask3.dtype, device=hidden.device))
+        act_c = action.view(n, cells, COMPONENTS_PER_CELL)[safe, cidx]
+        lp_c, en_c = ops.HeadEvalCells.apply(logits_c, mask_c.reshape(-1, LOGITS_PER_CELL).contiguous(),
+                                             act_c.reshape(-1, COMPONENTS_PER_CELL).contiguous())
+        flat = fidx.reshape(-1)
+        logprobs = hidden.new_zeros(n + 1).index_add(0, flat, lp_c)[:n]
+        entropy = hidden.new_zeros(n + 1).index_add(0, flat, en_c)[:n]
+        return logprobs, entropy
+
     def forward(self, input_dict: dict, agent_state=(), learning=False, inds=()):
         return self.network(self._obs(input_dict, learning))
 
@@ -213,7 +252,7 @@ class Agent(nn.Module):
         Q6; values and summed gradients are identical).
         """
         hidden = self.forward(input_dict, agent_state, learning, inds)
-        logits = self.actor(hidden)                                             # model.py:167
+        logits = None if (learning and self.sparse_head) else self.actor(hidden)   # model.py:167
         baseline = self.critic(hidden).view(1, -1)                              # model.py:205
         if not learning:
             action_mask = input_dict["action_mask"][0, ...]                     # model.py:173
@@ -228,6 +267,10 @@ class Agent(nn.Module):
             torch.cuda.current_stream().wait_event(ready)
         action = input_dict["action"]                                           # model.py:182
         action_mask = input_dict["action_mask"]                                 # model.py:188
+        if self.sparse_head:
+            logprobs, entropy = self._sparse_head(hidden, action_mask, action)
+            return (dict(action=action, policy_logits=None, logprobs=logprobs, baseline=baseline,
+                         entropy=entropy), ())
         logprobs, entropy = ops.HeadEval.apply(logits, action_mask, action)
         return (dict(action=action, policy_logits=logits, logprobs=logprobs, baseline=baseline,
                      entropy=entropy), ())

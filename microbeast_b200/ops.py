@@ -337,6 +337,41 @@ class HeadEval(torch.autograd.Function):
         return head_eval_bwd(logits, mask, action, g_logp.contiguous(), g_ent.contiguous()), None, None
 
 
+class HeadEvalCells(torch.autograd.Function):
+    """Cell-list form of :class:`HeadEval`: ``(logits [M,78], mask [M,78], action [M,7]) ->
+    (logp_cell [M], ent_cell [M])``; ``M`` a multiple of 64 (pad with fully masked cells)."""
+
+    @staticmethod
+    def forward(ctx, logits, mask, action):
+        dev = _need_cuda(logits=logits, mask=mask, action=action)
+        logits = _as(logits, torch.float32, "logits")
+        mask = _mask_u8(mask)
+        action = _as(action, torch.int64, "action")
+        m = logits.shape[0]
+        if logits.shape[1] != LOGITS_PER_CELL or tuple(mask.shape) != (m, LOGITS_PER_CELL) or \
+                tuple(action.shape) != (m, COMPONENTS_PER_CELL):
+            raise ValueError("cell lists must be logits/mask [M,78] and action [M,7]")
+        out4 = torch.empty((4, m), dtype=torch.float32, device=dev)
+        with torch.cuda.device(dev), _Launch("head_eval_cells_fwd"):
+            _check(lib.mb_head_eval_cells_fwd(_ptr(logits), _ptr(mask), _ptr(action), _ptr(out4), m,
+                                              _ptr(status_word(dev)), _stream()))
+        ctx.save_for_backward(logits, mask, action)
+        return out4[0] + out4[2], out4[1] + out4[3]
+
+    @staticmethod
+    def backward(ctx, g_logp, g_ent):
+        logits, mask, action = ctx.saved_tensors
+        m = logits.shape[0]
+        dev = logits.device
+        g_logp = torch.zeros(m, device=dev) if g_logp is None else g_logp.contiguous()
+        g_ent = torch.zeros(m, device=dev) if g_ent is None else g_ent.contiguous()
+        out = torch.empty_like(logits)
+        with torch.cuda.device(dev), _Launch("head_eval_cells_bwd"):
+            _check(lib.mb_head_eval_cells_bwd(_ptr(logits), _ptr(mask), _ptr(action), _ptr(g_logp), _ptr(g_ent),
+                                              _ptr(out), m, _ptr(status_word(dev)), _stream()))
+        return out, None, None
+
+
 class VTraceLoss(torch.autograd.Function):
     """Differentiable wrt ``lp_new``, ``values``, ``entropy``; everything V-trace is
     ``no_grad`` exactly as in the reference (``utils.py:289``).  Returns

@@ -332,3 +332,35 @@ def test_inference_server_batches_actors_and_keeps_their_actions():
         assert torch.equal(got[i]["action"], alone[i]["action"])
         assert got[i]["baseline"].shape == (1, n_envs) and got[i]["policy_logits"].shape == (n_envs, 78 * 64)
         assert torch.allclose(got[i]["logprobs"], alone[i]["logprobs"], rtol=1e-5, atol=1e-5)
+
+
+@pytest.mark.parametrize("preset,h", [("dense", 8), ("realistic", 8), ("all_masked", 8), ("all_valid", 8), ("dense", 16)])
+def test_sparse_head_equals_dense_head(preset, h):
+    """Agent.sparse_head: logits only for cells with a valid action; log-prob, entropy, losses and every
+    parameter gradient equal the dense path (fully masked cells contribute exactly 0, quirk Q1)."""
+    from microbeast_b200 import synth
+    from microbeast_b200.learner import PPO_learn
+    mine, _ = _pair(h, h, seed=31)
+    T, rows = 6, 5
+    batch = synth.make_rollout_batch(h, h, T, rows, seed=12, preset=preset, full_keys=False)
+    batch["logprobs"] = -torch.rand(batch["reward"].shape) * 20
+    dev = {k: v.cuda() for k, v in batch.items()}
+    with torch.no_grad():
+        a, _ = mine.get_action(dev, learning=True)
+        mine.sparse_head = True
+        b, _ = mine.get_action(dev, learning=True)
+        mine.sparse_head = False
+    assert b["policy_logits"] is None
+    for k in ("logprobs", "entropy"):
+        ok, worst = close_rms(b[k], a[k], 1e-5)
+        assert ok, (k, worst)
+    assert torch.equal(a["baseline"], b["baseline"])
+    four_d = PPO_learn(mine, mine, "d", batch, torch.optim.SGD(mine.parameters(), lr=0.0), rows, T, 1)
+    g_d = [p.grad.clone() for p in mine.parameters()]
+    mine.sparse_head = True
+    four_s = PPO_learn(mine, mine, "s", batch, torch.optim.SGD(mine.parameters(), lr=0.0), rows, T, 1)
+    mine.sparse_head = False
+    np.testing.assert_allclose(four_s, four_d, rtol=2e-5, atol=1e-7)
+    for (name, p), gd in zip(mine.named_parameters(), g_d):
+        ok, worst = close_rms(p.grad, gd, 1e-4)
+        assert ok, (name, worst)
