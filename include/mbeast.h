@@ -166,6 +166,11 @@ MB_API int mb_unpack_rollout(const uint8_t* mask_bits, const uint8_t* action_u8,
 MB_API int mb_unpack_obs(const uint32_t* obs_bits, float* obs_out, int64_t n_frames, int32_t cells,
                          int32_t planes, void* stream);
 
+/* active[c] = 1 if cell c of mask [n_cells,78] has any valid action, else 0 (the cell list of the
+ * sparse actor head; the reference has no counterpart -- it evaluates every cell,
+ * model.py:98-104, and fully masked cells contribute exactly 0, quirk Q1). */
+MB_API int mb_active_cells(const uint8_t* mask, uint8_t* active, int64_t n_cells, void* stream);
+
 /* Tuning knobs for benchmarking (not part of the reference surface).  Keys:
  *   "head_ctas_per_sm" (0 = as many as fit), "head_grid" (0 = auto), "head_variant" (tile /
  *   pipeline shape: 0 = 64 cells x 3 stages, 1 = 64x2, 2 = 64x4, 3 = 32x3, 4 = 32x5, 5 = 128x3, 6 = 128x2, 7 = 32x2; -1 = per-kernel default),

@@ -62,6 +62,39 @@ __global__ void __launch_bounds__(256) unpack_obs_kernel(const uint32_t* __restr
     }
 }
 
+// Which cells have any valid action (the cell list of Agent.sparse_head): one byte out per 78 in.
+// A warp stages 32 cells (2496 B = 156 x 16 B, coalesced) in shared memory, then every lane ORs
+// its own cell's 39 half-words.  78 B read + 1 B written per cell.
+__global__ void __launch_bounds__(256) active_cells_kernel(const uint8_t* __restrict__ mask, uint8_t* __restrict__ active,
+                                                           long long n_cells) {
+    constexpr int kGroupBytes = 32 * kLogitsPerCell, kVecs = kGroupBytes / 16;
+    static_assert(kGroupBytes % 16 == 0 && kLogitsPerCell % 2 == 0, "a 32-cell group is whole 16-byte vectors");
+    __shared__ __align__(16) uint8_t stage[8][kGroupBytes];
+    const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
+    const long long warp = blockIdx.x * 8ll + wib, n_warps = gridDim.x * 8ll;
+    const bool vec = (reinterpret_cast<uintptr_t>(mask) & 15) == 0;
+    const long long groups = vec ? n_cells / 32 : 0;
+    for (long long g = warp; g < groups; g += n_warps) {
+        const uint4* src = reinterpret_cast<const uint4*>(mask + g * kGroupBytes);
+        uint4* dst = reinterpret_cast<uint4*>(stage[wib]);
+#pragma unroll
+        for (int k = 0; k < (kVecs + 31) / 32; ++k)
+            if (lane + 32 * k < kVecs) dst[lane + 32 * k] = __ldg(src + lane + 32 * k);
+        __syncwarp();
+        const uint16_t* mine = reinterpret_cast<const uint16_t*>(stage[wib] + lane * kLogitsPerCell);
+        uint32_t any = 0;
+#pragma unroll
+        for (int k = 0; k < kLogitsPerCell / 2; ++k) any |= mine[k];
+        active[g * 32 + lane] = any ? 1 : 0;
+        __syncwarp();
+    }
+    for (long long c = groups * 32 + warp * 32 + lane; c < n_cells; c += n_warps * 32) {
+        uint32_t any = 0;
+        for (int k = 0; k < kLogitsPerCell; ++k) any |= mask[c * kLogitsPerCell + k];
+        active[c] = any ? 1 : 0;
+    }
+}
+
 }  // namespace mb
 
 extern "C" int mb_unpack_obs(const uint32_t* obs_bits, float* obs_out, int64_t n_frames, int32_t cells,
@@ -109,5 +142,23 @@ extern "C" int mb_unpack_rollout(const uint8_t* mask_bits, const uint8_t* action
                                                       (long long)n_frames * cells * mb::kCompsPerCell);
         MB_CUDA(cudaGetLastError());
     }
+    return MB_OK;
+}
+
+extern "C" int mb_active_cells(const uint8_t* mask, uint8_t* active, int64_t n_cells, void* stream) {
+    if (n_cells < 0) {
+        mb::set_error("mb_active_cells: n_cells=%lld out of range", (long long)n_cells);
+        return MB_ERR_INVALID;
+    }
+    if (n_cells == 0) return MB_OK;
+    if (!mask || !active) {
+        mb::set_error("mb_active_cells: null pointer");
+        return MB_ERR_INVALID;
+    }
+    int dev = 0;
+    MB_CUDA(cudaGetDevice(&dev));
+    mb::active_cells_kernel<<<mb::sm_count(dev) * 8, 256, 0, static_cast<cudaStream_t>(stream)>>>(mask, active,
+                                                                                                 n_cells);
+    MB_CUDA(cudaGetLastError());
     return MB_OK;
 }

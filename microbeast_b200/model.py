@@ -210,7 +210,7 @@ class Agent(nn.Module):
         ``policy_logits`` is not produced."""
         n, cells = hidden.shape[0], self.cells
         mask3 = action_mask.view(n, cells, LOGITS_PER_CELL)
-        active = (mask3 != 0).any(dim=2)                                   # [N, C]
+        active = ops.active_cells(action_mask, cells)                                   # [N, C]
         counts = active.sum(dim=0)                                         # active frames per cell
         pairs = active.t().nonzero()                                       # [P, 2] = (cell, frame), grouped by cell
         lmax = int(counts.max().item()) if pairs.shape[0] else 0           # host syncs: nonzero + this
@@ -221,7 +221,9 @@ class Agent(nn.Module):
         fidx = torch.full((cells, lmax), n, dtype=torch.int64, device=hidden.device)
         fidx[pairs[:, 0], pos] = pairs[:, 1]
         valid = fidx < n
-        hid = torch.cat([hidden, hidden.new_zeros(1, hidden.shape[1])])[fidx]                    # [C, lmax, 256]
+        # index_select: its backward is an index_add (atomics), not the sort-based index_put of x[idx]
+        hid = torch.cat([hidden, hidden.new_zeros(1, hidden.shape[1])]).index_select(0, fidx.reshape(-1))
+        hid = hid.view(cells, lmax, -1)                    # [C, lmax, 256]
         w = self.actor.weight.view(cells, LOGITS_PER_CELL, -1)
         b = self.actor.bias.view(cells, 1, LOGITS_PER_CELL)
         logits_c = torch.baddbmm(b, hid, w.transpose(1, 2)).reshape(-1, LOGITS_PER_CELL)      # [C*lmax, 78]

@@ -249,6 +249,19 @@ def unpack_obs(obs_bits: torch.Tensor, planes: int = 27, out: Optional[torch.Ten
     return out
 
 
+def active_cells(action_mask: torch.Tensor, cells: int) -> torch.Tensor:
+    """``[N, cells]`` bool: cells of ``action_mask [N, 78*cells]`` with at least one valid action."""
+    dev = _need_cuda(action_mask=action_mask)
+    action_mask = _as(action_mask, torch.uint8, "action_mask")
+    n = action_mask.shape[0]
+    if action_mask.dim() != 2 or action_mask.shape[1] != cells * LOGITS_PER_CELL:
+        raise ValueError("action_mask must be [N, 78*cells]")
+    out = torch.empty((n, cells), dtype=torch.uint8, device=dev)
+    with torch.cuda.device(dev), _Launch("active_cells"):
+        _check(lib.mb_active_cells(_ptr(action_mask), _ptr(out), n * cells, _stream()))
+    return out.view(torch.bool)
+
+
 def vtrace_workspace(device: torch.device, rows: int) -> torch.Tensor:
     """Zero-initialised scratch for ``mb_vtrace_loss`` (cached per device; the kernel keeps
     its ticket word at zero between calls).  Calls on different streams that may overlap

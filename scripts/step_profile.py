@@ -13,6 +13,7 @@ torch.manual_seed(0)
 model = Agent((h, w, 27), [6, 4, 4, 4, 4, 7, 49] * cells, cells).to(dev)
 with torch.no_grad():
     model.actor.weight.normal_(0, 0.01)
+model.sparse_head = "--sparse-head" in sys.argv
 opt = torch.optim.Adam(model.parameters(), lr=2.5e-4, eps=1e-5, fused=True)
 batch = synth.make_rollout_batch(h, w, T, rows, seed=1, device=dev, obs_dtype=torch.uint8, full_keys=False)
 batch["logprobs"] = -torch.rand(batch["reward"].shape, device=dev) * 30

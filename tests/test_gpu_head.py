@@ -220,3 +220,21 @@ def test_full_size_properties_c2():
     dz2 = ops.head_eval_bwd(logits, mask, act, 2 * g1, zero)
     assert torch.allclose(dz2, 2 * dz1, rtol=1e-6, atol=1e-7)
     ops.check_status(dev)
+
+
+@pytest.mark.parametrize("n,cells,offset", [(1, 1, 0), (3, 16, 0), (7, 37, 0), (129, 64, 0), (5, 16, 6), (2000, 256, 0)])
+def test_active_cells_matches_any(n, cells, offset):
+    """mb_active_cells == (mask != 0).any over each cell's 78 entries; ragged tails and a base that
+    is not 16-byte aligned take the scalar path."""
+    g = torch.Generator().manual_seed(n * 31 + cells)
+    flat = torch.zeros(offset + n * cells * 78, dtype=torch.uint8)
+    body = (torch.rand(n, cells, 78, generator=g) < 0.02) & (torch.rand(n, cells, 1, generator=g) < 0.3)
+    body[0, 0, 77] = True                      # last byte of a cell alone
+    if n * cells > 1:
+        body[-1, -1] = False
+        body[-1, -1, 0] = True                 # first byte of the last cell alone
+    flat[offset:] = body.reshape(-1).to(torch.uint8) * 255      # any non-zero byte counts
+    mask = flat.cuda()[offset:].view(n, cells * 78)
+    got = ops.active_cells(mask, cells)
+    assert got.dtype == torch.bool and got.shape == (n, cells)
+    assert torch.equal(got.cpu(), body.any(dim=2))
