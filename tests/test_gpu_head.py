@@ -226,6 +226,7 @@ def test_full_size_properties_c2():
 def test_active_cells_matches_any(n, cells, offset):
     """mb_active_cells == (mask != 0).any over each cell's 78 entries; ragged tails and a base that
     is not 16-byte aligned take the scalar path."""
+    ops, _, _ = _mods()
     g = torch.Generator().manual_seed(n * 31 + cells)
     flat = torch.zeros(offset + n * cells * 78, dtype=torch.uint8)
     body = (torch.rand(n, cells, 78, generator=g) < 0.02) & (torch.rand(n, cells, 1, generator=g) < 0.3)
