@@ -147,7 +147,7 @@ def learner_losses(learner_model: nn.Module, batch: Dict[str, torch.Tensor], row
 def PPO_learn(actor_model: nn.Module, learner_model, exp_name: str, batch, optimizer, B: int, T: int,
               n_envs: int, lock=threading.Lock(), *, gamma=0.99, rho_bar=1.0, c_bar=1.0, pg_rho_bar=1.0,
               entropy_coef=0.01, reducer: Optional[GradAllReducer] = None, time_major: bool = False,
-              sync: bool = True):
+              sync: bool = True, sparse_head=None):
     """Performs a learning (optimization) step -- reference ``libs/utils.py:223-342``.
 
     ``batch``: flat ``[N, ...]`` tensors, ``N = B*n_envs*(T+1)``, on the host (copied to the
@@ -155,7 +155,9 @@ def PPO_learn(actor_model: nn.Module, learner_model, exp_name: str, batch, optim
     Returns ``[pg_loss, value_loss, entropy_loss, total_loss]`` as python floats
     (``utils.py:342``); with ``sync=False`` the 4-element device tensor is returned instead
     and nothing synchronises.  ``reducer`` sums gradients across data-parallel ranks; the
-    returned losses are then the global ones.
+    returned losses are then the global ones.  ``sparse_head`` (False / True / "auto") overrides
+    ``learner_model.sparse_head`` for this step: evaluate the actor head only on cells with a valid
+    action (same losses and gradients; costs two host syncs inside the step).
     """
     if not isinstance(lock, type(threading.Lock())):
         lock = threading.Lock()      # reference quirk Q15: microbeast.py:251 passes exp_name here
@@ -166,6 +168,8 @@ def PPO_learn(actor_model: nn.Module, learner_model, exp_name: str, batch, optim
         if ready is not None:
             dev_batch["_ready"] = ready
         world = reducer.world_size if reducer is not None else 1
+        if sparse_head is not None:
+            learner_model.sparse_head = sparse_head
         loss4, _aux = learner_losses(learner_model, dev_batch, rows, T, gamma=gamma, rho_bar=rho_bar,
                                      c_bar=c_bar, pg_rho_bar=pg_rho_bar, entropy_coef=entropy_coef,
                                      global_rows=rows * world, time_major=time_major)

@@ -199,7 +199,8 @@ class Agent(nn.Module):
         return x.contiguous() if (x.is_cuda and self.nchw_copy) else x
 
     def _sparse_head(self, hidden, action_mask, action):
-        """Learner-mode head on the ACTIVE cells only (opt-in, ``self.sparse_head = True``).
+        """Learner-mode head on the ACTIVE cells only (opt-in: ``self.sparse_head = True``, or ``"auto"``
+        to fall back to the dense path -- by returning None -- when at least half the grid is active).
 
         A cell whose 78 mask bytes are all zero contributes exactly 0 to the frame's log-prob and
         entropy and gets zero gradient whatever its logits are (quirk Q1), so the actor Linear is
@@ -215,6 +216,8 @@ class Agent(nn.Module):
         pairs = active.t().nonzero()                                       # [P, 2] = (cell, frame), grouped by cell
         lmax = int(counts.max().item()) if pairs.shape[0] else 0           # host syncs: nonzero + this
         lmax = max(-(-max(lmax, 1) // 64) * 64, 64)                        # groups of 64 cells for the kernel
+        if self.sparse_head == "auto" and 2 * lmax > n:
+            return None                      # padded cell list >= half the dense grid: the dense path is cheaper
         # frame indices of the active pairs, one row per cell, padded with frame n (a zero row of `hid`)
         starts = torch.cumsum(counts, 0) - counts
         pos = torch.arange(pairs.shape[0], device=hidden.device) - starts[pairs[:, 0]]
@@ -233,10 +236,13 @@ class Agent(nn.Module):
         act_c = action.view(n, cells, COMPONENTS_PER_CELL)[safe, cidx]
         lp_c, en_c = ops.HeadEvalCells.apply(logits_c, mask_c.reshape(-1, LOGITS_PER_CELL).contiguous(),
                                              act_c.reshape(-1, COMPONENTS_PER_CELL).contiguous())
-        flat = fidx.reshape(-1)
-        logprobs = hidden.new_zeros(n + 1).index_add(0, flat, lp_c)[:n]
-        entropy = hidden.new_zeros(n + 1).index_add(0, flat, en_c)[:n]
-        return logprobs, entropy
+        # back to frames: every (frame, cell) slot is written at most once, then a fixed-order row sum
+        # (deterministic, unlike an atomic index_add); padding lands in the dropped row n
+        grid = hidden.new_zeros((2, n + 1, cells))
+        grid = grid.index_put((torch.arange(2, device=hidden.device).view(2, 1, 1), fidx, cidx),
+                              torch.stack([lp_c, en_c]).view(2, cells, lmax))
+        per_frame = grid[:, :n].sum(dim=2)
+        return per_frame[0], per_frame[1]
 
     def forward(self, input_dict: dict, agent_state=(), learning=False, inds=()):
         return self.network(self._obs(input_dict, learning))
@@ -254,9 +260,9 @@ class Agent(nn.Module):
         Q6; values and summed gradients are identical).
         """
         hidden = self.forward(input_dict, agent_state, learning, inds)
-        logits = None if (learning and self.sparse_head) else self.actor(hidden)   # model.py:167
         baseline = self.critic(hidden).view(1, -1)                              # model.py:205
         if not learning:
+            logits = self.actor(hidden)                                         # model.py:167
             action_mask = input_dict["action_mask"][0, ...]                     # model.py:173
             if uniforms is None:
                 uniforms = torch.rand((logits.shape[0], self.cells * COMPONENTS_PER_CELL),
@@ -269,10 +275,12 @@ class Agent(nn.Module):
             torch.cuda.current_stream().wait_event(ready)
         action = input_dict["action"]                                           # model.py:182
         action_mask = input_dict["action_mask"]                                 # model.py:188
-        if self.sparse_head:
-            logprobs, entropy = self._sparse_head(hidden, action_mask, action)
-            return (dict(action=action, policy_logits=None, logprobs=logprobs, baseline=baseline,
-                         entropy=entropy), ())
+        if self.sparse_head:                  # False (reference-shaped outputs) | True | "auto"
+            sparse = self._sparse_head(hidden, action_mask, action)
+            if sparse is not None:
+                return (dict(action=action, policy_logits=None, logprobs=sparse[0], baseline=baseline,
+                             entropy=sparse[1]), ())
+        logits = self.actor(hidden)                                             # model.py:167
         logprobs, entropy = ops.HeadEval.apply(logits, action_mask, action)
         return (dict(action=action, policy_logits=logits, logprobs=logprobs, baseline=baseline,
                      entropy=entropy), ())

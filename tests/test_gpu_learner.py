@@ -357,10 +357,28 @@ def test_sparse_head_equals_dense_head(preset, h):
     assert torch.equal(a["baseline"], b["baseline"])
     four_d = PPO_learn(mine, mine, "d", batch, torch.optim.SGD(mine.parameters(), lr=0.0), rows, T, 1)
     g_d = [p.grad.clone() for p in mine.parameters()]
-    mine.sparse_head = True
-    four_s = PPO_learn(mine, mine, "s", batch, torch.optim.SGD(mine.parameters(), lr=0.0), rows, T, 1)
+    four_s = PPO_learn(mine, mine, "s", batch, torch.optim.SGD(mine.parameters(), lr=0.0), rows, T, 1,
+                       sparse_head=True)
+    assert mine.sparse_head is True
     mine.sparse_head = False
     np.testing.assert_allclose(four_s, four_d, rtol=2e-5, atol=1e-7)
     for (name, p), gd in zip(mine.named_parameters(), g_d):
         ok, worst = close_rms(p.grad, gd, 1e-4)
         assert ok, (name, worst)
+
+
+@pytest.mark.parametrize("preset,expect_sparse", [("dense", True), ("all_valid", False), ("all_masked", True)])
+def test_sparse_head_auto_picks_by_density(preset, expect_sparse):
+    """sparse_head="auto": the cell list is used while its padded size is under half the dense grid."""
+    from microbeast_b200 import synth
+    mine, _ = _pair(8, 8, seed=5)
+    batch = synth.make_rollout_batch(8, 8, 9, 40, seed=3, preset=preset, full_keys=False)
+    dev = {k: v.cuda() for k, v in batch.items()}
+    with torch.no_grad():
+        a, _ = mine.get_action(dev, learning=True)
+        mine.sparse_head = "auto"
+        c, _ = mine.get_action(dev, learning=True)
+    assert (c["policy_logits"] is None) == expect_sparse
+    for k in ("logprobs", "entropy"):
+        ok, worst = close_rms(c[k], a[k], 1e-5)
+        assert ok, (k, worst)
