@@ -382,3 +382,47 @@ def test_sparse_head_auto_picks_by_density(preset, expect_sparse):
     for k in ("logprobs", "entropy"):
         ok, worst = close_rms(c[k], a[k], 1e-5)
         assert ok, (k, worst)
+
+
+@pytest.mark.parametrize("wire", ["plain", "compact"])
+@pytest.mark.parametrize("opt_name", ["adam", "sgd"])
+def test_graphed_learner_matches_eager_steps(wire, opt_name):
+    """GraphedLearner (one CUDA-graph replay per step) == PPO_learn (eager) over several steps on
+    different batches: losses, and the weights after the last step."""
+    import copy
+    from microbeast_b200 import buffers, synth
+    from microbeast_b200.graphed import GraphedLearner
+    from microbeast_b200.learner import PPO_learn
+    h = 8
+    eager, _ = _pair(h, h, seed=77)
+    with torch.no_grad():
+        eager.actor.weight.normal_(0, 0.01)
+    graphed = copy.deepcopy(eager)
+
+    def make_opt(m):
+        if opt_name == "adam":
+            return torch.optim.Adam(m.parameters(), lr=2.5e-4, eps=1e-5, capturable=True)
+        return torch.optim.SGD(m.parameters(), lr=1e-3)
+    opt_e, opt_g = make_opt(eager), make_opt(graphed)
+    T, rows = 6, 5
+    gl = GraphedLearner(graphed, opt_g, rows, T, 1)
+    for i in range(4):
+        batch = synth.make_rollout_batch(h, h, T, rows, seed=100 + i, preset="dense", full_keys=False)
+        batch["logprobs"] = -torch.rand(batch["reward"].shape) * 20
+        if wire == "compact":
+            batch = buffers.pack_batch(batch)
+        four_e = PPO_learn(eager, eager, "e", batch, opt_e, rows, T, 1)
+        four_g = gl.step(batch)
+        # Adam divides by sqrt(v): noise-level gradient differences (cuDNN's backward is not bit-deterministic)
+        # become lr-sized weight differences, so its trajectories are compared loosely and only through the losses
+        np.testing.assert_allclose(four_g, four_e, rtol=2e-4 if opt_name == "sgd" else 5e-3, atol=1e-6,
+                                   err_msg=f"step {i}")
+    assert gl.launches_per_step.get("head_eval_fwd") == 1 and gl.launches_per_step.get("vtrace_loss") == 1
+    if opt_name == "sgd":
+        for (name, pe), pg in zip(eager.named_parameters(), graphed.parameters()):
+            ok, worst = close_rms(pg, pe, 2e-4)
+            assert ok, (name, worst)
+    with pytest.raises(ValueError):
+        bad = dict(batch)
+        bad["reward"] = batch["reward"][:-1]
+        gl.step(bad)
