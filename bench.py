@@ -44,6 +44,8 @@ WORKLOADS = {
     "c1": (8, 8, 80, 32),
     "c2": (16, 16, 80, 256),
     "c4": (32, 32, 128, 64),
+    # configs[2]: B=1024 rows in total, split over the ranks (strong scaling); rows per GPU = 1024 / N
+    "c3": (16, 16, 80, 1024),
 }
 
 
@@ -158,13 +160,14 @@ def run_reference(args):
     h, w, T, _ = WORKLOADS[args.workload]
     rows = args.cpu_rows
     fps, sec, cores = time_cpu_reference(h, w, T, rows, args.steps, args.warmup, args.preset)
-    sample = (f"{rows} of {args.rows or WORKLOADS[args.workload][3]} rows per step ({rows * (T + 1)} frames), "
+    sample = (f"{rows} of {workload_shape(args)[3]} rows per step ({rows * (T + 1)} frames), "
               f"full reference learner step (oracle port of libs/utils.py:223-342 + model.py:165-216), "
               f"torch CPU, {cores} threads")
     line = {
         "impl": "reference", "metric": METRIC, "value": fps, "unit": UNIT, "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": sec * 1e3, "higher_is_better": True,
-        "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "scaling": "strong" if args.workload == "c3" else "weak", "vs_baseline": None, "dtype": "f32",
+        "data": "synthetic",
         "config": workload_config(args),
         "cpu_baseline": {"value": fps, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
         "e2e": {"value": fps, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
@@ -173,9 +176,17 @@ def run_reference(args):
     emit(line, args)
 
 
-def workload_config(args, rows_override=None):
+def workload_shape(args):
+    """(h, w, T, rows per GPU): c3 is strong scaling -- its 1024 rows are split over the ranks."""
     h, w, T, rows = WORKLOADS[args.workload]
-    rows = rows_override or args.rows or rows
+    if args.workload == "c3":
+        rows = rows // max(args.gpus, 1)
+    return h, w, T, (args.rows or rows)
+
+
+def workload_config(args, rows_override=None):
+    h, w, T, rows = workload_shape(args)
+    rows = rows_override or rows
     return {"workload": f"{args.workload}: {h}x{w} basesWorkers-shaped synthetic rollouts, T={T}, "
                         f"{rows} rows per GPU, full learner step",
             "map": f"{h}x{w}", "T": T, "rows_per_gpu": rows, "frames_per_step_per_gpu": rows * T,
@@ -216,8 +227,7 @@ def run_ours(args):
     torch.backends.cuda.matmul.allow_tf32 = False
     torch.backends.cudnn.benchmark = True
 
-    h, w, T, rows = WORKLOADS[args.workload]
-    rows = args.rows or rows
+    h, w, T, rows = workload_shape(args)
     cells = h * w
     n = rows * (T + 1)
     nvec = [6, 4, 4, 4, 4, 7, 49] * cells
@@ -386,7 +396,8 @@ def run_ours(args):
     if rank == 0:
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
-            "warmup": max(args.warmup, 3), "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak",
+            "warmup": max(args.warmup, 3), "ms_per_step": ms_step, "higher_is_better": True,
+            "scaling": "strong" if args.workload == "c3" else "weak",
             "vs_baseline": None, "dtype": "f32", "data": "synthetic", "config": workload_config(args),
             "clocks": clocks, "e2e": e2e, "gpu_launches": launches, "roofline": roof, "cpu_baseline": cpu,
             "kernels": kernels, "info": info,

@@ -60,5 +60,30 @@ dist.all_reduce(flag, op=dist.ReduceOp.MIN)
 if rank == 0:
     print(f"dp_check world={world} rel_loss={rel_loss:.2e} rel_grad={rel_grad:.2e} ->",
           "PASS" if int(flag.item()) else "FAIL", flush=True)
+
+# graphed data-parallel step (two graphs around the eager NCCL allreduce) vs the eager PPO_learn step
+import copy
+from microbeast_b200.graphed import GraphedLearner
+from microbeast_b200.learner import PPO_learn
+m_e, m_g = copy.deepcopy(model), copy.deepcopy(model)
+o_e, o_g = torch.optim.SGD(m_e.parameters(), lr=1e-3), torch.optim.SGD(m_g.parameters(), lr=1e-3)
+gl = GraphedLearner(m_g, o_g, hi - lo, T, 1, reducer=red)
+worst = 0.0
+for i in range(3):
+    b = synth.make_rollout_batch(h, w, T, rows, seed=200 + i, device=dev, full_keys=False)
+    b["logprobs"] = -torch.rand(b["reward"].shape, device=dev, generator=torch.Generator(device=dev).manual_seed(i)) * 20
+    sh = parallel.shard_batch(b, rows, T, rank, world)
+    four_e = PPO_learn(m_e, m_e, "e", sh, o_e, hi - lo, T, 1, reducer=red)
+    four_g = gl.step(sh)
+    worst = max(worst, max(abs(a - c) / max(abs(a), 1e-6) for a, c in zip(four_e, four_g)))
+pe = torch.cat([p.detach().reshape(-1) for p in m_e.parameters()])
+pg = torch.cat([p.detach().reshape(-1) for p in m_g.parameters()])
+rel_p = float((pe - pg).abs().max() / pe.abs().max())
+ok2 = worst < 2e-4 and rel_p < 1e-5
+flag2 = torch.tensor([1 if ok2 else 0], device=dev)
+dist.all_reduce(flag2, op=dist.ReduceOp.MIN)
+if rank == 0:
+    print(f"dp_check graphed world={world} rel_loss={worst:.2e} rel_param={rel_p:.2e} ->",
+          "PASS" if int(flag2.item()) else "FAIL", flush=True)
 dist.destroy_process_group()
-sys.exit(0 if int(flag.item()) else 1)
+sys.exit(0 if (int(flag.item()) and int(flag2.item())) else 1)

@@ -7,4 +7,7 @@ timeout 600 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --mas
   scripts/dp_check.py > gpurun_out/dp_check_$N.log 2>&1; echo "dp_check $N exit $?" | tee -a gpurun_out/summary_multi.txt
 timeout 900 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29518 \
   bench.py --gpus $N --steps 10 --warmup 3 --out gpurun_out/bench_n$N.jsonl > gpurun_out/bench_n$N.log 2>&1; echo "bench $N exit $?" | tee -a gpurun_out/summary_multi.txt
-tail -n 3 gpurun_out/dp_check_$N.log; tail -c 600 gpurun_out/bench_n$N.log
+# configs[2]: B=1024 rows in total over the N ranks (strong scaling)
+timeout 900 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29519 \
+  bench.py --gpus $N --workload c3 --steps 10 --warmup 3 --no-tf32-info --out gpurun_out/bench_c3_n$N.jsonl > gpurun_out/bench_c3_n$N.log 2>&1; echo "bench c3 $N exit $?" | tee -a gpurun_out/summary_multi.txt
+tail -n 4 gpurun_out/dp_check_$N.log; tail -c 300 gpurun_out/bench_n$N.log; tail -c 300 gpurun_out/bench_c3_n$N.log
