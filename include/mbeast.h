@@ -171,6 +171,18 @@ MB_API int mb_unpack_obs(const uint32_t* obs_bits, float* obs_out, int64_t n_fra
  * model.py:98-104, and fully masked cells contribute exactly 0, quirk Q1). */
 MB_API int mb_active_cells(const uint8_t* mask, uint8_t* active, int64_t n_cells, void* stream);
 
+/* Weight gradient of a 3x3 / stride 1 / pad 1 convolution in fp32 (the encoder's convolutions,
+ * reference model.py:56-109, differentiated by loss.backward() at libs/utils.py:334):
+ *   dW[co,ci,ky,kx] = sum_{n,y,x} dy[n,co,y,x] * x[n,ci,y+ky-1,x+kx-1],  x [n,cin,h,w], dy [n,cout,h,w],
+ * both NCHW contiguous, 16-byte aligned.  The kernel writes one partial dW per CTA:
+ * partials [n_blocks][cout*cin*9]; the caller adds the slots up (fixed order => deterministic).
+ * mb_conv3x3_wgrad_blocks returns n_blocks for a shape on the current device, 0 when the shape is not
+ * covered (the caller keeps its own path: square maps 2..16, (cin,cout) in {(27,16),(16,16),(16,32),
+ * (32,32)} as instantiated in csrc/convgrad.cu), -1 on error. */
+MB_API int mb_conv3x3_wgrad_blocks(int64_t n_frames, int32_t cin, int32_t cout, int32_t h, int32_t w);
+MB_API int mb_conv3x3_wgrad(const float* x, const float* dy, float* partials, int32_t n_blocks, int64_t n_frames,
+                            int32_t cin, int32_t cout, int32_t h, int32_t w, void* stream);
+
 /* Tuning knobs for benchmarking (not part of the reference surface).  Keys:
  *   "head_ctas_per_sm" (0 = as many as fit), "head_grid" (0 = auto), "head_variant" (tile /
  *   pipeline shape: 0 = 64 cells x 3 stages, 1 = 64x2, 2 = 64x4, 3 = 32x3, 4 = 32x5, 5 = 128x3, 6 = 128x2, 7 = 32x2; -1 = per-kernel default),

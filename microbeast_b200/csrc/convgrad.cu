@@ -1,0 +1,325 @@
+// Weight gradient of the encoder's 3x3 / stride 1 / pad 1 convolutions in fp32, for sm_100a.
+//
+// Reference: the encoder of model.py:56-137 (Residual_Block / ConvSequence) is differentiated by
+// loss.backward() at libs/utils.py:334.  The encoder stays on PyTorch; this file replaces ONE cuDNN
+// kernel family inside its backward pass.  For these shapes (16-32 channels, 2x2 .. 16x16 maps,
+// ~2e4 frames) the weight gradient
+//     dW[co, ci, ky, kx] = sum_{n, y, x} dY[n, co, y, x] * X[n, ci, y + ky - 1, x + kx - 1]
+// is a reduction over millions of positions into a tiny output (2.3 k - 9.2 k numbers); cuDNN's
+// fp32 kernels (wgrad_alg0 / alg1) run it at ~8 TFLOP/s and it was 13.6 ms of the 41 ms learner
+// step at 16x16 (profiles/r01_encoder_layers.txt).  Same mathematics, fp32 FMA, only the summation
+// order differs from cuDNN's (which is itself not deterministic; this kernel is).
+//
+// Design (FMA-bound, not HBM-bound: 72 flop per byte read):
+//   * the whole dW lives in REGISTERS: a thread owns 4 output channels x 1 input channel x 9 taps =
+//     36 accumulators; (COUT/4 x CIN) threads cover dW, and G such groups per 256-thread CTA work on
+//     different frames and are summed through shared memory at the end;
+//   * frames are staged into shared memory by cp.async (16-byte LDGSTS, zero-fill past the end),
+//     double buffered, in the NCHW order they have in global memory; channel planes are padded so
+//     that PLANE/4 is odd and the per-lane float4 reads of X (lanes = input channels) are
+//     conflict free while the dY reads are warp broadcasts;
+//   * rows slide through registers (up / mid / down), so per image row a thread issues 1 X-row load
+//     and 4 dY-row loads for 36 * W FMAs; taps that would fall outside the image are skipped at
+//     compile time, so there is no halo;
+//   * persistent CTAs walk the frame chunks; every CTA writes its partial dW to its own slot of a
+//     [grid, COUT*CIN*9] buffer, and the caller adds the slots up (fixed order: deterministic).
+#include "common.cuh"
+
+#include "../../include/mbeast.h"
+
+namespace mb {
+
+int sm_count(int device);
+
+namespace {
+
+constexpr int kWgThreads = 256;
+constexpr int kWgTM = 4;          // output channels per thread
+
+__device__ __forceinline__ void cp_async16(void* dst_smem, const void* src, bool valid) {
+    const uint32_t bytes = valid ? 16u : 0u;            // 0 source bytes: the 16 destination bytes are zero-filled
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(smem_u32(dst_smem)), "l"(src), "r"(bytes)
+                 : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait() {
+    asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory");
+}
+
+template <int CIN_, int COUT_, int H_, int CIS_, int G_, int FG_>
+struct WgCfg {
+    static constexpr int CIN = CIN_, COUT = COUT_, H = H_, W = H_, CIS = CIS_, G = G_, FG = FG_;
+    static constexpr int HW = H * W;
+    static constexpr int PLANE = ((HW / 4) % 2 == 1) ? HW : HW + 4;     // floats; PLANE/4 odd
+    static constexpr int COG = COUT / kWgTM;                            // groups of 4 output channels
+    static constexpr int P = COG * CIS;                                 // threads that cover dW once
+    static constexpr int CH = G * FG;                                   // frames per chunk
+    static constexpr int FRAME = (CIN + COUT) * PLANE;                  // floats per staged frame: X planes, dY planes
+    static constexpr int PIECES = (CIN + COUT) * (HW / 4);              // 16-byte pieces per frame
+    static constexpr int OUT = COUT * CIN * 9;
+    static constexpr int RED = G * P * kWgTM * 9;                       // floats of the end-of-kernel reduction
+    static constexpr int STAGE_FLOATS = 2 * CH * FRAME;
+    static constexpr int SMEM_FLOATS = STAGE_FLOATS > RED ? STAGE_FLOATS : RED;
+    static constexpr int SMEM = SMEM_FLOATS * 4;
+    static_assert(P * G == kWgThreads, "thread layout must fill the CTA");
+    static_assert(COUT % kWgTM == 0 && CIS >= CIN && HW % 4 == 0, "shape");
+    static_assert(H >= 2, "a 1x1 map has a single tap; not handled here");
+};
+
+// One image row of W floats from shared memory.
+template <int W>
+__device__ __forceinline__ void load_row(float (&r)[W], const float* p) {
+    if constexpr (W == 2) {
+        const float2 v = *reinterpret_cast<const float2*>(p);
+        r[0] = v.x;
+        r[1] = v.y;
+    } else {
+#pragma unroll
+        for (int i = 0; i < W / 4; ++i) {
+            const float4 v = *reinterpret_cast<const float4*>(p + 4 * i);
+            r[4 * i + 0] = v.x;
+            r[4 * i + 1] = v.y;
+            r[4 * i + 2] = v.z;
+            r[4 * i + 3] = v.w;
+        }
+    }
+}
+
+// acc[m][ky*3+kx] += dY[m][x] * Xrow_ky[x + kx - 1] for one output row; rows outside the image are
+// compiled out (UP / DN), and so are the columns (static range check on x + kx - 1).
+template <int W, bool UP, bool DN>
+__device__ __forceinline__ void row_fma(float (&acc)[kWgTM][9], const float (&up)[W], const float (&mid)[W],
+                                        const float (&dn)[W], const float* ybase, int plane) {
+    constexpr int XB = W < 8 ? W : 8;                    // dY columns held in registers at a time
+#pragma unroll
+    for (int x0 = 0; x0 < W; x0 += XB) {
+        float d[kWgTM][XB];
+#pragma unroll
+        for (int m = 0; m < kWgTM; ++m) load_row<XB>(d[m], ybase + m * plane + x0);
+#pragma unroll
+        for (int xx = 0; xx < XB; ++xx) {
+            const int x = x0 + xx;
+#pragma unroll
+            for (int kx = 0; kx < 3; ++kx) {
+                const int xi = x + kx - 1;
+                if (xi < 0 || xi >= W) continue;
+#pragma unroll
+                for (int m = 0; m < kWgTM; ++m) {
+                    if (UP) acc[m][0 + kx] = fmaf(d[m][xx], up[xi], acc[m][0 + kx]);
+                    acc[m][3 + kx] = fmaf(d[m][xx], mid[xi], acc[m][3 + kx]);
+                    if (DN) acc[m][6 + kx] = fmaf(d[m][xx], dn[xi], acc[m][6 + kx]);
+                }
+            }
+        }
+    }
+}
+
+// All rows of one frame for this thread's (4 output channels, 1 input channel).
+template <class C>
+__device__ __forceinline__ void frame_fma(float (&acc)[kWgTM][9], const float* xplane, const float* ybase) {
+    constexpr int W = C::W, H = C::H;
+    float up[W], mid[W], dn[W];
+    load_row<W>(mid, xplane);
+    load_row<W>(dn, xplane + W);
+    row_fma<W, false, true>(acc, mid, mid, dn, ybase, C::PLANE);                 // y = 0: no row above
+    if constexpr (H > 2) {
+        // small maps unroll completely; at 16x16 the 14 interior rows would be 8 k FMAs of straight-line
+        // code (> the instruction cache), so they run as a loop unrolled by two
+#pragma unroll(H <= 8 ? H : 2)
+        for (int y = 1; y < H - 1; ++y) {
+#pragma unroll
+            for (int i = 0; i < W; ++i) {
+                up[i] = mid[i];
+                mid[i] = dn[i];
+            }
+            load_row<W>(dn, xplane + (y + 1) * W);
+            row_fma<W, true, true>(acc, up, mid, dn, ybase + y * W, C::PLANE);
+        }
+    }
+#pragma unroll
+    for (int i = 0; i < W; ++i) {
+        up[i] = mid[i];
+        mid[i] = dn[i];
+    }
+    row_fma<W, true, false>(acc, up, mid, mid, ybase + (H - 1) * W, C::PLANE);   // y = H-1: no row below
+}
+
+template <class C>
+__global__ void __launch_bounds__(kWgThreads) conv3x3_wgrad_kernel(const float* __restrict__ x,
+                                                                    const float* __restrict__ dy,
+                                                                    float* __restrict__ partials, long long n_frames) {
+    extern __shared__ __align__(16) float wg_smem[];
+    const int tid = threadIdx.x;
+    const int g = tid / C::P;                       // frame group
+    const int r = tid % C::P;
+    const int cog = r / C::CIS;                     // output channels 4*cog .. 4*cog+3
+    const int ci = r % C::CIS;                      // input channel (lanes past CIN idle along on channel CIN-1)
+    const int ci_eff = ci < C::CIN ? ci : C::CIN - 1;
+    const long long n_chunks = (n_frames + C::CH - 1) / C::CH;
+
+    float acc[kWgTM][9];
+#pragma unroll
+    for (int m = 0; m < kWgTM; ++m)
+#pragma unroll
+        for (int t = 0; t < 9; ++t) acc[m][t] = 0.0f;
+
+    auto stage = [&](long long chunk, int buf) {
+        float* base = wg_smem + buf * (C::CH * C::FRAME);
+        const long long f0 = chunk * C::CH;
+        for (int i = tid; i < C::CH * C::PIECES; i += kWgThreads) {
+            const int fs = i / C::PIECES, piece = i % C::PIECES;
+            const int plane = piece / (C::HW / 4), within = piece % (C::HW / 4);
+            const long long f = f0 + fs;
+            const bool valid = f < n_frames;
+            const float* src = x;
+            if (valid) {
+                src = (plane < C::CIN) ? x + (f * C::CIN + plane) * C::HW + within * 4
+                                       : dy + (f * C::COUT + (plane - C::CIN)) * C::HW + within * 4;
+            }
+            cp_async16(base + fs * C::FRAME + plane * C::PLANE + within * 4, src, valid);
+        }
+        cp_async_commit();
+    };
+
+    long long chunk = blockIdx.x;
+    int buf = 0;
+    if (chunk < n_chunks) stage(chunk, 0);
+    for (; chunk < n_chunks; chunk += gridDim.x) {
+        const long long next = chunk + gridDim.x;
+        if (next < n_chunks) {
+            stage(next, buf ^ 1);           // its buffer was released by the barrier that ended the last iteration
+            cp_async_wait<1>();
+        } else {
+            cp_async_wait<0>();
+        }
+        __syncthreads();
+        const float* base = wg_smem + buf * (C::CH * C::FRAME);
+#pragma unroll 1
+        for (int j = 0; j < C::FG; ++j) {
+            const float* fr = base + (g * C::FG + j) * C::FRAME;
+            frame_fma<C>(acc, fr + ci_eff * C::PLANE, fr + (C::CIN + cog * kWgTM) * C::PLANE);
+        }
+        __syncthreads();
+        buf ^= 1;
+    }
+
+    // fold the G frame groups and write this CTA's slot
+    float* red = wg_smem;
+#pragma unroll
+    for (int m = 0; m < kWgTM; ++m)
+#pragma unroll
+        for (int t = 0; t < 9; ++t) red[tid * (kWgTM * 9) + m * 9 + t] = acc[m][t];
+    __syncthreads();
+    float* out = partials + (long long)blockIdx.x * C::OUT;
+    for (int e = tid; e < C::OUT; e += kWgThreads) {
+        const int co = e / (C::CIN * 9), rem = e % (C::CIN * 9);
+        const int ci2 = rem / 9, tap = rem % 9;
+        float s = 0.0f;
+#pragma unroll
+        for (int gg = 0; gg < C::G; ++gg)
+            s += red[((gg * C::COG + co / kWgTM) * C::CIS + ci2) * (kWgTM * 9) + (co % kWgTM) * 9 + tap];
+        out[e] = s;
+    }
+}
+
+template <class C>
+int wg_grid(int dev, long long n_frames, int* grid) {
+    static int occ[64] = {};
+    int& o = occ[(dev >= 0 && dev < 64) ? dev : 0];
+    if (o == 0) {
+        MB_CUDA(cudaFuncSetAttribute(conv3x3_wgrad_kernel<C>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM));
+        int n = 0;
+        MB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, conv3x3_wgrad_kernel<C>, kWgThreads, C::SMEM));
+        o = n > 0 ? n : 1;
+    }
+    const long long chunks = (n_frames + C::CH - 1) / C::CH;
+    const long long cap = (long long)sm_count(dev) * o;
+    *grid = int(chunks < cap ? (chunks > 0 ? chunks : 1) : cap);
+    return MB_OK;
+}
+
+template <class C>
+int wg_launch(const float* x, const float* dy, float* partials, int n_blocks, long long n_frames, cudaStream_t st) {
+    int dev = 0, grid = 0;
+    MB_CUDA(cudaGetDevice(&dev));
+    const int rc = wg_grid<C>(dev, n_frames, &grid);
+    if (rc != MB_OK) return rc;
+    if (n_blocks != grid) {
+        set_error("mb_conv3x3_wgrad: n_blocks=%d, but mb_conv3x3_wgrad_blocks gives %d for this shape", n_blocks, grid);
+        return MB_ERR_INVALID;
+    }
+    conv3x3_wgrad_kernel<C><<<grid, kWgThreads, C::SMEM, st>>>(x, dy, partials, n_frames);
+    MB_CUDA(cudaGetLastError());
+    return MB_OK;
+}
+
+// shape -> configuration <CIN, COUT, H, ci slots, frame groups, frames per group and chunk>
+#define MB_WG_SHAPES(X)                     \
+    X(27, 16, 16, 32, 2, 1) \
+    X(27, 16, 8, 32, 2, 2)   \
+    X(16, 16, 8, 16, 4, 1)   \
+    X(16, 16, 4, 16, 4, 2)   \
+    X(16, 32, 16, 16, 2, 1) \
+    X(16, 32, 8, 16, 2, 1)   \
+    X(16, 32, 4, 16, 2, 2)   \
+    X(32, 32, 8, 32, 1, 2)   \
+    X(32, 32, 4, 32, 1, 4)   \
+    X(32, 32, 2, 32, 1, 16)
+
+}  // namespace
+
+int conv3x3_wgrad_blocks(long long n_frames, int cin, int cout, int h, int w, int* grid) {
+    *grid = 0;
+    if (h != w) return MB_OK;
+    int dev = 0;
+    MB_CUDA(cudaGetDevice(&dev));
+#define X(CI, CO, HH, CIS, GG, FG) \
+    if (cin == CI && cout == CO && h == HH) return wg_grid<WgCfg<CI, CO, HH, CIS, GG, FG>>(dev, n_frames, grid);
+    MB_WG_SHAPES(X)
+#undef X
+    return MB_OK;          // *grid == 0: shape not covered, the caller keeps its own path
+}
+
+int conv3x3_wgrad(const float* x, const float* dy, float* partials, int n_blocks, long long n_frames, int cin,
+                  int cout, int h, int w, cudaStream_t st) {
+    if (h == w) {
+#define X(CI, CO, HH, CIS, GG, FG)              \
+    if (cin == CI && cout == CO && h == HH)     \
+        return wg_launch<WgCfg<CI, CO, HH, CIS, GG, FG>>(x, dy, partials, n_blocks, n_frames, st);
+        MB_WG_SHAPES(X)
+#undef X
+    }
+    set_error("mb_conv3x3_wgrad: shape cin=%d cout=%d %dx%d is not covered (see mb_conv3x3_wgrad_blocks)", cin, cout, h, w);
+    return MB_ERR_UNSUPPORTED;
+}
+
+}  // namespace mb
+
+extern "C" int mb_conv3x3_wgrad_blocks(int64_t n_frames, int32_t cin, int32_t cout, int32_t h, int32_t w) {
+    if (n_frames < 0 || cin <= 0 || cout <= 0 || h <= 0 || w <= 0) {
+        mb::set_error("mb_conv3x3_wgrad_blocks: n_frames=%lld cin=%d cout=%d %dx%d out of range", (long long)n_frames,
+                      cin, cout, h, w);
+        return -1;
+    }
+    int grid = 0;
+    if (mb::conv3x3_wgrad_blocks(n_frames, cin, cout, h, w, &grid) != MB_OK) return -1;
+    return grid;
+}
+
+extern "C" int mb_conv3x3_wgrad(const float* x, const float* dy, float* partials, int32_t n_blocks, int64_t n_frames,
+                                int32_t cin, int32_t cout, int32_t h, int32_t w, void* stream) {
+    if (n_frames < 0 || n_blocks <= 0) {
+        mb::set_error("mb_conv3x3_wgrad: n_frames=%lld n_blocks=%d out of range", (long long)n_frames, n_blocks);
+        return MB_ERR_INVALID;
+    }
+    if (!x || !dy || !partials) {
+        mb::set_error("mb_conv3x3_wgrad: null pointer");
+        return MB_ERR_INVALID;
+    }
+    if ((reinterpret_cast<uintptr_t>(x) | reinterpret_cast<uintptr_t>(dy)) & 15) {
+        mb::set_error("mb_conv3x3_wgrad: x and dy must be 16-byte aligned");
+        return MB_ERR_INVALID;
+    }
+    return mb::conv3x3_wgrad(x, dy, partials, n_blocks, n_frames, cin, cout, h, w, static_cast<cudaStream_t>(stream));
+}

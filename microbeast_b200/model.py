@@ -104,6 +104,9 @@ class _Conv3x3(torch.autograd.Function):
         gx = None
         if ctx.needs_input_grad[0]:
             gx = F.conv2d(g, weight.flip(2, 3).transpose(0, 1).contiguous(), None, padding=1)
+        gw = ops.conv3x3_wgrad(x, g) if FAST_CONV_WGRAD else None      # csrc/convgrad.cu; None: shape not covered
+        if gw is not None:
+            return gx, gw, g.sum(dim=(0, 2, 3))
         _, gw, gb = torch.ops.aten.convolution_backward(
             g, x, weight, [weight.shape[0]], [1, 1], [1, 1], [1, 1], False, [0, 0], 1, [False, True, True])
         return gx, gw, gb
@@ -117,6 +120,9 @@ def conv3x3(conv: nn.Conv2d, x: torch.Tensor) -> torch.Tensor:
 
 
 FAST_CONV_BACKWARD = True
+# weight gradients of the 3x3 convolutions by mb_conv3x3_wgrad (fp32 FMA, deterministic) instead of cuDNN's
+# wgrad kernels, which were a third of the learner step (profiles/r01_encoder_layers.txt)
+FAST_CONV_WGRAD = True
 
 
 class Residual_Block(nn.Module):

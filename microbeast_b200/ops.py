@@ -262,6 +262,32 @@ def active_cells(action_mask: torch.Tensor, cells: int) -> torch.Tensor:
     return out.view(torch.bool)
 
 
+def conv3x3_wgrad(x: torch.Tensor, dy: torch.Tensor) -> Optional[torch.Tensor]:
+    """Weight gradient ``[cout, cin, 3, 3]`` of a 3x3 / stride 1 / pad 1 convolution from its input
+    ``x [n,cin,h,w]`` and output gradient ``dy [n,cout,h,w]`` (fp32, NCHW contiguous), or ``None``
+    when the shape is not one ``csrc/convgrad.cu`` instantiates (the caller then uses cuDNN)."""
+    dev = _need_cuda(x=x, dy=dy)
+    if x.dtype != torch.float32 or dy.dtype != torch.float32 or x.dim() != 4 or dy.dim() != 4:
+        return None
+    n, cin, h, w = x.shape
+    cout = dy.shape[1]
+    if dy.shape[0] != n or tuple(dy.shape[2:]) != (h, w):
+        raise ValueError("conv3x3_wgrad: x and dy disagree on batch or map size")
+    with torch.cuda.device(dev):
+        blocks = lib.mb_conv3x3_wgrad_blocks(n, cin, cout, h, w)
+        if blocks < 0:
+            raise RuntimeError(_lib.last_error())
+        if blocks == 0 or n == 0:
+            return None
+        x, dy = x.contiguous(), dy.contiguous()
+        if (x.data_ptr() | dy.data_ptr()) & 15:
+            return None
+        partials = torch.empty((blocks, cout * cin * 9), dtype=torch.float32, device=dev)
+        with _Launch("conv3x3_wgrad"):
+            _check(lib.mb_conv3x3_wgrad(_ptr(x), _ptr(dy), _ptr(partials), blocks, n, cin, cout, h, w, _stream()))
+    return partials.sum(dim=0).view(cout, cin, 3, 3)
+
+
 def vtrace_workspace(device: torch.device, rows: int) -> torch.Tensor:
     """Zero-initialised scratch for ``mb_vtrace_loss`` (cached per device; the kernel keeps
     its ticket word at zero between calls).  Calls on different streams that may overlap

@@ -1,0 +1,28 @@
+"""Per-layer CUDA time of the encoder's convolutions (forward / backward) at config 2, by input shape."""
+import os, sys
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import torch
+from torch.profiler import profile, ProfilerActivity
+from microbeast_b200 import synth
+from microbeast_b200.learner import LEARNER_KEYS, PPO_learn
+from microbeast_b200.model import Agent
+dev = torch.device("cuda", 0)
+torch.backends.cudnn.allow_tf32 = False; torch.backends.cuda.matmul.allow_tf32 = False; torch.backends.cudnn.benchmark = True
+h = w = 16; T = 80; rows = 256; cells = h * w
+torch.manual_seed(0)
+model = Agent((h, w, 27), [6, 4, 4, 4, 4, 7, 49] * cells, cells).to(dev)
+with torch.no_grad():
+    model.actor.weight.normal_(0, 0.01)
+model.sparse_head = True
+opt = torch.optim.Adam(model.parameters(), lr=2.5e-4, eps=1e-5, fused=True)
+batch = synth.make_rollout_batch(h, w, T, rows, seed=1, device=dev, obs_dtype=torch.uint8, full_keys=False)
+batch["logprobs"] = -torch.rand(batch["reward"].shape, device=dev) * 30
+b = {k: batch[k] for k in LEARNER_KEYS}
+for _ in range(4):
+    PPO_learn(model, model, "p", b, opt, rows, T, 1, sync=False)
+torch.cuda.synchronize()
+with profile(activities=[ProfilerActivity.CUDA, ProfilerActivity.CPU], record_shapes=True) as prof:
+    for _ in range(3):
+        PPO_learn(model, model, "p", b, opt, rows, T, 1, sync=False)
+    torch.cuda.synchronize()
+print(prof.key_averages(group_by_input_shape=True).table(sort_by="cuda_time_total", row_limit=60, max_name_column_width=40, max_shapes_column_width=90))

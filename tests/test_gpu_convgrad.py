@@ -1,0 +1,110 @@
+"""mb_conv3x3_wgrad (csrc/convgrad.cu) against autograd's convolution weight gradient.  Needs a B200.
+
+The encoder stays on PyTorch (reference model.py:56-137); this kernel replaces cuDNN's fp32 wgrad
+kernels inside its backward pass.  Bar: same mathematics in fp32 -- compared with an fp64 evaluation
+of the same sum, the error must be of the size of fp32 rounding of that sum and no worse than
+cuDNN's own."""
+import pytest
+import torch
+import torch.nn.functional as F
+
+from conftest import close_rms
+
+pytestmark = pytest.mark.gpu
+
+SHAPES = [(27, 16, 16), (27, 16, 8), (16, 16, 8), (16, 16, 4), (16, 32, 16), (16, 32, 8), (16, 32, 4),
+          (32, 32, 8), (32, 32, 4), (32, 32, 2)]
+
+
+def _ref_wgrad(x, dy, dtype):
+    x = x.to(dtype).requires_grad_(False)
+    w = torch.zeros(dy.shape[1], x.shape[1], 3, 3, dtype=dtype, device=x.device, requires_grad=True)
+    y = F.conv2d(x, w, None, padding=1)
+    (gw,) = torch.autograd.grad(y, w, dy.to(dtype))
+    return gw
+
+
+@pytest.mark.parametrize("cin,cout,h", SHAPES)
+@pytest.mark.parametrize("n", [1, 3, 37, 1000])
+def test_wgrad_matches_autograd(cin, cout, h, n):
+    from microbeast_b200 import ops
+    g = torch.Generator(device="cuda").manual_seed(cin * 1000 + cout * 10 + h + n)
+    x = torch.randn(n, cin, h, h, device="cuda", generator=g)
+    x = torch.where(torch.rand(x.shape, device="cuda", generator=g) < 0.5, x, torch.zeros_like(x))   # relu-like
+    dy = torch.randn(n, cout, h, h, device="cuda", generator=g)
+    got = ops.conv3x3_wgrad(x, dy)
+    assert got is not None and got.shape == (cout, cin, 3, 3)
+    ref64 = _ref_wgrad(x, dy, torch.float64)
+    ok, worst = close_rms(got.double(), ref64, 2e-5)
+    assert ok, worst
+    again = ops.conv3x3_wgrad(x, dy)
+    assert torch.equal(got, again), "the kernel and its fixed-order partial sum are deterministic"
+
+
+def test_wgrad_one_hot_taps():
+    """Every tap lands where the definition says: x has a single 1, dy a single 1."""
+    from microbeast_b200 import ops
+    cin, cout, h = 16, 16, 8
+    for (yi, xi, yo, xo) in [(0, 0, 0, 0), (0, 0, 1, 1), (3, 4, 2, 5), (7, 7, 6, 6), (7, 0, 7, 1), (2, 2, 5, 5)]:
+        x = torch.zeros(5, cin, h, h, device="cuda")
+        dy = torch.zeros(5, cout, h, h, device="cuda")
+        x[3, 5, yi, xi] = 1.0
+        dy[3, 9, yo, xo] = 2.0
+        got = ops.conv3x3_wgrad(x, dy)
+        want = torch.zeros(cout, cin, 3, 3, device="cuda")
+        ky, kx = yi - yo + 1, xi - xo + 1
+        if 0 <= ky < 3 and 0 <= kx < 3:
+            want[9, 5, ky, kx] = 2.0
+        assert torch.equal(got, want), (yi, xi, yo, xo)
+
+
+def test_wgrad_uncovered_shape_returns_none():
+    from microbeast_b200 import ops
+    x = torch.randn(4, 8, 8, 8, device="cuda")
+    dy = torch.randn(4, 8, 8, 8, device="cuda")
+    assert ops.conv3x3_wgrad(x, dy) is None
+    assert ops.conv3x3_wgrad(torch.randn(4, 32, 1, 1, device="cuda"), torch.randn(4, 32, 1, 1, device="cuda")) is None
+
+
+def test_wgrad_at_learner_size_no_worse_than_cudnn():
+    """Config-2 sizes: error against fp64 compared with cuDNN's own fp32 error."""
+    from microbeast_b200 import ops
+    torch.backends.cudnn.allow_tf32 = False
+    n = 20736
+    for cin, cout, h in [(16, 16, 8), (32, 32, 4), (32, 32, 2), (27, 16, 16)]:
+        g = torch.Generator(device="cuda").manual_seed(h)
+        x = torch.relu(torch.randn(n, cin, h, h, device="cuda", generator=g))
+        dy = torch.randn(n, cout, h, h, device="cuda", generator=g) * 1e-3
+        ref64 = _ref_wgrad(x, dy, torch.float64)
+        got = ops.conv3x3_wgrad(x, dy)
+        cud = _ref_wgrad(x, dy, torch.float32)
+        scale = ref64.pow(2).mean().sqrt()
+        err_mine = float((got.double() - ref64).abs().max() / scale)
+        err_cudnn = float((cud.double() - ref64).abs().max() / scale)
+        assert err_mine < 2e-5, (cin, cout, h, err_mine)
+        assert err_mine < 4 * err_cudnn + 1e-6, (cin, cout, h, err_mine, err_cudnn)
+
+
+def test_encoder_backward_with_and_without_fast_wgrad():
+    """Agent gradients with FAST_CONV_WGRAD on == off (cuDNN wgrad)."""
+    from microbeast_b200 import model as mmodel, synth
+    from microbeast_b200.learner import PPO_learn
+    h = 8
+    torch.manual_seed(3)
+    agent = mmodel.Agent((h, h, 27), [6, 4, 4, 4, 4, 7, 49] * (h * h), h * h).cuda()
+    with torch.no_grad():
+        agent.actor.weight.normal_(0, 0.01)
+    T, rows = 6, 9
+    batch = synth.make_rollout_batch(h, h, T, rows, seed=4, preset="dense", full_keys=False)
+    batch["logprobs"] = -torch.rand(batch["reward"].shape) * 20
+    grads = {}
+    for flag in (True, False):
+        mmodel.FAST_CONV_WGRAD = flag
+        try:
+            PPO_learn(agent, agent, "w", batch, torch.optim.SGD(agent.parameters(), lr=0.0), rows, T, 1)
+        finally:
+            mmodel.FAST_CONV_WGRAD = True
+        grads[flag] = {k: p.grad.clone() for k, p in agent.named_parameters()}
+    for k in grads[True]:
+        ok, worst = close_rms(grads[True][k], grads[False][k], 1e-4)
+        assert ok, (k, worst)
