@@ -94,8 +94,14 @@ class GraphedLearner:
 
     # ---- the step, as PPO_learn runs it ------------------------------------------------------
     def _forward_backward(self):
-        loss4, _ = learner_losses(self.model, self._device_batch(), self.rows, self.T, **self.kw)
-        loss4[3].backward()                                                                # utils.py:334
+        # the cell-list backward of the actor head sizes tensors from the data (host syncs): dense here
+        keep = getattr(self.model, "sparse_backward", False)
+        self.model.sparse_backward = False
+        try:
+            loss4, _ = learner_losses(self.model, self._device_batch(), self.rows, self.T, **self.kw)
+            loss4[3].backward()                                                            # utils.py:334
+        finally:
+            self.model.sparse_backward = keep
         return loss4.detach()
 
     def _capture(self) -> None:

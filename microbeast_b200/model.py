@@ -125,6 +125,86 @@ FAST_CONV_BACKWARD = True
 FAST_CONV_WGRAD = True
 
 
+def cell_list(action_mask: torch.Tensor, cells: int, auto: bool):
+    """Active (frame, cell) pairs grouped by cell: ``(fidx [cells, lmax], cidx [cells, lmax])`` with
+    ``fidx`` the frame index, padded with ``n`` (one past the last frame) up to the longest group
+    rounded to 64.  ``None`` with ``auto`` when the padded list would be at least half the dense grid.
+    Costs two host synchronisations (``nonzero`` and the longest group's length)."""
+    n = action_mask.shape[0]
+    active = ops.active_cells(action_mask, cells)                       # [N, C]
+    counts = active.sum(dim=0)                                         # active frames per cell
+    pairs = active.t().nonzero()                                       # [P, 2] = (cell, frame), grouped by cell
+    lmax = int(counts.max().item()) if pairs.shape[0] else 0
+    lmax = max(-(-max(lmax, 1) // 64) * 64, 64)                        # groups of 64 cells for the kernel
+    if auto and 2 * lmax > n:
+        return None
+    dev = action_mask.device
+    starts = torch.cumsum(counts, 0) - counts
+    pos = torch.arange(pairs.shape[0], device=dev) - starts[pairs[:, 0]]
+    fidx = torch.full((cells, lmax), n, dtype=torch.int64, device=dev)
+    fidx[pairs[:, 0], pos] = pairs[:, 1]
+    cidx = torch.arange(cells, device=dev).unsqueeze(1).expand(cells, lmax)
+    return fidx, cidx
+
+
+def gather_cells(fidx, cidx, n, action_mask, action, cells):
+    """Mask / action rows of a cell list; padding entries get an all-zero mask (a dead cell: log-prob 0,
+    entropy 0, zero gradient -- quirk Q1) and any in-range action."""
+    valid = fidx < n
+    safe = fidx.clamp(max=n - 1)
+    mask3 = action_mask.view(n, cells, LOGITS_PER_CELL)
+    mask_c = torch.where(valid.unsqueeze(2), mask3[safe, cidx], torch.zeros((), dtype=mask3.dtype, device=mask3.device))
+    act_c = action.view(n, cells, COMPONENTS_PER_CELL)[safe, cidx]
+    return safe, mask_c.reshape(-1, LOGITS_PER_CELL), act_c.reshape(-1, COMPONENTS_PER_CELL)
+
+
+class _ActorHead(torch.autograd.Function):
+    """Actor ``Linear`` (model.py:136,167) + policy head with a DENSE forward -- ``policy_logits`` is an
+    output, as in the reference -- and a backward restricted to the cells that can have a gradient.
+
+    ``d loss / d logits`` is exactly zero on every cell without a valid action (quirk Q1), which is 94 %
+    of the rows at microRTS densities, so the two backward GEMMs of the Linear (``dlogits^T @ hidden`` and
+    ``dlogits @ W``, 7.5 ms of the 30 ms learner step at 16x16) multiply mostly zeros.  The backward
+    builds the list of active (frame, cell) pairs, runs the cell-list head-backward kernel on it and does
+    the two products as batched matmuls over the list: same fp32 arithmetic on the non-zero rows, only
+    the summation order differs.  ``mode="auto"`` falls back to the dense kernels when the padded list
+    would be at least half the grid; ``False`` always uses them (needed under CUDA-graph capture: the
+    list is sized from the data)."""
+
+    @staticmethod
+    def forward(ctx, hidden, weight, bias, action_mask, action, cells, mode):
+        logits = torch.addmm(bias, hidden, weight.t())                                     # model.py:167
+        logprobs, entropy = ops.head_eval_fwd(logits, action_mask, action)
+        ctx.save_for_backward(hidden, weight, logits, action_mask, action)
+        ctx.cells, ctx.mode = cells, mode
+        ctx.mark_non_differentiable(logits)
+        return logits, logprobs, entropy
+
+    @staticmethod
+    def backward(ctx, _g_logits, g_lp, g_ent):
+        hidden, weight, logits, action_mask, action = ctx.saved_tensors
+        n, cells = hidden.shape[0], ctx.cells
+        g_lp = torch.zeros(n, device=hidden.device) if g_lp is None else g_lp.contiguous()
+        g_ent = torch.zeros(n, device=hidden.device) if g_ent is None else g_ent.contiguous()
+        cl = cell_list(action_mask, cells, auto=(ctx.mode == "auto")) if ctx.mode else None
+        if cl is None:
+            dlogits = ops.head_eval_bwd(logits, action_mask, action, g_lp, g_ent)
+            return dlogits @ weight, dlogits.t() @ hidden, dlogits.sum(dim=0), None, None, None, None
+        fidx, cidx = cl
+        lmax, width = fidx.shape[1], hidden.shape[1]
+        safe, mask_c, act_c = gather_cells(fidx, cidx, n, action_mask, action, cells)
+        logits_c = logits.view(n, cells, LOGITS_PER_CELL)[safe, cidx].reshape(-1, LOGITS_PER_CELL)
+        dl = ops.head_eval_cells_bwd(logits_c, mask_c, act_c, g_lp[safe].reshape(-1), g_ent[safe].reshape(-1))
+        dl = dl.view(cells, lmax, LOGITS_PER_CELL)
+        flat = fidx.reshape(-1)
+        hid = torch.cat([hidden, hidden.new_zeros(1, width)]).index_select(0, flat).view(cells, lmax, width)
+        g_weight = torch.bmm(dl.transpose(1, 2), hid).reshape(cells * LOGITS_PER_CELL, width)
+        g_bias = dl.sum(dim=1).reshape(-1)
+        g_hid = torch.bmm(dl, weight.view(cells, LOGITS_PER_CELL, width))                   # [C, lmax, 256]
+        g_hidden = hidden.new_zeros((n + 1, width)).index_add_(0, flat, g_hid.reshape(-1, width))[:n]
+        return g_hidden, g_weight, g_bias, None, None, None, None
+
+
 class Residual_Block(nn.Module):
     """relu-conv-relu-conv + skip -- reference ``model.py:56-73``."""
 
@@ -177,7 +257,8 @@ class Agent(nn.Module):
         self.nvec = nvec
         self.cells = len(nvec) // COMPONENTS_PER_CELL
         self.nchw_copy = True
-        self.sparse_head = False
+        self.sparse_head = False           # True / "auto": no policy_logits for fully masked cells (see _sparse_head)
+        self.sparse_backward = "auto"      # backward of the actor head over the active cells only (see _ActorHead)
         self.obs_planes = c
         shape = (c, h, w)
         layers = []
@@ -216,32 +297,19 @@ class Agent(nn.Module):
         scattered back to their frames.  Same values as the dense path up to fp32 summation order;
         ``policy_logits`` is not produced."""
         n, cells = hidden.shape[0], self.cells
-        mask3 = action_mask.view(n, cells, LOGITS_PER_CELL)
-        active = ops.active_cells(action_mask, cells)                                   # [N, C]
-        counts = active.sum(dim=0)                                         # active frames per cell
-        pairs = active.t().nonzero()                                       # [P, 2] = (cell, frame), grouped by cell
-        lmax = int(counts.max().item()) if pairs.shape[0] else 0           # host syncs: nonzero + this
-        lmax = max(-(-max(lmax, 1) // 64) * 64, 64)                        # groups of 64 cells for the kernel
-        if self.sparse_head == "auto" and 2 * lmax > n:
+        cl = cell_list(action_mask, cells, auto=(self.sparse_head == "auto"))
+        if cl is None:
             return None                      # padded cell list >= half the dense grid: the dense path is cheaper
-        # frame indices of the active pairs, one row per cell, padded with frame n (a zero row of `hid`)
-        starts = torch.cumsum(counts, 0) - counts
-        pos = torch.arange(pairs.shape[0], device=hidden.device) - starts[pairs[:, 0]]
-        fidx = torch.full((cells, lmax), n, dtype=torch.int64, device=hidden.device)
-        fidx[pairs[:, 0], pos] = pairs[:, 1]
-        valid = fidx < n
+        fidx, cidx = cl
+        lmax = fidx.shape[1]
+        _, mask_c, act_c = gather_cells(fidx, cidx, n, action_mask, action, cells)
         # index_select: its backward is an index_add (atomics), not the sort-based index_put of x[idx]
         hid = torch.cat([hidden, hidden.new_zeros(1, hidden.shape[1])]).index_select(0, fidx.reshape(-1))
         hid = hid.view(cells, lmax, -1)                    # [C, lmax, 256]
         w = self.actor.weight.view(cells, LOGITS_PER_CELL, -1)
         b = self.actor.bias.view(cells, 1, LOGITS_PER_CELL)
         logits_c = torch.baddbmm(b, hid, w.transpose(1, 2)).reshape(-1, LOGITS_PER_CELL)      # [C*lmax, 78]
-        cidx = torch.arange(cells, device=hidden.device).unsqueeze(1).expand(cells, lmax)
-        safe = fidx.clamp(max=n - 1)
-        mask_c = torch.where(valid.unsqueeze(2), mask3[safe, cidx], torch.zeros((), dtype=mask3.dtype, device=hidden.device))
-        act_c = action.view(n, cells, COMPONENTS_PER_CELL)[safe, cidx]
-        lp_c, en_c = ops.HeadEvalCells.apply(logits_c, mask_c.reshape(-1, LOGITS_PER_CELL).contiguous(),
-                                             act_c.reshape(-1, COMPONENTS_PER_CELL).contiguous())
+        lp_c, en_c = ops.HeadEvalCells.apply(logits_c, mask_c, act_c)
         # back to frames: every (frame, cell) slot is written at most once, then a fixed-order row sum
         # (deterministic, unlike an atomic index_add); padding lands in the dropped row n
         grid = hidden.new_zeros((2, n + 1, cells))
@@ -286,7 +354,7 @@ class Agent(nn.Module):
             if sparse is not None:
                 return (dict(action=action, policy_logits=None, logprobs=sparse[0], baseline=baseline,
                              entropy=sparse[1]), ())
-        logits = self.actor(hidden)                                             # model.py:167
-        logprobs, entropy = ops.HeadEval.apply(logits, action_mask, action)
+        logits, logprobs, entropy = _ActorHead.apply(hidden, self.actor.weight, self.actor.bias, action_mask,
+                                                     action, self.cells, self.sparse_backward)
         return (dict(action=action, policy_logits=logits, logprobs=logprobs, baseline=baseline,
                      entropy=entropy), ())

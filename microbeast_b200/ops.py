@@ -400,15 +400,27 @@ class HeadEvalCells(torch.autograd.Function):
     @staticmethod
     def backward(ctx, g_logp, g_ent):
         logits, mask, action = ctx.saved_tensors
-        m = logits.shape[0]
-        dev = logits.device
-        g_logp = torch.zeros(m, device=dev) if g_logp is None else g_logp.contiguous()
-        g_ent = torch.zeros(m, device=dev) if g_ent is None else g_ent.contiguous()
-        out = torch.empty_like(logits)
-        with torch.cuda.device(dev), _Launch("head_eval_cells_bwd"):
-            _check(lib.mb_head_eval_cells_bwd(_ptr(logits), _ptr(mask), _ptr(action), _ptr(g_logp), _ptr(g_ent),
-                                              _ptr(out), m, _ptr(status_word(dev)), _stream()))
-        return out, None, None
+        return head_eval_cells_bwd(logits, mask, action, g_logp, g_ent), None, None
+
+
+def head_eval_cells_bwd(logits, mask, action, g_logp, g_ent) -> torch.Tensor:
+    """``d loss / d logits [M,78]`` of a cell list from the per-CELL upstream gradients ``g_logp [M]``,
+    ``g_ent [M]`` (the frame's gradients repeated for each of its cells); ``M`` a multiple of 64."""
+    dev = _need_cuda(logits=logits, mask=mask, action=action)
+    logits = _as(logits, torch.float32, "logits")
+    mask = _mask_u8(mask)
+    action = _as(action, torch.int64, "action")
+    m = logits.shape[0]
+    if logits.shape[1] != LOGITS_PER_CELL or tuple(mask.shape) != (m, LOGITS_PER_CELL) or \
+            tuple(action.shape) != (m, COMPONENTS_PER_CELL):
+        raise ValueError("cell lists must be logits/mask [M,78] and action [M,7]")
+    g_logp = torch.zeros(m, device=dev) if g_logp is None else _as(g_logp, torch.float32, "g_logp")
+    g_ent = torch.zeros(m, device=dev) if g_ent is None else _as(g_ent, torch.float32, "g_ent")
+    out = torch.empty_like(logits)
+    with torch.cuda.device(dev), _Launch("head_eval_cells_bwd"):
+        _check(lib.mb_head_eval_cells_bwd(_ptr(logits), _ptr(mask), _ptr(action), _ptr(g_logp), _ptr(g_ent),
+                                          _ptr(out), m, _ptr(status_word(dev)), _stream()))
+    return out
 
 
 class VTraceLoss(torch.autograd.Function):

@@ -426,3 +426,35 @@ def test_graphed_learner_matches_eager_steps(wire, opt_name):
         bad = dict(batch)
         bad["reward"] = batch["reward"][:-1]
         gl.step(bad)
+
+
+@pytest.mark.parametrize("preset", ["dense", "realistic", "all_masked", "all_valid"])
+@pytest.mark.parametrize("mode", [True, "auto"])
+def test_actor_head_sparse_backward_equals_dense_backward(preset, mode):
+    """Agent.sparse_backward: the backward of actor Linear + policy head over the active cells only gives
+    the same gradients as the dense kernels (dlogits is exactly zero on fully masked cells, quirk Q1);
+    the forward outputs, policy_logits included, are untouched."""
+    from microbeast_b200 import synth
+    from microbeast_b200.learner import PPO_learn
+    mine, _ = _pair(8, 8, seed=41)
+    with torch.no_grad():
+        mine.actor.weight.normal_(0, 0.02)
+    T, rows = 9, 40
+    batch = synth.make_rollout_batch(8, 8, T, rows, seed=17, preset=preset, full_keys=False)
+    batch["logprobs"] = -torch.rand(batch["reward"].shape) * 20
+    res = {}
+    for m in (False, mode):
+        mine.sparse_backward = m
+        dev = {k: v.cuda() for k, v in batch.items()}
+        with torch.no_grad():
+            out, _ = mine.get_action(dev, learning=True)
+        four = PPO_learn(mine, mine, "x", batch, torch.optim.SGD(mine.parameters(), lr=0.0), rows, T, 1)
+        res[m] = (out, four, {k: p.grad.clone() for k, p in mine.named_parameters()})
+    mine.sparse_backward = "auto"
+    (o_d, f_d, g_d), (o_s, f_s, g_s) = res[False], res[mode]
+    for k in ("policy_logits", "logprobs", "entropy", "baseline"):
+        assert torch.equal(o_d[k], o_s[k]), k
+    assert f_d == f_s
+    for k in g_d:
+        ok, worst = close_rms(g_s[k], g_d[k], 1e-4)
+        assert ok, (k, worst)
