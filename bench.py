@@ -299,13 +299,31 @@ def run_ours(args):
         "head_eval_bwd": 758 * cells * n + 8 * n,
         "vtrace_loss": 37 * rows * T + 4 * rows,
     }
+    for name, note in ops.launch_notes.items():       # kernels whose problem size depends on the data / layer
+        if name == "active_cells":
+            alg[name] = 79 * note["cells"]
+        elif name == "head_eval_cells_fwd":
+            alg[name] = (446 + 16) * note["cells"]
+        elif name == "head_eval_cells_bwd":
+            alg[name] = (758 + 8) * note["cells"]
+    sm_mhz = (clocks or {}).get("sm_mhz") or 1965.0
+    fp32_peak = 148 * 128 * 2 * sm_mhz * 1e6 / 1e12            # TFLOP/s: 128 FMA lanes per SM at the sampled clock
     kernels = {}
     for name, ts in ktimes.items():
         avg = sum(ts) / len(ts)
         gbs = alg[name] / (avg * 1e-3) / 1e9 if name in alg else None
         kernels[name] = {"launches": len(ts), "avg_ms": avg, "alg_bytes": alg.get(name),
                          "gbs": gbs, "frac_of_peak": (gbs / peak if gbs else None)}
-    dom = "head_eval_bwd"
+        if name.startswith("conv3x3_wgrad") and name in ops.launch_notes:
+            nt = ops.launch_notes[name]
+            flops = 2.0 * nt["n"] * nt["cout"] * nt["cin"] * (3 * nt["h"] - 2) ** 2      # taps inside the image only
+            kernels[name].update({"bound": "fp32 fma", "useful_flops": flops, "tflops": flops / (avg * 1e-3) / 1e12,
+                                  "frac_of_fp32_peak": flops / (avg * 1e-3) / 1e12 / fp32_peak,
+                                  "fp32_peak_tflops": fp32_peak})
+    # the roofline object is for the path's own dominant HBM-bound kernel: the dense policy-head backward when the
+    # step launches it, else the dense policy-head forward (the backward then runs on the list of active cells)
+    dom = max((k for k in ("head_eval_bwd", "head_eval_fwd") if k in kernels),
+              key=lambda k: kernels[k]["avg_ms"], default=None)
     roof = None
     if dom in kernels:
         roof = {"kernel": dom, "bound": "hbm", "achieved": kernels[dom]["gbs"], "peak": peak, "unit": "GB/s",

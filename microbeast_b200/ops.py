@@ -45,11 +45,16 @@ def stop_kernel_timing() -> Dict[str, list]:
     return out
 
 
+launch_notes: Dict[str, dict] = {}
+
+
 class _Launch:
     """Counts a launch and, when timing is on, brackets it with CUDA events."""
 
-    def __init__(self, name: str):
+    def __init__(self, name: str, note=None):
         self.name = name
+        if note is not None:
+            launch_notes[name] = note        # problem size of the latest launch under this name (bench.py reads it)
 
     def __enter__(self):
         if _timing is not None:
@@ -257,7 +262,7 @@ def active_cells(action_mask: torch.Tensor, cells: int) -> torch.Tensor:
     if action_mask.dim() != 2 or action_mask.shape[1] != cells * LOGITS_PER_CELL:
         raise ValueError("action_mask must be [N, 78*cells]")
     out = torch.empty((n, cells), dtype=torch.uint8, device=dev)
-    with torch.cuda.device(dev), _Launch("active_cells"):
+    with torch.cuda.device(dev), _Launch("active_cells", note={"cells": n * cells}):
         _check(lib.mb_active_cells(_ptr(action_mask), _ptr(out), n * cells, _stream()))
     return out.view(torch.bool)
 
@@ -283,7 +288,7 @@ def conv3x3_wgrad(x: torch.Tensor, dy: torch.Tensor) -> Optional[torch.Tensor]:
         if (x.data_ptr() | dy.data_ptr()) & 15:
             return None
         partials = torch.empty((blocks, cout * cin * 9), dtype=torch.float32, device=dev)
-        with _Launch("conv3x3_wgrad"):
+        with _Launch(f"conv3x3_wgrad_{cin}x{cout}x{h}", note={"n": n, "cin": cin, "cout": cout, "h": h}):
             _check(lib.mb_conv3x3_wgrad(_ptr(x), _ptr(dy), _ptr(partials), blocks, n, cin, cout, h, w, _stream()))
     return partials.sum(dim=0).view(cout, cin, 3, 3)
 
@@ -391,7 +396,7 @@ class HeadEvalCells(torch.autograd.Function):
                 tuple(action.shape) != (m, COMPONENTS_PER_CELL):
             raise ValueError("cell lists must be logits/mask [M,78] and action [M,7]")
         out4 = torch.empty((4, m), dtype=torch.float32, device=dev)
-        with torch.cuda.device(dev), _Launch("head_eval_cells_fwd"):
+        with torch.cuda.device(dev), _Launch("head_eval_cells_fwd", note={"cells": m}):
             _check(lib.mb_head_eval_cells_fwd(_ptr(logits), _ptr(mask), _ptr(action), _ptr(out4), m,
                                               _ptr(status_word(dev)), _stream()))
         ctx.save_for_backward(logits, mask, action)
@@ -417,7 +422,7 @@ def head_eval_cells_bwd(logits, mask, action, g_logp, g_ent) -> torch.Tensor:
     g_logp = torch.zeros(m, device=dev) if g_logp is None else _as(g_logp, torch.float32, "g_logp")
     g_ent = torch.zeros(m, device=dev) if g_ent is None else _as(g_ent, torch.float32, "g_ent")
     out = torch.empty_like(logits)
-    with torch.cuda.device(dev), _Launch("head_eval_cells_bwd"):
+    with torch.cuda.device(dev), _Launch("head_eval_cells_bwd", note={"cells": m}):
         _check(lib.mb_head_eval_cells_bwd(_ptr(logits), _ptr(mask), _ptr(action), _ptr(g_logp), _ptr(g_ent),
                                           _ptr(out), m, _ptr(status_word(dev)), _stream()))
     return out
