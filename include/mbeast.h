@@ -183,6 +183,12 @@ MB_API int mb_conv3x3_wgrad_blocks(int64_t n_frames, int32_t cin, int32_t cout, 
 MB_API int mb_conv3x3_wgrad(const float* x, const float* dy, float* partials, int32_t n_blocks, int64_t n_frames,
                             int32_t cin, int32_t cout, int32_t h, int32_t w, void* stream);
 
+/* Backward of max_pool2d(kernel 3, stride 2, padding 1) (reference model.py:96) from the argmax
+ * indices of the forward: dy, idx [planes, (h+1)/2, (w+1)/2] (idx = flat position in the h*w input
+ * plane, as torch.nn.functional.max_pool2d(..., return_indices=True) returns it), dx [planes, h, w]. */
+MB_API int mb_maxpool3s2_bwd(const float* dy, const int64_t* idx, float* dx, int64_t planes, int32_t h, int32_t w,
+                             void* stream);
+
 /* Tuning knobs for benchmarking (not part of the reference surface).  Keys:
  *   "head_ctas_per_sm" (0 = as many as fit), "head_grid" (0 = auto), "head_variant" (tile /
  *   pipeline shape: 0 = 64 cells x 3 stages, 1 = 64x2, 2 = 64x4, 3 = 32x3, 4 = 32x5, 5 = 128x3, 6 = 128x2, 7 = 32x2; -1 = per-kernel default),

@@ -112,6 +112,29 @@ class _Conv3x3(torch.autograd.Function):
         return gx, gw, gb
 
 
+class _MaxPool3s2(torch.autograd.Function):
+    """``max_pool2d(x, 3, stride=2, padding=1)`` (reference model.py:96) with the backward as a gather over
+    the saved argmax indices (``mb_maxpool3s2_bwd``) instead of ATen's ``max_pool_backward_nchw``."""
+
+    @staticmethod
+    def forward(ctx, x):
+        y, idx = F.max_pool2d(x, kernel_size=3, stride=2, padding=1, return_indices=True)
+        ctx.save_for_backward(idx)
+        ctx.hw = (x.shape[2], x.shape[3])
+        return y
+
+    @staticmethod
+    def backward(ctx, g):
+        (idx,) = ctx.saved_tensors
+        return ops.maxpool3s2_bwd(g, idx, *ctx.hw)
+
+
+def maxpool3s2(x: torch.Tensor) -> torch.Tensor:
+    if x.is_cuda and FAST_CONV_BACKWARD and torch.is_grad_enabled() and x.dtype == torch.float32:
+        return _MaxPool3s2.apply(x)
+    return F.max_pool2d(x, kernel_size=3, stride=2, padding=1)
+
+
 def conv3x3(conv: nn.Conv2d, x: torch.Tensor) -> torch.Tensor:
     """``conv(x)`` for the encoder's 3x3 convolutions; on CUDA it goes through :class:`_Conv3x3`."""
     if x.is_cuda and FAST_CONV_BACKWARD and torch.is_grad_enabled():
@@ -158,6 +181,20 @@ def gather_cells(fidx, cidx, n, action_mask, action, cells):
     return safe, mask_c.reshape(-1, LOGITS_PER_CELL), act_c.reshape(-1, COMPONENTS_PER_CELL)
 
 
+def _linear_bias_in_k(x: torch.Tensor, weight: torch.Tensor, bias: torch.Tensor) -> torch.Tensor:
+    """``x @ weight.T + bias`` as ONE matmul: the bias rides along as an extra column of ``weight`` against a
+    column of ones in ``x`` (K padded by 8 to keep rows 32-byte aligned).  For the [N, 78C] logits cuBLASLt
+    otherwise adds the bias in a separate pass over the output, 1.4 ms of a 25 ms step at 16x16."""
+    n, k = x.shape
+    xa = x.new_zeros((n, k + 8))
+    xa[:, :k] = x
+    xa[:, k] = 1.0
+    wa = weight.new_zeros((weight.shape[0], k + 8))
+    wa[:, :k] = weight
+    wa[:, k] = bias
+    return xa @ wa.t()
+
+
 class _ActorHead(torch.autograd.Function):
     """Actor ``Linear`` (model.py:136,167) + policy head with a DENSE forward -- ``policy_logits`` is an
     output, as in the reference -- and a backward restricted to the cells that can have a gradient.
@@ -173,7 +210,7 @@ class _ActorHead(torch.autograd.Function):
 
     @staticmethod
     def forward(ctx, hidden, weight, bias, action_mask, action, cells, mode):
-        logits = torch.addmm(bias, hidden, weight.t())                                     # model.py:167
+        logits = _linear_bias_in_k(hidden, weight, bias)                                   # model.py:167
         logprobs, entropy = ops.head_eval_fwd(logits, action_mask, action)
         ctx.save_for_backward(hidden, weight, logits, action_mask, action)
         ctx.cells, ctx.mode = cells, mode
@@ -236,7 +273,7 @@ class ConvSequence(nn.Module):
         return (self._out_channels, (h + 1) // 2, (w + 1) // 2)
 
     def forward(self, x):
-        x = F.max_pool2d(conv3x3(self.conv, x), kernel_size=3, stride=2, padding=1)
+        x = maxpool3s2(conv3x3(self.conv, x))
         return self.res_block1(self.res_block0(x))
 
 

@@ -293,6 +293,21 @@ def conv3x3_wgrad(x: torch.Tensor, dy: torch.Tensor) -> Optional[torch.Tensor]:
     return partials.sum(dim=0).view(cout, cin, 3, 3)
 
 
+def maxpool3s2_bwd(dy: torch.Tensor, idx: torch.Tensor, h: int, w: int) -> torch.Tensor:
+    """``dx [n,c,h,w]`` of ``max_pool2d(x, 3, stride=2, padding=1)`` from ``dy`` and the forward's argmax
+    indices (both ``[n,c,(h+1)//2,(w+1)//2]``)."""
+    dev = _need_cuda(dy=dy, idx=idx)
+    dy = _as(dy, torch.float32, "dy")
+    idx = _as(idx, torch.int64, "idx")
+    if dy.dim() != 4 or dy.shape != idx.shape or tuple(dy.shape[2:]) != ((h + 1) // 2, (w + 1) // 2):
+        raise ValueError("maxpool3s2_bwd: dy / idx must be [n, c, (h+1)//2, (w+1)//2]")
+    n, c = dy.shape[:2]
+    dx = torch.empty((n, c, h, w), dtype=torch.float32, device=dev)
+    with torch.cuda.device(dev), _Launch("maxpool3s2_bwd"):
+        _check(lib.mb_maxpool3s2_bwd(_ptr(dy), _ptr(idx), _ptr(dx), n * c, h, w, _stream()))
+    return dx
+
+
 def vtrace_workspace(device: torch.device, rows: int) -> torch.Tensor:
     """Zero-initialised scratch for ``mb_vtrace_loss`` (cached per device; the kernel keeps
     its ticket word at zero between calls).  Calls on different streams that may overlap

@@ -108,3 +108,20 @@ def test_encoder_backward_with_and_without_fast_wgrad():
     for k in grads[True]:
         ok, worst = close_rms(grads[True][k], grads[False][k], 1e-4)
         assert ok, (k, worst)
+
+
+@pytest.mark.parametrize("n,c,h", [(1, 1, 2), (3, 5, 4), (7, 16, 8), (5, 16, 16), (2, 3, 7), (4, 2, 1), (1000, 32, 4)])
+def test_maxpool_backward_matches_autograd(n, c, h):
+    """mb_maxpool3s2_bwd == autograd's max_pool2d backward, bit for bit (ties included: both follow the
+    forward's argmax indices; a pixel that wins several windows gets their gradients added)."""
+    from microbeast_b200 import ops
+    g = torch.Generator(device="cuda").manual_seed(n + c + h)
+    x = torch.randint(0, 4, (n, c, h, h), device="cuda", generator=g).float()       # many ties
+    x.requires_grad_(True)
+    y, idx = F.max_pool2d(x, 3, 2, 1, return_indices=True)
+    dy = torch.randn(y.shape, device="cuda", generator=g)
+    (want,) = torch.autograd.grad(y, x, dy)
+    got = ops.maxpool3s2_bwd(dy, idx, h, h)
+    # a pixel that is the argmax of several windows sums 2-4 gradients; ATen adds them with atomics in
+    # arbitrary order, so allow one rounding of that small sum
+    assert torch.allclose(got, want, rtol=0, atol=1e-6), float((got - want).abs().max())
