@@ -183,6 +183,16 @@ MB_API int mb_conv3x3_wgrad_blocks(int64_t n_frames, int32_t cin, int32_t cout, 
 MB_API int mb_conv3x3_wgrad(const float* x, const float* dy, float* partials, int32_t n_blocks, int64_t n_frames,
                             int32_t cin, int32_t cout, int32_t h, int32_t w, void* stream);
 
+/* Forward-type 3x3 / stride 1 / pad 1 convolution in fp32 (reference model.py:61-62,88: nn.Conv2d(.., 3, padding=1)):
+ *   out[n,co,y,x] = bias[co] + sum_{ci,ky,kx} wk[ci][co][ky*3+kx] * in[n,ci,y+ky-1,x+kx-1]
+ * in [n,cin,h,w], out [n,cout,h,w] NCHW contiguous, 16-byte aligned; wk [cin][cout][9] (the torch weight
+ * [cout,cin,3,3] permuted); bias [cout] or NULL.  The data gradient of such a convolution is the same
+ * operation with wk = weight.flip(2,3) viewed as [cout][cin][9] and no bias.  mb_conv3x3_fwd_supported
+ * returns 1 for the shapes instantiated in csrc/convgrad.cu, else 0 (the caller keeps cuDNN). */
+MB_API int mb_conv3x3_fwd_supported(int32_t cin, int32_t cout, int32_t h, int32_t w);
+MB_API int mb_conv3x3_fwd(const float* in, const float* wk, const float* bias, float* out, int64_t n_frames,
+                          int32_t cin, int32_t cout, int32_t h, int32_t w, void* stream);
+
 /* Backward of max_pool2d(kernel 3, stride 2, padding 1) (reference model.py:96) from the argmax
  * indices of the forward: dy, idx [planes, (h+1)/2, (w+1)/2] (idx = flat position in the h*w input
  * plane, as torch.nn.functional.max_pool2d(..., return_indices=True) returns it), dx [planes, h, w]. */

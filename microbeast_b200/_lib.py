@@ -41,6 +41,9 @@ SIGNATURES = {
     "mb_unpack_rollout": (ctypes.c_int, [_P, _P, _P, _P, ctypes.c_int64, ctypes.c_int32, _P]),
     "mb_unpack_obs": (ctypes.c_int, [_P, _P, ctypes.c_int64, ctypes.c_int32, ctypes.c_int32, _P]),
     "mb_active_cells": (ctypes.c_int, [_P, _P, ctypes.c_int64, _P]),
+    "mb_conv3x3_fwd_supported": (ctypes.c_int, [ctypes.c_int32, ctypes.c_int32, ctypes.c_int32, ctypes.c_int32]),
+    "mb_conv3x3_fwd": (ctypes.c_int, [_P, _P, _P, _P, ctypes.c_int64, ctypes.c_int32, ctypes.c_int32, ctypes.c_int32,
+                                      ctypes.c_int32, _P]),
     "mb_maxpool3s2_bwd": (ctypes.c_int, [_P, _P, _P, ctypes.c_int64, ctypes.c_int32, ctypes.c_int32, _P]),
     "mb_conv3x3_wgrad_blocks": (ctypes.c_int, [ctypes.c_int64, ctypes.c_int32, ctypes.c_int32, ctypes.c_int32,
                                                ctypes.c_int32]),

@@ -295,6 +295,234 @@ int conv3x3_wgrad(const float* x, const float* dy, float* partials, int n_blocks
 }
 
 // ---------------------------------------------------------------------------------------------
+// Forward-type 3x3 / stride 1 / pad 1 convolution in fp32:
+//     out[n, co, y, x] = bias[co] + sum_{ci, ky, kx} wk[ci][co][ky*3+kx] * in[n, ci, y+ky-1, x+kx-1]
+// used for the encoder's forward convolutions (wk = W permuted to [cin][cout][9]) and, with the kernel
+// flipped and the channel axes swapped, for their data gradients (wk = W.flip(2,3) viewed [cout][cin][9],
+// no bias).  cuDNN runs these small-channel shapes at ~20 TFLOP/s (implicit_convolve_sgemm / winograd,
+// 9 ms of a 23 ms step at 16x16).
+//
+// A thread owns 4 output channels x one row segment of up to 8 pixels (32 accumulators) of one frame and
+// walks the input channels: per channel it reads its three input rows and the 36 weights of its channel
+// group from shared memory (float4) and issues 36*8 FMAs; taps outside the image are compiled out.  Lanes
+// of a warp that share a row read the same input addresses, lanes that share a channel group the same
+// weights (broadcasts), so shared-memory traffic is ~15 wavefronts per 288 FMA issue slots.  Frames are
+// staged by cp.async, double buffered, exactly as they lie in global memory; the weights stay resident.
+// ---------------------------------------------------------------------------------------------
+template <int CIN_, int COUT_, int H_, int FG_>
+struct FwCfg {
+    static constexpr int CIN = CIN_, COUT = COUT_, H = H_, W = H_, FG = FG_;
+    static constexpr int HW = H * W;
+    static constexpr int XW = W < 8 ? W : 8;                // pixels of a row per thread
+    static constexpr int SEG = W / XW;
+    static constexpr int RPT = (H == 2) ? 2 : 1;            // rows per thread (a 2x2 map is one thread's)
+    static constexpr int ROWS = H / RPT;
+    static constexpr int COG = COUT / kWgTM;
+    static constexpr int TPF = COG * ROWS * SEG;            // threads per frame
+    static constexpr int FPP = kWgThreads / TPF;            // frames per pass
+    static constexpr int CH = FPP * FG;                     // frames per chunk
+    // staged planes carry one zero row above and below (not for 2x2, where the row index is static), so every
+    // lane of a warp runs the same three-row code whatever its row
+    static constexpr int HALO = (H > 2) ? 1 : 0;
+    static constexpr int PLANE = (H + 2 * HALO) * W;        // floats per staged plane
+    static constexpr int XFRAME = CIN * HW;                 // floats per frame in global memory
+    static constexpr int SFRAME = CIN * PLANE;              // floats per staged frame
+    static constexpr int WK = CIN * COUT * 9;
+    static constexpr int SMEM = (2 * CH * SFRAME + WK + COUT) * 4;
+    static_assert(kWgThreads % TPF == 0 && FPP >= 1, "thread layout");
+    static_assert(COUT % kWgTM == 0 && HW % 4 == 0 && (WK + COUT) % 4 == 0 && (W * HALO) % 4 == 0, "shape / alignment");
+};
+
+// acc[m][x] += w[m][ky*3+kx] * row_ky[X0 + x + kx - 1] over one input channel; columns outside the image are
+// compiled out (X0, the segment's first column, is a template constant)
+template <int W, int XW, int X0, bool UP, bool DN>
+__device__ __forceinline__ void fwd_fma(float (&acc)[kWgTM][XW], const float (&wt)[kWgTM][9], const float (&up)[W],
+                                        const float (&mid)[W], const float (&dn)[W]) {
+#pragma unroll
+    for (int x = 0; x < XW; ++x) {
+#pragma unroll
+        for (int kx = 0; kx < 3; ++kx) {
+            const int xi = X0 + x + kx - 1;
+            if (xi < 0 || xi >= W) continue;
+#pragma unroll
+            for (int m = 0; m < kWgTM; ++m) {
+                if (UP) acc[m][x] = fmaf(wt[m][0 + kx], up[xi], acc[m][x]);
+                acc[m][x] = fmaf(wt[m][3 + kx], mid[xi], acc[m][x]);
+                if (DN) acc[m][x] = fmaf(wt[m][6 + kx], dn[xi], acc[m][x]);
+            }
+        }
+    }
+}
+
+// one output row segment over all input channels; `rowp` points at the row's first float in the staged
+// plane of channel 0 (the rows above / below are at -W / +W: halo rows make that valid for every row)
+template <class C, int X0, bool UP, bool DN>
+__device__ __forceinline__ void fwd_row(float (&acc)[kWgTM][C::XW], const float* rowp, const float* wcog) {
+    constexpr int W = C::W;
+#pragma unroll 2
+    for (int ci = 0; ci < C::CIN; ++ci) {
+        float wt[kWgTM][9];
+        const float* wp = wcog + ci * (C::COUT * 9);
+#pragma unroll
+        for (int q = 0; q < 9; ++q) {
+            const float4 v = *reinterpret_cast<const float4*>(wp + 4 * q);
+            (&wt[0][0])[4 * q + 0] = v.x;
+            (&wt[0][0])[4 * q + 1] = v.y;
+            (&wt[0][0])[4 * q + 2] = v.z;
+            (&wt[0][0])[4 * q + 3] = v.w;
+        }
+        const float* pr = rowp + ci * C::PLANE;
+        float up[W], mid[W], dn[W];
+        load_row<W>(mid, pr);
+        if (UP) load_row<W>(up, pr - W);
+        if (DN) load_row<W>(dn, pr + W);
+        fwd_fma<W, C::XW, X0, UP, DN>(acc, wt, UP ? up : mid, mid, DN ? dn : mid);
+    }
+}
+
+template <class C>
+__global__ void __launch_bounds__(kWgThreads) conv3x3_fwd_kernel(const float* __restrict__ in, const float* __restrict__ wk,
+                                                                  const float* __restrict__ bias, float* __restrict__ out,
+                                                                  long long n_frames) {
+    extern __shared__ __align__(16) float fw_smem[];
+    float* wsm = fw_smem;                              // [CIN][COUT][9]
+    float* bsm = wsm + C::WK;                          // [COUT]
+    float* xsm = bsm + C::COUT;                        // 2 x [CH][CIN][H + halo][W]
+    const int tid = threadIdx.x;
+    for (int i = tid; i < C::WK; i += kWgThreads) wsm[i] = wk[i];
+    for (int i = tid; i < C::COUT; i += kWgThreads) bsm[i] = bias ? bias[i] : 0.0f;
+    for (int i = tid; i < 2 * C::CH * C::SFRAME; i += kWgThreads) xsm[i] = 0.0f;      // halo rows stay zero for good
+    __syncthreads();                                   // before any cp.async lands on the zeroed interior
+
+    // thread -> (frame slot, row segment, channel group, row): lanes of a warp vary the row, then the channel
+    // group; the segment is uniform per warp
+    const int slot = tid / C::TPF;
+    const int r = tid % C::TPF;
+    const int seg = r / (C::COG * C::ROWS);
+    const int cog = (r / C::ROWS) % C::COG;
+    const int yy = r % C::ROWS;
+    const float* wcog = wsm + cog * (kWgTM * 9);
+
+    const long long n_chunks = (n_frames + C::CH - 1) / C::CH;
+    auto stage = [&](long long chunk, int buf) {
+        float* base = xsm + buf * (C::CH * C::SFRAME);
+        const long long f0 = chunk * C::CH;
+        constexpr int PIECES = C::CH * C::XFRAME / 4;
+        for (int i = tid; i < PIECES; i += kWgThreads) {
+            const int e = i * 4;
+            const int fs = e / C::XFRAME, rem = e % C::XFRAME;
+            const int plane = rem / C::HW, off = rem % C::HW;
+            const bool valid = f0 + fs < n_frames;
+            cp_async16(base + fs * C::SFRAME + plane * C::PLANE + C::HALO * C::W + off,
+                       valid ? in + f0 * C::XFRAME + e : in, valid);
+        }
+        cp_async_commit();
+    };
+
+    long long chunk = blockIdx.x;
+    int buf = 0;
+    if (chunk < n_chunks) stage(chunk, 0);
+    for (; chunk < n_chunks; chunk += gridDim.x) {
+        const long long next = chunk + gridDim.x;
+        if (next < n_chunks) {
+            stage(next, buf ^ 1);
+            cp_async_wait<1>();
+        } else {
+            cp_async_wait<0>();
+        }
+        __syncthreads();
+        const float* base = xsm + buf * (C::CH * C::SFRAME);
+#pragma unroll 1
+        for (int j = 0; j < C::FG; ++j) {
+            const int fs = j * C::FPP + slot;
+            const long long f = chunk * C::CH + fs;
+            const float* xin = base + fs * C::SFRAME;
+#pragma unroll
+            for (int rr = 0; rr < C::RPT; ++rr) {
+                const int y = yy * C::RPT + rr;
+                float acc[kWgTM][C::XW];
+#pragma unroll
+                for (int m = 0; m < kWgTM; ++m)
+#pragma unroll
+                    for (int x = 0; x < C::XW; ++x) acc[m][x] = bsm[cog * kWgTM + m];
+                const float* rowp = xin + (y + C::HALO) * C::W;
+                if constexpr (C::H == 2) {             // rr is the row: static
+                    if (rr == 0) fwd_row<C, 0, false, true>(acc, rowp, wcog);
+                    else fwd_row<C, 0, true, false>(acc, rowp, wcog);
+                } else if (C::SEG == 1 || seg == 0) {  // uniform per warp
+                    fwd_row<C, 0, true, true>(acc, rowp, wcog);
+                } else {
+                    fwd_row<C, (C::SEG > 1 ? 8 : 0), true, true>(acc, rowp, wcog);
+                }
+                if (f < n_frames) {
+#pragma unroll
+                    for (int m = 0; m < kWgTM; ++m) {
+                        float* o = out + ((f * C::COUT + cog * kWgTM + m) * C::H + y) * C::W + seg * C::XW;
+                        if constexpr (C::XW == 2) {
+                            *reinterpret_cast<float2*>(o) = make_float2(acc[m][0], acc[m][1]);
+                        } else {
+#pragma unroll
+                            for (int q = 0; q < C::XW / 4; ++q)
+                                *reinterpret_cast<float4*>(o + 4 * q) =
+                                    make_float4(acc[m][4 * q], acc[m][4 * q + 1], acc[m][4 * q + 2], acc[m][4 * q + 3]);
+                        }
+                    }
+                }
+            }
+        }
+        __syncthreads();
+        buf ^= 1;
+    }
+}
+
+template <class C>
+int fw_launch(const float* in, const float* wk, const float* bias, float* out, long long n_frames, cudaStream_t st) {
+    int dev = 0;
+    MB_CUDA(cudaGetDevice(&dev));
+    static int occ[64] = {};
+    int& o = occ[(dev >= 0 && dev < 64) ? dev : 0];
+    if (o == 0) {
+        MB_CUDA(cudaFuncSetAttribute(conv3x3_fwd_kernel<C>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM));
+        int n = 0;
+        MB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, conv3x3_fwd_kernel<C>, kWgThreads, C::SMEM));
+        o = n > 0 ? n : 1;
+    }
+    const long long chunks = (n_frames + C::CH - 1) / C::CH;
+    const long long cap = (long long)sm_count(dev) * o;
+    const int grid = int(chunks < cap ? (chunks > 0 ? chunks : 1) : cap);
+    conv3x3_fwd_kernel<C><<<grid, kWgThreads, C::SMEM, st>>>(in, wk, bias, out, n_frames);
+    MB_CUDA(cudaGetLastError());
+    return MB_OK;
+}
+
+// (cin, cout, h, frames per thread and chunk): the encoder's forward shapes and their data-gradient mirrors
+#define MB_FW_SHAPES(X) \
+    X(27, 16, 16, 1) X(27, 16, 8, 1) X(16, 16, 16, 1) X(16, 16, 8, 1) X(16, 16, 4, 1) \
+    X(16, 32, 16, 1) X(16, 32, 8, 1) X(16, 32, 4, 1) X(32, 16, 16, 1) X(32, 16, 8, 1) X(32, 16, 4, 1) \
+    X(32, 32, 8, 1) X(32, 32, 4, 1) X(32, 32, 2, 2)
+
+int conv3x3_fwd_supported(int cin, int cout, int h, int w) {
+    if (h != w) return 0;
+#define X(CI, CO, HH, FG) \
+    if (cin == CI && cout == CO && h == HH) return 1;
+    MB_FW_SHAPES(X)
+#undef X
+    return 0;
+}
+
+int conv3x3_fwd(const float* in, const float* wk, const float* bias, float* out, long long n_frames, int cin, int cout,
+                int h, int w, cudaStream_t st) {
+    if (h == w) {
+#define X(CI, CO, HH, FG) \
+    if (cin == CI && cout == CO && h == HH) return fw_launch<FwCfg<CI, CO, HH, FG>>(in, wk, bias, out, n_frames, st);
+        MB_FW_SHAPES(X)
+#undef X
+    }
+    set_error("mb_conv3x3_fwd: shape cin=%d cout=%d %dx%d is not covered (see mb_conv3x3_fwd_supported)", cin, cout, h, w);
+    return MB_ERR_UNSUPPORTED;
+}
+
+// ---------------------------------------------------------------------------------------------
 // Backward of max_pool2d(kernel 3, stride 2, padding 1) (reference model.py:96) from the argmax
 // indices the forward saved.  ATen's max_pool_backward_nchw took 2.0 ms of the step for ~0.9 GB of
 // traffic; this is a gather: one thread per INPUT pixel looks at the (at most four) windows that
@@ -324,9 +552,57 @@ __global__ void __launch_bounds__(256) maxpool3s2_bwd_kernel(const float* __rest
     }
 }
 
+// Same gather, four input pixels of a row per thread (w % 4 == 0): one float4 store, the six windows that can
+// cover them read once.  LW / LH = log2 of the (power of two) map size, so the index split is shifts only.
+template <int LW, int LH>
+__global__ void __launch_bounds__(256) maxpool3s2_bwd_vec_kernel(const float* __restrict__ dy,
+                                                                 const long long* __restrict__ idx,
+                                                                 float* __restrict__ dx, long long planes) {
+    constexpr int W = 1 << LW, H = 1 << LH, OW = W / 2, OH = H / 2, QW = W / 4;
+    const long long total = planes * (H * QW);
+    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total;
+         i += (long long)gridDim.x * blockDim.x) {
+        const long long pl = i / (H * QW);                       // compile-time power of two: a shift
+        const int r = int(i - pl * (H * QW));
+        const int y = r / QW, x0 = (r - y * QW) * 4;
+        const int oy0 = y >> 1, oy1 = min((y + 1) >> 1, OH - 1);
+        const int oxa = x0 >> 1;                                 // windows oxa, oxa+1, oxa+2 (if inside)
+        const float* g = dy + pl * (OH * OW);
+        const long long* ix = idx + pl * (OH * OW);
+        float o[4] = {0.f, 0.f, 0.f, 0.f};
+        const int base = y * W + x0;
+#pragma unroll
+        for (int k = 0; k < 2; ++k) {
+            const int oy = k == 0 ? oy0 : oy1;
+            if (k == 1 && oy1 == oy0) break;
+#pragma unroll
+            for (int j = 0; j < 3; ++j) {
+                const int ox = oxa + j;
+                if (ox >= OW) break;
+                const int d = int(__ldg(ix + oy * OW + ox)) - base;     // which of my four pixels, if any
+                const float v = __ldg(g + oy * OW + ox);
+#pragma unroll
+                for (int e = 0; e < 4; ++e) o[e] += (d == e) ? v : 0.0f;
+            }
+        }
+        *reinterpret_cast<float4*>(dx + pl * (H * W) + base) = make_float4(o[0], o[1], o[2], o[3]);
+    }
+}
+
 int maxpool3s2_bwd(const float* dy, const long long* idx, float* dx, long long planes, int h, int w, cudaStream_t st) {
     int dev = 0;
     MB_CUDA(cudaGetDevice(&dev));
+    if (h == w && (h == 4 || h == 8 || h == 16 || h == 32) && (reinterpret_cast<uintptr_t>(dx) & 15) == 0) {
+        const long long total = planes * h * (w / 4);
+        const long long want = (total + 255) / 256, cap = (long long)sm_count(dev) * 16;
+        const int grid = int(want < cap ? want : cap);
+        if (h == 4) maxpool3s2_bwd_vec_kernel<2, 2><<<grid, 256, 0, st>>>(dy, idx, dx, planes);
+        if (h == 8) maxpool3s2_bwd_vec_kernel<3, 3><<<grid, 256, 0, st>>>(dy, idx, dx, planes);
+        if (h == 16) maxpool3s2_bwd_vec_kernel<4, 4><<<grid, 256, 0, st>>>(dy, idx, dx, planes);
+        if (h == 32) maxpool3s2_bwd_vec_kernel<5, 5><<<grid, 256, 0, st>>>(dy, idx, dx, planes);
+        MB_CUDA(cudaGetLastError());
+        return MB_OK;
+    }
     const int oh = (h + 1) / 2, ow = (w + 1) / 2;
     const long long total = planes * h * w;
     const long long want = (total + 255) / 256;
@@ -337,6 +613,28 @@ int maxpool3s2_bwd(const float* dy, const long long* idx, float* dx, long long p
 }
 
 }  // namespace mb
+
+extern "C" int mb_conv3x3_fwd_supported(int32_t cin, int32_t cout, int32_t h, int32_t w) {
+    return mb::conv3x3_fwd_supported(cin, cout, h, w);
+}
+
+extern "C" int mb_conv3x3_fwd(const float* in, const float* wk, const float* bias, float* out, int64_t n_frames,
+                              int32_t cin, int32_t cout, int32_t h, int32_t w, void* stream) {
+    if (n_frames < 0) {
+        mb::set_error("mb_conv3x3_fwd: n_frames=%lld out of range", (long long)n_frames);
+        return MB_ERR_INVALID;
+    }
+    if (n_frames == 0) return MB_OK;
+    if (!in || !wk || !out) {
+        mb::set_error("mb_conv3x3_fwd: null pointer");
+        return MB_ERR_INVALID;
+    }
+    if ((reinterpret_cast<uintptr_t>(in) | reinterpret_cast<uintptr_t>(out)) & 15) {
+        mb::set_error("mb_conv3x3_fwd: in and out must be 16-byte aligned");
+        return MB_ERR_INVALID;
+    }
+    return mb::conv3x3_fwd(in, wk, bias, out, n_frames, cin, cout, h, w, static_cast<cudaStream_t>(stream));
+}
 
 extern "C" int mb_maxpool3s2_bwd(const float* dy, const int64_t* idx, float* dx, int64_t planes, int32_t h, int32_t w,
                                  void* stream) {

@@ -95,6 +95,11 @@ class _Conv3x3(torch.autograd.Function):
     @staticmethod
     def forward(ctx, x, weight, bias):
         ctx.save_for_backward(x, weight)
+        if FAST_CONV_FORWARD:
+            cout, cin = weight.shape[:2]
+            y = ops.conv3x3_fwd(x, weight.permute(1, 0, 2, 3).reshape(cin, cout, 9).contiguous(), bias)
+            if y is not None:
+                return y
         return F.conv2d(x, weight, bias, padding=1)
 
     @staticmethod
@@ -103,7 +108,11 @@ class _Conv3x3(torch.autograd.Function):
         g = g.contiguous()
         gx = None
         if ctx.needs_input_grad[0]:
-            gx = F.conv2d(g, weight.flip(2, 3).transpose(0, 1).contiguous(), None, padding=1)
+            cout, cin = weight.shape[:2]
+            if FAST_CONV_FORWARD:           # the data gradient is a forward-type convolution with the kernel flipped
+                gx = ops.conv3x3_fwd(g, weight.flip(2, 3).reshape(cout, cin, 9).contiguous(), None)
+            if gx is None:
+                gx = F.conv2d(g, weight.flip(2, 3).transpose(0, 1).contiguous(), None, padding=1)
         gw = ops.conv3x3_wgrad(x, g) if FAST_CONV_WGRAD else None      # csrc/convgrad.cu; None: shape not covered
         if gw is not None:
             return gx, gw, g.sum(dim=(0, 2, 3))
@@ -146,6 +155,9 @@ FAST_CONV_BACKWARD = True
 # weight gradients of the 3x3 convolutions by mb_conv3x3_wgrad (fp32 FMA, deterministic) instead of cuDNN's
 # wgrad kernels, which were a third of the learner step (profiles/r01_encoder_layers.txt)
 FAST_CONV_WGRAD = True
+# forward convolutions and their data gradients by mb_conv3x3_fwd (fp32 FMA, register tiled) instead of cuDNN's
+# implicit-GEMM / winograd kernels
+FAST_CONV_FORWARD = True
 
 
 def cell_list(action_mask: torch.Tensor, cells: int, auto: bool):

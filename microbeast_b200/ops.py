@@ -293,6 +293,28 @@ def conv3x3_wgrad(x: torch.Tensor, dy: torch.Tensor) -> Optional[torch.Tensor]:
     return partials.sum(dim=0).view(cout, cin, 3, 3)
 
 
+def conv3x3_fwd(x: torch.Tensor, wk: torch.Tensor, bias: Optional[torch.Tensor]) -> Optional[torch.Tensor]:
+    """``out [n,cout,h,w]`` of a 3x3 / stride 1 / pad 1 convolution of ``x [n,cin,h,w]`` with the kernel
+    given as ``wk [cin, cout, 9]`` (see ``mb_conv3x3_fwd``), or ``None`` for a shape that is not covered."""
+    dev = _need_cuda(x=x, wk=wk, bias=bias)
+    if x.dtype != torch.float32 or x.dim() != 4 or wk.dim() != 3:
+        return None
+    n, cin, h, w = x.shape
+    cout = wk.shape[1]
+    if wk.shape[0] != cin or wk.shape[2] != 9 or not lib.mb_conv3x3_fwd_supported(cin, cout, h, w):
+        return None
+    x = x.contiguous()
+    wk = _as(wk, torch.float32, "wk")
+    if bias is not None:
+        bias = _as(bias, torch.float32, "bias")
+    if x.data_ptr() & 15:
+        return None
+    out = torch.empty((n, cout, h, w), dtype=torch.float32, device=dev)
+    with torch.cuda.device(dev), _Launch(f"conv3x3_fwd_{cin}x{cout}x{h}", note={"n": n, "cin": cin, "cout": cout, "h": h}):
+        _check(lib.mb_conv3x3_fwd(_ptr(x), _ptr(wk), _ptr(bias), _ptr(out), n, cin, cout, h, w, _stream()))
+    return out
+
+
 def maxpool3s2_bwd(dy: torch.Tensor, idx: torch.Tensor, h: int, w: int) -> torch.Tensor:
     """``dx [n,c,h,w]`` of ``max_pool2d(x, 3, stride=2, padding=1)`` from ``dy`` and the forward's argmax
     indices (both ``[n,c,(h+1)//2,(w+1)//2]``)."""

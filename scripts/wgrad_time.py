@@ -25,3 +25,16 @@ for cin, cout, h in [(27, 16, 16), (16, 16, 8), (16, 32, 8), (32, 32, 4), (32, 3
     useful = 2.0 * n * cout * cin * (3 * h - 2) ** 2
     print(f"cin={cin} cout={cout} {h}x{h}: cudnn {t_c*1e3:8.1f} us   mb_conv3x3_wgrad+bias {t_m*1e3:8.1f} us   "
           f"({useful / t_m / 1e9:.1f} TFLOP/s useful, x{t_c / t_m:.2f})", flush=True)
+
+print("forward-type convolution (forward and data gradient):")
+for cin, cout, h in [(27, 16, 16), (16, 16, 8), (16, 32, 8), (32, 16, 8), (32, 32, 4), (32, 32, 2)]:
+    x = torch.relu(torch.randn(n, cin, h, h, device="cuda"))
+    w = torch.randn(cout, cin, 3, 3, device="cuda") * 0.1
+    b = torch.randn(cout, device="cuda")
+    wk = w.permute(1, 0, 2, 3).reshape(cin, cout, 9).contiguous()
+    cudnn = lambda: torch.nn.functional.conv2d(x, w, b, padding=1)
+    mine = lambda: ops.conv3x3_fwd(x, wk, b)
+    t_c, t_m = timeit(cudnn), timeit(mine)
+    useful = 2.0 * n * cout * cin * (3 * h - 2) ** 2
+    print(f"cin={cin} cout={cout} {h}x{h}: cudnn {t_c*1e3:8.1f} us   mb_conv3x3_fwd {t_m*1e3:8.1f} us   "
+          f"({useful / t_m / 1e9:.1f} TFLOP/s useful, x{t_c / t_m:.2f})", flush=True)

@@ -125,3 +125,74 @@ def test_maxpool_backward_matches_autograd(n, c, h):
     # a pixel that is the argmax of several windows sums 2-4 gradients; ATen adds them with atomics in
     # arbitrary order, so allow one rounding of that small sum
     assert torch.allclose(got, want, rtol=0, atol=1e-6), float((got - want).abs().max())
+
+
+FWD_SHAPES = [(27, 16, 16), (27, 16, 8), (16, 16, 16), (16, 16, 8), (16, 16, 4), (16, 32, 16), (16, 32, 8), (16, 32, 4),
+              (32, 16, 16), (32, 16, 8), (32, 16, 4), (32, 32, 8), (32, 32, 4), (32, 32, 2)]
+
+
+@pytest.mark.parametrize("cin,cout,h", FWD_SHAPES)
+@pytest.mark.parametrize("n", [1, 5, 67, 300])
+def test_conv_forward_matches_conv2d(cin, cout, h, n):
+    """mb_conv3x3_fwd == F.conv2d(padding=1) (fp64 reference), with and without bias; frames past the last
+    chunk are not written."""
+    from microbeast_b200 import ops
+    g = torch.Generator(device="cuda").manual_seed(cin * 100 + cout + h + n)
+    x = torch.randn(n, cin, h, h, device="cuda", generator=g)
+    w = torch.randn(cout, cin, 3, 3, device="cuda", generator=g) * 0.2
+    b = torch.randn(cout, device="cuda", generator=g)
+    wk = w.permute(1, 0, 2, 3).reshape(cin, cout, 9).contiguous()
+    for bias in (b, None):
+        got = ops.conv3x3_fwd(x, wk, bias)
+        assert got is not None and got.shape == (n, cout, h, h)
+        ref = F.conv2d(x.double(), w.double(), None if bias is None else bias.double(), padding=1)
+        ok, worst = close_rms(got.double(), ref, 1e-5)
+        assert ok, worst
+
+
+def test_conv_forward_as_data_gradient():
+    """The data gradient through mb_conv3x3_fwd (flipped kernel, channel axes swapped) == autograd's."""
+    from microbeast_b200 import ops
+    for cin, cout, h in [(16, 16, 8), (16, 32, 8), (32, 32, 4), (32, 32, 2)]:
+        g = torch.Generator(device="cuda").manual_seed(h)
+        x = torch.randn(33, cin, h, h, device="cuda", generator=g, dtype=torch.float64, requires_grad=True)
+        w = torch.randn(cout, cin, 3, 3, device="cuda", generator=g, dtype=torch.float64)
+        dy = torch.randn(33, cout, h, h, device="cuda", generator=g, dtype=torch.float64)
+        (want,) = torch.autograd.grad(F.conv2d(x, w, None, padding=1), x, dy)
+        got = ops.conv3x3_fwd(dy.float(), w.float().flip(2, 3).reshape(cout, cin, 9).contiguous(), None)
+        ok, worst = close_rms(got.double(), want, 1e-5)
+        assert ok, (cin, cout, h, worst)
+
+
+def test_conv_forward_uncovered_shape_returns_none():
+    from microbeast_b200 import ops
+    assert ops.conv3x3_fwd(torch.randn(2, 8, 8, 8, device="cuda"), torch.randn(8, 8, 9, device="cuda"), None) is None
+
+
+def test_encoder_with_and_without_fast_forward():
+    """Agent outputs and gradients with FAST_CONV_FORWARD on == off (cuDNN forward and data gradient)."""
+    from microbeast_b200 import model as mmodel, synth
+    from microbeast_b200.learner import PPO_learn
+    for h in (8, 16):
+        torch.manual_seed(5)
+        agent = mmodel.Agent((h, h, 27), [6, 4, 4, 4, 4, 7, 49] * (h * h), h * h).cuda()
+        with torch.no_grad():
+            agent.actor.weight.normal_(0, 0.01)
+        T, rows = 5, 7
+        batch = synth.make_rollout_batch(h, h, T, rows, seed=6, preset="dense", full_keys=False)
+        batch["logprobs"] = -torch.rand(batch["reward"].shape) * 20
+        res = {}
+        for flag in (True, False):
+            mmodel.FAST_CONV_FORWARD = flag
+            try:
+                four = PPO_learn(agent, agent, "w", batch, torch.optim.SGD(agent.parameters(), lr=0.0), rows, T, 1)
+            finally:
+                mmodel.FAST_CONV_FORWARD = True
+            res[flag] = (four, {k: p.grad.clone() for k, p in agent.named_parameters()})
+        import numpy as np
+        np.testing.assert_allclose(res[True][0], res[False][0], rtol=2e-5, atol=1e-7)
+        # two fp32 implementations of 15 convolution layers and their data gradients: rounding differences of
+        # the activations (~1e-6) reach the gradients amplified by the network; 3e-4 of the gradient's rms
+        for k in res[True][1]:
+            ok, worst = close_rms(res[True][1][k], res[False][1][k], 3e-4)
+            assert ok, (h, k, worst)
