@@ -193,6 +193,16 @@ MB_API int mb_conv3x3_fwd_supported(int32_t cin, int32_t cout, int32_t h, int32_
 MB_API int mb_conv3x3_fwd(const float* in, const float* wk, const float* bias, float* out, int64_t n_frames,
                           int32_t cin, int32_t cout, int32_t h, int32_t w, void* stream);
 
+/* Actor Linear forward (reference model.py:136,167: logits = actor(hidden)) on the tcgen05 tensor cores at
+ * fp32 accuracy: c[m,n] = a[m,k] * b[n,k]^T + bias[n] with both operands given as a TF32 "hi" part and a TF32
+ * "lo" remainder (mb_split_tf32: x = hi + lo up to 2^-22 |x|) and three TF32 products accumulated in fp32:
+ * a_hi*b_hi + a_lo*b_hi + a_hi*b_lo.  a_* [m,k], b_* [n,k], c [m,n] row-major fp32, 16-byte aligned;
+ * k % 32 == 0, n % 4 == 0; bias [n] or NULL; status = optional device word (pipeline-timeout bit). */
+MB_API int mb_split_tf32(const float* x, float* hi, float* lo, int64_t n, void* stream);
+MB_API int mb_linear_tf32x3(const float* a_hi, const float* a_lo, const float* b_hi, const float* b_lo,
+                            const float* bias, float* c, int64_t m, int64_t n, int32_t k, int32_t* status,
+                            void* stream);
+
 /* Backward of max_pool2d(kernel 3, stride 2, padding 1) (reference model.py:96) from the argmax
  * indices of the forward: dy, idx [planes, (h+1)/2, (w+1)/2] (idx = flat position in the h*w input
  * plane, as torch.nn.functional.max_pool2d(..., return_indices=True) returns it), dx [planes, h, w]. */

@@ -1,0 +1,354 @@
+// Actor Linear forward on the 5th-generation tensor cores (tcgen05, TMEM accumulators, TMA operands)
+// at fp32 accuracy, for sm_100a.
+//
+// Reference: model.py:136,167 -- logits = actor(hidden), a Linear 256 -> 78*C evaluated for every
+// frame of the learner batch.  In fp32 on the CUDA cores (cuBLAS SIMT SGEMM) this product was 3.7 ms of a
+// 17 ms learner step at 16x16, T=80, 256 rows.  A single TF32 tensor-core product would be 8x faster but
+// carries 10 mantissa bits, far outside the 1e-5 parity budget.  This kernel keeps fp32 accuracy by
+// splitting both operands into a TF32 "hi" part and a TF32 "lo" remainder (x = hi + lo exactly, up to
+// 2^-22) and accumulating three tensor-core products in the fp32 TMEM accumulator:
+//     A*B ~= A_hi*B_hi + A_lo*B_hi + A_hi*B_lo          (the dropped A_lo*B_lo term is <= 2^-22 |A||B|)
+//
+// C[M,N] = A[M,K] * B[N,K]^T + bias[N];  A = hidden (K-major), B = the Linear's weight [N,K] (K-major).
+//
+// Layout of one CTA (192 threads, one per SM, persistent over 128 x 256 output tiles):
+//   warp 0, one lane: TMA producer -- per 32-wide K block four boxes (A_hi, A_lo 128x32; B_hi, B_lo
+//                     256x32 fp32, 128-byte swizzle) into a 2-stage shared-memory ring (96 KB a stage);
+//   warp 1, one lane: issues tcgen05.mma.kind::tf32 (M=128, N=256, K=8): 4 K-steps x 3 products per
+//                     K block into one of two 256-column TMEM accumulators; tcgen05.commit releases the
+//                     stage to the producer and, after the last K block, hands the accumulator over;
+//   warps 2-5:        epilogue -- tcgen05.ld the finished accumulator (a warp reads its own 32-lane
+//                     quadrant, a thread one output row), add the bias, store; meanwhile warp 1 is
+//                     already filling the other accumulator.
+#include "common.cuh"
+
+#include <cuda.h>
+
+#include <mutex>
+
+#include "../../include/mbeast.h"
+
+namespace mb {
+
+int sm_count(int device);
+
+namespace {
+
+constexpr int kGemmBM = 128, kGemmBN = 256, kGemmBK = 32, kGemmStages = 2;
+constexpr int kGemmThreads = 192;
+constexpr int kTileA = kGemmBM * kGemmBK * 4;        // 16 KB
+constexpr int kTileB = kGemmBN * kGemmBK * 4;        // 32 KB
+constexpr int kStageBytes = 2 * kTileA + 2 * kTileB; // 96 KB
+constexpr int kGemmSmem = kGemmStages * kStageBytes + 1024;
+constexpr uint32_t kTmemCols = 512;                  // two 256-column fp32 accumulators
+
+struct GemmMaps {
+    CUtensorMap a_hi, a_lo, b_hi, b_lo;
+};
+
+// ---- tcgen05 wrappers -------------------------------------------------------------------------
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+
+__device__ __forceinline__ void tmem_alloc(uint32_t* slot_smem, uint32_t cols) {       // whole warp
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(slot_smem)), "r"(cols)
+                 : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tmem_dealloc(uint32_t addr, uint32_t cols) {           // whole warp
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(addr), "r"(cols) : "memory");
+}
+__device__ __forceinline__ void tc_commit(uint64_t* bar) {                             // one thread
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar))
+                 : "memory");
+}
+// D[tmem] (+)= A[smem] * B[smem]^T, TF32 inputs, fp32 accumulate; one thread issues for the CTA
+__device__ __forceinline__ void mma_tf32(uint32_t d_tmem, uint64_t desc_a, uint64_t desc_b, uint32_t idesc,
+                                         uint32_t accumulate) {
+    asm volatile(
+        "{\n\t"
+        ".reg .pred p;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, {%5, %6, %7, %8}, p;\n\t"
+        "}\n" ::"r"(d_tmem),
+        "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accumulate), "r"(0), "r"(0), "r"(0), "r"(0)
+        : "memory");
+}
+// 32 lanes x 32 columns of fp32: thread i of the warp gets lane (base lane + i), columns col .. col+31
+__device__ __forceinline__ void tmem_ld32(uint32_t taddr, float (&v)[32]) {
+    uint32_t r[32];
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+        "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+        "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+        : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
+          "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]), "=r"(r[16]),
+          "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]), "=r"(r[24]),
+          "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+        : "r"(taddr)
+        : "memory");
+    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+#pragma unroll
+    for (int i = 0; i < 32; ++i) v[i] = __uint_as_float(r[i]);
+}
+
+// Shared-memory matrix descriptor of a K-major operand tile staged by TMA with 128-byte swizzle: rows of
+// 32 fp32 (128 B), 8-row groups 1024 B apart.  Bits: [0,14) start address >> 4; [16,30) leading byte offset
+// >> 4 (unused for swizzled K-major, 1); [32,46) stride byte offset >> 4 (1024 B between 8-row groups);
+// [46,48) descriptor version 1 (sm_100); [61,64) layout type 2 = SWIZZLE_128B.
+__device__ __forceinline__ uint64_t make_kmajor_sw128_desc(uint32_t smem_addr) {
+    uint64_t d = 0;
+    d |= uint64_t((smem_addr & 0x3ffffu) >> 4);
+    d |= uint64_t(1) << 16;
+    d |= uint64_t(1024 >> 4) << 32;
+    d |= uint64_t(1) << 46;
+    d |= uint64_t(2) << 61;
+    return d;
+}
+
+// Instruction descriptor of tcgen05.mma.kind::tf32: [4,6) D format 1 = F32; [7,10) A format 2 = TF32;
+// [10,13) B format 2 = TF32; bits 15 / 16 = 0: A and B are K-major; [17,23) N >> 3; [24,29) M >> 4.
+constexpr uint32_t kIdescTf32 = (1u << 4) | (2u << 7) | (2u << 10) | (uint32_t(kGemmBN >> 3) << 17) |
+                                (uint32_t(kGemmBM >> 4) << 24);
+
+__global__ void __launch_bounds__(256) split_tf32_kernel(const float* __restrict__ x, float* __restrict__ hi,
+                                                         float* __restrict__ lo, long long n) {
+    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+        const float v = x[i];
+        uint32_t h, l;
+        asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(h) : "f"(v));                    // nearest TF32: low 13 mantissa bits zero
+        const float r = v - __uint_as_float(h);                                // exact
+        asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(l) : "f"(r));
+        hi[i] = __uint_as_float(h);
+        lo[i] = __uint_as_float(l);
+    }
+}
+
+__global__ void __launch_bounds__(kGemmThreads, 1) linear_tf32x3_kernel(const __grid_constant__ GemmMaps maps,
+                                                                        const float* __restrict__ bias,
+                                                                        float* __restrict__ C, int M, int N, int K,
+                                                                        int* status) {
+    extern __shared__ uint8_t gemm_smem_raw[];
+    __shared__ __align__(8) uint64_t full_bar[kGemmStages];      // TMA boxes of a stage have landed
+    __shared__ __align__(8) uint64_t empty_bar[kGemmStages];     // the MMAs reading a stage have completed
+    __shared__ __align__(8) uint64_t tfull_bar[2];               // an accumulator is complete
+    __shared__ __align__(8) uint64_t tempty_bar[2];              // the epilogue has drained an accumulator
+    __shared__ uint32_t tmem_slot;
+    uint8_t* smem = gemm_smem_raw + ((1024u - (smem_u32(gemm_smem_raw) & 1023u)) & 1023u);     // swizzle atoms: 1024 B
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < kGemmStages; ++s) {
+            mbar_init(&full_bar[s], 1);
+            mbar_init(&empty_bar[s], 1);
+        }
+        for (int b = 0; b < 2; ++b) {
+            mbar_init(&tfull_bar[b], 1);
+            mbar_init(&tempty_bar[b], 4);                        // one arrival per epilogue warp
+        }
+        fence_mbar_init();
+        tma_prefetch_desc(&maps.a_hi);
+        tma_prefetch_desc(&maps.a_lo);
+        tma_prefetch_desc(&maps.b_hi);
+        tma_prefetch_desc(&maps.b_lo);
+    }
+    if (warp == 1) tmem_alloc(&tmem_slot, kTmemCols);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = tmem_slot;
+
+    const int tiles_m = (M + kGemmBM - 1) / kGemmBM, tiles_n = (N + kGemmBN - 1) / kGemmBN;
+    const int n_tiles = tiles_m * tiles_n;
+    const int kblocks = K / kGemmBK;
+
+    if (warp == 0) {
+        // ===================== TMA producer =====================
+        if (lane == 0) {
+            uint32_t it = 0;
+            for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+                const int m0 = (tile / tiles_n) * kGemmBM, n0 = (tile % tiles_n) * kGemmBN;
+                for (int kb = 0; kb < kblocks; ++kb, ++it) {
+                    const int s = it % kGemmStages;
+                    const uint32_t ph = (it / kGemmStages) & 1;
+                    mbar_wait(&empty_bar[s], ph ^ 1, status);     // passes at once the first time round
+                    uint8_t* st = smem + s * kStageBytes;
+                    mbar_arrive_expect_tx(&full_bar[s], uint32_t(kStageBytes));
+                    tma_load_2d(st, &maps.a_hi, kb * kGemmBK, m0, &full_bar[s]);
+                    tma_load_2d(st + kTileA, &maps.a_lo, kb * kGemmBK, m0, &full_bar[s]);
+                    tma_load_2d(st + 2 * kTileA, &maps.b_hi, kb * kGemmBK, n0, &full_bar[s]);
+                    tma_load_2d(st + 2 * kTileA + kTileB, &maps.b_lo, kb * kGemmBK, n0, &full_bar[s]);
+                }
+            }
+        }
+    } else if (warp == 1) {
+        // ===================== MMA issuer =====================
+        if (lane == 0) {
+            uint32_t it = 0, tcount = 0;
+            for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, ++tcount) {
+                const uint32_t b = tcount & 1, tph = (tcount >> 1) & 1;
+                mbar_wait(&tempty_bar[b], tph ^ 1, status);       // accumulator b is free (at once for the first two)
+                tc_fence_after();
+                const uint32_t d_tmem = tmem_base + b * uint32_t(kGemmBN);
+                for (int kb = 0; kb < kblocks; ++kb, ++it) {
+                    const int s = it % kGemmStages;
+                    const uint32_t ph = (it / kGemmStages) & 1;
+                    mbar_wait(&full_bar[s], ph, status);
+                    tc_fence_after();
+                    const uint32_t st = smem_u32(smem + s * kStageBytes);
+                    const uint64_t a_hi = make_kmajor_sw128_desc(st), a_lo = make_kmajor_sw128_desc(st + kTileA);
+                    const uint64_t b_hi = make_kmajor_sw128_desc(st + 2 * kTileA);
+                    const uint64_t b_lo = make_kmajor_sw128_desc(st + 2 * kTileA + kTileB);
+#pragma unroll
+                    for (int k = 0; k < kGemmBK / 8; ++k) {
+                        const uint64_t adv = uint64_t((k * 8 * 4) >> 4);      // 8 TF32 = 32 B along K inside the swizzle atom
+                        mma_tf32(d_tmem, a_hi + adv, b_hi + adv, kIdescTf32, (kb | k) != 0);
+                        mma_tf32(d_tmem, a_lo + adv, b_hi + adv, kIdescTf32, 1);
+                        mma_tf32(d_tmem, a_hi + adv, b_lo + adv, kIdescTf32, 1);
+                    }
+                    tc_commit(&empty_bar[s]);                     // the stage is free once these MMAs have read it
+                }
+                tc_commit(&tfull_bar[b]);                         // accumulator b is complete
+            }
+        }
+    } else {
+        // ===================== epilogue (warps 2..5) =====================
+        const int q = warp & 3;                                   // the TMEM lane quadrant this warp may read
+        uint32_t tcount = 0;
+        for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, ++tcount) {
+            const uint32_t b = tcount & 1, tph = (tcount >> 1) & 1;
+            const int m0 = (tile / tiles_n) * kGemmBM, n0 = (tile % tiles_n) * kGemmBN;
+            mbar_wait(&tfull_bar[b], tph, status);
+            tc_fence_after();
+            const int row = m0 + q * 32 + lane;
+            float* crow = C + (long long)row * N;
+#pragma unroll 1
+            for (int c0 = 0; c0 < kGemmBN; c0 += 32) {
+                float v[32];
+                tmem_ld32(tmem_base + b * uint32_t(kGemmBN) + uint32_t(c0) + (uint32_t(q * 32) << 16), v);
+                if (row < M) {
+#pragma unroll
+                    for (int j = 0; j < 32; j += 4) {
+                        const int col = n0 + c0 + j;
+                        if (col < N) {                            // N % 4 == 0 (checked by the host)
+                            const float4 bb = bias ? __ldg(reinterpret_cast<const float4*>(bias + col))
+                                                   : make_float4(0.f, 0.f, 0.f, 0.f);
+                            *reinterpret_cast<float4*>(crow + col) =
+                                make_float4(v[j] + bb.x, v[j + 1] + bb.y, v[j + 2] + bb.z, v[j + 3] + bb.w);
+                        }
+                    }
+                }
+            }
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&tempty_bar[b]);
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    if (warp == 1) tmem_dealloc(tmem_base, kTmemCols);
+}
+
+// ---- host ------------------------------------------------------------------------------------
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+EncodeTiledFn gemm_encode_fn() {
+    static EncodeTiledFn fn = nullptr;
+    static std::once_flag once;
+    std::call_once(once, [] {
+        void* ptr = nullptr;
+        cudaDriverEntryPointQueryResult qres;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &ptr, cudaEnableDefault, &qres) == cudaSuccess &&
+            qres == cudaDriverEntryPointSuccess)
+            fn = reinterpret_cast<EncodeTiledFn>(ptr);
+    });
+    return fn;
+}
+
+// [rows, K] fp32 row-major -> boxes of box_rows x 32 floats (128 B), 128-byte swizzle, zero fill past the edges
+bool gemm_map(EncodeTiledFn enc, CUtensorMap* m, const float* base, long long rows, int K, int box_rows) {
+    const cuuint64_t gdim[2] = {cuuint64_t(K), cuuint64_t(rows)};
+    const cuuint64_t gstride[1] = {cuuint64_t(K) * 4u};
+    const cuuint32_t box[2] = {cuuint32_t(kGemmBK), cuuint32_t(box_rows)};
+    const cuuint32_t estr[2] = {1, 1};
+    return enc(m, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<float*>(base), gdim, gstride, box, estr,
+               CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+               CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+}
+
+}  // namespace
+
+int split_tf32(const float* x, float* hi, float* lo, long long n, cudaStream_t st) {
+    if (n == 0) return MB_OK;
+    int dev = 0;
+    MB_CUDA(cudaGetDevice(&dev));
+    const long long want = (n + 255) / 256, cap = (long long)sm_count(dev) * 8;
+    split_tf32_kernel<<<int(want < cap ? want : cap), 256, 0, st>>>(x, hi, lo, n);
+    MB_CUDA(cudaGetLastError());
+    return MB_OK;
+}
+
+int linear_tf32x3(const float* a_hi, const float* a_lo, const float* b_hi, const float* b_lo, const float* bias, float* c,
+                  long long M, long long N, int K, int* status, cudaStream_t st) {
+    EncodeTiledFn enc = gemm_encode_fn();
+    if (!enc) {
+        set_error("mb_linear_tf32x3: cuTensorMapEncodeTiled is not available from this driver");
+        return MB_ERR_UNSUPPORTED;
+    }
+    GemmMaps maps;
+    if (!gemm_map(enc, &maps.a_hi, a_hi, M, K, kGemmBM) || !gemm_map(enc, &maps.a_lo, a_lo, M, K, kGemmBM) ||
+        !gemm_map(enc, &maps.b_hi, b_hi, N, K, kGemmBN) || !gemm_map(enc, &maps.b_lo, b_lo, N, K, kGemmBN)) {
+        set_error("mb_linear_tf32x3: cuTensorMapEncodeTiled rejected M=%lld N=%lld K=%d", M, N, K);
+        return MB_ERR_INVALID;
+    }
+    int dev = 0;
+    MB_CUDA(cudaGetDevice(&dev));
+    static bool attr_set[64] = {};
+    bool& done = attr_set[(dev >= 0 && dev < 64) ? dev : 0];
+    if (!done) {
+        MB_CUDA(cudaFuncSetAttribute(linear_tf32x3_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kGemmSmem));
+        done = true;
+    }
+    const long long tiles = ((M + kGemmBM - 1) / kGemmBM) * ((N + kGemmBN - 1) / kGemmBN);
+    const int sms = sm_count(dev);
+    const int grid = int(tiles < sms ? tiles : sms);
+    linear_tf32x3_kernel<<<grid, kGemmThreads, kGemmSmem, st>>>(maps, bias, c, int(M), int(N), K, status);
+    MB_CUDA(cudaGetLastError());
+    return MB_OK;
+}
+
+}  // namespace mb
+
+extern "C" int mb_split_tf32(const float* x, float* hi, float* lo, int64_t n, void* stream) {
+    if (n < 0 || (n > 0 && (!x || !hi || !lo))) {
+        mb::set_error("mb_split_tf32: bad arguments (n=%lld)", (long long)n);
+        return MB_ERR_INVALID;
+    }
+    return mb::split_tf32(x, hi, lo, n, static_cast<cudaStream_t>(stream));
+}
+
+extern "C" int mb_linear_tf32x3(const float* a_hi, const float* a_lo, const float* b_hi, const float* b_lo,
+                                const float* bias, float* c, int64_t m, int64_t n, int32_t k, int32_t* status,
+                                void* stream) {
+    if (m < 0 || n < 0 || k <= 0 || k % 32 != 0 || n % 4 != 0 || m > 0x7fffffff || n > 0x7fffffff) {
+        mb::set_error("mb_linear_tf32x3: m=%lld n=%lld k=%d: need k %% 32 == 0 and n %% 4 == 0", (long long)m,
+                      (long long)n, k);
+        return MB_ERR_INVALID;
+    }
+    if (m == 0 || n == 0) return MB_OK;
+    if (!a_hi || !a_lo || !b_hi || !b_lo || !c) {
+        mb::set_error("mb_linear_tf32x3: null pointer");
+        return MB_ERR_INVALID;
+    }
+    const uintptr_t all = reinterpret_cast<uintptr_t>(a_hi) | reinterpret_cast<uintptr_t>(a_lo) |
+                          reinterpret_cast<uintptr_t>(b_hi) | reinterpret_cast<uintptr_t>(b_lo) |
+                          reinterpret_cast<uintptr_t>(c) | reinterpret_cast<uintptr_t>(bias);
+    if (all & 15) {
+        mb::set_error("mb_linear_tf32x3: operands must be 16-byte aligned");
+        return MB_ERR_INVALID;
+    }
+    return mb::linear_tf32x3(a_hi, a_lo, b_hi, b_lo, bias, c, m, n, k, status, static_cast<cudaStream_t>(stream));
+}

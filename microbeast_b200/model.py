@@ -158,6 +158,9 @@ FAST_CONV_WGRAD = True
 # forward convolutions and their data gradients by mb_conv3x3_fwd (fp32 FMA, register tiled) instead of cuDNN's
 # implicit-GEMM / winograd kernels
 FAST_CONV_FORWARD = True
+# actor Linear forward (learner mode) by mb_linear_tf32x3: tcgen05 tensor cores, three TF32 products of hi/lo-split
+# operands accumulated in fp32 (error ~1e-6 of max|logit|; cuBLAS fp32: 4e-7) instead of a SIMT SGEMM
+TENSOR_CORE_ACTOR = True
 
 
 def cell_list(action_mask: torch.Tensor, cells: int, auto: bool):
@@ -222,7 +225,9 @@ class _ActorHead(torch.autograd.Function):
 
     @staticmethod
     def forward(ctx, hidden, weight, bias, action_mask, action, cells, mode):
-        logits = _linear_bias_in_k(hidden, weight, bias)                                   # model.py:167
+        logits = ops.linear_tf32x3(hidden, weight, bias) if TENSOR_CORE_ACTOR else None    # model.py:167
+        if logits is None:
+            logits = _linear_bias_in_k(hidden, weight, bias)
         logprobs, entropy = ops.head_eval_fwd(logits, action_mask, action)
         ctx.save_for_backward(hidden, weight, logits, action_mask, action)
         ctx.cells, ctx.mode = cells, mode
