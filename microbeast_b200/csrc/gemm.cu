@@ -11,15 +11,17 @@
 //
 // C[M,N] = A[M,K] * B[N,K]^T + bias[N];  A = hidden (K-major), B = the Linear's weight [N,K] (K-major).
 //
-// Layout of one CTA (192 threads, one per SM, persistent over 128 x 256 output tiles):
+// Layout of one CTA (320 threads, one per SM, persistent over 128 x 256 output tiles):
 //   warp 0, one lane: TMA producer -- per 32-wide K block four boxes (A_hi, A_lo 128x32; B_hi, B_lo
 //                     256x32 fp32, 128-byte swizzle) into a 2-stage shared-memory ring (96 KB a stage);
 //   warp 1, one lane: issues tcgen05.mma.kind::tf32 (M=128, N=256, K=8): 4 K-steps x 3 products per
-//                     K block into one of two 256-column TMEM accumulators; tcgen05.commit releases the
-//                     stage to the producer and, after the last K block, hands the accumulator over;
-//   warps 2-5:        epilogue -- tcgen05.ld the finished accumulator (a warp reads its own 32-lane
-//                     quadrant, a thread one output row), add the bias, store; meanwhile warp 1 is
-//                     already filling the other accumulator.
+//                     K block; the hi*hi products accumulate in TMEM columns [0,256), the two small cross
+//                     terms in columns [256,512) (see the comment at the issue loop: it is what brings the
+//                     error down to cuBLAS fp32 level); tcgen05.commit releases the stage to the producer
+//                     and, after the last K block, hands both accumulators over;
+//   warps 2-9:        epilogue -- tcgen05.ld both accumulators (a warp reads its own 32-lane quadrant, a
+//                     thread 128 columns of one output row), sum them in registers, release the
+//                     accumulators, then add the bias and store while warp 1 already runs the next tile.
 #include "common.cuh"
 
 #include <cuda.h>
@@ -35,12 +37,12 @@ int sm_count(int device);
 namespace {
 
 constexpr int kGemmBM = 128, kGemmBN = 256, kGemmBK = 32, kGemmStages = 2;
-constexpr int kGemmThreads = 192;
+constexpr int kGemmThreads = 320;                   // TMA warp, MMA warp, 8 epilogue warps
 constexpr int kTileA = kGemmBM * kGemmBK * 4;        // 16 KB
 constexpr int kTileB = kGemmBN * kGemmBK * 4;        // 32 KB
 constexpr int kStageBytes = 2 * kTileA + 2 * kTileB; // 96 KB
 constexpr int kGemmSmem = kGemmStages * kStageBytes + 1024;
-constexpr uint32_t kTmemCols = 512;                  // two 256-column fp32 accumulators
+constexpr uint32_t kTmemCols = 512;                  // 256 columns for the hi*hi sum + 256 for the lo terms
 
 struct GemmMaps {
     CUtensorMap a_hi, a_lo, b_hi, b_lo;
@@ -144,7 +146,7 @@ __global__ void __launch_bounds__(kGemmThreads, 1) linear_tf32x3_kernel(const __
         }
         for (int b = 0; b < 2; ++b) {
             mbar_init(&tfull_bar[b], 1);
-            mbar_init(&tempty_bar[b], 4);                        // one arrival per epilogue warp
+            mbar_init(&tempty_bar[b], 8);                        // one arrival per epilogue warp
         }
         fence_mbar_init();
         tma_prefetch_desc(&maps.a_hi);
@@ -183,13 +185,16 @@ __global__ void __launch_bounds__(kGemmThreads, 1) linear_tf32x3_kernel(const __
         }
     } else if (warp == 1) {
         // ===================== MMA issuer =====================
+        // The tensor core truncates when it adds a product into the fp32 accumulator, so every MMA into a LARGE
+        // accumulator costs a fraction of an ulp of the result.  The hi*hi products (the bulk of the value) go to
+        // columns [0,256), the two small cross terms to columns [256,512): their accumulator is 2^-11 the size, so
+        // are its truncation errors, and the big one sees 32 additions instead of 96 at K = 256.
         if (lane == 0) {
             uint32_t it = 0, tcount = 0;
+            const uint32_t d_main = tmem_base, d_lo = tmem_base + uint32_t(kGemmBN);
             for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, ++tcount) {
-                const uint32_t b = tcount & 1, tph = (tcount >> 1) & 1;
-                mbar_wait(&tempty_bar[b], tph ^ 1, status);       // accumulator b is free (at once for the first two)
+                mbar_wait(&tempty_bar[0], (tcount & 1) ^ 1, status);      // the epilogue has read the last tile out
                 tc_fence_after();
-                const uint32_t d_tmem = tmem_base + b * uint32_t(kGemmBN);
                 for (int kb = 0; kb < kblocks; ++kb, ++it) {
                     const int s = it % kGemmStages;
                     const uint32_t ph = (it / kGemmStages) & 1;
@@ -202,46 +207,54 @@ __global__ void __launch_bounds__(kGemmThreads, 1) linear_tf32x3_kernel(const __
 #pragma unroll
                     for (int k = 0; k < kGemmBK / 8; ++k) {
                         const uint64_t adv = uint64_t((k * 8 * 4) >> 4);      // 8 TF32 = 32 B along K inside the swizzle atom
-                        mma_tf32(d_tmem, a_hi + adv, b_hi + adv, kIdescTf32, (kb | k) != 0);
-                        mma_tf32(d_tmem, a_lo + adv, b_hi + adv, kIdescTf32, 1);
-                        mma_tf32(d_tmem, a_hi + adv, b_lo + adv, kIdescTf32, 1);
+                        mma_tf32(d_main, a_hi + adv, b_hi + adv, kIdescTf32, (kb | k) != 0);
+                        mma_tf32(d_lo, a_lo + adv, b_hi + adv, kIdescTf32, (kb | k) != 0);
+                        mma_tf32(d_lo, a_hi + adv, b_lo + adv, kIdescTf32, 1);
                     }
                     tc_commit(&empty_bar[s]);                     // the stage is free once these MMAs have read it
                 }
-                tc_commit(&tfull_bar[b]);                         // accumulator b is complete
+                tc_commit(&tfull_bar[0]);                         // both accumulators are complete
             }
         }
     } else {
-        // ===================== epilogue (warps 2..5) =====================
-        const int q = warp & 3;                                   // the TMEM lane quadrant this warp may read
+        // ===================== epilogue (warps 2..9) =====================
+        // warp w reads TMEM lane quadrant w % 4 (a hardware rule); warps 2-5 take columns [0,128), warps 6-9
+        // [128,256).  A thread pulls its 128 sums (main + lo) into registers, releases the accumulators to the MMA
+        // warp at once, and only then does the slow part: bias and the stores.
+        const int q = warp & 3;
+        const int half = (warp - 2) >> 2;
         uint32_t tcount = 0;
         for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, ++tcount) {
-            const uint32_t b = tcount & 1, tph = (tcount >> 1) & 1;
-            const int m0 = (tile / tiles_n) * kGemmBM, n0 = (tile % tiles_n) * kGemmBN;
-            mbar_wait(&tfull_bar[b], tph, status);
+            const int m0 = (tile / tiles_n) * kGemmBM, n0 = (tile % tiles_n) * kGemmBN + half * 128;
+            mbar_wait(&tfull_bar[0], tcount & 1, status);
             tc_fence_after();
-            const int row = m0 + q * 32 + lane;
-            float* crow = C + (long long)row * N;
-#pragma unroll 1
-            for (int c0 = 0; c0 < kGemmBN; c0 += 32) {
-                float v[32];
-                tmem_ld32(tmem_base + b * uint32_t(kGemmBN) + uint32_t(c0) + (uint32_t(q * 32) << 16), v);
-                if (row < M) {
+            const uint32_t lane_base = uint32_t(q * 32) << 16;
+            float acc[128];
 #pragma unroll
-                    for (int j = 0; j < 32; j += 4) {
-                        const int col = n0 + c0 + j;
-                        if (col < N) {                            // N % 4 == 0 (checked by the host)
-                            const float4 bb = bias ? __ldg(reinterpret_cast<const float4*>(bias + col))
-                                                   : make_float4(0.f, 0.f, 0.f, 0.f);
-                            *reinterpret_cast<float4*>(crow + col) =
-                                make_float4(v[j] + bb.x, v[j + 1] + bb.y, v[j + 2] + bb.z, v[j + 3] + bb.w);
-                        }
-                    }
-                }
+            for (int c = 0; c < 4; ++c) {
+                float v[32], w[32];
+                tmem_ld32(tmem_base + lane_base + uint32_t(half * 128 + c * 32), v);
+                tmem_ld32(tmem_base + lane_base + uint32_t(kGemmBN + half * 128 + c * 32), w);
+#pragma unroll
+                for (int j = 0; j < 32; ++j) acc[c * 32 + j] = v[j] + w[j];
             }
             tc_fence_before();
             __syncwarp();
-            if (lane == 0) mbar_arrive(&tempty_bar[b]);
+            if (lane == 0) mbar_arrive(&tempty_bar[0]);
+            const int row = m0 + q * 32 + lane;
+            if (row < M) {
+                float* crow = C + (long long)row * N;
+#pragma unroll
+                for (int j = 0; j < 128; j += 4) {
+                    const int col = n0 + j;
+                    if (col < N) {                                // N % 4 == 0 (checked by the host)
+                        const float4 bb = bias ? __ldg(reinterpret_cast<const float4*>(bias + col))
+                                               : make_float4(0.f, 0.f, 0.f, 0.f);
+                        *reinterpret_cast<float4*>(crow + col) =
+                            make_float4(acc[j] + bb.x, acc[j + 1] + bb.y, acc[j + 2] + bb.z, acc[j + 3] + bb.w);
+                    }
+                }
+            }
         }
     }
     tc_fence_before();
