@@ -341,6 +341,11 @@ def test_sparse_head_equals_dense_head(preset, h):
     from microbeast_b200 import synth
     from microbeast_b200.learner import PPO_learn
     mine, _ = _pair(h, h, seed=31)
+    with torch.no_grad():
+        # the golden weights give logits of O(100..7000), where the entropy is ill-conditioned in fp32 whatever
+        # computes the logits (scripts/actor_precision.py: cuBLAS itself is 46e-5 off at 16x16); a policy-sized
+        # actor layer keeps the comparison about the two code paths
+        mine.actor.weight.normal_(0, 0.02)
     T, rows = 6, 5
     batch = synth.make_rollout_batch(h, h, T, rows, seed=12, preset=preset, full_keys=False)
     batch["logprobs"] = -torch.rand(batch["reward"].shape) * 20
@@ -352,10 +357,9 @@ def test_sparse_head_equals_dense_head(preset, h):
         mine.sparse_head = False
     assert b["policy_logits"] is None
     # the dense path forms its logits with mb_linear_tf32x3 (tensor cores, split precision), the cell list with a
-    # cuBLAS fp32 bmm: two independent fp32-level roundings of logits that the golden weights make O(100), so
-    # the entropies agree to a few 1e-5 rather than to the 1e-5 the kernels keep on identical logits
+    # cuBLAS fp32 bmm: two independent fp32-level roundings of the same logits
     for k in ("logprobs", "entropy"):
-        ok, worst = close_rms(b[k], a[k], 5e-5)
+        ok, worst = close_rms(b[k], a[k], 1e-5)
         assert ok, (k, worst)
     assert torch.equal(a["baseline"], b["baseline"])
     four_d = PPO_learn(mine, mine, "d", batch, torch.optim.SGD(mine.parameters(), lr=0.0), rows, T, 1)
@@ -375,6 +379,8 @@ def test_sparse_head_auto_picks_by_density(preset, expect_sparse):
     """sparse_head="auto": the cell list is used while its padded size is under half the dense grid."""
     from microbeast_b200 import synth
     mine, _ = _pair(8, 8, seed=5)
+    with torch.no_grad():
+        mine.actor.weight.normal_(0, 0.02)
     batch = synth.make_rollout_batch(8, 8, 9, 40, seed=3, preset=preset, full_keys=False)
     dev = {k: v.cuda() for k, v in batch.items()}
     with torch.no_grad():
@@ -383,7 +389,7 @@ def test_sparse_head_auto_picks_by_density(preset, expect_sparse):
         c, _ = mine.get_action(dev, learning=True)
     assert (c["policy_logits"] is None) == expect_sparse
     for k in ("logprobs", "entropy"):
-        ok, worst = close_rms(c[k], a[k], 5e-5)
+        ok, worst = close_rms(c[k], a[k], 1e-5)
         assert ok, (k, worst)
 
 
