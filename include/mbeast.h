@@ -174,8 +174,9 @@ MB_API int mb_active_cells(const uint8_t* mask, uint8_t* active, int64_t n_cells
 /* Weight gradient of a 3x3 / stride 1 / pad 1 convolution in fp32 (the encoder's convolutions,
  * reference model.py:56-109, differentiated by loss.backward() at libs/utils.py:334):
  *   dW[co,ci,ky,kx] = sum_{n,y,x} dy[n,co,y,x] * x[n,ci,y+ky-1,x+kx-1],  x [n,cin,h,w], dy [n,cout,h,w],
- * both NCHW contiguous, 16-byte aligned.  The kernel writes one partial dW per CTA:
- * partials [n_blocks][cout*cin*9]; the caller adds the slots up (fixed order => deterministic).
+ * both NCHW contiguous, 16-byte aligned.  The kernel writes one partial result per CTA:
+ * partials [n_blocks][cout*cin*9 + cout] -- dW, then the bias gradient sum_{n,y,x} dy[n,co,y,x]; the caller
+ * adds the slots up (fixed order => deterministic).
  * mb_conv3x3_wgrad_blocks returns n_blocks for a shape on the current device, 0 when the shape is not
  * covered (the caller keeps its own path: square maps 2..16, (cin,cout) in {(27,16),(16,16),(16,32),
  * (32,32)} as instantiated in csrc/convgrad.cu), -1 on error. */

@@ -58,7 +58,9 @@ struct WgCfg {
     static constexpr int FRAME = (CIN + COUT) * PLANE;                  // floats per staged frame: X planes, dY planes
     static constexpr int PIECES = (CIN + COUT) * (HW / 4);              // 16-byte pieces per frame
     static constexpr int OUT = COUT * CIN * 9;
-    static constexpr int RED = G * P * kWgTM * 9;                       // floats of the end-of-kernel reduction
+    static constexpr int SLOT = OUT + COUT;                             // a CTA's partial: dW, then the bias gradient
+    static constexpr int BSL = kWgThreads / COUT;                       // threads per output channel for sum(dY)
+    static constexpr int RED = G * P * kWgTM * 9 + kWgThreads;          // floats of the end-of-kernel reduction
     static constexpr int STAGE_FLOATS = 2 * CH * FRAME;
     static constexpr int SMEM_FLOATS = STAGE_FLOATS > RED ? STAGE_FLOATS : RED;
     static constexpr int SMEM = SMEM_FLOATS * 4;
@@ -163,6 +165,8 @@ __global__ void __launch_bounds__(kWgThreads) conv3x3_wgrad_kernel(const float* 
     for (int m = 0; m < kWgTM; ++m)
 #pragma unroll
         for (int t = 0; t < 9; ++t) acc[m][t] = 0.0f;
+    const int b_co = tid % C::COUT, b_sl = tid / C::COUT;
+    float bsum = 0.0f;
 
     auto stage = [&](long long chunk, int buf) {
         float* base = wg_smem + buf * (C::CH * C::FRAME);
@@ -200,6 +204,16 @@ __global__ void __launch_bounds__(kWgThreads) conv3x3_wgrad_kernel(const float* 
             const float* fr = base + (g * C::FG + j) * C::FRAME;
             frame_fma<C>(acc, fr + ci_eff * C::PLANE, fr + (C::CIN + cog * kWgTM) * C::PLANE);
         }
+        // bias gradient = sum of dY over frames and pixels: thread (b_co, b_sl) adds its share of the staged dY
+        // planes of channel b_co (a handful of float4 per chunk next to thousands of FMAs)
+#pragma unroll 1
+        for (int fs = 0; fs < C::CH; ++fs) {
+            const float* pl = base + fs * C::FRAME + (C::CIN + b_co) * C::PLANE;
+            for (int q4 = b_sl; q4 < C::HW / 4; q4 += C::BSL) {
+                const float4 v = *reinterpret_cast<const float4*>(pl + 4 * q4);
+                bsum += (v.x + v.y) + (v.z + v.w);
+            }
+        }
         __syncthreads();
         buf ^= 1;
     }
@@ -210,8 +224,16 @@ __global__ void __launch_bounds__(kWgThreads) conv3x3_wgrad_kernel(const float* 
     for (int m = 0; m < kWgTM; ++m)
 #pragma unroll
         for (int t = 0; t < 9; ++t) red[tid * (kWgTM * 9) + m * 9 + t] = acc[m][t];
+    float* bred = red + kWgThreads * (kWgTM * 9);
+    bred[tid] = bsum;
     __syncthreads();
-    float* out = partials + (long long)blockIdx.x * C::OUT;
+    float* out = partials + (long long)blockIdx.x * C::SLOT;
+    if (tid < C::COUT) {
+        float s = 0.0f;
+#pragma unroll
+        for (int k = 0; k < C::BSL; ++k) s += bred[k * C::COUT + tid];
+        out[C::OUT + tid] = s;
+    }
     for (int e = tid; e < C::OUT; e += kWgThreads) {
         const int co = e / (C::CIN * 9), rem = e % (C::CIN * 9);
         const int ci2 = rem / 9, tap = rem % 9;

@@ -113,9 +113,9 @@ class _Conv3x3(torch.autograd.Function):
                 gx = ops.conv3x3_fwd(g, weight.flip(2, 3).reshape(cout, cin, 9).contiguous(), None)
             if gx is None:
                 gx = F.conv2d(g, weight.flip(2, 3).transpose(0, 1).contiguous(), None, padding=1)
-        gw = ops.conv3x3_wgrad(x, g) if FAST_CONV_WGRAD else None      # csrc/convgrad.cu; None: shape not covered
-        if gw is not None:
-            return gx, gw, g.sum(dim=(0, 2, 3))
+        both = ops.conv3x3_wgrad(x, g) if FAST_CONV_WGRAD else None    # csrc/convgrad.cu; None: shape not covered
+        if both is not None:
+            return gx, both[0], both[1]
         _, gw, gb = torch.ops.aten.convolution_backward(
             g, x, weight, [weight.shape[0]], [1, 1], [1, 1], [1, 1], False, [0, 0], 1, [False, True, True])
         return gx, gw, gb

@@ -267,8 +267,8 @@ def active_cells(action_mask: torch.Tensor, cells: int) -> torch.Tensor:
     return out.view(torch.bool)
 
 
-def conv3x3_wgrad(x: torch.Tensor, dy: torch.Tensor) -> Optional[torch.Tensor]:
-    """Weight gradient ``[cout, cin, 3, 3]`` of a 3x3 / stride 1 / pad 1 convolution from its input
+def conv3x3_wgrad(x: torch.Tensor, dy: torch.Tensor):
+    """``(dW [cout, cin, 3, 3], dbias [cout])`` of a 3x3 / stride 1 / pad 1 convolution from its input
     ``x [n,cin,h,w]`` and output gradient ``dy [n,cout,h,w]`` (fp32, NCHW contiguous), or ``None``
     when the shape is not one ``csrc/convgrad.cu`` instantiates (the caller then uses cuDNN)."""
     dev = _need_cuda(x=x, dy=dy)
@@ -287,10 +287,11 @@ def conv3x3_wgrad(x: torch.Tensor, dy: torch.Tensor) -> Optional[torch.Tensor]:
         x, dy = x.contiguous(), dy.contiguous()
         if (x.data_ptr() | dy.data_ptr()) & 15:
             return None
-        partials = torch.empty((blocks, cout * cin * 9), dtype=torch.float32, device=dev)
+        partials = torch.empty((blocks, cout * cin * 9 + cout), dtype=torch.float32, device=dev)
         with _Launch(f"conv3x3_wgrad_{cin}x{cout}x{h}", note={"n": n, "cin": cin, "cout": cout, "h": h}):
             _check(lib.mb_conv3x3_wgrad(_ptr(x), _ptr(dy), _ptr(partials), blocks, n, cin, cout, h, w, _stream()))
-    return partials.sum(dim=0).view(cout, cin, 3, 3)
+    total = partials.sum(dim=0)
+    return total[: cout * cin * 9].view(cout, cin, 3, 3), total[cout * cin * 9:]
 
 
 def conv3x3_fwd(x: torch.Tensor, wk: torch.Tensor, bias: Optional[torch.Tensor]) -> Optional[torch.Tensor]:

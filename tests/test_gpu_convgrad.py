@@ -32,13 +32,15 @@ def test_wgrad_matches_autograd(cin, cout, h, n):
     x = torch.randn(n, cin, h, h, device="cuda", generator=g)
     x = torch.where(torch.rand(x.shape, device="cuda", generator=g) < 0.5, x, torch.zeros_like(x))   # relu-like
     dy = torch.randn(n, cout, h, h, device="cuda", generator=g)
-    got = ops.conv3x3_wgrad(x, dy)
-    assert got is not None and got.shape == (cout, cin, 3, 3)
+    got, gb = ops.conv3x3_wgrad(x, dy)
+    assert got.shape == (cout, cin, 3, 3) and gb.shape == (cout,)
     ref64 = _ref_wgrad(x, dy, torch.float64)
     ok, worst = close_rms(got.double(), ref64, 2e-5)
     assert ok, worst
-    again = ops.conv3x3_wgrad(x, dy)
-    assert torch.equal(got, again), "the kernel and its fixed-order partial sum are deterministic"
+    ok, worst = close_rms(gb.double(), dy.double().sum(dim=(0, 2, 3)), 2e-5)
+    assert ok, ("bias gradient", worst)
+    again, gb2 = ops.conv3x3_wgrad(x, dy)
+    assert torch.equal(got, again) and torch.equal(gb, gb2), "the kernel and its fixed-order partial sum are deterministic"
 
 
 def test_wgrad_one_hot_taps():
@@ -50,7 +52,7 @@ def test_wgrad_one_hot_taps():
         dy = torch.zeros(5, cout, h, h, device="cuda")
         x[3, 5, yi, xi] = 1.0
         dy[3, 9, yo, xo] = 2.0
-        got = ops.conv3x3_wgrad(x, dy)
+        got, _ = ops.conv3x3_wgrad(x, dy)
         want = torch.zeros(cout, cin, 3, 3, device="cuda")
         ky, kx = yi - yo + 1, xi - xo + 1
         if 0 <= ky < 3 and 0 <= kx < 3:
@@ -76,7 +78,7 @@ def test_wgrad_at_learner_size_no_worse_than_cudnn():
         x = torch.relu(torch.randn(n, cin, h, h, device="cuda", generator=g))
         dy = torch.randn(n, cout, h, h, device="cuda", generator=g) * 1e-3
         ref64 = _ref_wgrad(x, dy, torch.float64)
-        got = ops.conv3x3_wgrad(x, dy)
+        got, _ = ops.conv3x3_wgrad(x, dy)
         cud = _ref_wgrad(x, dy, torch.float32)
         scale = ref64.pow(2).mean().sqrt()
         err_mine = float((got.double() - ref64).abs().max() / scale)
