@@ -331,9 +331,9 @@ int conv3x3_wgrad(const float* x, const float* dy, float* partials, int n_blocks
 // weights (broadcasts), so shared-memory traffic is ~15 wavefronts per 288 FMA issue slots.  Frames are
 // staged by cp.async, double buffered, exactly as they lie in global memory; the weights stay resident.
 // ---------------------------------------------------------------------------------------------
-template <int CIN_, int COUT_, int H_, int FG_>
+template <int CIN_, int COUT_, int H_, int FG_, int FPT_>
 struct FwCfg {
-    static constexpr int CIN = CIN_, COUT = COUT_, H = H_, W = H_, FG = FG_;
+    static constexpr int CIN = CIN_, COUT = COUT_, H = H_, W = H_, FG = FG_, FPT = FPT_;
     static constexpr int HW = H * W;
     static constexpr int XW = W < 8 ? W : 8;                // pixels of a row per thread
     static constexpr int SEG = W / XW;
@@ -342,7 +342,7 @@ struct FwCfg {
     static constexpr int COG = COUT / kWgTM;
     static constexpr int TPF = COG * ROWS * SEG;            // threads per frame
     static constexpr int FPP = kWgThreads / TPF;            // frames per pass
-    static constexpr int CH = FPP * FG;                     // frames per chunk
+    static constexpr int CH = FPP * FG * FPT;               // frames per chunk; a thread takes FPT of them at a time
     // staged planes carry one zero row above and below (not for 2x2, where the row index is static), so every
     // lane of a warp runs the same three-row code whatever its row
     static constexpr int HALO = (H > 2) ? 1 : 0;
@@ -351,7 +351,14 @@ struct FwCfg {
     static constexpr int SFRAME = CIN * PLANE;              // floats per staged frame
     static constexpr int WK = CIN * COUT * 9;
     static constexpr int SMEM = (2 * CH * SFRAME + WK + COUT) * 4;
+    // lanes of a quarter warp (the unit a 128-bit shared load is served in) cover YL consecutive rows -- 128 B,
+    // every bank once -- times CL channel groups (which read the same row addresses: broadcasts)
+    static constexpr int YL0 = (32 / W) < 1 ? 1 : (32 / W);
+    static constexpr int YL = ROWS < YL0 ? ROWS : YL0;
+    static constexpr int CL = 8 / YL;
+    static constexpr int YH = ROWS / YL;
     static_assert(kWgThreads % TPF == 0 && FPP >= 1, "thread layout");
+    static_assert(COG % CL == 0 && ROWS % YL == 0, "quarter-warp layout");
     static_assert(COUT % kWgTM == 0 && HW % 4 == 0 && (WK + COUT) % 4 == 0 && (W * HALO) % 4 == 0, "shape / alignment");
 };
 
@@ -376,10 +383,12 @@ __device__ __forceinline__ void fwd_fma(float (&acc)[kWgTM][XW], const float (&w
     }
 }
 
-// one output row segment over all input channels; `rowp` points at the row's first float in the staged
-// plane of channel 0 (the rows above / below are at -W / +W: halo rows make that valid for every row)
-template <class C, int X0, bool UP, bool DN>
-__device__ __forceinline__ void fwd_row(float (&acc)[kWgTM][C::XW], const float* rowp, const float* wcog) {
+// FPT frames x RPT rows of one thread over all input channels: the 36 weights of a channel are read once
+// and used for every frame and row the thread holds.  `rowp[t]` points at the thread's (first) row in the
+// staged plane of channel 0 of frame t.
+template <class C, int X0>
+__device__ __forceinline__ void fwd_rows(float (&acc)[C::FPT][C::RPT][kWgTM][C::XW], const float* const (&rowp)[C::FPT],
+                                         const float* wcog) {
     constexpr int W = C::W;
 #pragma unroll 2
     for (int ci = 0; ci < C::CIN; ++ci) {
@@ -393,12 +402,23 @@ __device__ __forceinline__ void fwd_row(float (&acc)[kWgTM][C::XW], const float*
             (&wt[0][0])[4 * q + 2] = v.z;
             (&wt[0][0])[4 * q + 3] = v.w;
         }
-        const float* pr = rowp + ci * C::PLANE;
-        float up[W], mid[W], dn[W];
-        load_row<W>(mid, pr);
-        if (UP) load_row<W>(up, pr - W);
-        if (DN) load_row<W>(dn, pr + W);
-        fwd_fma<W, C::XW, X0, UP, DN>(acc, wt, UP ? up : mid, mid, DN ? dn : mid);
+#pragma unroll
+        for (int t = 0; t < C::FPT; ++t) {
+            const float* pr = rowp[t] + ci * C::PLANE;
+            if constexpr (C::H == 2) {                     // the whole 2x2 plane: row 0 then row 1
+                float r0[W], r1[W];
+                load_row<W>(r0, pr);
+                load_row<W>(r1, pr + W);
+                fwd_fma<W, C::XW, X0, false, true>(acc[t][0], wt, r0, r0, r1);
+                fwd_fma<W, C::XW, X0, true, false>(acc[t][1], wt, r0, r1, r1);
+            } else {                                       // halo rows make -W / +W valid for every row
+                float up[W], mid[W], dn[W];
+                load_row<W>(mid, pr);
+                load_row<W>(up, pr - W);
+                load_row<W>(dn, pr + W);
+                fwd_fma<W, C::XW, X0, true, true>(acc[t][0], wt, up, mid, dn);
+            }
+        }
     }
 }
 
@@ -416,13 +436,16 @@ __global__ void __launch_bounds__(kWgThreads) conv3x3_fwd_kernel(const float* __
     for (int i = tid; i < 2 * C::CH * C::SFRAME; i += kWgThreads) xsm[i] = 0.0f;      // halo rows stay zero for good
     __syncthreads();                                   // before any cp.async lands on the zeroed interior
 
-    // thread -> (frame slot, row segment, channel group, row): lanes of a warp vary the row, then the channel
-    // group; the segment is uniform per warp
+    // thread -> (frame slot, row segment, channel group, row); the segment is uniform per warp and the low lane
+    // bits follow the quarter-warp layout of FwCfg (YL rows x CL channel groups)
     const int slot = tid / C::TPF;
     const int r = tid % C::TPF;
     const int seg = r / (C::COG * C::ROWS);
-    const int cog = (r / C::ROWS) % C::COG;
-    const int yy = r % C::ROWS;
+    const int r2 = r % (C::COG * C::ROWS);
+    const int yl = r2 % C::YL, cl = (r2 / C::YL) % C::CL;
+    const int yh = (r2 / (C::YL * C::CL)) % C::YH, chh = r2 / (C::YL * C::CL * C::YH);
+    const int yy = yl + C::YL * yh;
+    const int cog = cl + C::CL * chh;
     const float* wcog = wsm + cog * (kWgTM * 9);
 
     const long long n_chunks = (n_frames + C::CH - 1) / C::CH;
@@ -456,39 +479,44 @@ __global__ void __launch_bounds__(kWgThreads) conv3x3_fwd_kernel(const float* __
         const float* base = xsm + buf * (C::CH * C::SFRAME);
 #pragma unroll 1
         for (int j = 0; j < C::FG; ++j) {
-            const int fs = j * C::FPP + slot;
-            const long long f = chunk * C::CH + fs;
-            const float* xin = base + fs * C::SFRAME;
+            float acc[C::FPT][C::RPT][kWgTM][C::XW];
+            const float* rowp[C::FPT];
 #pragma unroll
-            for (int rr = 0; rr < C::RPT; ++rr) {
-                const int y = yy * C::RPT + rr;
-                float acc[kWgTM][C::XW];
+            for (int t = 0; t < C::FPT; ++t) {
+                const int fs = (j * C::FPT + t) * C::FPP + slot;
+                rowp[t] = base + fs * C::SFRAME + (yy * C::RPT + C::HALO) * C::W;
 #pragma unroll
-                for (int m = 0; m < kWgTM; ++m)
+                for (int rr = 0; rr < C::RPT; ++rr)
 #pragma unroll
-                    for (int x = 0; x < C::XW; ++x) acc[m][x] = bsm[cog * kWgTM + m];
-                const float* rowp = xin + (y + C::HALO) * C::W;
-                if constexpr (C::H == 2) {             // rr is the row: static
-                    if (rr == 0) fwd_row<C, 0, false, true>(acc, rowp, wcog);
-                    else fwd_row<C, 0, true, false>(acc, rowp, wcog);
-                } else if (C::SEG == 1 || seg == 0) {  // uniform per warp
-                    fwd_row<C, 0, true, true>(acc, rowp, wcog);
-                } else {
-                    fwd_row<C, (C::SEG > 1 ? 8 : 0), true, true>(acc, rowp, wcog);
-                }
+                    for (int m = 0; m < kWgTM; ++m)
+#pragma unroll
+                        for (int x = 0; x < C::XW; ++x) acc[t][rr][m][x] = bsm[cog * kWgTM + m];
+            }
+            if (C::SEG == 1 || seg == 0) {             // uniform per warp
+                fwd_rows<C, 0>(acc, rowp, wcog);
+            } else {
+                fwd_rows<C, (C::SEG > 1 ? 8 : 0)>(acc, rowp, wcog);
+            }
+#pragma unroll
+            for (int t = 0; t < C::FPT; ++t) {
+                const long long f = chunk * C::CH + (j * C::FPT + t) * C::FPP + slot;
                 if (f < n_frames) {
 #pragma unroll
-                    for (int m = 0; m < kWgTM; ++m) {
-                        float* o = out + ((f * C::COUT + cog * kWgTM + m) * C::H + y) * C::W + seg * C::XW;
-                        if constexpr (C::XW == 2) {
-                            *reinterpret_cast<float2*>(o) = make_float2(acc[m][0], acc[m][1]);
-                        } else {
+                    for (int rr = 0; rr < C::RPT; ++rr)
 #pragma unroll
-                            for (int q = 0; q < C::XW / 4; ++q)
-                                *reinterpret_cast<float4*>(o + 4 * q) =
-                                    make_float4(acc[m][4 * q], acc[m][4 * q + 1], acc[m][4 * q + 2], acc[m][4 * q + 3]);
+                        for (int m = 0; m < kWgTM; ++m) {
+                            float* o = out + ((f * C::COUT + cog * kWgTM + m) * C::H + yy * C::RPT + rr) * C::W +
+                                       seg * C::XW;
+                            if constexpr (C::XW == 2) {
+                                *reinterpret_cast<float2*>(o) = make_float2(acc[t][rr][m][0], acc[t][rr][m][1]);
+                            } else {
+#pragma unroll
+                                for (int q = 0; q < C::XW / 4; ++q)
+                                    *reinterpret_cast<float4*>(o + 4 * q) =
+                                        make_float4(acc[t][rr][m][4 * q], acc[t][rr][m][4 * q + 1],
+                                                    acc[t][rr][m][4 * q + 2], acc[t][rr][m][4 * q + 3]);
+                            }
                         }
-                    }
                 }
             }
         }
@@ -517,15 +545,16 @@ int fw_launch(const float* in, const float* wk, const float* bias, float* out, l
     return MB_OK;
 }
 
-// (cin, cout, h, frames per thread and chunk): the encoder's forward shapes and their data-gradient mirrors
+// (cin, cout, h, passes per chunk, frames per thread and pass): the encoder's forward shapes and their
+// data-gradient mirrors
 #define MB_FW_SHAPES(X) \
-    X(27, 16, 16, 1) X(27, 16, 8, 1) X(16, 16, 16, 1) X(16, 16, 8, 1) X(16, 16, 4, 1) \
-    X(16, 32, 16, 1) X(16, 32, 8, 1) X(16, 32, 4, 1) X(32, 16, 16, 1) X(32, 16, 8, 1) X(32, 16, 4, 1) \
-    X(32, 32, 8, 1) X(32, 32, 4, 1) X(32, 32, 2, 2)
+    X(27, 16, 16, 1, 1) X(27, 16, 8, 1, 1) X(16, 16, 16, 1, 1) X(16, 16, 8, 1, 1) X(16, 16, 4, 1, 1) \
+    X(16, 32, 16, 1, 1) X(16, 32, 8, 1, 1) X(16, 32, 4, 1, 1) X(32, 16, 16, 1, 1) X(32, 16, 8, 1, 1) X(32, 16, 4, 1, 1) \
+    X(32, 32, 8, 1, 1) X(32, 32, 4, 1, 1) X(32, 32, 2, 1, 2)
 
 int conv3x3_fwd_supported(int cin, int cout, int h, int w) {
     if (h != w) return 0;
-#define X(CI, CO, HH, FG) \
+#define X(CI, CO, HH, FG, FPT) \
     if (cin == CI && cout == CO && h == HH) return 1;
     MB_FW_SHAPES(X)
 #undef X
@@ -535,8 +564,8 @@ int conv3x3_fwd_supported(int cin, int cout, int h, int w) {
 int conv3x3_fwd(const float* in, const float* wk, const float* bias, float* out, long long n_frames, int cin, int cout,
                 int h, int w, cudaStream_t st) {
     if (h == w) {
-#define X(CI, CO, HH, FG) \
-    if (cin == CI && cout == CO && h == HH) return fw_launch<FwCfg<CI, CO, HH, FG>>(in, wk, bias, out, n_frames, st);
+#define X(CI, CO, HH, FG, FPT) \
+    if (cin == CI && cout == CO && h == HH) return fw_launch<FwCfg<CI, CO, HH, FG, FPT>>(in, wk, bias, out, n_frames, st);
         MB_FW_SHAPES(X)
 #undef X
     }
