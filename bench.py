@@ -84,16 +84,25 @@ def hbm_peak():
 class ClockSampler:
     """nvidia-smi clocks / throttle reasons sampled DURING the timed region."""
     Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
-         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap,timestamp")
 
     def __init__(self, index: int):
         self.index, self.proc = index, None
+        self.t_begin = self.t_end = None
+
+    # nvidia-smi needs ~0.1 s to come up and the timed region may be shorter than that, so the sampler is started
+    # before the warm-up steps (the same load) and the samples are filtered by time stamp afterwards
+    def mark_begin(self):
+        self.t_begin = time.time()
+
+    def mark_end(self):
+        self.t_end = time.time()
 
     def start(self):
         try:
             self.proc = subprocess.Popen(
                 ["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
-                 "-lms", "100"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+                 "-lms", "20"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
         except Exception:
             self.proc = None
 
@@ -107,21 +116,33 @@ class ClockSampler:
         except Exception:
             self.proc.kill()
             out = ""
-        sm, mx, reasons = [], [], set()
+        import datetime
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        rows = []
         for line in out.strip().splitlines():
             f = [x.strip() for x in line.split(",")]
             if len(f) < 6:
                 continue
             try:
-                sm.append(float(f[0])); mx.append(float(f[1]))
+                rec = (float(f[0]), float(f[1]), [n for n, v in zip(names, f[2:6]) if v.lower().startswith("active")])
             except ValueError:
                 continue
-            for name, val in zip(names, f[2:6]):
-                if val.lower().startswith("active"):
-                    reasons.add(name)
+            ts = None
+            if len(f) > 6:
+                try:
+                    ts = datetime.datetime.strptime(f[6], "%Y/%m/%d %H:%M:%S.%f").timestamp()
+                except ValueError:
+                    ts = None
+            rows.append((ts, rec))
+        inside = [rec for ts, rec in rows if ts is not None and self.t_begin is not None and self.t_end is not None
+                  and self.t_begin - 0.02 <= ts <= self.t_end + 0.02]
+        window = "timed region"
+        if not inside:            # region shorter than the sampling period: the warm-up steps ran the same load
+            inside, window = [rec for _, rec in rows], "warm-up + timed region"
+        sm = [r[0] for r in inside]; mx = [r[1] for r in inside]
+        reasons = sorted({n for r in inside for n in r[2]})
         return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(mx) if mx else None,
-                "samples": len(sm), "reasons": sorted(reasons)}
+                "samples": len(sm), "window": window, "reasons": reasons}
 
 
 # ------------------------------------------------------------------------------------------
@@ -262,12 +283,14 @@ def run_ours(args):
         torch.cuda.synchronize()
 
     def timed(fn, steps, warmup, sample_clocks=False, kernel_timing=False):
-        for _ in range(warmup):
-            fn()
-        barrier()
         sampler = ClockSampler(local) if sample_clocks else None
         if sampler:
             sampler.start()
+        for _ in range(warmup):
+            fn()
+        barrier()
+        if sampler:
+            sampler.mark_begin()
         launches0 = ops.total_launches()
         if kernel_timing:
             ops.start_kernel_timing()
@@ -277,6 +300,8 @@ def run_ours(args):
             fn()
         t1.record()
         barrier()
+        if sampler:
+            sampler.mark_end()
         ms = t0.elapsed_time(t1)
         kt = ops.stop_kernel_timing() if kernel_timing else {}
         clocks = sampler.stop() if sampler else None
