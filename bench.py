@@ -213,7 +213,11 @@ def workload_config(args, rows_override=None):
             "map": f"{h}x{w}", "T": T, "rows_per_gpu": rows, "frames_per_step_per_gpu": rows * T,
             "mask_preset": args.preset, "l2_policy": "inputs larger than L2 (logits alone are "
             f"{rows * (T + 1) * h * w * 78 * 4 / 1e6:.0f} MB per GPU vs 126 MB L2)",
-            "parallelism": f"dp{args.gpus}"}
+            "parallelism": f"dp{args.gpus}",
+            "arithmetic": "fp32 throughout (TF32 off in cuDNN / cuBLAS); the actor Linear forward runs on tcgen05 as three "
+                          "TF32 products of hi/lo-split operands with fp32 accumulation (error 5e-7 of max|logit|, "
+                          "cuBLAS fp32: 5e-7); its backward runs over the cells with a valid action only (the others "
+                          "have exactly zero gradient)"}
 
 
 def emit(line, args):
