@@ -216,6 +216,8 @@ MB_API int mb_maxpool3s2_bwd(const float* dy, const int64_t* idx, float* dx, int
  *   "vtrace_force_generic" (0/1), "vtrace_l2_promo" (0/64/128/256 bytes),
  *   "vtrace_variant" (stages x steps per tile: -1 = by grid size, 0 = 2x32, 1 = 3x32, 2 = 4x32,
  *   3 = 3x16, 4 = 4x16, 5 = 5x16, 6 = 6x16, 7 = 8x16).
+ *   "gemm_group_m" (mb_linear_tf32x3 tile order: 0 = row-major, g > 0 = bands of g tile rows walked column by
+ *   column), "gemm_stream_store" (0/1: store the output with the streaming cache hint).
  * Returns MB_ERR_INVALID for an unknown key. */
 MB_API int mb_set_tuning(const char* key, int32_t value);
 

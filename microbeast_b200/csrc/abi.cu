@@ -43,6 +43,7 @@ int head_eval_cells_bwd(const float*, const uint8_t*, const int64_t*, const floa
                         cudaStream_t);
 void head_set_tuning(int ctas_per_sm, int grid_override, int variant);
 void vtrace_set_tuning(int force_generic, int variant, int l2_promo);
+void gemm_set_tuning(int group_m, int stream_store);
 size_t vtrace_workspace_bytes(long long rows);
 
 struct VtParams;
@@ -93,6 +94,7 @@ size_t mb_vtrace_workspace_bytes(int64_t rows) { return mb::vtrace_workspace_byt
 
 int mb_set_tuning(const char* key, int32_t value) {
     static int head_ctas = 0, head_grid = 0, head_variant = -1, vt_generic = 0, vt_variant = -1, vt_promo = 256;
+    static int gemm_group_m = 0, gemm_stream_store = 0;
     if (!key) {
         mb::set_error("mb_set_tuning: null key");
         return MB_ERR_INVALID;
@@ -103,12 +105,15 @@ int mb_set_tuning(const char* key, int32_t value) {
     else if (!strcmp(key, "vtrace_force_generic")) vt_generic = value;
     else if (!strcmp(key, "vtrace_variant")) vt_variant = value;
     else if (!strcmp(key, "vtrace_l2_promo")) vt_promo = value;
+    else if (!strcmp(key, "gemm_group_m")) gemm_group_m = value;
+    else if (!strcmp(key, "gemm_stream_store")) gemm_stream_store = value;
     else {
         mb::set_error("mb_set_tuning: unknown key '%s'", key);
         return MB_ERR_INVALID;
     }
     mb::head_set_tuning(head_ctas, head_grid, head_variant);
     mb::vtrace_set_tuning(vt_generic, vt_variant, vt_promo);
+    mb::gemm_set_tuning(gemm_group_m, gemm_stream_store);
     return MB_OK;
 }
 

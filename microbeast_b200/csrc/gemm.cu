@@ -129,7 +129,7 @@ __global__ void __launch_bounds__(256) split_tf32_kernel(const float* __restrict
 __global__ void __launch_bounds__(kGemmThreads, 1) linear_tf32x3_kernel(const __grid_constant__ GemmMaps maps,
                                                                         const float* __restrict__ bias,
                                                                         float* __restrict__ C, int M, int N, int K,
-                                                                        int* status) {
+                                                                        int* status, int group_m, int stream_store) {
     extern __shared__ uint8_t gemm_smem_raw[];
     __shared__ __align__(8) uint64_t full_bar[kGemmStages];      // TMA boxes of a stage have landed
     __shared__ __align__(8) uint64_t empty_bar[kGemmStages];     // the MMAs reading a stage have completed
@@ -162,6 +162,19 @@ __global__ void __launch_bounds__(kGemmThreads, 1) linear_tf32x3_kernel(const __
 
     const int tiles_m = (M + kGemmBM - 1) / kGemmBM, tiles_n = (N + kGemmBN - 1) / kGemmBN;
     const int n_tiles = tiles_m * tiles_n;
+    // tile order: row-major (group_m = 0), or bands of group_m tile rows walked column by column so that the
+    // CTAs running at the same time share a few A tiles and a few B tiles
+    auto tile_mn = [&](int tile, int& tm, int& tn) {
+        if (group_m <= 0) {
+            tm = tile / tiles_n;
+            tn = tile % tiles_n;
+        } else {
+            const int band = tile / (group_m * tiles_n), first = band * group_m;
+            const int rows = min(group_m, tiles_m - first), in_band = tile - band * group_m * tiles_n;
+            tm = first + in_band % rows;
+            tn = in_band / rows;
+        }
+    };
     const int kblocks = K / kGemmBK;
 
     if (warp == 0) {
@@ -169,7 +182,9 @@ __global__ void __launch_bounds__(kGemmThreads, 1) linear_tf32x3_kernel(const __
         if (lane == 0) {
             uint32_t it = 0;
             for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
-                const int m0 = (tile / tiles_n) * kGemmBM, n0 = (tile % tiles_n) * kGemmBN;
+                int tm, tn;
+                tile_mn(tile, tm, tn);
+                const int m0 = tm * kGemmBM, n0 = tn * kGemmBN;
                 for (int kb = 0; kb < kblocks; ++kb, ++it) {
                     const int s = it % kGemmStages;
                     const uint32_t ph = (it / kGemmStages) & 1;
@@ -225,7 +240,9 @@ __global__ void __launch_bounds__(kGemmThreads, 1) linear_tf32x3_kernel(const __
         const int half = (warp - 2) >> 2;
         uint32_t tcount = 0;
         for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, ++tcount) {
-            const int m0 = (tile / tiles_n) * kGemmBM, n0 = (tile % tiles_n) * kGemmBN + half * 128;
+            int tm, tn;
+            tile_mn(tile, tm, tn);
+            const int m0 = tm * kGemmBM, n0 = tn * kGemmBN + half * 128;
             mbar_wait(&tfull_bar[0], tcount & 1, status);
             tc_fence_after();
             const uint32_t lane_base = uint32_t(q * 32) << 16;
@@ -250,8 +267,9 @@ __global__ void __launch_bounds__(kGemmThreads, 1) linear_tf32x3_kernel(const __
                     if (col < N) {                                // N % 4 == 0 (checked by the host)
                         const float4 bb = bias ? __ldg(reinterpret_cast<const float4*>(bias + col))
                                                : make_float4(0.f, 0.f, 0.f, 0.f);
-                        *reinterpret_cast<float4*>(crow + col) =
-                            make_float4(acc[j] + bb.x, acc[j + 1] + bb.y, acc[j + 2] + bb.z, acc[j + 3] + bb.w);
+                        const float4 o = make_float4(acc[j] + bb.x, acc[j + 1] + bb.y, acc[j + 2] + bb.z, acc[j + 3] + bb.w);
+                        if (stream_store) __stcs(reinterpret_cast<float4*>(crow + col), o);   // written once, read later:
+                        else *reinterpret_cast<float4*>(crow + col) = o;                     // keep the operands in L2 instead
                     }
                 }
             }
@@ -294,6 +312,12 @@ bool gemm_map(EncodeTiledFn enc, CUtensorMap* m, const float* base, long long ro
 
 }  // namespace
 
+static int g_gemm_group_m = 0, g_gemm_stream_store = 0;
+void gemm_set_tuning(int group_m, int stream_store) {
+    g_gemm_group_m = group_m;
+    g_gemm_stream_store = stream_store;
+}
+
 int split_tf32(const float* x, float* hi, float* lo, long long n, cudaStream_t st) {
     if (n == 0) return MB_OK;
     int dev = 0;
@@ -328,7 +352,8 @@ int linear_tf32x3(const float* a_hi, const float* a_lo, const float* b_hi, const
     const long long tiles = ((M + kGemmBM - 1) / kGemmBM) * ((N + kGemmBN - 1) / kGemmBN);
     const int sms = sm_count(dev);
     const int grid = int(tiles < sms ? tiles : sms);
-    linear_tf32x3_kernel<<<grid, kGemmThreads, kGemmSmem, st>>>(maps, bias, c, int(M), int(N), K, status);
+    linear_tf32x3_kernel<<<grid, kGemmThreads, kGemmSmem, st>>>(maps, bias, c, int(M), int(N), K, status, g_gemm_group_m,
+                                                                g_gemm_stream_store);
     MB_CUDA(cudaGetLastError());
     return MB_OK;
 }

@@ -25,3 +25,14 @@ ref = x[:512].double() @ w.double().t() + b.double()
 got = ops.linear_tf32x3(x, w, b)[:512]
 print("max err / max|ref|:", float((got.double() - ref).abs().max() / ref.abs().max()),
       " cuBLAS:", float((torch.addmm(b, x, w.t())[:512].double() - ref).abs().max() / ref.abs().max()))
+
+import microbeast_b200
+for gm in (0, 4, 8, 16, 32):
+    for ss in (0, 1):
+        microbeast_b200.set_tuning("gemm_group_m", gm); microbeast_b200.set_tuning("gemm_stream_store", ss)
+        a_hi, a_lo = ops.split_tf32(x); b_hi, b_lo = ops.split_tf32(w)
+        ops.start_kernel_timing()
+        for _ in range(6): ops.linear_tf32x3(x, w, b)
+        kt = ops.stop_kernel_timing()["linear_tf32x3"]
+        ok = torch.equal(ops.linear_tf32x3(x, w, b)[:512], got)
+        print(f"group_m={gm:2d} stream_store={ss}: {sorted(kt)[len(kt)//2]:.3f} ms  same result: {ok}", flush=True)
