@@ -185,6 +185,18 @@ def cell_list(action_mask: torch.Tensor, cells: int, auto: bool):
     return fidx, cidx
 
 
+_PAD_ROWS = 1024
+
+
+def spread_padding(fidx: torch.Tensor, n: int) -> torch.Tensor:
+    """Row indices for gathering / scatter-adding ``[n + _PAD_ROWS, width]`` tensors through a cell list: the
+    padding entries (``fidx == n``) are spread over ``_PAD_ROWS`` dummy rows instead of all hitting row ``n`` --
+    an ``index_add`` of ~10 % padding rows into ONE row serialises its atomics."""
+    lmax = fidx.shape[1]
+    dummy = n + (torch.arange(lmax, device=fidx.device) % _PAD_ROWS)
+    return torch.where(fidx < n, fidx, dummy.unsqueeze(0).expand_as(fidx)).reshape(-1)
+
+
 def gather_cells(fidx, cidx, n, action_mask, action, cells):
     """Mask / action rows of a cell list; padding entries get an all-zero mask (a dead cell: log-prob 0,
     entropy 0, zero gradient -- quirk Q1) and any in-range action."""
@@ -250,12 +262,12 @@ class _ActorHead(torch.autograd.Function):
         logits_c = logits.view(n, cells, LOGITS_PER_CELL)[safe, cidx].reshape(-1, LOGITS_PER_CELL)
         dl = ops.head_eval_cells_bwd(logits_c, mask_c, act_c, g_lp[safe].reshape(-1), g_ent[safe].reshape(-1))
         dl = dl.view(cells, lmax, LOGITS_PER_CELL)
-        flat = fidx.reshape(-1)
-        hid = torch.cat([hidden, hidden.new_zeros(1, width)]).index_select(0, flat).view(cells, lmax, width)
+        flat = spread_padding(fidx, n)
+        hid = torch.cat([hidden, hidden.new_zeros(_PAD_ROWS, width)]).index_select(0, flat).view(cells, lmax, width)
         g_weight = torch.bmm(dl.transpose(1, 2), hid).reshape(cells * LOGITS_PER_CELL, width)
         g_bias = dl.sum(dim=1).reshape(-1)
         g_hid = torch.bmm(dl, weight.view(cells, LOGITS_PER_CELL, width))                   # [C, lmax, 256]
-        g_hidden = hidden.new_zeros((n + 1, width)).index_add_(0, flat, g_hid.reshape(-1, width))[:n]
+        g_hidden = hidden.new_zeros((n + _PAD_ROWS, width)).index_add_(0, flat, g_hid.reshape(-1, width))[:n]
         return g_hidden, g_weight, g_bias, None, None, None, None
 
 
@@ -358,7 +370,7 @@ class Agent(nn.Module):
         lmax = fidx.shape[1]
         _, mask_c, act_c = gather_cells(fidx, cidx, n, action_mask, action, cells)
         # index_select: its backward is an index_add (atomics), not the sort-based index_put of x[idx]
-        hid = torch.cat([hidden, hidden.new_zeros(1, hidden.shape[1])]).index_select(0, fidx.reshape(-1))
+        hid = torch.cat([hidden, hidden.new_zeros(_PAD_ROWS, hidden.shape[1])]).index_select(0, spread_padding(fidx, n))
         hid = hid.view(cells, lmax, -1)                    # [C, lmax, 256]
         w = self.actor.weight.view(cells, LOGITS_PER_CELL, -1)
         b = self.actor.bias.view(cells, 1, LOGITS_PER_CELL)
