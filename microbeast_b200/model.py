@@ -168,15 +168,20 @@ def cell_list(action_mask: torch.Tensor, cells: int, auto: bool):
     ``fidx`` the frame index, padded with ``n`` (one past the last frame) up to the longest group
     rounded to 64.  ``None`` with ``auto`` when the padded list would be at least half the dense grid.
     Costs two host synchronisations (``nonzero`` and the longest group's length)."""
-    n = action_mask.shape[0]
-    active = ops.active_cells(action_mask, cells)                       # [N, C]
+    return cell_list_from_active(ops.active_cells(action_mask, cells), auto)
+
+
+def cell_list_from_active(active: torch.Tensor, auto: bool):
+    """``cell_list`` from the ``[N, C]`` bool map of cells with a valid action (pure index bookkeeping; runs on
+    any device, which is how ``tests/test_host_logic.py`` covers it without a GPU)."""
+    n, cells = active.shape
     counts = active.sum(dim=0)                                         # active frames per cell
     pairs = active.t().nonzero()                                       # [P, 2] = (cell, frame), grouped by cell
     lmax = int(counts.max().item()) if pairs.shape[0] else 0
     lmax = max(-(-max(lmax, 1) // 64) * 64, 64)                        # groups of 64 cells for the kernel
     if auto and 2 * lmax > n:
         return None
-    dev = action_mask.device
+    dev = active.device
     starts = torch.cumsum(counts, 0) - counts
     pos = torch.arange(pairs.shape[0], device=dev) - starts[pairs[:, 0]]
     fidx = torch.full((cells, lmax), n, dtype=torch.int64, device=dev)

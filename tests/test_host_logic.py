@@ -76,3 +76,72 @@ def test_agent_matches_reference_architecture_and_loads_its_weights():
     for side, feat in ((10, 128), (16, 128), (32, 512)):
         a = model.Agent((side, side, 27), list(NVEC_CELL) * side * side, side * side)
         assert a.network[5].in_features == feat
+
+
+# ---- cell list of the sparse actor-head paths (model.cell_list_from_active / gather_cells / spread_padding) ----
+def _active_map(n, cells, p, seed):
+    g = torch.Generator().manual_seed(seed)
+    return torch.rand(n, cells, generator=g) < p
+
+
+@pytest.mark.parametrize("n,cells,p", [(300, 16, 0.06), (1, 4, 1.0), (500, 64, 0.02), (129, 8, 0.0), (200, 4, 0.3)])
+def test_cell_list_holds_every_active_pair_once(n, cells, p):
+    from microbeast_b200.model import cell_list_from_active
+    active = _active_map(n, cells, p, seed=n + cells)
+    fidx, cidx = cell_list_from_active(active, auto=False)
+    lmax = fidx.shape[1]
+    assert fidx.shape == (cells, lmax) and cidx.shape == (cells, lmax) and lmax % 64 == 0 and lmax >= 64
+    longest = int(active.sum(0).max())
+    assert lmax == max(-(-longest // 64) * 64, 64)                    # padded to the longest group, no further
+    assert torch.equal(cidx, torch.arange(cells).unsqueeze(1).expand(cells, lmax))
+    valid = fidx < n
+    assert torch.equal(fidx[~valid], torch.full_like(fidx[~valid], n))     # padding = one past the last frame
+    rebuilt = torch.zeros(n + 1, cells, dtype=torch.int64)
+    rebuilt.index_put_((fidx.reshape(-1), cidx.reshape(-1)), torch.ones(cells * lmax, dtype=torch.int64), accumulate=True)
+    assert torch.equal(rebuilt[:n], active.to(torch.int64))               # each active pair exactly once, nothing else
+    for c in range(cells):                                                 # frames ascending inside a cell, padding last
+        row = fidx[c]
+        assert torch.equal(row, row.sort().values)
+
+
+def test_cell_list_auto_falls_back_when_dense():
+    from microbeast_b200.model import cell_list_from_active
+    assert cell_list_from_active(_active_map(400, 8, 0.9, 1), auto=True) is None       # longest group > n/2
+    assert cell_list_from_active(_active_map(400, 8, 0.05, 2), auto=True) is not None
+    assert cell_list_from_active(_active_map(100, 8, 0.05, 3), auto=True) is None      # 64-entry minimum > n/2
+
+
+def test_gather_cells_and_list_products_equal_dense_products():
+    """The cell-list backward of model._ActorHead in plain torch on the CPU: with d logits zero outside the
+    active cells, dW, dbias and dhidden from the list (bmm over gathered rows, index_add over spread rows)
+    equal the dense products dlogits^T @ hidden, dlogits.sum(0), dlogits @ W."""
+    from microbeast_b200.model import _PAD_ROWS, cell_list_from_active, gather_cells, spread_padding
+    n, cells, width = 150, 8, 12
+    g = torch.Generator().manual_seed(5)
+    active = _active_map(n, cells, 0.2, seed=9)
+    mask = (torch.rand(n, cells, 78, generator=g) < 0.5) & active.unsqueeze(2)
+    mask[..., 0] |= active                                                  # an active cell has a valid entry
+    mask = mask.to(torch.uint8).view(n, cells * 78)
+    action = torch.randint(0, 4, (n, cells * 7), generator=g)
+    hidden = torch.randn(n, width, generator=g, dtype=torch.float64)
+    weight = torch.randn(cells * 78, width, generator=g, dtype=torch.float64)
+    dlogits = torch.randn(n, cells, 78, generator=g, dtype=torch.float64) * active.unsqueeze(2)
+    fidx, cidx = cell_list_from_active(active, auto=False)
+    lmax = fidx.shape[1]
+    safe, mask_c, act_c = gather_cells(fidx, cidx, n, mask, action, cells)
+    valid = (fidx < n).reshape(-1)
+    assert torch.equal(mask_c[~valid], torch.zeros_like(mask_c[~valid]))     # padding = fully masked cells
+    assert torch.equal(mask_c[valid], mask.view(n, cells, 78)[fidx.reshape(-1)[valid], cidx.reshape(-1)[valid]])
+    assert torch.equal(act_c[valid], action.view(n, cells, 7)[fidx.reshape(-1)[valid], cidx.reshape(-1)[valid]])
+    dl = dlogits[safe, cidx] * (fidx < n).unsqueeze(2)                      # what the cell-list kernel returns
+    flat = spread_padding(fidx, n)
+    assert int(flat.max()) < n + _PAD_ROWS and torch.equal(flat[valid], fidx.reshape(-1)[valid])
+    hid = torch.cat([hidden, hidden.new_zeros(_PAD_ROWS, width)]).index_select(0, flat).view(cells, lmax, width)
+    g_weight = torch.bmm(dl.transpose(1, 2), hid).reshape(cells * 78, width)
+    g_bias = dl.sum(dim=1).reshape(-1)
+    g_hid = torch.bmm(dl, weight.view(cells, 78, width))
+    g_hidden = hidden.new_zeros((n + _PAD_ROWS, width)).index_add_(0, flat, g_hid.reshape(-1, width))[:n]
+    dense = dlogits.view(n, cells * 78)
+    torch.testing.assert_close(g_weight, dense.t() @ hidden, rtol=1e-12, atol=1e-12)
+    torch.testing.assert_close(g_bias, dense.sum(0), rtol=1e-12, atol=1e-12)
+    torch.testing.assert_close(g_hidden, dense @ weight, rtol=1e-12, atol=1e-12)
