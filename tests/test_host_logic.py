@@ -145,3 +145,21 @@ def test_gather_cells_and_list_products_equal_dense_products():
     torch.testing.assert_close(g_weight, dense.t() @ hidden, rtol=1e-12, atol=1e-12)
     torch.testing.assert_close(g_bias, dense.sum(0), rtol=1e-12, atol=1e-12)
     torch.testing.assert_close(g_hidden, dense @ weight, rtol=1e-12, atol=1e-12)
+
+
+def test_linear_bias_in_k_equals_addmm():
+    """model._linear_bias_in_k (the cuBLAS fallback of the actor Linear: bias as an extra K column)."""
+    g = torch.Generator().manual_seed(11)
+    x = torch.randn(37, 24, generator=g, dtype=torch.float64)
+    w = torch.randn(19, 24, generator=g, dtype=torch.float64)
+    b = torch.randn(19, generator=g, dtype=torch.float64)
+    torch.testing.assert_close(model._linear_bias_in_k(x, w, b), torch.addmm(b, x, w.t()), rtol=1e-12, atol=1e-12)
+
+
+def test_graphed_learner_refuses_the_sparse_head():
+    """The cell-list forward sizes tensors from the data and synchronises: it cannot be captured."""
+    from microbeast_b200.graphed import GraphedLearner
+    agent = model.Agent((4, 4, 27), list(NVEC_CELL) * 16, 16)
+    agent.sparse_head = True
+    with pytest.raises(ValueError):
+        GraphedLearner(agent, torch.optim.SGD(agent.parameters(), lr=0.1), 2, 3, 1)
