@@ -191,6 +191,7 @@ def cell_list_from_active(active: torch.Tensor, auto: bool):
 
 
 _PAD_ROWS = 1024
+_SPARSE_BACKWARD_MIN_PAIRS = 1 << 20
 
 
 def spread_padding(fidx: torch.Tensor, n: int) -> torch.Tensor:
@@ -257,7 +258,10 @@ class _ActorHead(torch.autograd.Function):
         n, cells = hidden.shape[0], ctx.cells
         g_lp = torch.zeros(n, device=hidden.device) if g_lp is None else g_lp.contiguous()
         g_ent = torch.zeros(n, device=hidden.device) if g_ent is None else g_ent.contiguous()
-        cl = cell_list(action_mask, cells, auto=(ctx.mode == "auto")) if ctx.mode else None
+        # "auto": below ~1e6 (frame, cell) pairs the dense GEMMs cost less than the list's bookkeeping and its two
+        # host synchronisations (8x8 maps are launch-bound, profiles/r01_bench_c1_n1.json)
+        small = ctx.mode == "auto" and n * cells < _SPARSE_BACKWARD_MIN_PAIRS
+        cl = cell_list(action_mask, cells, auto=(ctx.mode == "auto")) if (ctx.mode and not small) else None
         if cl is None:
             dlogits = ops.head_eval_bwd(logits, action_mask, action, g_lp, g_ent)
             return dlogits @ weight, dlogits.t() @ hidden, dlogits.sum(dim=0), None, None, None, None
