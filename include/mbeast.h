@@ -186,13 +186,15 @@ MB_API int mb_conv3x3_wgrad(const float* x, const float* dy, float* partials, in
 
 /* Forward-type 3x3 / stride 1 / pad 1 convolution in fp32 (reference model.py:61-62,88: nn.Conv2d(.., 3, padding=1)):
  *   out[n,co,y,x] = bias[co] + sum_{ci,ky,kx} wk[ci][co][ky*3+kx] * in[n,ci,y+ky-1,x+kx-1]
- * in [n,cin,h,w], out [n,cout,h,w] NCHW contiguous, 16-byte aligned; wk [cin][cout][9] (the torch weight
- * [cout,cin,3,3] permuted); bias [cout] or NULL.  The data gradient of such a convolution is the same
- * operation with wk = weight.flip(2,3) viewed as [cout][cin][9] and no bias.  mb_conv3x3_fwd_supported
- * returns 1 for the shapes instantiated in csrc/convgrad.cu, else 0 (the caller keeps cuDNN). */
+ * in [n,cin,h,w], out [n,cout,h,w] NCHW contiguous, 16-byte aligned; bias [cout] or NULL.  The kernel weights
+ * come in one of three layouts: wmode 0 = wk [cin][cout][9] as written above; 1 = a torch Conv2d weight
+ * [cout][cin][3][3] (forward pass); 2 = the data gradient of a convolution whose torch weight is
+ * [cin][cout][3][3] (here cin / cout are those of THIS operation: the gradient's channels in, the input's
+ * channels out): the kernel flips the taps itself, pass no bias.  mb_conv3x3_fwd_supported returns 1 for the
+ * shapes instantiated in csrc/convgrad.cu, else 0 (the caller keeps cuDNN). */
 MB_API int mb_conv3x3_fwd_supported(int32_t cin, int32_t cout, int32_t h, int32_t w);
 MB_API int mb_conv3x3_fwd(const float* in, const float* wk, const float* bias, float* out, int64_t n_frames,
-                          int32_t cin, int32_t cout, int32_t h, int32_t w, void* stream);
+                          int32_t cin, int32_t cout, int32_t h, int32_t w, int32_t wmode, void* stream);
 
 /* Actor Linear forward (reference model.py:136,167: logits = actor(hidden)) on the tcgen05 tensor cores at
  * fp32 accuracy: c[m,n] = a[m,k] * b[n,k]^T + bias[n] with both operands given as a TF32 "hi" part and a TF32

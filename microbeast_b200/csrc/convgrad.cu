@@ -425,13 +425,18 @@ __device__ __forceinline__ void fwd_rows(float (&acc)[C::FPT][C::RPT][kWgTM][C::
 template <class C>
 __global__ void __launch_bounds__(kWgThreads) conv3x3_fwd_kernel(const float* __restrict__ in, const float* __restrict__ wk,
                                                                   const float* __restrict__ bias, float* __restrict__ out,
-                                                                  long long n_frames) {
+                                                                  long long n_frames, int wmode) {
     extern __shared__ __align__(16) float fw_smem[];
     float* wsm = fw_smem;                              // [CIN][COUT][9]
     float* bsm = wsm + C::WK;                          // [COUT]
     float* xsm = bsm + C::COUT;                        // 2 x [CH][CIN][H + halo][W]
     const int tid = threadIdx.x;
-    for (int i = tid; i < C::WK; i += kWgThreads) wsm[i] = wk[i];
+    // weights into [CIN][COUT][9]: wmode 0 = given so; 1 = a torch Conv2d weight [COUT][CIN][3][3] (forward);
+    // 2 = the torch weight of the convolution whose DATA GRADIENT this is, [CIN][COUT][3][3] with the taps flipped
+    for (int i = tid; i < C::WK; i += kWgThreads) {
+        const int k = i % 9, co = (i / 9) % C::COUT, ci = i / (9 * C::COUT);
+        wsm[i] = wmode == 0 ? wk[i] : wmode == 1 ? wk[(co * C::CIN + ci) * 9 + k] : wk[(ci * C::COUT + co) * 9 + (8 - k)];
+    }
     for (int i = tid; i < C::COUT; i += kWgThreads) bsm[i] = bias ? bias[i] : 0.0f;
     for (int i = tid; i < 2 * C::CH * C::SFRAME; i += kWgThreads) xsm[i] = 0.0f;      // halo rows stay zero for good
     __syncthreads();                                   // before any cp.async lands on the zeroed interior
@@ -526,7 +531,8 @@ __global__ void __launch_bounds__(kWgThreads) conv3x3_fwd_kernel(const float* __
 }
 
 template <class C>
-int fw_launch(const float* in, const float* wk, const float* bias, float* out, long long n_frames, cudaStream_t st) {
+int fw_launch(const float* in, const float* wk, const float* bias, float* out, long long n_frames, int wmode,
+              cudaStream_t st) {
     int dev = 0;
     MB_CUDA(cudaGetDevice(&dev));
     static int occ[64] = {};
@@ -540,7 +546,7 @@ int fw_launch(const float* in, const float* wk, const float* bias, float* out, l
     const long long chunks = (n_frames + C::CH - 1) / C::CH;
     const long long cap = (long long)sm_count(dev) * o;
     const int grid = int(chunks < cap ? (chunks > 0 ? chunks : 1) : cap);
-    conv3x3_fwd_kernel<C><<<grid, kWgThreads, C::SMEM, st>>>(in, wk, bias, out, n_frames);
+    conv3x3_fwd_kernel<C><<<grid, kWgThreads, C::SMEM, st>>>(in, wk, bias, out, n_frames, wmode);
     MB_CUDA(cudaGetLastError());
     return MB_OK;
 }
@@ -562,10 +568,10 @@ int conv3x3_fwd_supported(int cin, int cout, int h, int w) {
 }
 
 int conv3x3_fwd(const float* in, const float* wk, const float* bias, float* out, long long n_frames, int cin, int cout,
-                int h, int w, cudaStream_t st) {
+                int h, int w, int wmode, cudaStream_t st) {
     if (h == w) {
 #define X(CI, CO, HH, FG, FPT) \
-    if (cin == CI && cout == CO && h == HH) return fw_launch<FwCfg<CI, CO, HH, FG, FPT>>(in, wk, bias, out, n_frames, st);
+    if (cin == CI && cout == CO && h == HH) return fw_launch<FwCfg<CI, CO, HH, FG, FPT>>(in, wk, bias, out, n_frames, wmode, st);
         MB_FW_SHAPES(X)
 #undef X
     }
@@ -670,9 +676,9 @@ extern "C" int mb_conv3x3_fwd_supported(int32_t cin, int32_t cout, int32_t h, in
 }
 
 extern "C" int mb_conv3x3_fwd(const float* in, const float* wk, const float* bias, float* out, int64_t n_frames,
-                              int32_t cin, int32_t cout, int32_t h, int32_t w, void* stream) {
-    if (n_frames < 0) {
-        mb::set_error("mb_conv3x3_fwd: n_frames=%lld out of range", (long long)n_frames);
+                              int32_t cin, int32_t cout, int32_t h, int32_t w, int32_t wmode, void* stream) {
+    if (n_frames < 0 || wmode < 0 || wmode > 2) {
+        mb::set_error("mb_conv3x3_fwd: n_frames=%lld wmode=%d out of range", (long long)n_frames, wmode);
         return MB_ERR_INVALID;
     }
     if (n_frames == 0) return MB_OK;
@@ -684,7 +690,7 @@ extern "C" int mb_conv3x3_fwd(const float* in, const float* wk, const float* bia
         mb::set_error("mb_conv3x3_fwd: in and out must be 16-byte aligned");
         return MB_ERR_INVALID;
     }
-    return mb::conv3x3_fwd(in, wk, bias, out, n_frames, cin, cout, h, w, static_cast<cudaStream_t>(stream));
+    return mb::conv3x3_fwd(in, wk, bias, out, n_frames, cin, cout, h, w, wmode, static_cast<cudaStream_t>(stream));
 }
 
 extern "C" int mb_maxpool3s2_bwd(const float* dy, const int64_t* idx, float* dx, int64_t planes, int32_t h, int32_t w,

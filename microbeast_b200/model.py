@@ -96,8 +96,7 @@ class _Conv3x3(torch.autograd.Function):
     def forward(ctx, x, weight, bias):
         ctx.save_for_backward(x, weight)
         if FAST_CONV_FORWARD:
-            cout, cin = weight.shape[:2]
-            y = ops.conv3x3_fwd(x, weight.permute(1, 0, 2, 3).reshape(cin, cout, 9).contiguous(), bias)
+            y = ops.conv3x3_fwd(x, weight, bias, wmode=1)          # the kernel reads the torch layout itself
             if y is not None:
                 return y
         return F.conv2d(x, weight, bias, padding=1)
@@ -110,7 +109,7 @@ class _Conv3x3(torch.autograd.Function):
         if ctx.needs_input_grad[0]:
             cout, cin = weight.shape[:2]
             if FAST_CONV_FORWARD:           # the data gradient is a forward-type convolution with the kernel flipped
-                gx = ops.conv3x3_fwd(g, weight.flip(2, 3).reshape(cout, cin, 9).contiguous(), None)
+                gx = ops.conv3x3_fwd(g, weight, None, wmode=2)
             if gx is None:
                 gx = F.conv2d(g, weight.flip(2, 3).transpose(0, 1).contiguous(), None, padding=1)
         both = ops.conv3x3_wgrad(x, g) if FAST_CONV_WGRAD else None    # csrc/convgrad.cu; None: shape not covered

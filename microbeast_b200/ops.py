@@ -294,15 +294,18 @@ def conv3x3_wgrad(x: torch.Tensor, dy: torch.Tensor):
     return total[: cout * cin * 9].view(cout, cin, 3, 3), total[cout * cin * 9:]
 
 
-def conv3x3_fwd(x: torch.Tensor, wk: torch.Tensor, bias: Optional[torch.Tensor]) -> Optional[torch.Tensor]:
-    """``out [n,cout,h,w]`` of a 3x3 / stride 1 / pad 1 convolution of ``x [n,cin,h,w]`` with the kernel
-    given as ``wk [cin, cout, 9]`` (see ``mb_conv3x3_fwd``), or ``None`` for a shape that is not covered."""
+def conv3x3_fwd(x: torch.Tensor, wk: torch.Tensor, bias: Optional[torch.Tensor], wmode: int = 0) -> Optional[torch.Tensor]:
+    """``out [n,cout,h,w]`` of a 3x3 / stride 1 / pad 1 convolution of ``x [n,cin,h,w]`` (``mb_conv3x3_fwd``), or
+    ``None`` for a shape that is not covered.  ``wmode`` 0: ``wk [cin, cout, 9]``; 1: ``wk`` is a torch Conv2d
+    weight ``[cout, cin, 3, 3]`` (forward); 2: ``x`` is an output gradient and ``wk`` the torch weight
+    ``[cin, cout, 3, 3]`` of the convolution it came from -- the result is that convolution's input gradient."""
     dev = _need_cuda(x=x, wk=wk, bias=bias)
-    if x.dtype != torch.float32 or x.dim() != 4 or wk.dim() != 3:
+    if x.dtype != torch.float32 or x.dim() != 4 or wk.dim() not in (3, 4):
         return None
     n, cin, h, w = x.shape
-    cout = wk.shape[1]
-    if wk.shape[0] != cin or wk.shape[2] != 9 or not lib.mb_conv3x3_fwd_supported(cin, cout, h, w):
+    cout = wk.shape[0] if wmode == 1 else wk.shape[1]
+    if wk.numel() != cin * cout * 9 or (wk.shape[1] if wmode == 1 else wk.shape[0]) != cin or \
+            not lib.mb_conv3x3_fwd_supported(cin, cout, h, w):
         return None
     x = x.contiguous()
     wk = _as(wk, torch.float32, "wk")
@@ -312,40 +315,7 @@ def conv3x3_fwd(x: torch.Tensor, wk: torch.Tensor, bias: Optional[torch.Tensor])
         return None
     out = torch.empty((n, cout, h, w), dtype=torch.float32, device=dev)
     with torch.cuda.device(dev), _Launch(f"conv3x3_fwd_{cin}x{cout}x{h}", note={"n": n, "cin": cin, "cout": cout, "h": h}):
-        _check(lib.mb_conv3x3_fwd(_ptr(x), _ptr(wk), _ptr(bias), _ptr(out), n, cin, cout, h, w, _stream()))
-    return out
-
-
-def split_tf32(x: torch.Tensor) -> Tuple[torch.Tensor, torch.Tensor]:
-    """``(hi, lo)``: ``hi`` = ``x`` rounded to TF32, ``lo`` = the remainder rounded to TF32 (``x = hi + lo`` up
-    to 2^-22 |x|) -- the operand form ``linear_tf32x3`` takes."""
-    dev = _need_cuda(x=x)
-    x = _as(x, torch.float32, "x")
-    hi, lo = torch.empty_like(x), torch.empty_like(x)
-    with torch.cuda.device(dev), _Launch("split_tf32"):
-        _check(lib.mb_split_tf32(_ptr(x), _ptr(hi), _ptr(lo), x.numel(), _stream()))
-    return hi, lo
-
-
-def linear_tf32x3(x: torch.Tensor, weight: torch.Tensor, bias: Optional[torch.Tensor]) -> Optional[torch.Tensor]:
-    """``x @ weight.T + bias`` (``x [M,K]``, ``weight [N,K]``) on the tcgen05 tensor cores as three TF32 products
-    of hi/lo-split operands with fp32 accumulation (``mb_linear_tf32x3``): fp32-level accuracy.  ``None`` when
-    the shape is not covered (``K % 32``, ``N % 4``)."""
-    dev = _need_cuda(x=x, weight=weight, bias=bias)
-    if x.dtype != torch.float32 or weight.dtype != torch.float32 or x.dim() != 2 or weight.dim() != 2:
-        return None
-    m, k = x.shape
-    n = weight.shape[0]
-    if weight.shape[1] != k or k % 32 or n % 4 or m == 0:
-        return None
-    a_hi, a_lo = split_tf32(x)
-    b_hi, b_lo = split_tf32(weight)
-    if bias is not None:
-        bias = _as(bias, torch.float32, "bias")
-    out = torch.empty((m, n), dtype=torch.float32, device=dev)
-    with torch.cuda.device(dev), _Launch("linear_tf32x3", note={"m": m, "n": n, "k": k}):
-        _check(lib.mb_linear_tf32x3(_ptr(a_hi), _ptr(a_lo), _ptr(b_hi), _ptr(b_lo), _ptr(bias), _ptr(out), m, n, k,
-                                    _ptr(status_word(dev)), _stream()))
+        _check(lib.mb_conv3x3_fwd(_ptr(x), _ptr(wk), _ptr(bias), _ptr(out), n, cin, cout, h, w, int(wmode), _stream()))
     return out
 
 

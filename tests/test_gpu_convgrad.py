@@ -150,6 +150,7 @@ def test_conv_forward_matches_conv2d(cin, cout, h, n):
         ref = F.conv2d(x.double(), w.double(), None if bias is None else bias.double(), padding=1)
         ok, worst = close_rms(got.double(), ref, 1e-5)
         assert ok, worst
+        assert torch.equal(ops.conv3x3_fwd(x, w, bias, wmode=1), got), "torch weight layout read in the kernel"
 
 
 def test_conv_forward_as_data_gradient():
@@ -164,6 +165,7 @@ def test_conv_forward_as_data_gradient():
         got = ops.conv3x3_fwd(dy.float(), w.float().flip(2, 3).reshape(cout, cin, 9).contiguous(), None)
         ok, worst = close_rms(got.double(), want, 1e-5)
         assert ok, (cin, cout, h, worst)
+        assert torch.equal(ops.conv3x3_fwd(dy.float(), w.float(), None, wmode=2), got), "tap flip done in the kernel"
 
 
 def test_conv_forward_uncovered_shape_returns_none():
