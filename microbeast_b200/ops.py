@@ -319,6 +319,39 @@ def conv3x3_fwd(x: torch.Tensor, wk: torch.Tensor, bias: Optional[torch.Tensor],
     return out
 
 
+def split_tf32(x: torch.Tensor) -> Tuple[torch.Tensor, torch.Tensor]:
+    """``(hi, lo)``: ``hi`` = ``x`` rounded to TF32, ``lo`` = the remainder rounded to TF32 (``x = hi + lo`` up
+    to 2^-22 |x|) -- the operand form ``linear_tf32x3`` takes."""
+    dev = _need_cuda(x=x)
+    x = _as(x, torch.float32, "x")
+    hi, lo = torch.empty_like(x), torch.empty_like(x)
+    with torch.cuda.device(dev), _Launch("split_tf32"):
+        _check(lib.mb_split_tf32(_ptr(x), _ptr(hi), _ptr(lo), x.numel(), _stream()))
+    return hi, lo
+
+
+def linear_tf32x3(x: torch.Tensor, weight: torch.Tensor, bias: Optional[torch.Tensor]) -> Optional[torch.Tensor]:
+    """``x @ weight.T + bias`` (``x [M,K]``, ``weight [N,K]``) on the tcgen05 tensor cores as three TF32 products
+    of hi/lo-split operands with fp32 accumulation (``mb_linear_tf32x3``): fp32-level accuracy.  ``None`` when
+    the shape is not covered (``K % 32``, ``N % 4``)."""
+    dev = _need_cuda(x=x, weight=weight, bias=bias)
+    if x.dtype != torch.float32 or weight.dtype != torch.float32 or x.dim() != 2 or weight.dim() != 2:
+        return None
+    m, k = x.shape
+    n = weight.shape[0]
+    if weight.shape[1] != k or k % 32 or n % 4 or m == 0:
+        return None
+    a_hi, a_lo = split_tf32(x)
+    b_hi, b_lo = split_tf32(weight)
+    if bias is not None:
+        bias = _as(bias, torch.float32, "bias")
+    out = torch.empty((m, n), dtype=torch.float32, device=dev)
+    with torch.cuda.device(dev), _Launch("linear_tf32x3", note={"m": m, "n": n, "k": k}):
+        _check(lib.mb_linear_tf32x3(_ptr(a_hi), _ptr(a_lo), _ptr(b_hi), _ptr(b_lo), _ptr(bias), _ptr(out), m, n, k,
+                                    _ptr(status_word(dev)), _stream()))
+    return out
+
+
 def maxpool3s2_bwd(dy: torch.Tensor, idx: torch.Tensor, h: int, w: int) -> torch.Tensor:
     """``dx [n,c,h,w]`` of ``max_pool2d(x, 3, stride=2, padding=1)`` from ``dy`` and the forward's argmax
     indices (both ``[n,c,(h+1)//2,(w+1)//2]``)."""

@@ -65,3 +65,14 @@ def test_ops_refuse_cpu_tensors():
     x = torch.zeros(4, 16)
     with pytest.raises(RuntimeError, match="no CPU fallback"):
         ops.vtrace_loss(x, x, x, torch.zeros(4), x, x.bool(), x)
+
+
+def test_every_entry_point_has_a_python_wrapper():
+    """Each compute entry point of the C ABI is called from microbeast_b200/ops.py (a wrapper dropped by
+    accident would otherwise only show up on the GPU box)."""
+    import inspect
+    from microbeast_b200 import _lib, ops
+    src = inspect.getsource(ops)
+    housekeeping = {"mb_version", "mb_last_error", "mb_set_tuning", "mb_vtrace_loss_static"}
+    missing = [name for name in _lib.SIGNATURES if name not in housekeeping and f"lib.{name}" not in src]
+    assert not missing, missing
