@@ -1,4 +1,5 @@
-// Weight gradient of the encoder's 3x3 / stride 1 / pad 1 convolutions in fp32, for sm_100a.
+// The encoder's 3x3 / stride 1 / pad 1 convolutions in fp32, for sm_100a: weight (+ bias) gradient first,
+// then the forward / data-gradient kernel and the max-pool backward further down.
 //
 // Reference: the encoder of model.py:56-137 (Residual_Block / ConvSequence) is differentiated by
 // loss.backward() at libs/utils.py:334.  The encoder stays on PyTorch; this file replaces ONE cuDNN
@@ -21,8 +22,9 @@
 //   * rows slide through registers (up / mid / down), so per image row a thread issues 1 X-row load
 //     and 4 dY-row loads for 36 * W FMAs; taps that would fall outside the image are skipped at
 //     compile time, so there is no halo;
-//   * persistent CTAs walk the frame chunks; every CTA writes its partial dW to its own slot of a
-//     [grid, COUT*CIN*9] buffer, and the caller adds the slots up (fixed order: deterministic).
+//   * persistent CTAs walk the frame chunks; every CTA writes its partial dW -- and the bias gradient,
+//     summed from the dY planes it staged anyway -- to its own slot of a [grid, COUT*CIN*9 + COUT]
+//     buffer, and the caller adds the slots up (fixed order: deterministic).
 #include "common.cuh"
 
 #include "../../include/mbeast.h"
