@@ -148,30 +148,64 @@ class ClockSampler:
 # ------------------------------------------------------------------------------------------
 # reference arm / cpu baseline: the oracle port of the reference's CPU learner step
 # ------------------------------------------------------------------------------------------
-def time_cpu_reference(h, w, T, rows, steps, warmup, preset, threads=None):
+def load_synth():
+    """``microbeast_b200/synth.py`` loaded from its file, WITHOUT importing the package: importing
+    ``microbeast_b200`` dlopens ``libmbeast_sm100.so`` and the reference arm must not load any of the product's
+    native code (the generators are pure torch)."""
+    import importlib.util
+    spec = importlib.util.spec_from_file_location("_mb_synth_standalone",
+                                                  os.path.join(ROOT, "microbeast_b200", "synth.py"))
+    mod = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(mod)
+    return mod
+
+
+def time_cpu_reference(h, w, T, rows, steps, warmup, preset, threads=None, budget_s=None):
+    """Times the reference's CPU learner step on ``rows`` rows.  When the unmodified reference can be imported
+    (``/root/reference`` here, ``oracle/_ref`` staged by ``oracle/stage_ref.py`` on the GPU box) it is the REAL
+    ``libs.utils.PPO_learn`` driving the REAL ``model.Agent`` (``kind: "reference"``, stdout swallowed because
+    ``PPO_learn`` prints tensors, ``utils.py:321-340``); else the oracle's restatement (``kind: "port"``).
+    Returns ``(frames_per_s, s_per_step, threads, kind)``."""
+    import contextlib
+    import io
     import torch
-    from microbeast_b200 import synth
-    from oracle import NVEC_CELL
-    from oracle.learner import RefAgent, ref_learn_step
+    synth = load_synth()
+    from oracle import NVEC_CELL, refload
     cores = threads or os.cpu_count() or 1
     torch.set_num_threads(cores)
     torch.manual_seed(1234)
-    agent = RefAgent((h, w, 27), list(NVEC_CELL) * (h * w), h * w)
+    nvec = list(NVEC_CELL) * (h * w)
+    if refload.available():
+        ref_model, ref_utils = refload.load()
+        agent, kind = ref_model.Agent((h, w, 27), nvec, h * w), "reference"
+
+        def one_step(b):
+            with contextlib.redirect_stdout(io.StringIO()):
+                return ref_utils.PPO_learn(agent, agent, "bench_ref", b, opt, rows, T, 1)
+    else:
+        from oracle.learner import RefAgent, ref_learn_step
+        agent, kind = RefAgent((h, w, 27), nvec, h * w), "port"
+
+        def one_step(b):
+            return ref_learn_step(agent, b, opt, rows, T, 1)
     with torch.no_grad():
         agent.actor.weight.normal_(0, 0.01)          # SURVEY 8d: reference init is all-zero
     opt = torch.optim.Adam(agent.parameters(), lr=2.5e-4, eps=1e-5)        # microbeast.py:200
     batch = synth.make_rollout_batch(h, w, T, rows, seed=1234, preset=preset)
-    with torch.no_grad():
+    with torch.no_grad(), contextlib.redirect_stdout(io.StringIO()):
         o, _ = agent.get_action(batch, learning=True)
     batch["logprobs"] = o["logprobs"] + 0.3 * torch.randn(o["logprobs"].shape)
     times = []
+    t_start = time.perf_counter()
     for i in range(warmup + steps):
         t0 = time.perf_counter()
-        ref_learn_step(agent, {k: v.clone() for k, v in batch.items()}, opt, rows, T, 1)
+        one_step({k: v.clone() for k, v in batch.items()})
         if i >= warmup:
             times.append(time.perf_counter() - t0)
+        if budget_s and times and time.perf_counter() - t_start > budget_s:
+            break                                    # bounded sample: stop once the time budget is spent
     sec = sum(times) / max(len(times), 1)
-    return rows * T / sec, sec, cores
+    return rows * T / sec, sec, cores, kind
 
 
 def run_reference(args):
@@ -180,17 +214,19 @@ def run_reference(args):
         return
     h, w, T, _ = WORKLOADS[args.workload]
     rows = args.cpu_rows
-    fps, sec, cores = time_cpu_reference(h, w, T, rows, args.steps, args.warmup, args.preset)
+    fps, sec, cores, kind = time_cpu_reference(h, w, T, rows, args.steps, args.warmup, args.preset, budget_s=240)
+    what = ("the unmodified reference (libs/utils.py PPO_learn + model.py Agent)" if kind == "reference"
+            else "oracle port of libs/utils.py:223-342 + model.py:165-216")
     sample = (f"{rows} of {workload_shape(args)[3]} rows per step ({rows * (T + 1)} frames), "
-              f"full reference learner step (oracle port of libs/utils.py:223-342 + model.py:165-216), "
-              f"torch CPU, {cores} threads")
+              f"full reference learner step: {what}, torch CPU, {cores} threads")
+    cfg = workload_config(args)
     line = {
         "impl": "reference", "metric": METRIC, "value": fps, "unit": UNIT, "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": sec * 1e3, "higher_is_better": True,
         "scaling": "strong" if args.workload == "c3" else "weak", "vs_baseline": None, "dtype": "f32",
         "data": "synthetic",
-        "config": workload_config(args),
-        "cpu_baseline": {"value": fps, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
+        "config": cfg,
+        "cpu_baseline": {"value": fps, "unit": UNIT, "cores": cores, "kind": kind, "sample": sample},
         "e2e": {"value": fps, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
@@ -214,6 +250,10 @@ def workload_config(args, rows_override=None):
             "mask_preset": args.preset, "l2_policy": "inputs larger than L2 (logits alone are "
             f"{rows * (T + 1) * h * w * 78 * 4 / 1e6:.0f} MB per GPU vs 126 MB L2)",
             "parallelism": f"dp{args.gpus}",
+            # both arms print this same config; the CPU arm's step is a bounded sample of it and says so here
+            "reference_arm_rows_per_step": args.cpu_rows,
+            "reference_arm_note": f"--impl reference (and cpu_baseline) time {args.cpu_rows} of the {rows} rows per "
+                                  "step on the host cores; its frames/s does not rise with rows (measured 8/32/96)",
             "arithmetic": "fp32 throughout (TF32 off in cuDNN / cuBLAS); the actor Linear forward runs on tcgen05 as three "
                           "TF32 products of hi/lo-split operands with fp32 accumulation (error 5e-7 of max|logit|, "
                           "cuBLAS fp32: 5e-7); its backward runs over the cells with a valid action only (the others "
@@ -430,12 +470,12 @@ def run_ours(args):
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         crow = args.cpu_rows
-        fps, sec, cores = time_cpu_reference(h, w, T, crow, 2, 1, args.preset)
-        cpu = {"value": fps, "unit": UNIT, "cores": cores, "kind": "port",
+        fps, sec, cores, kind = time_cpu_reference(h, w, T, crow, 2, 1, args.preset)
+        cpu = {"value": fps, "unit": UNIT, "cores": cores, "kind": kind,
                "sample": f"{crow} of {rows} rows ({crow * (T + 1)} frames) per step, 2 timed steps after 1 "
                          f"warm-up, full reference learner step on torch CPU ({sec:.2f} s/step)"}
         # the reference's nominal setting is OMP_NUM_THREADS=1 (microbeast.py:16): one timed step on a quarter sample
-        fps1, sec1, _ = time_cpu_reference(h, w, T, max(crow // 4, 1), 1, 1, args.preset, threads=1)
+        fps1, sec1, _, _ = time_cpu_reference(h, w, T, max(crow // 4, 1), 1, 1, args.preset, threads=1)
         cpu["single_thread"] = {"value": fps1, "unit": UNIT, "cores": 1,
                                 "sample": f"{max(crow // 4, 1)} rows per step, 1 timed step ({sec1:.2f} s/step)"}
         torch.set_num_threads(os.cpu_count() or 1)

@@ -10,6 +10,7 @@ loop blocks on the queue instead of spinning on ``free_queue.empty()`` (``microb
 """
 from __future__ import annotations
 
+import contextlib
 from typing import Optional
 
 import torch
@@ -24,11 +25,15 @@ def _to_device(env_output: dict, device) -> dict:
 
 
 def act(agent, n_envs: int, T: int, buffers, a_id: int, free_queue, full_queue, unroll_length: int,
-        exp_name: str, envs=None, max_unrolls: Optional[int] = None, seed: Optional[int] = None, server=None):
+        exp_name: str, envs=None, max_unrolls: Optional[int] = None, seed: Optional[int] = None, server=None,
+        model_lock=None):
     """Fills rollout buffers until ``None`` arrives on ``free_queue`` (or ``max_unrolls``).
 
     ``server``: an ``inference.InferenceServer``; the actor then sends its ``get_action`` requests
-    there (batched with the other actors') instead of running the model itself."""
+    there (batched with the other actors') instead of running the model itself.  ``model_lock``: held while
+    this thread enqueues its ``get_action`` kernels, so that they cannot land between the kernels of a learner
+    step that updates the same weights in place (``train()`` passes the lock its learner loop takes; all threads
+    launch on the device's default stream, so enqueue order is execution order)."""
     if envs is None:
         raise RuntimeError("act(): pass envs= (gym-microRTS is unavailable here; see env_packer.SyntheticVecEnv)")
     packer = envs if isinstance(envs, Env_Packer) else Env_Packer(envs, a_id, exp_name)
@@ -44,7 +49,7 @@ def act(agent, n_envs: int, T: int, buffers, a_id: int, free_queue, full_queue, 
             return server.infer(env_output)
         dev = _to_device({k: env_output[k] for k in ("obs", "action_mask")}, device)
         u = torch.rand((n_envs, 7 * cells), device=device, generator=gen)
-        with torch.no_grad():
+        with torch.no_grad(), (model_lock if model_lock is not None else contextlib.nullcontext()):
             out, _ = agent.get_action(dev, uniforms=u)
         return {k: out[k].cpu() for k in AGENT_KEYS}
 

@@ -24,8 +24,13 @@ def _format_obs(obs: np.ndarray, dtype=torch.float32) -> torch.Tensor:
 
 
 def _format_action_masks(action_mask: np.ndarray) -> torch.Tensor:
-    """``(n, 78*cells)`` -> ``(1, n, 78*cells)`` -- reference ``env_packer.py:12-14``."""
+    """``(n, 78*cells)`` -> ``(1, n, 78*cells)`` uint8, non-zero = valid -- reference ``env_packer.py:12-14``.
+    gym-microRTS returns an int32 array and the reference only casts it inside ``CategoricalMasked``
+    (``masks.type(torch.BoolTensor)``, ``model.py:40``); the kernels and the rollout store take one byte per
+    entry, so the cast happens here, once, for every integer / bool dtype."""
     action_mask = torch.from_numpy(np.ascontiguousarray(action_mask))
+    if action_mask.dtype != torch.uint8:
+        action_mask = (action_mask != 0).to(torch.uint8)
     return action_mask.view((1,) + tuple(action_mask.shape))
 
 

@@ -10,6 +10,7 @@ in the policy head, so an actor gets bit-identical actions whether it is served 
 """
 from __future__ import annotations
 
+import contextlib
 import queue
 import threading
 import time
@@ -34,8 +35,12 @@ class _Request:
 class InferenceServer:
     """Dynamic batching of acting-mode ``Agent.get_action`` calls from many actor threads."""
 
-    def __init__(self, agent, max_batch_envs: int = 256, max_wait_ms: float = 0.5, seed: Optional[int] = None):
+    def __init__(self, agent, max_batch_envs: int = 256, max_wait_ms: float = 0.5, seed: Optional[int] = None,
+                 model_lock=None):
         self.agent = agent
+        # held while a batch's kernels are enqueued: a learner that updates ``agent``'s weights in place takes the
+        # same lock around its step, so inference never reads a half-updated parameter set
+        self.model_lock = model_lock if model_lock is not None else contextlib.nullcontext()
         self.device = next(agent.parameters()).device
         self.max_batch_envs = max_batch_envs
         self.max_wait = max_wait_ms * 1e-3
@@ -107,7 +112,7 @@ class InferenceServer:
                     if r.uniforms is not None:
                         u[off:off + r.n] = r.uniforms.to(self.device)
                     off += r.n
-                with torch.no_grad():
+                with torch.no_grad(), self.model_lock:
                     out, _ = self.agent.get_action(dict(obs=obs.view((1, 1) + tuple(obs.shape)),
                                                         action_mask=mask.view((1,) + tuple(mask.shape))), uniforms=u)
                 host = {k: out[k].cpu() for k in AGENT_KEYS}

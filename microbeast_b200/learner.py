@@ -168,11 +168,16 @@ def PPO_learn(actor_model: nn.Module, learner_model, exp_name: str, batch, optim
         if ready is not None:
             dev_batch["_ready"] = ready
         world = reducer.world_size if reducer is not None else 1
+        keep = getattr(learner_model, "sparse_head", None)
         if sparse_head is not None:
-            learner_model.sparse_head = sparse_head
-        loss4, _aux = learner_losses(learner_model, dev_batch, rows, T, gamma=gamma, rho_bar=rho_bar,
-                                     c_bar=c_bar, pg_rho_bar=pg_rho_bar, entropy_coef=entropy_coef,
-                                     global_rows=rows * world, time_major=time_major)
+            learner_model.sparse_head = sparse_head            # for this step only: restored below
+        try:
+            loss4, _aux = learner_losses(learner_model, dev_batch, rows, T, gamma=gamma, rho_bar=rho_bar,
+                                         c_bar=c_bar, pg_rho_bar=pg_rho_bar, entropy_coef=entropy_coef,
+                                         global_rows=rows * world, time_major=time_major)
+        finally:
+            if sparse_head is not None:
+                learner_model.sparse_head = keep
         optimizer.zero_grad()                                                              # utils.py:333
         loss4[3].backward()                                                                # utils.py:334
         losses = loss4.detach()

@@ -23,6 +23,7 @@ launch_counts: Dict[str, int] = {}
 
 _status_words: Dict[int, torch.Tensor] = {}
 _workspaces: Dict[Tuple[int, int], torch.Tensor] = {}
+_retired_workspaces: list = []
 
 
 _timing = None      # list of (name, start_event, end_event) while kernel timing is on
@@ -115,8 +116,12 @@ def _as(t: torch.Tensor, dtype, name: str) -> torch.Tensor:
 
 
 def _mask_u8(mask: torch.Tensor) -> torch.Tensor:
+    """Any mask the reference accepts (it casts with ``masks.type(torch.BoolTensor)``, ``model.py:40``: uint8,
+    bool, the int32 of gym-microRTS ``get_action_mask()``, floats) as contiguous uint8, non-zero = valid."""
     if mask.dtype == torch.bool:
-        mask = mask.view(torch.uint8)
+        mask = mask.contiguous().view(torch.uint8)
+    elif mask.dtype != torch.uint8:
+        mask = (mask != 0).view(torch.uint8)
     return _as(mask, torch.uint8, "mask")
 
 
@@ -257,7 +262,7 @@ def unpack_obs(obs_bits: torch.Tensor, planes: int = 27, out: Optional[torch.Ten
 def active_cells(action_mask: torch.Tensor, cells: int) -> torch.Tensor:
     """``[N, cells]`` bool: cells of ``action_mask [N, 78*cells]`` with at least one valid action."""
     dev = _need_cuda(action_mask=action_mask)
-    action_mask = _as(action_mask, torch.uint8, "action_mask")
+    action_mask = _mask_u8(action_mask)
     n = action_mask.shape[0]
     if action_mask.dim() != 2 or action_mask.shape[1] != cells * LOGITS_PER_CELL:
         raise ValueError("action_mask must be [N, 78*cells]")
@@ -376,6 +381,10 @@ def vtrace_workspace(device: torch.device, rows: int) -> torch.Tensor:
     key = (idx, 0)
     ws = _workspaces.get(key)
     if ws is None or ws.numel() < need:
+        if ws is not None:
+            # an outgrown workspace may still be addressed by a captured CUDA graph (GraphedLearner records the
+            # raw pointer): keep it alive for the life of the process instead of handing it back to the allocator
+            _retired_workspaces.append(ws)
         ws = torch.zeros(max(need, 1 << 16), dtype=torch.uint8, device=torch.device("cuda", idx))
         _workspaces[key] = ws
     return ws

@@ -66,16 +66,19 @@ def train(exp_name: str, *, env_factory: Optional[Callable[[int, int, int], obje
     for index in range(n_buffers):
         free_queue.put(index)                                                # microbeast.py:174-175
 
-    model_lock = threading.Lock()         # actors read the weights the learner updates in place
+    # the learner updates the weights in place while actors / the inference server read them: each side holds this
+    # lock while it ENQUEUES its kernels (one default stream per device => enqueue order is execution order)
+    model_lock = threading.Lock()
     server = None
     if batched_inference:                 # one batched get_action for all actors (inference.py)
         from .inference import InferenceServer
-        server = InferenceServer(model, max_batch_envs=n_actors * n_envs, seed=seed).start()
+        server = InferenceServer(model, max_batch_envs=n_actors * n_envs, seed=seed, model_lock=model_lock).start()
     threads = []
     for i in range(n_actors):                                                # microbeast.py:179-191
         th = threading.Thread(target=act, daemon=True,
                               args=(model, n_envs, T, buffers, i, free_queue, full_queue, T, exp_name),
-                              kwargs=dict(envs=env_factory(i, n_envs, env_size), seed=seed * 7919 + i, server=server))
+                              kwargs=dict(envs=env_factory(i, n_envs, env_size), seed=seed * 7919 + i, server=server,
+                                          model_lock=model_lock))
         th.start()
         threads.append(th)
 

@@ -18,6 +18,27 @@ def test_formatters_match_reference_shapes():
     assert _format_obs(obs, torch.uint8).dtype == torch.uint8
 
 
+def test_int32_masks_of_gym_microrts_become_uint8():
+    """gym-microRTS ``get_action_mask()`` returns int32 and the reference only casts inside ``CategoricalMasked``
+    (``model.py:40``); the packer normalises once so the rollout store and the kernels see one byte per entry."""
+    rs = np.random.RandomState(3)
+    for dtype in (np.int32, np.int64, np.bool_, np.float32, np.uint8):
+        raw = (rs.randint(0, 3, (2, 78 * 16)) * (rs.rand(2, 78 * 16) < 0.5)).astype(dtype)     # values 0 / 1 / 2
+        m = _format_action_masks(raw)
+        assert m.dtype == torch.uint8 and m.shape == (1, 2, 78 * 16)
+        assert torch.equal(m[0] != 0, torch.from_numpy(raw != 0))
+
+    class Int32Env(SyntheticVecEnv):
+        def get_action_mask(self):
+            return super().get_action_mask().astype(np.int32)
+
+    packer = Env_Packer(Int32Env(2, 8, seed=5), 0, "")
+    out = packer.initial()
+    assert out["action_mask"].dtype == torch.uint8
+    out = packer.step(torch.zeros((2, 7 * 64), dtype=torch.int64))
+    assert out["action_mask"].dtype == torch.uint8
+
+
 def test_packer_outputs_fit_the_rollout_buffers(tmp_path):
     n_envs, T = 3, 4
     env = SyntheticVecEnv(n_envs, 8, seed=2, episode_len=3)
