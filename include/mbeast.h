@@ -137,7 +137,9 @@ MB_API int mb_vtrace_loss_tmajor(const float* lp_old, const float* lp_new, const
  * per GPU that loads the library, kept until the process exits.
  *   - rows <= 65536 per call; more is rejected with MB_ERR_INVALID (use mb_vtrace_loss then);
  *   - the first call on each device looks the array's device address up (cudaGetSymbolAddress, with
- *     that device current); make that first call outside any stream capture;
+ *     that device current); make that first call outside any stream capture -- a first call whose
+ *     `stream` is being captured is refused with MB_ERR_INVALID and leaves the capture intact;
+ *   - device indices 0..63 only (MB_ERR_UNSUPPORTED beyond);
  *   - the call never allocates or frees device memory; it clears the part of the scratch that must
  *     start at zero on `stream` before the launch;
  *   - every call on a GPU shares the one array: calls that may overlap on the GPU race with each
@@ -215,9 +217,12 @@ MB_API int mb_maxpool3s2_bwd(const float* dy, const int64_t* idx, float* dx, int
 /* Tuning knobs for benchmarking (not part of the reference surface).  Keys:
  *   "head_ctas_per_sm" (0 = as many as fit), "head_grid" (0 = auto), "head_variant" (tile /
  *   pipeline shape: 0 = 64 cells x 3 stages, 1 = 64x2, 2 = 64x4, 3 = 32x3, 4 = 32x5, 5 = 128x3, 6 = 128x2, 7 = 32x2; -1 = per-kernel default),
+ *   "vtrace_static_poison" (1: the next mb_vtrace_loss_static call first fills its built-in scratch with
+ *   0xA5 on the caller's stream -- a test hook that stands in for whatever an earlier user left there),
  *   "vtrace_force_generic" (0/1), "vtrace_l2_promo" (0/64/128/256 bytes),
  *   "vtrace_variant" (stages x steps per tile: -1 = by grid size, 0 = 2x32, 1 = 3x32, 2 = 4x32,
- *   3 = 3x16, 4 = 4x16, 5 = 5x16, 6 = 6x16, 7 = 8x16).
+ *   3 = 3x16, 4 = 4x16, 5 = 5x16, 6 = 6x16, 7 = 8x16, 8 = 6x32, 9 = 12x16, 10 = 8x32; with 16-row instead of
+ *   32-row groups: 11 = 4x32, 12 = 6x32, 13 = 8x32, 14 = 8x16, 15 = 6x16).
  *   "gemm_group_m" (mb_linear_tf32x3 tile order: 0 = row-major, g > 0 = bands of g tile rows walked column by
  *   column), "gemm_stream_store" (0/1: store the output with the streaming cache hint).
  * Returns MB_ERR_INVALID for an unknown key. */

@@ -44,6 +44,8 @@ int head_eval_cells_bwd(const float*, const uint8_t*, const int64_t*, const floa
 void head_set_tuning(int ctas_per_sm, int grid_override, int variant);
 void vtrace_set_tuning(int force_generic, int variant, int l2_promo);
 void gemm_set_tuning(int group_m, int stream_store);
+void vtrace_static_poison(int on);
+void vtrace_set_debug(int v);
 size_t vtrace_workspace_bytes(long long rows);
 
 struct VtParams;
@@ -105,6 +107,8 @@ int mb_set_tuning(const char* key, int32_t value) {
     else if (!strcmp(key, "vtrace_force_generic")) vt_generic = value;
     else if (!strcmp(key, "vtrace_variant")) vt_variant = value;
     else if (!strcmp(key, "vtrace_l2_promo")) vt_promo = value;
+    else if (!strcmp(key, "vtrace_static_poison")) mb::vtrace_static_poison(value);
+    else if (!strcmp(key, "vtrace_debug")) mb::vtrace_set_debug(value);
     else if (!strcmp(key, "gemm_group_m")) gemm_group_m = value;
     else if (!strcmp(key, "gemm_stream_store")) gemm_stream_store = value;
     else {

@@ -52,6 +52,7 @@ struct VtParams {
     long long in_stride;     // elements between consecutive rows of the inputs
     long long out_stride;    // elements between consecutive rows of the outputs
     float gamma, rho_bar, c_bar, pg_rho_bar, ent_coef, inv_n;
+    int debug;               // diagnostics (mb_set_tuning "vtrace_debug"): 1 = skip the arithmetic, 2 = no entropy, 4 = no stores
 };
 
 struct VtMaps {
@@ -126,11 +127,12 @@ __device__ __forceinline__ void vt_finalize(const VtParams& p, int lane) {
 // ---------------------------------------------------------------------------------------------
 constexpr int kVtRows = 32;
 
-template <int TS>
+template <int TS, int ROWS = kVtRows>
 struct VtTile {
     static_assert(TS == 32 || TS == 16, "tile steps");
-    static constexpr int kF32 = kVtRows * TS * 4;          // 4096 / 2048 B; rows of 128 / 64 B, swizzled
-    static constexpr int kU8 = kVtRows * TS;               // 1024 / 512 B; rows of 32 / 16 B, no swizzle
+    static_assert(ROWS == 32 || ROWS == 16, "rows per group");
+    static constexpr int kF32 = ROWS * TS * 4;             // 32 rows: 4096 / 2048 B; rows of 128 / 64 B, swizzled
+    static constexpr int kU8 = ROWS * TS;                  // 32 rows: 1024 / 512 B; rows of 32 / 16 B, no swizzle
     static constexpr int kStage = 4 * kF32 + 1024;         // lp_old, lp_new, values, rewards, done (padded)
     static constexpr int kChunks = TS / 4;                 // float4 chunks per row
     static constexpr int kRowPitch = TS * 4;
@@ -143,13 +145,16 @@ struct VtTile {
 
 // DONE_TMA = false: the rows' byte pitch is not a multiple of 16 (e.g. T = 20), which a tensor map
 // cannot describe for the u8 `done` array; each thread then reads its row's done bytes directly.
-template <int NSTAGE, int TS, bool DONE_TMA = true>
+// ROWS = 16: half the lanes of the compute warp idle, but a launch with few rows splits into twice as many groups
+// (16 384 rows are 512 groups of 32: 3.46 per SM, so a quarter of the SMs carry 4 while the rest carry 3).
+template <int NSTAGE, int TS, bool DONE_TMA = true, int ROWS = kVtRows>
 __global__ void __launch_bounds__(64) vtrace_tma_kernel(const __grid_constant__ VtMaps maps, const VtParams p) {
-    using Tile = VtTile<TS>;
+    using Tile = VtTile<TS, ROWS>;
     constexpr int kStageBytes = Tile::kStage;              // multiple of 1024
     extern __shared__ uint8_t smem_raw[];
     __shared__ __align__(8) uint64_t full[NSTAGE];     // TMA loads of a stage have landed
     __shared__ __align__(8) uint64_t done[NSTAGE];     // the compute warp has overwritten the stage with outputs
+    __shared__ double ent_sum;
     // swizzled tiles need 1024-B alignment
     uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
 
@@ -160,7 +165,7 @@ __global__ void __launch_bounds__(64) vtrace_tma_kernel(const __grid_constant__ 
     const bool want_grads = (p.dlp != nullptr);
     // persistent: this CTA owns the 32-row groups blockIdx.x, blockIdx.x + gridDim.x, ... and runs
     // their time tiles as ONE stream through the ring, so the pipeline never drains between groups
-    const int n_groups = int((p.rows + kVtRows - 1) / kVtRows);
+    const int n_groups = int((p.rows + ROWS - 1) / ROWS);
     const int my_groups = (n_groups - int(blockIdx.x) + int(gridDim.x) - 1) / int(gridDim.x);
 
     if (threadIdx.x == 0) {
@@ -180,13 +185,13 @@ __global__ void __launch_bounds__(64) vtrace_tma_kernel(const __grid_constant__ 
     const int nt = (p.T + TS - 1) / TS;
 
     const long long total_q = (long long)my_groups * nt;
-    // producer-side cursor (lane 0): tile lq = (group lg, tile lk counted from the END of the rows)
-    long long lq = 0;
-    int lg = 0, lk = 0;
-    auto issue_load = [&]() {             // lane 0 only: loads tile lq and advances the cursor
-        const int s = int(lq % NSTAGE);
-        const int t0 = (nt - 1 - lk) * TS;
-        const int row0 = (int(blockIdx.x) + lg * int(gridDim.x)) * kVtRows;
+    // lane 0 of the TMA warp: loads the tile with consumption index x = (group x / nt, tile x % nt counted from
+    // the END of the rows) into stage x % NSTAGE
+    auto issue_load = [&](long long x) {
+        const int s = int(x % NSTAGE);
+        const int xg = int(x / nt), xk = int(x % nt);
+        const int t0 = (nt - 1 - xk) * TS;
+        const int row0 = (int(blockIdx.x) + xg * int(gridDim.x)) * ROWS;
         uint8_t* st = smem + size_t(s) * kStageBytes;
         mbar_arrive_expect_tx(&full[s], uint32_t(4 * Tile::kF32 + (DONE_TMA ? Tile::kU8 : 0)));
         tma_load_2d(st + 0 * Tile::kF32, &maps.lp_old, t0, row0, &full[s]);
@@ -194,38 +199,104 @@ __global__ void __launch_bounds__(64) vtrace_tma_kernel(const __grid_constant__ 
         tma_load_2d(st + 2 * Tile::kF32, &maps.values, t0, row0, &full[s]);
         tma_load_2d(st + 3 * Tile::kF32, &maps.rewards, t0, row0, &full[s]);
         if (DONE_TMA) tma_load_2d(st + 4 * Tile::kF32, &maps.done, t0, row0, &full[s]);
-        ++lq;
-        if (++lk == nt) { lk = 0; ++lg; }
+    };
+    // Tiles are CONSUMED from the end of a row towards its start, but they are REQUESTED in blocks of kBlk
+    // consecutive tiles (256 B of a row), lowest address first: with the tensor maps' 256-B L2 promotion a miss on
+    // the lower half of a 256-B block brings in the upper half as well, which only an ascending request order can
+    // use (measured, scripts/micro/tma_multi.cu: 5.96 TB/s descending, 6.68 TB/s in ascending pairs, 6.72 TB/s
+    // ascending throughout).  Block b of a group holds its tiles [b*kBlk, b*kBlk + kBlk) in consumption order.
+    constexpr int kBlk = (256 / (TS * 4)) < (NSTAGE / 2) ? (256 / (TS * 4)) : (NSTAGE / 2 > 0 ? NSTAGE / 2 : 1);
+    long long lq = 0;                     // first consumption index that has not been requested yet
+    auto block_len = [&](long long q0) { return int(min((long long)kBlk, (long long)(nt - int(q0 % nt)))); };
+    auto issue_block = [&]() {            // requests tiles [lq, lq + n) in DEscending consumption = AScending address order
+        const int n = block_len(lq);
+        for (int i = n - 1; i >= 0; --i) issue_load(lq + i);
+        lq += n;
     };
 
     if (warp == 1) {
         // ===================== TMA warp =====================
-        if (lane == 0) {
-            for (int i = 0; i < NSTAGE && lq < total_q; ++i) issue_load();
-            int sg = 0, sk = 0;                            // store cursor: tile sk of group sg
-            for (long long q = 0; q < total_q; ++q) {
-                const int s = int(q % NSTAGE);
+        // lane 0 issues every tensor copy; ALL lanes stream the group's entropy, which only feeds a mean: the group's
+        // [rows_here x T] block is a list of float4 slots (nq per row), lane l owns slots l, l+32, ... and fetches the
+        // tile's share (kEntSlots per lane) at the top of an iteration; the values are summed at its end, after the
+        // wait for the compute warp and the TMA work, so their latency is off every critical path (on the compute
+        // warp they stalled the recurrence once per tile: 15 % of its stall samples in profiles/r01_ncu_stalls.md)
+        constexpr int kEntSlots = ROWS * TS / 128;
+        const int nq = (p.T + 3) >> 2;
+        const int tail = p.T - 4 * (nq - 1);               // valid floats in a row's last slot (1..4)
+        int ent_r = 0, ent_c = 0, e_row0 = 0, e_rows = 0;
+        float s_en = 0.0f;
+        double s_en_d = 0.0;
+        if (lane == 0)
+            while (lq < total_q && lq + block_len(lq) <= NSTAGE) issue_block();
+        int sg = 0, sk = 0;                                // store cursor: tile sk of group sg
+        float4 eprev[kEntSlots];                           // the previous iteration's loads: summed one iteration late
+#pragma unroll
+        for (int i = 0; i < kEntSlots; ++i) eprev[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+        for (long long q = 0; q < total_q; ++q) {
+            const int s = int(q % NSTAGE);
+            if (sk == 0) {
+                e_row0 = (int(blockIdx.x) + sg * int(gridDim.x)) * ROWS;
+                e_rows = int(min((long long)ROWS, p.rows - e_row0));
+                ent_r = 0;
+                ent_c = lane;
+                while (ent_c >= nq) { ent_c -= nq; ++ent_r; }
+                s_en_d += double(s_en);
+                s_en = 0.0f;
+            }
+            float4 ebuf[kEntSlots];
+#pragma unroll
+            for (int i = 0; i < kEntSlots; ++i) {
+                ebuf[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+                if (ent_r < e_rows && !(p.debug & 2)) {
+                    const float* src = p.entropy + (long long)(e_row0 + ent_r) * p.in_stride + 4 * ent_c;
+                    float4 v;
+                    if (ent_c == nq - 1 && tail < 4) {     // never read past T in a row's last slot
+                        v = make_float4(__ldg(src), tail > 1 ? __ldg(src + 1) : 0.f, tail > 2 ? __ldg(src + 2) : 0.f, 0.f);
+                    } else {
+                        // volatile asm: stays ahead of the mbarrier wait below
+                        asm volatile("ld.global.nc.v4.f32 {%0, %1, %2, %3}, [%4];"
+                                     : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w)
+                                     : "l"(src));
+                    }
+                    ebuf[i] = v;
+                }
+                ent_c += 32;
+                while (ent_c >= nq) { ent_c -= nq; ++ent_r; }
+            }
+            if (lane == 0) {
                 mbar_wait(&done[s], uint32_t((q / NSTAGE) & 1), nullptr);
                 uint8_t* st = smem + size_t(s) * kStageBytes;
                 const int t0 = (nt - 1 - sk) * TS;
-                const int row0 = (int(blockIdx.x) + sg * int(gridDim.x)) * kVtRows;
                 // in place: vs over rewards, adv over lp_old, d_logp over lp_new, d_values over values
-                tma_store_2d(&maps.vs, t0, row0, st + 3 * Tile::kF32);
-                tma_store_2d(&maps.adv, t0, row0, st + 0 * Tile::kF32);
-                if (want_grads) {
-                    tma_store_2d(&maps.dlp, t0, row0, st + 1 * Tile::kF32);
-                    tma_store_2d(&maps.dv, t0, row0, st + 2 * Tile::kF32);
+                if (!(p.debug & 4)) tma_store_2d(&maps.vs, t0, e_row0, st + 3 * Tile::kF32);
+                if (!(p.debug & 4)) tma_store_2d(&maps.adv, t0, e_row0, st + 0 * Tile::kF32);
+                if (want_grads && !(p.debug & 4)) {
+                    tma_store_2d(&maps.dlp, t0, e_row0, st + 1 * Tile::kF32);
+                    tma_store_2d(&maps.dv, t0, e_row0, st + 2 * Tile::kF32);
                 }
                 bulk_commit();
-                if (q >= 1 && lq < total_q) {
-                    // tile q-1+NSTAGE goes into the stage tile q-1 was stored from one iteration ago
+                // a block may be requested once the stages it lands in are free: its last tile x = lq + n - 1 reuses
+                // the stage of tile x - NSTAGE, whose store must have finished reading shared memory (<= q - 1)
+                if (lq < total_q && lq + block_len(lq) - 1 - NSTAGE <= q - 1) {
                     bulk_wait_read<1>();
-                    issue_load();
+                    issue_block();
                 }
-                if (++sk == nt) { sk = 0; ++sg; }
             }
-            bulk_wait_all<0>();     // output tiles are in global memory before the CTA retires
+            __syncwarp();
+#pragma unroll
+            for (int i = 0; i < kEntSlots; ++i) {
+                s_en += (eprev[i].x + eprev[i].y) + (eprev[i].z + eprev[i].w);
+                eprev[i] = ebuf[i];
+            }
+            if (++sk == nt) { sk = 0; ++sg; }
         }
+#pragma unroll
+        for (int i = 0; i < kEntSlots; ++i) s_en += (eprev[i].x + eprev[i].y) + (eprev[i].z + eprev[i].w);
+        if (lane == 0) bulk_wait_all<0>();     // output tiles are in global memory before the CTA retires
+        const double tot = warp_sum(s_en_d + double(s_en));
+        if (lane == 0) ent_sum = tot;
+        __syncthreads();
         return;
     }
     // ===================== compute warp =====================
@@ -234,64 +305,30 @@ __global__ void __launch_bounds__(64) vtrace_tma_kernel(const __grid_constant__ 
     carry.acc = 0.0f;
     carry.v_next = 0.0f;
     carry.vs_next = 0.0f;
-    double s_pg = 0.0, s_v = 0.0, s_en_d = 0.0;
-    float s_en = 0.0f;
+    double s_pg = 0.0, s_v = 0.0;
     float t_pg = 0.0f, t_v = 0.0f;
     // bootstrap of the NEXT group is fetched one group ahead so its latency is never exposed
     float boot_next = 0.0f;
     {
-        const long long r = (long long)blockIdx.x * kVtRows + lane;
-        if (r < p.rows) boot_next = __ldg(p.bootstrap + r);
+        const long long r = (long long)blockIdx.x * ROWS + lane;
+        if (lane < ROWS && r < p.rows) boot_next = __ldg(p.bootstrap + r);
     }
     int row0 = 0, rows_here = 0;
     bool row_ok = false;
-
-    // entropy: the CTA's [rows_here x T] block is a list of float4 slots (nq per row); lane l owns
-    // slots l, l+32, ... and fetches its next kEntSlots of them at the top of every iteration, so
-    // the loads fly while the warp waits for / works on the TMA tile and are summed afterwards
-    constexpr int kEntSlots = TS / 4;                      // 32*TS floats per iteration per array
-    const int nq = (p.T + 3) >> 2;
-    const int tail = p.T - 4 * (nq - 1);                   // valid floats in a row's last slot (1..4)
-    int ent_r = 0, ent_c = 0;                              // (row, slot) of this lane's next slot
+    const int lrow = lane & (ROWS - 1);                    // idle lanes (ROWS = 16) read a live row and never write
 
     int k = 0, g = 0;                                      // consumer-side cursor: tile k of group g
     for (long long q = 0; q < total_q; ++q) {
         const int s = int(q % NSTAGE);
         if (k == 0) {                                      // a new group of 32 rows starts
-            row0 = (int(blockIdx.x) + g * int(gridDim.x)) * kVtRows;
-            rows_here = int(min((long long)kVtRows, p.rows - row0));
+            row0 = (int(blockIdx.x) + g * int(gridDim.x)) * ROWS;
+            rows_here = int(min((long long)ROWS, p.rows - row0));
             row_ok = lane < rows_here;
             carry.acc = 0.0f;                              // utils.py:300
             carry.v_next = boot_next;                      // utils.py:296: V_T = bootstrap
             carry.vs_next = boot_next;                     // utils.py:313-314
-            const long long rn = (long long)(row0 + int(gridDim.x) * kVtRows) + lane;
-            boot_next = (g + 1 < my_groups && rn < p.rows) ? __ldg(p.bootstrap + rn) : 0.0f;
-            ent_r = 0;
-            ent_c = lane;
-            while (ent_c >= nq) { ent_c -= nq; ++ent_r; }
-            s_en_d += double(s_en);
-            s_en = 0.0f;
-        }
-        float4 ebuf[kEntSlots];
-#pragma unroll
-        for (int i = 0; i < kEntSlots; ++i) {
-            ebuf[i] = make_float4(0.f, 0.f, 0.f, 0.f);
-            if (ent_r < rows_here) {
-                const float* src = p.entropy + (long long)(row0 + ent_r) * p.in_stride + 4 * ent_c;
-                float4 v;
-                if (ent_c == nq - 1 && tail < 4) {         // never read past T in a row's last slot
-                    v = make_float4(__ldg(src), tail > 1 ? __ldg(src + 1) : 0.f, tail > 2 ? __ldg(src + 2) : 0.f, 0.f);
-                } else {
-                    // volatile asm: stays ahead of the mbarrier wait below (the compiler would otherwise
-                    // sink the load to its use after the tile and expose its latency there)
-                    asm volatile("ld.global.nc.v4.f32 {%0, %1, %2, %3}, [%4];"
-                                 : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w)
-                                 : "l"(src));
-                }
-                ebuf[i] = v;
-            }
-            ent_c += 32;
-            while (ent_c >= nq) { ent_c -= nq; ++ent_r; }
+            const long long rn = (long long)(row0 + int(gridDim.x) * ROWS) + lane;
+            boot_next = (g + 1 < my_groups && lane < ROWS && rn < p.rows) ? __ldg(p.bootstrap + rn) : 0.0f;
         }
         mbar_wait(&full[s], uint32_t((q / NSTAGE) & 1), nullptr);
 
@@ -310,7 +347,7 @@ __global__ void __launch_bounds__(64) vtrace_tma_kernel(const __grid_constant__ 
             // chunk j-1 are issued before chunk j is computed, so shared-memory latency and the next
             // chunk's exp() overlap the serial part of the recurrence
             auto load_dn = [&](int j) -> uint32_t {
-                if (DONE_TMA) return *reinterpret_cast<const uint32_t*>(q_dn + lane * TS + j * 4);
+                if (DONE_TMA) return *reinterpret_cast<const uint32_t*>(q_dn + lrow * TS + j * 4);
                 uint32_t d = 0;
                 const uint8_t* drow = p.done + (long long)(row0 + lane) * p.in_stride + t0 + 4 * j;
 #pragma unroll
@@ -321,7 +358,7 @@ __global__ void __launch_bounds__(64) vtrace_tma_kernel(const __grid_constant__ 
             float4 n_old, n_new, n_val, n_rew;
             uint32_t n_dn;
             {
-                const uint32_t off0 = Tile::off(lane, Tile::kChunks - 1);
+                const uint32_t off0 = Tile::off(lrow, Tile::kChunks - 1);
                 n_old = *reinterpret_cast<const float4*>(q_old + off0);
                 n_new = *reinterpret_cast<const float4*>(q_new + off0);
                 n_val = *reinterpret_cast<const float4*>(q_val + off0);
@@ -330,11 +367,11 @@ __global__ void __launch_bounds__(64) vtrace_tma_kernel(const __grid_constant__ 
             }
 #pragma unroll
             for (int j = Tile::kChunks - 1; j >= 0; --j) {
-                const uint32_t off = Tile::off(lane, j);
+                const uint32_t off = Tile::off(lrow, j);
                 const float4 a_old = n_old, a_new = n_new, a_val = n_val, a_rew = n_rew;
                 const uint32_t dn = n_dn;
                 if (j > 0) {
-                    const uint32_t offn = Tile::off(lane, j - 1);
+                    const uint32_t offn = Tile::off(lrow, j - 1);
                     n_old = *reinterpret_cast<const float4*>(q_old + offn);
                     n_new = *reinterpret_cast<const float4*>(q_new + offn);
                     n_val = *reinterpret_cast<const float4*>(q_val + offn);
@@ -362,15 +399,18 @@ __global__ void __launch_bounds__(64) vtrace_tma_kernel(const __grid_constant__ 
                     t_v = __fadd_rn(t_v, ok ? __fmul_rn(dvs, dvs) : 0.0f);
                 }
                 // in place: vs over rewards, adv over lp_old, d_logp over lp_new, d_values over values
-                *reinterpret_cast<float4*>(q_rew + off) = make_float4(o_vs[0], o_vs[1], o_vs[2], o_vs[3]);
-                *reinterpret_cast<float4*>(q_old + off) = make_float4(o_adv[0], o_adv[1], o_adv[2], o_adv[3]);
-                if (want_grads) {
+                if (ROWS == 32 || lane < ROWS) {
+                    *reinterpret_cast<float4*>(q_rew + off) = make_float4(o_vs[0], o_vs[1], o_vs[2], o_vs[3]);
+                    *reinterpret_cast<float4*>(q_old + off) = make_float4(o_adv[0], o_adv[1], o_adv[2], o_adv[3]);
+                }
+                if (want_grads && (ROWS == 32 || lane < ROWS)) {
                     *reinterpret_cast<float4*>(q_new + off) = make_float4(o_dlp[0], o_dlp[1], o_dlp[2], o_dlp[3]);
                     *reinterpret_cast<float4*>(q_val + off) = make_float4(o_dv[0], o_dv[1], o_dv[2], o_dv[3]);
                 }
             }
         };
-        if ((k == 0) || !row_ok)
+        if (p.debug & 1) {
+        } else if ((k == 0) || rows_here < 32)
             tile_body(std::true_type{});
         else
             tile_body(std::false_type{});
@@ -381,9 +421,6 @@ __global__ void __launch_bounds__(64) vtrace_tma_kernel(const __grid_constant__ 
             t_pg = 0.0f;
             t_v = 0.0f;
         }
-#pragma unroll
-        for (int i = 0; i < kEntSlots; ++i) s_en += (ebuf[i].x + ebuf[i].y) + (ebuf[i].z + ebuf[i].w);
-
         fence_proxy_async_smem();       // generic-proxy writes -> visible to the TMA store
         __syncwarp();
         if (lane == 0) mbar_arrive(&done[s]);
@@ -392,12 +429,12 @@ __global__ void __launch_bounds__(64) vtrace_tma_kernel(const __grid_constant__ 
 
     s_pg = warp_sum(s_pg);
     s_v = warp_sum(s_v);
-    const double s_en_w = warp_sum(s_en_d + double(s_en));
+    __syncthreads();                    // the TMA warp's entropy sum is in shared memory
     unsigned int tk = 0;
     if (lane == 0) {
         p.partials[size_t(blockIdx.x) * 3 + 0] = s_pg;
         p.partials[size_t(blockIdx.x) * 3 + 1] = s_v;
-        p.partials[size_t(blockIdx.x) * 3 + 2] = s_en_w;
+        p.partials[size_t(blockIdx.x) * 3 + 2] = ent_sum;
         __threadfence();
         tk = atomicAdd(p.ticket, 1u);
     }
@@ -579,10 +616,10 @@ static EncodeTiledFn get_encode_fn() {
 static int g_vt_l2_promo = 256;      // bytes: 0 (none), 64, 128, 256
 
 static bool encode_map_2d(EncodeTiledFn enc, CUtensorMap* m, const void* base, bool is_u8, long long rows, int T,
-                          long long stride_elems, int tile_steps) {
+                          long long stride_elems, int tile_steps, int box_rows) {
     const cuuint64_t gdim[2] = {cuuint64_t(T), cuuint64_t(rows)};
     const cuuint64_t gstride[1] = {cuuint64_t(stride_elems) * (is_u8 ? 1u : 4u)};
-    const cuuint32_t box[2] = {cuuint32_t(tile_steps), cuuint32_t(kVtRows)};
+    const cuuint32_t box[2] = {cuuint32_t(tile_steps), cuuint32_t(box_rows)};
     const cuuint32_t estr[2] = {1, 1};
     // 256-B L2 promotion: a row's next (earlier) time tile sits in the other half of the same
     // 256-B block, so one DRAM page activation serves two consecutive tiles of the walk
@@ -604,10 +641,10 @@ static bool encode_map_2d(EncodeTiledFn enc, CUtensorMap* m, const void* base, b
 struct MapKey {
     const void* base;
     long long rows, stride;
-    int T, is_u8, promo, ts;
+    int T, is_u8, promo, ts, box_rows;
     bool operator==(const MapKey& o) const {
         return base == o.base && rows == o.rows && stride == o.stride && T == o.T && is_u8 == o.is_u8 &&
-               promo == o.promo && ts == o.ts;
+               promo == o.promo && ts == o.ts && box_rows == o.box_rows;
     }
 };
 struct MapSlot {
@@ -619,24 +656,26 @@ static MapSlot g_map_cache[256];
 static std::mutex g_map_mutex;
 
 static bool make_map_2d(EncodeTiledFn enc, CUtensorMap* m, const void* base, bool is_u8, long long rows, int T,
-                        long long stride_elems, int tile_steps) {
-    const MapKey key{base, rows, stride_elems, T, is_u8 ? 1 : 0, g_vt_l2_promo, tile_steps};
+                        long long stride_elems, int tile_steps, int box_rows) {
+    const MapKey key{base, rows, stride_elems, T, is_u8 ? 1 : 0, g_vt_l2_promo, tile_steps, box_rows};
     size_t h = reinterpret_cast<uintptr_t>(base) >> 8;
     h ^= size_t(rows) * 0x9E3779B97F4A7C15ull ^ size_t(T) * 0xC2B2AE3D27D4EB4Full ^ size_t(stride_elems) << 17 ^
-         size_t(tile_steps) << 3;
+         size_t(tile_steps) << 3 ^ size_t(box_rows) << 9;
     MapSlot& slot = g_map_cache[(h ^ (h >> 29)) & 255];
     std::lock_guard<std::mutex> lock(g_map_mutex);
     if (slot.valid && slot.key == key) {
         *m = slot.map;
         return true;
     }
-    if (!encode_map_2d(enc, m, base, is_u8, rows, T, stride_elems, tile_steps)) return false;
+    if (!encode_map_2d(enc, m, base, is_u8, rows, T, stride_elems, tile_steps, box_rows)) return false;
     slot.key = key;
     slot.map = *m;
     slot.valid = true;
     return true;
 }
 
+static int g_vt_debug = 0;
+void vtrace_set_debug(int v) { g_vt_debug = v; }
 static int g_vt_force_generic = 0;
 static int g_vt_variant = -1;        // -1 = by grid size; see the switch in vtrace_loss_launch
 void vtrace_set_tuning(int force_generic, int variant, int l2_promo) {
@@ -653,37 +692,55 @@ size_t vtrace_workspace_bytes(long long rows) {
 
 static inline bool al16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; }
 
-template <int NSTAGE, int TS, bool DONE_TMA = true>
+template <int NSTAGE, int TS, bool DONE_TMA = true, int ROWS = kVtRows>
 static int launch_vt_tma(const VtMaps& maps, const VtParams& p, cudaStream_t stream) {
-    constexpr size_t smem = size_t(NSTAGE) * VtTile<TS>::kStage + 1024;
+    constexpr size_t smem = size_t(NSTAGE) * VtTile<TS, ROWS>::kStage + 1024;
     static bool attr_set[64] = {};
+    static int per_sm[64] = {};
     int dev = 0;
     MB_CUDA(cudaGetDevice(&dev));
-    if (dev < 64 && !attr_set[dev]) {
-        MB_CUDA(cudaFuncSetAttribute(vtrace_tma_kernel<NSTAGE, TS, DONE_TMA>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                     int(smem)));
+    if (dev < 0 || dev >= 64) {
+        set_error("vtrace_loss: device index %d not supported (0..63)", dev);
+        return MB_ERR_UNSUPPORTED;
+    }
+    if (!attr_set[dev]) {
+        MB_CUDA(cudaFuncSetAttribute(vtrace_tma_kernel<NSTAGE, TS, DONE_TMA, ROWS>,
+                                     cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));
+        int n = 0;
+        MB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, vtrace_tma_kernel<NSTAGE, TS, DONE_TMA, ROWS>, 64, smem));
+        per_sm[dev] = n > 0 ? n : 1;
         attr_set[dev] = true;
     }
-    static int per_sm[64] = {};
-    if (dev < 64 && per_sm[dev] == 0) {
-        int n = 0;
-        MB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, vtrace_tma_kernel<NSTAGE, TS, DONE_TMA>, 64, smem));
-        per_sm[dev] = n > 0 ? n : 1;
-    }
-    const long long groups = (p.rows + kVtRows - 1) / kVtRows;
-    const long long resident = (long long)sm_count(dev) * (dev < 64 ? per_sm[dev] : 1);
-    const unsigned grid = unsigned(groups < resident ? groups : resident);
-    vtrace_tma_kernel<NSTAGE, TS, DONE_TMA><<<grid, 64, smem, stream>>>(maps, p);
+    const long long groups = (p.rows + ROWS - 1) / ROWS;
+    const long long resident = (long long)sm_count(dev) * per_sm[dev];
+    // one partial-sum slot per CTA: the workspace holds ceil(rows / 32) + 1 of them
+    const long long slots = (p.rows + kVtRows - 1) / kVtRows + 1;
+    long long grid = groups < resident ? groups : resident;
+    if (grid > slots) grid = slots;
+    vtrace_tma_kernel<NSTAGE, TS, DONE_TMA, ROWS><<<unsigned(grid), 64, smem, stream>>>(maps, p);
     MB_CUDA(cudaGetLastError());
     return MB_OK;
 }
 
-// pipeline shapes (stages x steps per tile) selectable with mb_set_tuning("vtrace_variant", v)
-static const int kVtVariantSteps[8] = {32, 32, 32, 16, 16, 16, 16, 16};
+// Default pipeline shape by problem size (measured on B200, profiles/r02_sweep_vtrace_variants.jsonl).
+static int vt_default_variant(long long rows, int T) {
+    if (T <= 128) return 4;                                  // short rows: 4 stages x 16 steps, 6 CTAs per SM
+    // long rows: 6 stages x 32 steps (2 CTAs per SM) when there are several waves of groups or less than one;
+    // in between (about one wave) 3 x 32 keeps 4 CTAs per SM and every group resident at once
+    return (rows >= 32768 || rows <= 8192) ? 8 : 1;
+}
+
+// pipeline shapes selectable with mb_set_tuning("vtrace_variant", v): stages, steps per tile, rows per group
+struct VtShape { int stages, ts, rows; };
+static const VtShape kVtShapes[16] = {{2, 32, 32}, {3, 32, 32}, {4, 32, 32}, {3, 16, 32}, {4, 16, 32}, {5, 16, 32},
+                                      {6, 16, 32}, {8, 16, 32}, {6, 32, 32}, {12, 16, 32}, {8, 32, 32}, {4, 32, 16},
+                                      {6, 32, 16}, {8, 32, 16}, {8, 16, 16}, {6, 16, 16}};
 
 // `scratch` holds the ticket word at offset 0 (must be zero on entry; the kernel leaves it zero)
 // and the per-CTA partial sums from offset 256.
-int vtrace_loss_launch(VtParams p, void* scratch, size_t scratch_bytes, cudaStream_t stream) {
+// `clear_header`: zero the header on `stream` once the arguments have passed validation (callers whose scratch
+// is not known to start at zero).
+int vtrace_loss_launch(VtParams p, void* scratch, size_t scratch_bytes, cudaStream_t stream, bool clear_header = false) {
     if (p.rows < 0 || p.T <= 0) {
         set_error("vtrace_loss: rows=%lld T=%d out of range", p.rows, p.T);
         return MB_ERR_INVALID;
@@ -714,9 +771,11 @@ int vtrace_loss_launch(VtParams p, void* scratch, size_t scratch_bytes, cudaStre
                   vtrace_workspace_bytes(p.rows));
         return MB_ERR_INVALID;
     }
+    if (clear_header) MB_CUDA(cudaMemsetAsync(scratch, 0, 256, stream));
     p.ticket = reinterpret_cast<unsigned int*>(scratch);
     p.partials = reinterpret_cast<double*>(reinterpret_cast<uint8_t*>(scratch) + 256);
     if (p.inv_n <= 0.0f) p.inv_n = float(1.0 / (double(p.rows) * double(p.T)));
+    p.debug = g_vt_debug;
 
     EncodeTiledFn enc = get_encode_fn();
     bool tma_ok = enc && !g_vt_force_generic && (p.in_stride % 4 == 0) && (p.out_stride % 4 == 0) &&
@@ -724,23 +783,23 @@ int vtrace_loss_launch(VtParams p, void* scratch, size_t scratch_bytes, cudaStre
                   al16(p.vs) && al16(p.adv) && (!p.dlp || (al16(p.dlp) && al16(p.dv)));
     const bool done_tma = (p.in_stride % 16 == 0) && al16(p.done);
     if (tma_ok) {
-        // Few CTAs (latency bound) -> deep prefetch; many CTAs (bandwidth bound) -> more CTAs per SM.
         int v = g_vt_variant;
-        // measured on B200 (profiles/): 4 stages x 32 steps for long rows, 4 x 16 when a row has few tiles
-        if (v < 0 || v > 7) v = (p.T <= 128) ? 4 : 2;
-        const int ts = kVtVariantSteps[v];
+        if (v < 0 || v > 15) v = vt_default_variant(p.rows, p.T);
+        if (!done_tma) v = (kVtShapes[v].ts == 16) ? 4 : 2;      // the direct-`done` kernel exists in two shapes
+        const VtShape sh = kVtShapes[v];
+        const int ts = sh.ts, br = sh.rows;
         VtMaps maps;
         memset(&maps, 0, sizeof(maps));
-        bool ok = make_map_2d(enc, &maps.lp_old, p.lp_old, false, p.rows, p.T, p.in_stride, ts) &&
-                  make_map_2d(enc, &maps.lp_new, p.lp_new, false, p.rows, p.T, p.in_stride, ts) &&
-                  make_map_2d(enc, &maps.values, p.values, false, p.rows, p.T, p.in_stride, ts) &&
-                  make_map_2d(enc, &maps.rewards, p.rewards, false, p.rows, p.T, p.in_stride, ts) &&
-                  (!done_tma || make_map_2d(enc, &maps.done, p.done, true, p.rows, p.T, p.in_stride, ts)) &&
-                  make_map_2d(enc, &maps.vs, p.vs, false, p.rows, p.T, p.out_stride, ts) &&
-                  make_map_2d(enc, &maps.adv, p.adv, false, p.rows, p.T, p.out_stride, ts);
+        bool ok = make_map_2d(enc, &maps.lp_old, p.lp_old, false, p.rows, p.T, p.in_stride, ts, br) &&
+                  make_map_2d(enc, &maps.lp_new, p.lp_new, false, p.rows, p.T, p.in_stride, ts, br) &&
+                  make_map_2d(enc, &maps.values, p.values, false, p.rows, p.T, p.in_stride, ts, br) &&
+                  make_map_2d(enc, &maps.rewards, p.rewards, false, p.rows, p.T, p.in_stride, ts, br) &&
+                  (!done_tma || make_map_2d(enc, &maps.done, p.done, true, p.rows, p.T, p.in_stride, ts, br)) &&
+                  make_map_2d(enc, &maps.vs, p.vs, false, p.rows, p.T, p.out_stride, ts, br) &&
+                  make_map_2d(enc, &maps.adv, p.adv, false, p.rows, p.T, p.out_stride, ts, br);
         if (ok && p.dlp)
-            ok = make_map_2d(enc, &maps.dlp, p.dlp, false, p.rows, p.T, p.out_stride, ts) &&
-                 make_map_2d(enc, &maps.dv, p.dv, false, p.rows, p.T, p.out_stride, ts);
+            ok = make_map_2d(enc, &maps.dlp, p.dlp, false, p.rows, p.T, p.out_stride, ts, br) &&
+                 make_map_2d(enc, &maps.dv, p.dv, false, p.rows, p.T, p.out_stride, ts, br);
         if (ok && !done_tma) {
             if (ts == 16) return launch_vt_tma<4, 16, false>(maps, p, stream);
             return launch_vt_tma<4, 32, false>(maps, p, stream);
@@ -748,13 +807,21 @@ int vtrace_loss_launch(VtParams p, void* scratch, size_t scratch_bytes, cudaStre
         if (ok) {
             switch (v) {
                 case 0: return launch_vt_tma<2, 32>(maps, p, stream);
+                case 1: return launch_vt_tma<3, 32>(maps, p, stream);
                 case 2: return launch_vt_tma<4, 32>(maps, p, stream);
                 case 3: return launch_vt_tma<3, 16>(maps, p, stream);
                 case 4: return launch_vt_tma<4, 16>(maps, p, stream);
                 case 5: return launch_vt_tma<5, 16>(maps, p, stream);
                 case 6: return launch_vt_tma<6, 16>(maps, p, stream);
                 case 7: return launch_vt_tma<8, 16>(maps, p, stream);
-                default: return launch_vt_tma<3, 32>(maps, p, stream);
+                case 8: return launch_vt_tma<6, 32>(maps, p, stream);
+                case 9: return launch_vt_tma<12, 16>(maps, p, stream);
+                case 10: return launch_vt_tma<8, 32>(maps, p, stream);
+                case 11: return launch_vt_tma<4, 32, true, 16>(maps, p, stream);
+                case 12: return launch_vt_tma<6, 32, true, 16>(maps, p, stream);
+                case 13: return launch_vt_tma<8, 32, true, 16>(maps, p, stream);
+                case 14: return launch_vt_tma<8, 16, true, 16>(maps, p, stream);
+                default: return launch_vt_tma<6, 16, true, 16>(maps, p, stream);
             }
         }
         // tensor-map encoding refused the shape: fall through to the generic kernel
@@ -814,7 +881,9 @@ constexpr size_t kVtStaticScratchBytes = 64 * 1024;
 
 static __device__ __align__(256) unsigned char g_vt_static_scratch[kVtStaticScratchBytes];
 
-static int vt_static_scratch(void** out) {
+static int g_vt_static_poison = 0;    // test hook, see mb_set_tuning("vtrace_static_poison")
+
+static int vt_static_scratch(void** out, cudaStream_t stream) {
     static std::mutex mu;
     static void* ptrs[64] = {};
     int dev = -1;
@@ -825,6 +894,15 @@ static int vt_static_scratch(void** out) {
     }
     std::lock_guard<std::mutex> lock(mu);
     if (!ptrs[dev]) {
+        // The look-up may load the module lazily, which is not allowed while a stream is being captured:
+        // refuse with a clear message instead of letting the runtime invalidate the caller's capture.
+        cudaStreamCaptureStatus cap = cudaStreamCaptureStatusNone;
+        MB_CUDA(cudaStreamIsCapturing(stream, &cap));
+        if (cap != cudaStreamCaptureStatusNone) {
+            set_error("mb_vtrace_loss_static: the first call on a device looks up the scratch array's address and "
+                      "must be made outside stream capture (device %d has not been set up yet)", dev);
+            return MB_ERR_INVALID;
+        }
         void* p = nullptr;
         MB_CUDA(cudaGetSymbolAddress(&p, g_vt_static_scratch));      // device address on the CURRENT device
         ptrs[dev] = p;
@@ -832,6 +910,8 @@ static int vt_static_scratch(void** out) {
     *out = ptrs[dev];
     return MB_OK;
 }
+
+void vtrace_static_poison(int on) { g_vt_static_poison = on; }
 
 }  // namespace mb
 
@@ -850,9 +930,12 @@ extern "C" int mb_vtrace_loss_static(const float* lp_old, const float* lp_new, c
     static_assert(mb::kVtStaticScratchBytes >= 256 + (mb::kVtStaticMaxRows / mb::kVtRows + 1) * 3 * sizeof(double),
                   "static scratch too small for the advertised row limit");
     void* scratch = nullptr;
-    if (int rc = mb::vt_static_scratch(&scratch)) return rc;
     cudaStream_t st = static_cast<cudaStream_t>(stream);
-    if (rows > 0) MB_CUDA(cudaMemsetAsync(scratch, 0, 256, st));      // ticket word (and its padding) start at zero
+    if (int rc = mb::vt_static_scratch(&scratch, st)) return rc;
+    if (mb::g_vt_static_poison) {       // test hook: leave the array as dirty as a previous user could have
+        mb::g_vt_static_poison = 0;
+        MB_CUDA(cudaMemsetAsync(scratch, 0xA5, mb::kVtStaticScratchBytes, st));
+    }
     mb::VtParams p;
     memset(&p, 0, sizeof(p));
     p.lp_old = lp_old; p.lp_new = lp_new; p.values = values; p.rewards = rewards; p.entropy = entropy;
@@ -860,7 +943,9 @@ extern "C" int mb_vtrace_loss_static(const float* lp_old, const float* lp_new, c
     p.loss4 = loss4_out; p.rows = rows; p.T = T; p.in_stride = in_row_stride; p.out_stride = out_row_stride;
     p.gamma = gamma; p.rho_bar = rho_bar; p.c_bar = c_bar; p.pg_rho_bar = pg_rho_bar; p.ent_coef = ent_coef;
     p.inv_n = inv_n;
-    return mb::vtrace_loss_launch(p, scratch, mb::kVtStaticScratchBytes, st);
+    // the header (ticket word and its padding) must start at zero: cleared on `stream`, after the arguments
+    // have been validated, right before the launch
+    return mb::vtrace_loss_launch(p, scratch, mb::kVtStaticScratchBytes, st, /*clear_header=*/true);
 }
 
 

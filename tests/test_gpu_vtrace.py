@@ -81,7 +81,7 @@ def test_vs_oracle_shapes(rows, T):
     assert torch.equal(out["loss4"], out3["loss4"]) and torch.equal(out["vs"], out3["vs"])
 
 
-@pytest.mark.parametrize("variant", [0, 1, 2, 3, 4, 5, 6, 7])
+@pytest.mark.parametrize("variant", list(range(16)))
 def test_pipeline_shapes_agree(variant):
     """Every stages x steps-per-tile shape of the TMA kernel gives the same targets, bit for bit."""
     mb, ops, synth, _ = _mods()
@@ -104,6 +104,37 @@ def test_pipeline_shapes_agree(variant):
         mb.set_tuning("vtrace_l2_promo", 256)
     for k in ("vs", "pg_advantages", "d_logp", "d_values", "loss4"):
         assert torch.equal(base[k], out[k]), k
+
+
+@pytest.mark.parametrize("variant", range(0, 16))
+@pytest.mark.parametrize("rows,T", [(300, 160), (33, 80), (70, 112), (1000, 48), (17, 512), (5000, 96), (40, 16)])
+def test_request_order_of_every_pipeline_shape(variant, rows, T):
+    """Tiles are requested in ascending blocks of 256 B per row while they are consumed backwards in time; every
+    stages x steps shape (block lengths 1, 2, 4; rows shorter than a block; tile counts that are not a multiple of the
+    block; more groups than resident CTAs) must still give the generic kernel's bits and the oracle's values."""
+    mb, ops, synth, ovt = _mods()
+    g = torch.Generator().manual_seed(rows * 977 + T)
+    t = synth.make_vtrace_inputs(rows, T, gen=g)
+    t["done"] = torch.rand((rows, T), generator=g) < 0.05
+    mb.set_tuning("vtrace_force_generic", 1)
+    try:
+        base = _run(ops, t)
+    finally:
+        mb.set_tuning("vtrace_force_generic", 0)
+    mb.set_tuning("vtrace_variant", variant)
+    try:
+        out = _run(ops, t)
+        again = _run(ops, t)
+    finally:
+        mb.set_tuning("vtrace_variant", -1)
+    for k in ("vs", "pg_advantages", "d_logp", "d_values"):
+        assert torch.equal(base[k], out[k]), k
+        assert torch.equal(again[k], out[k]), k
+    assert torch.equal(again["loss4"], out["loss4"])
+    ref = ovt.vtrace_losses_and_grads(t["lp_old"], t["lp_new"], t["values"], t["bootstrap"], t["rewards"],
+                                      t["done"], t["entropy"])
+    ref["lp_new_in"] = t["lp_new"]
+    _compare(out, ref)
 
 
 def test_persistent_groups_more_rows_than_resident_ctas():
