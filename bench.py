@@ -61,6 +61,8 @@ def parse_args():
     ap.add_argument("--cpu-rows", type=int, default=32, help="rows of the CPU-baseline sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-parity", action="store_true", help="skip the parity gate that runs before any timing")
+    ap.add_argument("--parity-rows", type=int, default=32, help="rows of the parity-gate sample")
     ap.add_argument("--no-graph-info", action="store_true")
     ap.add_argument("--sparse-head", action="store_true",
                     help="headline with Agent.sparse_head (actor logits only for cells with a valid action)")
@@ -269,6 +271,66 @@ def emit(line, args):
 
 
 # ------------------------------------------------------------------------------------------
+# parity gate: runs BEFORE any timing
+# ------------------------------------------------------------------------------------------
+PARITY_FLOOR, PARITY_SLACK, PARITY_GRAD_CAP = 1e-5, 4.0, 5e-2
+
+
+def parity_gate(model, h, w, T, rows, preset, timed_rows):
+    """One lr = 0 learner step on a `rows`-row sample of the benchmarked workload, on the GPU (the product, same weights,
+    same code path as the timed step) and on the CPU through the oracle's fp32 restatement of the reference and
+    through a float64 evaluation (oracle/parity.py).  Returns the `parity` object of the JSON line: errors of
+    log-prob, entropy, baseline, V-trace targets, advantages, the four losses and the parameter gradients, GPU and
+    CPU-fp32 each against float64, and GPU against CPU-fp32.  pass = the GPU is within 1e-5 of float64, or at most
+    PARITY_SLACK times as far from it as the reference's own fp32 arithmetic is (gradients capped at 5e-2)."""
+    import torch
+    from microbeast_b200.learner import LEARNER_KEYS, learner_losses
+    from microbeast_b200 import synth
+    from oracle import NVEC_CELL, parity
+    from oracle.learner import RefAgent
+    t_start = time.perf_counter()
+    cells = h * w
+    ref = RefAgent((h, w, 27), list(NVEC_CELL) * cells, cells)
+    ref.load_state_dict({k: v.detach().cpu() for k, v in model.state_dict().items()})
+    batch = synth.make_rollout_batch(h, w, T, rows, seed=4321, preset=preset)
+    with torch.no_grad():
+        o, _ = ref.get_action(batch, learning=True)
+    batch["logprobs"] = o["logprobs"] + 0.3 * torch.randn(o["logprobs"].shape, generator=torch.Generator().manual_seed(9))
+    dev = next(model.parameters()).device
+    dev_batch = {k: batch[k].to(dev) for k in LEARNER_KEYS}
+    keep = model.sparse_backward
+    # the timed step takes the cell-list backward when it has >= 2^20 (frame, cell) pairs: the gate must too
+    if keep == "auto" and timed_rows * (T + 1) * cells >= (1 << 20):
+        model.sparse_backward = True
+    try:
+        model.zero_grad(set_to_none=True)
+        loss4, aux = learner_losses(model, dev_batch, rows, T)
+        loss4[3].backward()
+        torch.cuda.synchronize()
+    finally:
+        model.sparse_backward = keep
+    ours = dict(logprobs=aux["logprobs"].detach().flatten(), entropy=aux["entropy"].detach().flatten(),
+                baseline=aux["baseline"].detach().flatten(), vs=aux["vs"].detach(),
+                pg_advantages=aux["pg_advantages"].detach(), loss4=loss4.detach(),
+                grads={n: p.grad.detach().clone() for n, p in model.named_parameters()})
+    model.zero_grad(set_to_none=True)
+    rep = parity.step_report(ours, ref, batch, rows, T)
+    ok = True
+    for key in ("logprobs", "entropy", "baseline", "vs", "pg_advantages"):
+        ok &= rep["gpu_vs_fp64"][key] <= max(PARITY_FLOOR, PARITY_SLACK * rep["cpu_fp32_vs_fp64"][key])
+    for i in range(4):
+        ok &= rep["gpu_vs_fp64"]["loss4_rel"][i] <= max(PARITY_FLOOR, PARITY_SLACK * rep["cpu_fp32_vs_fp64"]["loss4_rel"][i])
+    ok &= rep["gpu_vs_fp64"]["grad_max"] <= min(PARITY_GRAD_CAP,
+                                                max(PARITY_FLOOR, PARITY_SLACK * rep["cpu_fp32_vs_fp64"]["grad_max"]))
+    rep["pass"] = bool(ok)
+    rep["rule"] = (f"gpu_vs_fp64 <= max({PARITY_FLOOR:g}, {PARITY_SLACK:g} x cpu_fp32_vs_fp64) for every value and loss; "
+                   f"gradients additionally <= {PARITY_GRAD_CAP:g}")
+    rep["sample"] = f"{rows} rows ({rows * (T + 1)} frames) of the benchmarked workload, lr = 0, same weights on both sides"
+    rep["seconds"] = round(time.perf_counter() - t_start, 1)
+    return rep
+
+
+# ------------------------------------------------------------------------------------------
 # our arm
 # ------------------------------------------------------------------------------------------
 def run_ours(args):
@@ -316,6 +378,15 @@ def run_ours(args):
         # expanded to NCHW fp32 by mb_unpack_obs inside the step
         shifts = torch.arange(27, device=dev, dtype=torch.int32)
         dev_batch["obs"] = (batch["obs"].to(torch.int32) << shifts).sum(-1, dtype=torch.int32)
+
+    # ---- parity gate: nothing is timed (and no number is printed) unless the step agrees with the oracle -------
+    parity = None
+    if not args.no_parity and rank == 0:
+        parity = parity_gate(model, h, w, T, args.parity_rows, args.preset, rows)
+        if not parity["pass"]:
+            emit({"metric": METRIC, "value": None, "unit": UNIT, "error": "parity gate failed: no timing reported",
+                  "parity": parity, "config": workload_config(args)}, args)
+            raise SystemExit(3)
 
     def step(b, sync):
         return PPO_learn(model, model, "bench", b, opt, rows, T, 1, reducer=reducer, sync=sync)
@@ -487,6 +558,7 @@ def run_ours(args):
             "scaling": "strong" if args.workload == "c3" else "weak",
             "vs_baseline": None, "dtype": "f32", "data": "synthetic", "config": workload_config(args),
             "clocks": clocks, "e2e": e2e, "gpu_launches": launches, "roofline": roof, "cpu_baseline": cpu,
+            "parity": parity,
             "kernels": kernels, "info": info,
         }
         emit(line, args)
