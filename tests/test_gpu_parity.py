@@ -34,13 +34,15 @@ def _fp32_exact():
     torch.backends.cudnn.allow_tf32, torch.backends.cuda.matmul.allow_tf32 = old
 
 
-def _pair(h, w, seed, actor_std=0.05):
+def _pair(h, w, seed, actor_std=0.05, torch_init=False):
     from microbeast_b200.model import Agent
     from oracle import NVEC_CELL
     from oracle.learner import RefAgent
     nvec = list(NVEC_CELL) * (h * w)
+    torch.manual_seed(seed)
     ref = RefAgent((h, w, 27), nvec, h * w)
-    ref.load_state_dict(golden_agent_weights(ref.state_dict(), seed))
+    if not torch_init:
+        ref.load_state_dict(golden_agent_weights(ref.state_dict(), seed))
     with torch.no_grad():
         ref.actor.weight.normal_(0, actor_std, generator=torch.Generator().manual_seed(seed))
     mine = Agent((h, w, 27), nvec, h * w).cuda()
@@ -102,11 +104,21 @@ def test_config1_at_its_real_32_rows():
 
 
 def test_benchmarked_geometry_16x16():
-    """BASELINE configs[1] geometry (16x16, T=80) on 8 rows (648 frames, 1 792 categoricals per frame)."""
+    """BASELINE configs[1] geometry (16x16, T=80) on 8 rows (648 frames, 1 792 categoricals per frame), weights as the
+    benchmark initialises them (torch's default init, actor N(0, 0.01^2)).
+
+    Gradients of a network with max-pooling are only piecewise continuous: with the N(0, 0.15^2) weights of the golden
+    fixtures this very case has ONE of its 82 944 third-stage pooling windows whose two largest entries differ by
+    4.7e-7 relative in float64; the product's forward convolutions (1.3e-6 from float64, cuDNN: 3.5e-6) round them
+    the other way, the gradient takes the other branch, and ``network.2.conv.weight`` moves by 0.18 of its rms while
+    every value stays within 2e-5 (measured with each convolution checked against float64 in place: all of them
+    within 1e-6).  cuDNN flips 525 exactly tied first-stage windows instead.  Neither is an arithmetic error, which
+    is why the gradient criterion is relative to the reference's own distance from float64 and capped, and why this
+    test uses the benchmark's well-conditioned weights."""
     from oracle import parity
     h = w = 16
     T, rows = 80, 8
-    mine, ref = _pair(h, w, seed=43, actor_std=0.01)
+    mine, ref = _pair(h, w, seed=43, actor_std=0.01, torch_init=True)
     batch = _batch(ref, h, w, T, rows, seed=77)
     _check(parity.step_report(gpu_step(mine, batch, rows, T), ref, batch, rows, T), "c2 geometry 16x16 T=80 8 rows")
 
