@@ -208,6 +208,30 @@ MB_API int mb_linear_tf32x3(const float* a_hi, const float* a_lo, const float* b
                             const float* bias, float* c, int64_t m, int64_t n, int32_t k, int32_t* status,
                             void* stream);
 
+/* Actor Linear + policy head in one tensor-core kernel (reference model.py:167 followed by model.py:168-214; the
+ * learner, libs/utils.py:237-329, reads only the per-frame log-prob / entropy sums, so the [n_frames, 78*cells] logits
+ * need not exist in memory).  Three steps:
+ *   mb_pack_cells         mask [n_frames, 78*cells] u8 + action [n_frames, 7*cells] i64 -> cell_meta [cells][n_frames]
+ *                         records of 16 B (78 mask bits, seven 6-bit action indices); out-of-range actions are clamped
+ *                         and flagged in `status` (torch validate_args raises there, model.py:38).
+ *   mb_pack_actor_weight  weight [78*cells, k], bias [78*cells] -> TF32 hi / lo copies w_hi, w_lo [80*cells, k] with
+ *                         every cell's 78 rows padded to 80, bias_p [80*cells].  Once per weight update.
+ *   mb_actor_head_fwd     a_hi, a_lo [n_frames, k] = the TF32 hi / lo parts of `hidden` (mb_split_tf32); three TF32
+ *                         products accumulated in fp32 on tcgen05 (as mb_linear_tf32x3), the epilogue adds the bias and
+ *                         evaluates the head of each (frame, cell) from tensor memory:
+ *                         cell_out [cells][n_frames][2] f32 = (log-prob, entropy) of the cell's seven components;
+ *                         logp_out / ent_out [n_frames] (both or neither) = their sums in cell order;
+ *                         logits_out [n_frames, 78*cells] or NULL = policy_logits (model.py:208) on request.
+ * k % 32 == 0; every pointer 16-byte aligned. */
+MB_API int mb_pack_cells(const uint8_t* mask, const int64_t* action, void* cell_meta, int64_t n_frames, int32_t cells,
+                         int32_t* status, void* stream);
+MB_API int mb_pack_actor_weight(const float* weight, const float* bias, float* w_hi, float* w_lo, float* bias_p,
+                                int32_t cells, int32_t k, void* stream);
+MB_API int mb_actor_head_fwd(const float* a_hi, const float* a_lo, const float* w_hi, const float* w_lo,
+                             const float* bias_p, const void* cell_meta, float* cell_out, float* logits_out,
+                             float* logp_out, float* ent_out, int64_t n_frames, int32_t cells, int32_t k,
+                             int32_t* status, void* stream);
+
 /* Backward of max_pool2d(kernel 3, stride 2, padding 1) (reference model.py:96) from the argmax
  * indices of the forward: dy, idx [planes, (h+1)/2, (w+1)/2] (idx = flat position in the h*w input
  * plane, as torch.nn.functional.max_pool2d(..., return_indices=True) returns it), dx [planes, h, w]. */

@@ -23,6 +23,7 @@
 //                     thread 128 columns of one output row), sum them in registers, release the
 //                     accumulators, then add the bias and store while warp 1 already runs the next tile.
 #include "common.cuh"
+#include "tc.cuh"
 
 #include <cuda.h>
 
@@ -47,66 +48,6 @@ constexpr uint32_t kTmemCols = 512;                  // 256 columns for the hi*h
 struct GemmMaps {
     CUtensorMap a_hi, a_lo, b_hi, b_lo;
 };
-
-// ---- tcgen05 wrappers -------------------------------------------------------------------------
-__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
-__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
-
-__device__ __forceinline__ void tmem_alloc(uint32_t* slot_smem, uint32_t cols) {       // whole warp
-    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(slot_smem)), "r"(cols)
-                 : "memory");
-    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
-}
-__device__ __forceinline__ void tmem_dealloc(uint32_t addr, uint32_t cols) {           // whole warp
-    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(addr), "r"(cols) : "memory");
-}
-__device__ __forceinline__ void tc_commit(uint64_t* bar) {                             // one thread
-    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar))
-                 : "memory");
-}
-// D[tmem] (+)= A[smem] * B[smem]^T, TF32 inputs, fp32 accumulate; one thread issues for the CTA
-__device__ __forceinline__ void mma_tf32(uint32_t d_tmem, uint64_t desc_a, uint64_t desc_b, uint32_t idesc,
-                                         uint32_t accumulate) {
-    asm volatile(
-        "{\n\t"
-        ".reg .pred p;\n\t"
-        "setp.ne.b32 p, %4, 0;\n\t"
-        "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, {%5, %6, %7, %8}, p;\n\t"
-        "}\n" ::"r"(d_tmem),
-        "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accumulate), "r"(0), "r"(0), "r"(0), "r"(0)
-        : "memory");
-}
-// 32 lanes x 32 columns of fp32: thread i of the warp gets lane (base lane + i), columns col .. col+31
-__device__ __forceinline__ void tmem_ld32(uint32_t taddr, float (&v)[32]) {
-    uint32_t r[32];
-    asm volatile(
-        "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
-        "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
-        "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
-        : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
-          "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]), "=r"(r[16]),
-          "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]), "=r"(r[24]),
-          "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
-        : "r"(taddr)
-        : "memory");
-    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
-#pragma unroll
-    for (int i = 0; i < 32; ++i) v[i] = __uint_as_float(r[i]);
-}
-
-// Shared-memory matrix descriptor of a K-major operand tile staged by TMA with 128-byte swizzle: rows of
-// 32 fp32 (128 B), 8-row groups 1024 B apart.  Bits: [0,14) start address >> 4; [16,30) leading byte offset
-// >> 4 (unused for swizzled K-major, 1); [32,46) stride byte offset >> 4 (1024 B between 8-row groups);
-// [46,48) descriptor version 1 (sm_100); [61,64) layout type 2 = SWIZZLE_128B.
-__device__ __forceinline__ uint64_t make_kmajor_sw128_desc(uint32_t smem_addr) {
-    uint64_t d = 0;
-    d |= uint64_t((smem_addr & 0x3ffffu) >> 4);
-    d |= uint64_t(1) << 16;
-    d |= uint64_t(1024 >> 4) << 32;
-    d |= uint64_t(1) << 46;
-    d |= uint64_t(2) << 61;
-    return d;
-}
 
 // Instruction descriptor of tcgen05.mma.kind::tf32: [4,6) D format 1 = F32; [7,10) A format 2 = TF32;
 // [10,13) B format 2 = TF32; bits 15 / 16 = 0: A and B are K-major; [17,23) N >> 3; [24,29) M >> 4.

@@ -357,6 +357,64 @@ def linear_tf32x3(x: torch.Tensor, weight: torch.Tensor, bias: Optional[torch.Te
     return out
 
 
+def pack_cells(action_mask: torch.Tensor, action: torch.Tensor, cells: int) -> torch.Tensor:
+    """``cell_meta [cells, N, 4]`` int32: one 16-byte record per (cell, frame) -- 78 mask bits and the seven action
+    indices as 6-bit fields -- the operand form of the fused actor-head kernels (``mb_pack_cells``)."""
+    dev = _need_cuda(action_mask=action_mask, action=action)
+    action_mask = _mask_u8(action_mask)
+    action = _as(action, torch.int64, "action")
+    n = action_mask.shape[0]
+    if tuple(action_mask.shape) != (n, cells * LOGITS_PER_CELL) or tuple(action.shape) != (n, cells * COMPONENTS_PER_CELL):
+        raise ValueError("pack_cells: action_mask must be [N, 78*cells] and action [N, 7*cells]")
+    meta = torch.empty((cells, n, 4), dtype=torch.int32, device=dev)
+    with torch.cuda.device(dev), _Launch("pack_cells", note={"cells": n * cells}):
+        _check(lib.mb_pack_cells(_ptr(action_mask), _ptr(action), _ptr(meta), n, cells, _ptr(status_word(dev)), _stream()))
+    return meta
+
+
+def pack_actor_weight(weight: torch.Tensor, bias: Optional[torch.Tensor], cells: int):
+    """``(w_hi, w_lo [80*cells, K], bias_p [80*cells])``: the actor Linear's weight as TF32 hi / lo parts with each
+    cell's 78 rows padded to 80 (``mb_pack_actor_weight``)."""
+    dev = _need_cuda(weight=weight, bias=bias)
+    weight = _as(weight, torch.float32, "weight")
+    if weight.dim() != 2 or weight.shape[0] != cells * LOGITS_PER_CELL:
+        raise ValueError("pack_actor_weight: weight must be [78*cells, K]")
+    k = weight.shape[1]
+    if bias is not None:
+        bias = _as(bias, torch.float32, "bias")
+    w_hi = torch.empty((cells * 80, k), dtype=torch.float32, device=dev)
+    w_lo = torch.empty_like(w_hi)
+    bias_p = torch.empty(cells * 80, dtype=torch.float32, device=dev)
+    with torch.cuda.device(dev), _Launch("pack_actor_weight"):
+        _check(lib.mb_pack_actor_weight(_ptr(weight), _ptr(bias), _ptr(w_hi), _ptr(w_lo), _ptr(bias_p), cells, k, _stream()))
+    return w_hi, w_lo, bias_p
+
+
+def actor_head_fwd(hidden: torch.Tensor, packed_weight, cell_meta: torch.Tensor, want_logits: bool = False):
+    """Actor Linear + policy head in one tcgen05 kernel (``mb_actor_head_fwd``, reference ``model.py:167-214``).
+
+    ``hidden [N, K]`` fp32, ``packed_weight`` from :func:`pack_actor_weight`, ``cell_meta`` from :func:`pack_cells`.
+    Returns ``(logprobs [N], entropy [N], cell_out [cells, N, 2], policy_logits [N, 78*cells] or None)``; ``None`` when
+    the shape is not covered (``K % 32``)."""
+    dev = _need_cuda(hidden=hidden, cell_meta=cell_meta)
+    w_hi, w_lo, bias_p = packed_weight
+    hidden = _as(hidden, torch.float32, "hidden")
+    n, k = hidden.shape
+    cells = cell_meta.shape[0]
+    if k % 32 or w_hi.shape != (cells * 80, k) or tuple(cell_meta.shape) != (cells, n, 4) or n == 0:
+        return None
+    a_hi, a_lo = split_tf32(hidden)
+    cell_out = torch.empty((cells, n, 2), dtype=torch.float32, device=dev)
+    logp = torch.empty(n, dtype=torch.float32, device=dev)
+    ent = torch.empty(n, dtype=torch.float32, device=dev)
+    logits = torch.empty((n, cells * LOGITS_PER_CELL), dtype=torch.float32, device=dev) if want_logits else None
+    with torch.cuda.device(dev), _Launch("actor_head_fwd", note={"m": n, "cells": cells, "k": k, "logits": bool(want_logits)}):
+        _check(lib.mb_actor_head_fwd(_ptr(a_hi), _ptr(a_lo), _ptr(w_hi), _ptr(w_lo), _ptr(bias_p), _ptr(cell_meta),
+                                     _ptr(cell_out), _ptr(logits), _ptr(logp), _ptr(ent), n, cells, k,
+                                     _ptr(status_word(dev)), _stream()))
+    return logp, ent, cell_out, logits
+
+
 def maxpool3s2_bwd(dy: torch.Tensor, idx: torch.Tensor, h: int, w: int) -> torch.Tensor:
     """``dx [n,c,h,w]`` of ``max_pool2d(x, 3, stride=2, padding=1)`` from ``dy`` and the forward's argmax
     indices (both ``[n,c,(h+1)//2,(w+1)//2]``)."""
