@@ -446,6 +446,8 @@ def run_ours(args):
             alg[name] = (446 + 16) * note["cells"]
         elif name == "head_eval_cells_bwd":
             alg[name] = (758 + 8) * note["cells"]
+        elif name == "pack_cells":
+            alg[name] = (78 + 56 + 16) * note["cells"]          # mask + i64 actions in, one 16-B record out per cell
     sm_mhz = (clocks or {}).get("sm_mhz") or 1965.0
     fp32_peak = 148 * 128 * 2 * sm_mhz * 1e6 / 1e12            # TFLOP/s: 128 FMA lanes per SM at the sampled clock
     kernels = {}
@@ -462,7 +464,7 @@ def run_ours(args):
                                   "fp32_peak_tflops": fp32_peak})
     # the roofline object is for the path's own dominant HBM-bound kernel: the dense policy-head backward when the
     # step launches it, else the dense policy-head forward (the backward then runs on the list of active cells)
-    dom = max((k for k in ("head_eval_bwd", "head_eval_fwd") if k in kernels),
+    dom = max((k for k in ("head_eval_bwd", "head_eval_fwd", "pack_cells") if k in kernels),
               key=lambda k: kernels[k]["avg_ms"], default=None)
     roof = None
     if dom in kernels:
@@ -476,6 +478,22 @@ def run_ours(args):
                 roof["traffic"] = json.load(open(tr)).get(dom, {}).get(args.workload)
             except Exception:
                 pass
+
+    # the fused actor Linear + policy head is tensor-bound: three TF32 products per fp32 product (3xTF32 split precision)
+    if "actor_head_fwd" in kernels and "actor_head_fwd" in ops.launch_notes:
+        nt = ops.launch_notes["actor_head_fwd"]
+        alg_flops = 2.0 * nt["m"] * (78 * nt["cells"]) * nt["k"]
+        issued = 3.0 * 2.0 * nt["m"] * (80 * nt["cells"]) * nt["k"]
+        sec = kernels["actor_head_fwd"]["avg_ms"] * 1e-3
+        try:
+            bf16 = float(json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))["bf16_tflops"])
+        except Exception:
+            bf16 = 1646.0
+        kernels["actor_head_fwd"].update({
+            "bound": "tensor", "algorithmic_tflops_fp32": alg_flops / sec / 1e12, "issued_tf32_tflops": issued / sec / 1e12,
+            "tf32_peak_tflops": bf16 / 2, "frac_of_tf32_peak_issued": issued / sec / 1e12 / (bf16 / 2),
+            "note": "fp32-accurate product as three TF32 tensor-core products of hi/lo-split operands; TF32 peak taken as "
+                    "half the measured dense bf16 rate of MEASURED_PEAKS.json"})
 
     # ---- e2e: host batch through the public call ---------------------------------------
     e2e = None

@@ -221,7 +221,9 @@ MB_API int mb_linear_tf32x3(const float* a_hi, const float* a_lo, const float* b
  *                         evaluates the head of each (frame, cell) from tensor memory:
  *                         cell_out [cells][n_frames][2] f32 = (log-prob, entropy) of the cell's seven components;
  *                         logp_out / ent_out [n_frames] (both or neither) = their sums in cell order;
- *                         logits_out [n_frames, 78*cells] or NULL = policy_logits (model.py:208) on request.
+ *                         logits_out [n_frames, 78*cells] or NULL = policy_logits (model.py:208) on request; with
+ *                         logits_alive_only != 0 only cells that have a valid action are written (the rest of the
+ *                         buffer is left untouched) -- all a backward pass needs, at a fraction of the traffic.
  * k % 32 == 0; every pointer 16-byte aligned. */
 MB_API int mb_pack_cells(const uint8_t* mask, const int64_t* action, void* cell_meta, int64_t n_frames, int32_t cells,
                          int32_t* status, void* stream);
@@ -229,8 +231,8 @@ MB_API int mb_pack_actor_weight(const float* weight, const float* bias, float* w
                                 int32_t cells, int32_t k, void* stream);
 MB_API int mb_actor_head_fwd(const float* a_hi, const float* a_lo, const float* w_hi, const float* w_lo,
                              const float* bias_p, const void* cell_meta, float* cell_out, float* logits_out,
-                             float* logp_out, float* ent_out, int64_t n_frames, int32_t cells, int32_t k,
-                             int32_t* status, void* stream);
+                             int32_t logits_alive_only, float* logp_out, float* ent_out, int64_t n_frames,
+                             int32_t cells, int32_t k, int32_t* status, void* stream);
 
 /* Backward of max_pool2d(kernel 3, stride 2, padding 1) (reference model.py:96) from the argmax
  * indices of the forward: dy, idx [planes, (h+1)/2, (w+1)/2] (idx = flat position in the h*w input

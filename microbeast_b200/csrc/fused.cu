@@ -67,16 +67,31 @@ __global__ void __launch_bounds__(kPackThreads) pack_cells_kernel(const uint8_t*
     const bool vec = (cells % 8 == 0) && nc == kPackCells &&
                      ((reinterpret_cast<uintptr_t>(mask) | reinterpret_cast<uintptr_t>(action)) & 15) == 0;
     if (vec) {
-        // 39 + 28 sixteen-byte pieces per frame; rows are padded by 4 / 8 bytes, so the pieces are stored as words
-        for (int i = threadIdx.x; i < nf * 67; i += kPackThreads) {
-            const int fi = i / 67, r = i - fi * 67;
-            const bool is_m = r < 39;
-            const int j = is_m ? r : r - 39;
-            const uint8_t* g = is_m ? mask + ((f0 + fi) * cells + c0) * kLogitsPerCell
-                                    : reinterpret_cast<const uint8_t*>(action + ((f0 + fi) * cells + c0) * kCompsPerCell);
-            const uint4 v = __ldg(reinterpret_cast<const uint4*>(g + 16 * j));
-            uint32_t* d = reinterpret_cast<uint32_t*>((is_m ? s_mask + fi * kPackMaskPitch : s_act + fi * kPackActPitch) + 16 * j);
-            d[0] = v.x; d[1] = v.y; d[2] = v.z; d[3] = v.w;
+        // 39 + 28 sixteen-byte pieces per frame; rows are padded by 4 / 8 bytes, so the pieces are stored as words.
+        // All of a thread's loads are issued before the first store (9 x 16 B in flight per thread).
+        constexpr int kPer = (kPackFrames * 67 + kPackThreads - 1) / kPackThreads;
+        uint4 v[kPer];
+#pragma unroll
+        for (int u = 0; u < kPer; ++u) {
+            const int i = threadIdx.x + u * kPackThreads;
+            if (i < nf * 67) {
+                const int fi = i / 67, r = i - fi * 67;
+                const bool is_m = r < 39;
+                const uint8_t* g = is_m ? mask + ((f0 + fi) * cells + c0) * kLogitsPerCell
+                                        : reinterpret_cast<const uint8_t*>(action + ((f0 + fi) * cells + c0) * kCompsPerCell);
+                v[u] = __ldg(reinterpret_cast<const uint4*>(g + 16 * (is_m ? r : r - 39)));
+            }
+        }
+#pragma unroll
+        for (int u = 0; u < kPer; ++u) {
+            const int i = threadIdx.x + u * kPackThreads;
+            if (i < nf * 67) {
+                const int fi = i / 67, r = i - fi * 67;
+                const bool is_m = r < 39;
+                uint32_t* d = reinterpret_cast<uint32_t*>((is_m ? s_mask + fi * kPackMaskPitch : s_act + fi * kPackActPitch) +
+                                                          16 * (is_m ? r : r - 39));
+                d[0] = v[u].x; d[1] = v[u].y; d[2] = v[u].z; d[3] = v[u].w;
+            }
         }
     } else {
         for (int fi = 0; fi < nf; ++fi) {
@@ -198,8 +213,8 @@ __global__ void __launch_bounds__(kFuThreads, 1) actor_head_fwd_kernel(const __g
                                                                        const float* __restrict__ bias_p,
                                                                        const uint4* __restrict__ meta,
                                                                        float2* __restrict__ cell_out,
-                                                                       float* __restrict__ logits_out, int M, int cells,
-                                                                       int K, int* status) {
+                                                                       float* __restrict__ logits_out, int alive_only,
+                                                                       int M, int cells, int K, int* status) {
     extern __shared__ uint8_t fu_smem_raw[];
     __shared__ __align__(8) uint64_t full_bar[kFuStages];
     __shared__ __align__(8) uint64_t empty_bar[kFuStages];
@@ -308,14 +323,17 @@ __global__ void __launch_bounds__(kFuThreads, 1) actor_head_fwd_kernel(const __g
                     const float4 b = __ldg(bp + i);
                     z[4 * i] += b.x; z[4 * i + 1] += b.y; z[4 * i + 2] += b.z; z[4 * i + 3] += b.w;
                 }
-                if (logits_out) {                          // model.py:208 policy_logits, on request
+                const uint4 mt = __ldg(meta + (long long)cell * M + row);
+                const bool alive = meta_alive(mt);
+                // model.py:208 policy_logits, on request: every cell, or only the cells that have a valid action (all
+                // the backward pass needs: the gradient of a cell without one is exactly zero, quirk Q1)
+                if (logits_out && (alive || !alive_only)) {
                     float2* o = reinterpret_cast<float2*>(logits_out + ((long long)row * cells + cell) * kLogitsPerCell);
 #pragma unroll
                     for (int i = 0; i < kLogitsPerCell / 2; ++i) o[i] = make_float2(z[2 * i], z[2 * i + 1]);
                 }
-                const uint4 mt = __ldg(meta + (long long)cell * M + row);
                 float lp = 0.f, en = 0.f;
-                if (meta_alive(mt)) cell_forward(z, mt, lp, en);       // a cell without a valid action adds exactly 0
+                if (alive) cell_forward(z, mt, lp, en);       // a cell without a valid action adds exactly 0
                 cell_out[(long long)cell * M + row] = make_float2(lp, en);
             }
         }
@@ -424,8 +442,8 @@ int pack_actor_weight(const float* w, const float* b, float* hi, float* lo, floa
 }
 
 int actor_head_fwd(const float* a_hi, const float* a_lo, const float* wp_hi, const float* wp_lo, const float* bias_p,
-                   const void* meta, float* cell_out, float* logits_out, float* logp, float* ent, long long M, int cells,
-                   int K, int* status, cudaStream_t st) {
+                   const void* meta, float* cell_out, float* logits_out, int alive_only, float* logp, float* ent,
+                   long long M, int cells, int K, int* status, cudaStream_t st) {
     FuEncodeFn enc = fu_encode_fn();
     if (!enc) {
         set_error("mb_actor_head_fwd: cuTensorMapEncodeTiled is not available from this driver");
@@ -450,8 +468,8 @@ int actor_head_fwd(const float* a_hi, const float* a_lo, const float* wp_hi, con
     const int sms = sm_count(dev);
     const int grid = int(tiles < sms ? tiles : sms);
     actor_head_fwd_kernel<<<grid, kFuThreads, kFuSmem, st>>>(maps, bias_p, reinterpret_cast<const uint4*>(meta),
-                                                            reinterpret_cast<float2*>(cell_out), logits_out, int(M), cells,
-                                                            K, status);
+                                                            reinterpret_cast<float2*>(cell_out), logits_out, alive_only,
+                                                            int(M), cells, K, status);
     MB_CUDA(cudaGetLastError());
     if (logp && ent) {
         frame_sum_kernel<<<unsigned((M + 255) / 256), 256, 0, st>>>(reinterpret_cast<const float2*>(cell_out), logp, ent, M, cells);
@@ -488,8 +506,8 @@ extern "C" int mb_pack_actor_weight(const float* weight, const float* bias, floa
 
 extern "C" int mb_actor_head_fwd(const float* a_hi, const float* a_lo, const float* w_hi, const float* w_lo,
                                  const float* bias_p, const void* cell_meta, float* cell_out, float* logits_out,
-                                 float* logp_out, float* ent_out, int64_t n_frames, int32_t cells, int32_t k,
-                                 int32_t* status, void* stream) {
+                                 int32_t logits_alive_only, float* logp_out, float* ent_out, int64_t n_frames,
+                                 int32_t cells, int32_t k, int32_t* status, void* stream) {
     if (n_frames < 0 || cells <= 0 || k <= 0 || k % 32 != 0 || n_frames > 0x7fffffff) {
         mb::set_error("mb_actor_head_fwd: n_frames=%lld cells=%d k=%d: need k %% 32 == 0", (long long)n_frames, cells, k);
         return MB_ERR_INVALID;
@@ -507,6 +525,6 @@ extern "C" int mb_actor_head_fwd(const float* a_hi, const float* a_lo, const flo
         mb::set_error("mb_actor_head_fwd: operands must be 16-byte aligned");
         return MB_ERR_INVALID;
     }
-    return mb::actor_head_fwd(a_hi, a_lo, w_hi, w_lo, bias_p, cell_meta, cell_out, logits_out, logp_out, ent_out, n_frames,
-                              cells, k, status, static_cast<cudaStream_t>(stream));
+    return mb::actor_head_fwd(a_hi, a_lo, w_hi, w_lo, bias_p, cell_meta, cell_out, logits_out, logits_alive_only, logp_out,
+                              ent_out, n_frames, cells, k, status, static_cast<cudaStream_t>(stream));
 }

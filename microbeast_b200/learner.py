@@ -111,7 +111,10 @@ def learner_losses(learner_model: nn.Module, batch: Dict[str, torch.Tensor], row
     ``(t, b, e)`` order (quirk Q7); ``True`` treats the flat batch as what it is, ``[T+1, rows]``,
     so that a row really is one trajectory, and runs the time-major V-trace kernel on it in place.
     """
-    out, _ = learner_model.get_action(batch, learning=True, inds=[], agent_state=())      # utils.py:234
+    kw = {}
+    if getattr(learner_model, "skips_policy_logits", False):
+        kw["policy_logits"] = False          # never read below (utils.py:237-329): the fused kernel need not store them
+    out, _ = learner_model.get_action(batch, learning=True, inds=[], agent_state=(), **kw)      # utils.py:234
 
     ready = batch.get("_ready")
     if ready is not None:

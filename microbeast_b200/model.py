@@ -160,6 +160,9 @@ FAST_CONV_FORWARD = True
 # actor Linear forward (learner mode) by mb_linear_tf32x3: tcgen05 tensor cores, three TF32 products of hi/lo-split
 # operands accumulated in fp32 (error 5.5e-7 of max|logit|; cuBLAS fp32: 5.0e-7) instead of a SIMT SGEMM
 TENSOR_CORE_ACTOR = True
+# learner mode: actor Linear and policy head as ONE tcgen05 kernel (mb_actor_head_fwd): the logits stay in tensor memory,
+# only the cells that have a valid action are written out (for the backward pass); off: mb_linear_tf32x3 + mb_head_eval_fwd
+FUSED_ACTOR_HEAD = True
 
 
 def cell_list(action_mask: torch.Tensor, cells: int, auto: bool):
@@ -241,11 +244,21 @@ class _ActorHead(torch.autograd.Function):
     list is sized from the data)."""
 
     @staticmethod
-    def forward(ctx, hidden, weight, bias, action_mask, action, cells, mode):
-        logits = ops.linear_tf32x3(hidden, weight, bias) if TENSOR_CORE_ACTOR else None    # model.py:167
-        if logits is None:
-            logits = _linear_bias_in_k(hidden, weight, bias)
-        logprobs, entropy = ops.head_eval_fwd(logits, action_mask, action)
+    def forward(ctx, hidden, weight, bias, action_mask, action, cells, mode, want_logits=True):
+        fused = None
+        if TENSOR_CORE_ACTOR and FUSED_ACTOR_HEAD and hidden.shape[1] % 32 == 0 and hidden.shape[0] > 0:
+            # model.py:167-214 in one kernel; ``logits`` then holds the cells with a valid action only (enough for
+            # the backward: every other cell has exactly zero gradient) unless the caller wants policy_logits
+            meta = ops.pack_cells(action_mask, action, cells)
+            fused = ops.actor_head_fwd(hidden, ops.pack_actor_weight(weight, bias, cells), meta,
+                                       want_logits=True if want_logits else "alive")
+        if fused is not None:
+            logprobs, entropy, _cell_out, logits = fused
+        else:
+            logits = ops.linear_tf32x3(hidden, weight, bias) if TENSOR_CORE_ACTOR else None    # model.py:167
+            if logits is None:
+                logits = _linear_bias_in_k(hidden, weight, bias)
+            logprobs, entropy = ops.head_eval_fwd(logits, action_mask, action)
         ctx.save_for_backward(hidden, weight, logits, action_mask, action)
         ctx.cells, ctx.mode = cells, mode
         ctx.mark_non_differentiable(logits)
@@ -263,7 +276,7 @@ class _ActorHead(torch.autograd.Function):
         cl = cell_list(action_mask, cells, auto=(ctx.mode == "auto")) if (ctx.mode and not small) else None
         if cl is None:
             dlogits = ops.head_eval_bwd(logits, action_mask, action, g_lp, g_ent)
-            return dlogits @ weight, dlogits.t() @ hidden, dlogits.sum(dim=0), None, None, None, None
+            return dlogits @ weight, dlogits.t() @ hidden, dlogits.sum(dim=0), None, None, None, None, None
         fidx, cidx = cl
         lmax, width = fidx.shape[1], hidden.shape[1]
         safe, mask_c, act_c = gather_cells(fidx, cidx, n, action_mask, action, cells)
@@ -276,7 +289,7 @@ class _ActorHead(torch.autograd.Function):
         g_bias = dl.sum(dim=1).reshape(-1)
         g_hid = torch.bmm(dl, weight.view(cells, LOGITS_PER_CELL, width))                   # [C, lmax, 256]
         g_hidden = hidden.new_zeros((n + _PAD_ROWS, width)).index_add_(0, flat, g_hid.reshape(-1, width))[:n]
-        return g_hidden, g_weight, g_bias, None, None, None, None
+        return g_hidden, g_weight, g_bias, None, None, None, None, None
 
 
 class Residual_Block(nn.Module):
@@ -333,6 +346,7 @@ class Agent(nn.Module):
         self.nchw_copy = True
         self.sparse_head = False           # True / "auto": no policy_logits for fully masked cells (see _sparse_head)
         self.sparse_backward = "auto"      # backward of the actor head over the active cells only (see _ActorHead)
+        self.skips_policy_logits = True    # get_action(..., policy_logits=False) is understood (learner.learner_losses)
         self.obs_planes = c
         shape = (c, h, w)
         layers = []
@@ -399,13 +413,15 @@ class Agent(nn.Module):
         return self.critic(self.forward(input_dict, agent_state, learning, inds))
 
     def get_action(self, input_dict: dict, learning=False, inds=(), agent_state=(),
-                   uniforms: Optional[torch.Tensor] = None):
+                   uniforms: Optional[torch.Tensor] = None, policy_logits: bool = True):
         """Same outputs as reference ``model.py:165-216``.
 
         acting:   ``dict(action [n,7C], policy_logits [n,78C], logprobs [n], baseline [1,n])``
         learning: the same plus ``entropy [N]``; ``action`` is the batch's action.
         One encoder pass feeds both heads (the reference runs the encoder twice, quirk
-        Q6; values and summed gradients are identical).
+        Q6; values and summed gradients are identical).  ``policy_logits=False`` (learning mode; what
+        ``learner_losses`` passes, since ``PPO_learn`` never reads them, libs/utils.py:237-329) returns ``None`` under
+        that key and lets the fused actor-head kernel skip the [N, 78C] store.
         """
         hidden = self.forward(input_dict, agent_state, learning, inds)
         baseline = self.critic(hidden).view(1, -1)                              # model.py:205
@@ -429,6 +445,6 @@ class Agent(nn.Module):
                 return (dict(action=action, policy_logits=None, logprobs=sparse[0], baseline=baseline,
                              entropy=sparse[1]), ())
         logits, logprobs, entropy = _ActorHead.apply(hidden, self.actor.weight, self.actor.bias, action_mask,
-                                                     action, self.cells, self.sparse_backward)
-        return (dict(action=action, policy_logits=logits, logprobs=logprobs, baseline=baseline,
-                     entropy=entropy), ())
+                                                     action, self.cells, self.sparse_backward, bool(policy_logits))
+        return (dict(action=action, policy_logits=logits if policy_logits else None, logprobs=logprobs,
+                     baseline=baseline, entropy=entropy), ())

@@ -390,10 +390,12 @@ def pack_actor_weight(weight: torch.Tensor, bias: Optional[torch.Tensor], cells:
     return w_hi, w_lo, bias_p
 
 
-def actor_head_fwd(hidden: torch.Tensor, packed_weight, cell_meta: torch.Tensor, want_logits: bool = False):
+def actor_head_fwd(hidden: torch.Tensor, packed_weight, cell_meta: torch.Tensor, want_logits=False):
     """Actor Linear + policy head in one tcgen05 kernel (``mb_actor_head_fwd``, reference ``model.py:167-214``).
 
     ``hidden [N, K]`` fp32, ``packed_weight`` from :func:`pack_actor_weight`, ``cell_meta`` from :func:`pack_cells`.
+    ``want_logits``: False, True (``policy_logits`` of every cell) or ``"alive"`` (only cells with a valid action are
+    written into an otherwise uninitialised buffer: what a backward pass needs).
     Returns ``(logprobs [N], entropy [N], cell_out [cells, N, 2], policy_logits [N, 78*cells] or None)``; ``None`` when
     the shape is not covered (``K % 32``)."""
     dev = _need_cuda(hidden=hidden, cell_meta=cell_meta)
@@ -408,9 +410,10 @@ def actor_head_fwd(hidden: torch.Tensor, packed_weight, cell_meta: torch.Tensor,
     logp = torch.empty(n, dtype=torch.float32, device=dev)
     ent = torch.empty(n, dtype=torch.float32, device=dev)
     logits = torch.empty((n, cells * LOGITS_PER_CELL), dtype=torch.float32, device=dev) if want_logits else None
-    with torch.cuda.device(dev), _Launch("actor_head_fwd", note={"m": n, "cells": cells, "k": k, "logits": bool(want_logits)}):
+    with torch.cuda.device(dev), _Launch("actor_head_fwd", note={"m": n, "cells": cells, "k": k, "logits": str(want_logits)}):
         _check(lib.mb_actor_head_fwd(_ptr(a_hi), _ptr(a_lo), _ptr(w_hi), _ptr(w_lo), _ptr(bias_p), _ptr(cell_meta),
-                                     _ptr(cell_out), _ptr(logits), _ptr(logp), _ptr(ent), n, cells, k,
+                                     _ptr(cell_out), _ptr(logits), 1 if want_logits == "alive" else 0, _ptr(logp),
+                                     _ptr(ent), n, cells, k,
                                      _ptr(status_word(dev)), _stream()))
     return logp, ent, cell_out, logits
 
