@@ -76,6 +76,15 @@ MB_API int mb_head_sample(const float* logits, const uint8_t* mask, const float*
                    float* logp_out, float* ent_out, int64_t n_frames, int32_t cells, int32_t* status,
                    void* stream);
 
+/* The reference's own sampling rule with caller-supplied randomness: reference model.py:177, Categorical.sample() ->
+ * torch.multinomial(probs, 1, True) = argmax_i(probs_i / q_i), q_i ~ Exp(1) per category.  exponentials
+ * [n_frames, 78*cells] f32 > 0 (torch.empty_like(logits).exponential_() draws them the way torch.multinomial does);
+ * action_out [n_frames, 7*cells] i64.  A fully masked component has probs = 1/n (quirk Q1) and so samples uniformly;
+ * masked entries of a partly valid component have probability 0 and are never chosen.  Log-prob and entropy of the
+ * result: mb_head_eval_fwd. */
+MB_API int mb_head_sample_exp(const float* logits, const uint8_t* mask, const float* exponentials, int64_t* action_out,
+                              int64_t n_frames, int32_t cells, void* stream);
+
 /* Cell-list forms of the two eval entry points, for a sparse actor head that computes logits only for
  * cells with at least one valid action (a fully masked cell contributes exactly 0 to log-prob, entropy
  * and gradients whatever its logits are: reference model.py:43 + fp32 absorption, quirk Q1).

@@ -20,6 +20,7 @@ SIGNATURES = {
     "mb_head_eval_fwd": (ctypes.c_int, [_P, _P, _P, _P, _P, ctypes.c_int64, ctypes.c_int32, _P, _P]),
     "mb_head_eval_bwd": (ctypes.c_int, [_P, _P, _P, _P, _P, _P, ctypes.c_int64, ctypes.c_int32, _P, _P]),
     "mb_head_sample": (ctypes.c_int, [_P, _P, _P, _P, _P, _P, ctypes.c_int64, ctypes.c_int32, _P, _P]),
+    "mb_head_sample_exp": (ctypes.c_int, [_P, _P, _P, _P, ctypes.c_int64, ctypes.c_int32, _P]),
     "mb_head_eval_cells_fwd": (ctypes.c_int, [_P, _P, _P, _P, ctypes.c_int64, _P, _P]),
     "mb_head_eval_cells_bwd": (ctypes.c_int, [_P, _P, _P, _P, _P, _P, ctypes.c_int64, _P, _P]),
     "mb_vtrace_workspace_bytes": (ctypes.c_size_t, [ctypes.c_int64]),

@@ -12,6 +12,7 @@ mkdir -p "$OBJ"
 UNITS="abi head vtrace unpack convgrad gemm"
 [ -f "$HERE/cells.cu" ] && UNITS="$UNITS cells"
 [ -f "$HERE/fused.cu" ] && UNITS="$UNITS fused"
+[ -f "$HERE/sampler.cu" ] && UNITS="$UNITS sampler"
 [ -f "$HERE/convtc.cu" ] && UNITS="$UNITS convtc"
 pids=""
 for u in $UNITS; do

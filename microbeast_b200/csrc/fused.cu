@@ -104,10 +104,23 @@ __global__ void __launch_bounds__(kPackThreads) pack_cells_kernel(const uint8_t*
     __syncthreads();
     const int fi = threadIdx.x & 31, ci = threadIdx.x >> 5;
     if (fi >= nf || ci >= nc) return;
-    const uint8_t* m = s_mask + fi * kPackMaskPitch + ci * kLogitsPerCell;
+    // 78 mask bytes -> 78 bits, four bytes at a time: the cell starts on an even byte of a 4-byte aligned row, so its
+    // bytes are read as 21 aligned words shifted by 0 or 16 bits; per word, vcmpne4 gives 0xff per non-zero byte and
+    // a multiply gathers one bit of each byte into a nibble
+    const uint32_t* mw = reinterpret_cast<const uint32_t*>(s_mask + fi * kPackMaskPitch + ((ci * kLogitsPerCell) & ~3));
+    const int sh = ((ci * kLogitsPerCell) & 2) * 8;
     uint32_t w[3] = {0u, 0u, 0u};
+    uint32_t prev = mw[0];
 #pragma unroll
-    for (int i = 0; i < kLogitsPerCell; ++i) w[i >> 5] |= (m[i] != 0 ? 1u : 0u) << (i & 31);
+    for (int i = 0; i < 20; ++i) {                     // 20 words = 80 bytes; bytes 78, 79 are masked off below
+        const uint32_t next = mw[i + 1];
+        const uint32_t word = __funnelshift_r(prev, next, sh);
+        prev = next;
+        const uint32_t nz = __vcmpne4(word, 0u) & 0x08040201u;
+        const uint32_t nib = (nz * 0x01010101u) >> 24;              // bit j = byte j of the word is non-zero
+        w[(4 * i) >> 5] |= nib << ((4 * i) & 31);
+    }
+    w[2] &= 0x3fffu;
     const long long* a = reinterpret_cast<const long long*>(s_act + fi * kPackActPitch + ci * kCompsPerCell * 8);
     constexpr int LEN[7] = {6, 4, 4, 4, 4, 7, 49};
     uint32_t act[7];

@@ -55,8 +55,16 @@ class CategoricalMasked:
             self._cache = (action, logp, ent)
         return self._cache
 
-    def sample(self, uniforms: Optional[torch.Tensor] = None) -> torch.Tensor:
-        """``action [N,7C]``; inverse-CDF from ``uniforms [N,7C]`` (``torch.rand`` when omitted)."""
+    def sample(self, uniforms: Optional[torch.Tensor] = None, exponentials: Optional[torch.Tensor] = None,
+               mode: str = "invcdf") -> torch.Tensor:
+        """``action [N,7C]``.  ``mode="invcdf"``: inverse-CDF from ``uniforms [N,7C]`` (``torch.rand`` when omitted).
+        ``mode="multinomial"`` (or ``exponentials=`` given): the reference's own rule, ``torch.multinomial`` =
+        ``argmax(probs / Exp(1))`` (``model.py:177``), from ``exponentials [N,78C]`` (torch's generator when omitted)."""
+        if mode == "multinomial" or exponentials is not None:
+            with torch.no_grad():
+                action, logp, ent = ops.head_sample_exp(self.logits.detach(), self.masks, exponentials, want_entropy=True)
+            self._cache = (action, logp, ent)
+            return action
         if uniforms is None:
             n, width = self.logits.shape
             uniforms = torch.rand((n, width // LOGITS_PER_CELL * COMPONENTS_PER_CELL),
@@ -346,6 +354,7 @@ class Agent(nn.Module):
         self.nchw_copy = True
         self.sparse_head = False           # True / "auto": no policy_logits for fully masked cells (see _sparse_head)
         self.sparse_backward = "auto"      # backward of the actor head over the active cells only (see _ActorHead)
+        self.sampler = "invcdf"            # acting mode: "invcdf" (one uniform per component) | "multinomial" (torch's rule)
         self.skips_policy_logits = True    # get_action(..., policy_logits=False) is understood (learner.learner_losses)
         self.obs_planes = c
         shape = (c, h, w)
@@ -413,7 +422,8 @@ class Agent(nn.Module):
         return self.critic(self.forward(input_dict, agent_state, learning, inds))
 
     def get_action(self, input_dict: dict, learning=False, inds=(), agent_state=(),
-                   uniforms: Optional[torch.Tensor] = None, policy_logits: bool = True):
+                   uniforms: Optional[torch.Tensor] = None, policy_logits: bool = True,
+                   exponentials: Optional[torch.Tensor] = None):
         """Same outputs as reference ``model.py:165-216``.
 
         acting:   ``dict(action [n,7C], policy_logits [n,78C], logprobs [n], baseline [1,n])``
@@ -428,6 +438,10 @@ class Agent(nn.Module):
         if not learning:
             logits = self.actor(hidden)                                         # model.py:167
             action_mask = input_dict["action_mask"][0, ...]                     # model.py:173
+            if exponentials is not None or (self.sampler == "multinomial" and uniforms is None):
+                # the reference's sampling rule (model.py:177): argmax(probs / Exp(1)), one draw per category
+                action, logprobs, _ = ops.head_sample_exp(logits.detach(), action_mask, exponentials)
+                return (dict(action=action, policy_logits=logits, logprobs=logprobs, baseline=baseline), ())
             if uniforms is None:
                 uniforms = torch.rand((logits.shape[0], self.cells * COMPONENTS_PER_CELL),
                                       device=logits.device)

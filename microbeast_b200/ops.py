@@ -219,6 +219,30 @@ def head_sample(logits, mask, uniforms, want_entropy: bool = True):
     return action, logp, ent
 
 
+def head_sample_exp(logits, mask, exponentials: Optional[torch.Tensor] = None, generator=None, want_entropy: bool = False):
+    """The reference's sampling rule (``model.py:177``: ``Categorical.sample`` -> ``torch.multinomial`` =
+    ``argmax(probs / Exp(1))``) with the exponentials as an input: ``exponentials [N, 78C]`` f32, drawn with
+    ``torch.empty_like(logits).exponential_(generator=...)`` when omitted.  Returns
+    ``(action [N,7C] i64, logprobs [N], entropy [N] or None)``."""
+    dev = _need_cuda(logits=logits, mask=mask, exponentials=exponentials)
+    logits = _as(logits, torch.float32, "logits")
+    mask = _mask_u8(mask)
+    n = logits.shape[0]
+    cells = _cells(logits.shape[1], LOGITS_PER_CELL, "logits")
+    if mask.shape != logits.shape:
+        raise ValueError("shape mismatch between logits / mask")
+    if exponentials is None:
+        exponentials = torch.empty_like(logits).exponential_(generator=generator)
+    exponentials = _as(exponentials, torch.float32, "exponentials")
+    if exponentials.shape != logits.shape:
+        raise ValueError("exponentials must be shaped like logits (one draw per category)")
+    action = torch.empty((n, cells * COMPONENTS_PER_CELL), dtype=torch.int64, device=dev)
+    with torch.cuda.device(dev), _Launch("head_sample_exp"):
+        _check(lib.mb_head_sample_exp(_ptr(logits), _ptr(mask), _ptr(exponentials), _ptr(action), n, cells, _stream()))
+    logp, ent = head_eval_fwd(logits, mask, action)
+    return action, logp, (ent if want_entropy else None)
+
+
 def unpack_rollout(mask_bits: Optional[torch.Tensor], action_u8: Optional[torch.Tensor], cells: int,
                    mask_out: Optional[torch.Tensor] = None, action_out: Optional[torch.Tensor] = None):
     """Device-side expansion of the rollout store's wire format: bit-packed masks

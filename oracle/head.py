@@ -147,6 +147,24 @@ def sample_invcdf(logits: torch.Tensor, mask: torch.Tensor, uniforms: torch.Tens
     return torch.from_numpy(act.reshape(n, cells * COMPONENTS_PER_CELL))
 
 
+def sample_expdiv(logits: torch.Tensor, mask: torch.Tensor, exponentials: torch.Tensor) -> torch.Tensor:
+    """The reference's sampling rule with the randomness made explicit: ``Categorical.sample()`` (``model.py:177``)
+    is ``torch.multinomial(probs, 1, True)``, which draws ``q ~ Exp(1)`` per category and returns
+    ``argmax(probs / q)`` (``tests/test_oracle_golden.py`` checks that this reproduces
+    ``torch.multinomial`` bit for bit on the CPU with the same generator state).
+    ``exponentials [N, 78C]`` f32 -> ``action [N, 7C]`` i64; fp32 arithmetic on the reference class's ``probs``."""
+    n, width = logits.shape
+    cells = width // LOGITS_PER_CELL
+    lg = logits.view(n, cells, LOGITS_PER_CELL)
+    mk = mask.view(n, cells, LOGITS_PER_CELL)
+    q = exponentials.view(n, cells, LOGITS_PER_CELL)
+    acts = []
+    for s, w in zip(_SEG_START, NVEC_CELL):
+        p = MaskedCategorical(lg[:, :, s:s + w], mk[:, :, s:s + w]).probs
+        acts.append((p / q[:, :, s:s + w]).argmax(dim=2))
+    return torch.stack(acts, dim=2).reshape(n, cells * COMPONENTS_PER_CELL)
+
+
 def head_sample(logits, mask, uniforms):
     """Actor branch (``model.py:171-177,194,199-210``) with the defined sampler.
 

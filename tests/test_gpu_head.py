@@ -239,3 +239,60 @@ def test_active_cells_matches_any(n, cells, offset):
     got = ops.active_cells(mask, cells)
     assert got.dtype == torch.bool and got.shape == (n, cells)
     assert torch.equal(got.cpu(), body.any(dim=2))
+
+
+def test_multinomial_rule_sampler_matches_oracle_and_torch_distribution():
+    """mb_head_sample_exp: the reference's own rule, argmax(probs / Exp(1)) (model.py:177 -> torch.multinomial).
+    (1) with the same exponentials the actions equal the oracle's fp32 evaluation (which reproduces the real
+    ``.sample()`` bit for bit, tests/test_oracle_golden.py) except where the two largest ratios are a rounding apart;
+    (2) over many draws the action frequencies follow the masked soft-max (chi-square), as do torch.multinomial's."""
+    import numpy as np
+    from microbeast_b200 import ops, synth
+    from oracle.head import MaskedCategorical, sample_expdiv
+    n, cells = 4096, 16
+    g = torch.Generator().manual_seed(5)
+    logits = synth.make_logits(n, cells, gen=g)
+    mask = synth.make_masks(n, cells, "dense", gen=g) | synth.make_masks(n, cells, "one_valid", gen=g)
+    mask[:, :78] = 0                                         # one fully masked cell per frame (uniform, quirk Q1)
+    expo = torch.empty(n, 78 * cells).exponential_(generator=g)
+    act, logp, ent = ops.head_sample_exp(logits.cuda(), mask.cuda(), expo.cuda(), want_entropy=True)
+    want = sample_expdiv(logits, mask, expo)
+    same = (act.cpu() == want)
+    assert float(same.float().mean()) >= 0.9999, float(same.float().mean())
+    lp_ref, en_ref = ohead_eval(logits, mask, act.cpu())
+    assert torch.allclose(logp.cpu(), lp_ref, rtol=1e-5, atol=1e-4) and torch.allclose(ent.cpu(), en_ref, rtol=1e-5, atol=1e-4)
+    # masked entries of partly valid components are never drawn
+    seg_start = (0, 6, 10, 14, 18, 22, 29)
+    mk = mask.view(n, cells, 78)
+    a = act.cpu().view(n, cells, 7)
+    for k, s in enumerate(seg_start):
+        w = (6, 4, 4, 4, 4, 7, 49)[k]
+        seg = mk[:, :, s:s + w]
+        landed = seg.gather(2, a[:, :, k:k + 1]).squeeze(2) != 0
+        assert bool((landed | (seg.sum(2) == 0)).all())
+    # distribution: one (logits, mask) row repeated, fresh exponentials from torch's CUDA generator
+    reps = 20000
+    row_l, row_m = logits[:1].repeat(reps, 1).cuda(), mask[:1].repeat(reps, 1).cuda()
+    gen = torch.Generator(device="cuda").manual_seed(1)
+    drawn, _, _ = ops.head_sample_exp(row_l, row_m, generator=gen)
+    drawn = drawn.cpu().view(reps, cells, 7)
+    worst = 0.0
+    for cell in (0, 1, 5):
+        for k, s in enumerate(seg_start):
+            w = (6, 4, 4, 4, 4, 7, 49)[k]
+            p = MaskedCategorical(logits[0, cell * 78 + s: cell * 78 + s + w].double()[None],
+                                  mask[0, cell * 78 + s: cell * 78 + s + w][None]).probs[0].numpy()
+            counts = np.bincount(drawn[:, cell, k].numpy(), minlength=w).astype(np.float64)
+            assert counts[p < 1e-12].sum() == 0
+            keep = p * reps >= 5
+            if keep.sum() < 2:
+                continue
+            chi2 = float((((counts - p * reps) ** 2)[keep] / (p * reps)[keep]).sum())
+            dof = int(keep.sum()) - 1
+            worst = max(worst, (chi2 - dof) / np.sqrt(2.0 * dof))
+    assert worst < 6.0, f"chi-square {worst:.1f} standard deviations above its mean"
+
+
+def ohead_eval(logits, mask, action):
+    from oracle.head import head_eval_fast
+    return head_eval_fast(logits, mask, action)

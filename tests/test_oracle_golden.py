@@ -143,3 +143,24 @@ def test_restatement_equals_imported_reference_live():
         assert torch.equal(real.log_prob(a), mine.log_prob(a))
         assert torch.equal(real.entropy(), mine.entropy())
         assert torch.equal(real.probs, mine.probs)
+
+
+def test_expdiv_sampler_reproduces_the_reference_sample_call():
+    """``oracle.head.sample_expdiv`` fed with exponentials drawn in the order the reference draws them equals the real
+    ``CategoricalMasked(...).sample()`` of every component (``model.py:176-177``), bit for bit."""
+    if not refload.available():
+        pytest.skip("reference checkout not present")
+    ref_model, _ = refload.load()
+    from oracle.head import sample_expdiv
+    n, cells = 40, 6
+    g = torch.Generator().manual_seed(21)
+    logits = torch.randn(n, 78 * cells, generator=g) * 2
+    mask = (torch.rand(n, 78 * cells, generator=g) < 0.4).to(torch.uint8)
+    mask[:, :78] = 0                                        # a fully masked cell: uniform over all entries (Q1)
+    nvec = list(NVEC_CELL) * cells
+    torch.manual_seed(77)
+    real = torch.stack([ref_model.CategoricalMasked(logits=l, masks=m).sample()
+                        for l, m in zip(torch.split(logits, nvec, dim=1), torch.split(mask, nvec, dim=1))]).T
+    torch.manual_seed(77)
+    expo = torch.cat([torch.empty(n, w).exponential_() for w in nvec], dim=1)      # same draws, same order
+    assert torch.equal(sample_expdiv(logits, mask, expo), real)
