@@ -181,11 +181,16 @@ def PPO_learn(actor_model: nn.Module, learner_model, exp_name: str, batch, optim
         finally:
             if sparse_head is not None:
                 learner_model.sparse_head = keep
-        optimizer.zero_grad()                                                              # utils.py:333
-        loss4[3].backward()                                                                # utils.py:334
-        losses = loss4.detach()
-        if reducer is not None:
-            losses = reducer.allreduce(learner_model, losses)
+        if reducer is not None and reducer.world_size > 1:
+            # gradients live in the reducer's flat bucket: zeroed there, the head's slice goes on the wire as soon as
+            # the actor-head backward has run and overlaps the encoder's backward (parallel.GradAllReducer)
+            reducer.begin(learner_model)                                                   # utils.py:333
+            loss4[3].backward()                                                            # utils.py:334
+            losses = reducer.finish(loss4.detach())
+        else:
+            optimizer.zero_grad()                                                          # utils.py:333
+            loss4[3].backward()                                                            # utils.py:334
+            losses = loss4.detach()
         optimizer.step()                                                                   # utils.py:335
         if actor_model is not learner_model:
             actor_model.load_state_dict(learner_model.state_dict())                        # utils.py:337

@@ -59,6 +59,77 @@ class GradAllReducer:
             self._flat = torch.empty(numel, dtype=torch.float32, device=like.device)
         return self._flat
 
+    # ---- overlapped path: gradients ARE the bucket ----------------------------------------------------------
+    # ``attach`` makes every ``p.grad`` a view into one flat buffer, the parameters that finish their backward first
+    # (the actor / critic heads: 97 % of the bytes at 16x16) at its start.  ``begin`` zeroes the buffer in place of
+    # ``optimizer.zero_grad()`` (autograd then accumulates into the views) and arms a hook on the head parameters: as
+    # soon as their gradients exist, that slice is all-reduced asynchronously while the encoder's backward is still
+    # running; ``finish`` reduces the rest (plus the logged loss scalars) and waits for both.  No copy in, no copy out.
+    def attach(self, model: torch.nn.Module, first: Tuple[str, ...] = ("actor.", "critic.")) -> None:
+        named = [(n, p) for n, p in model.named_parameters() if p.requires_grad]
+        head = [(n, p) for n, p in named if n.startswith(first)]
+        rest = [(n, p) for n, p in named if not n.startswith(first)]
+        order = head + rest
+        sizes = [p.numel() for _, p in order]
+        dev = order[0][1].device
+        self._n_extra = 8
+        self._grads = torch.zeros(sum(sizes) + self._n_extra, dtype=torch.float32, device=dev)
+        off = 0
+        for (_, p), n in zip(order, sizes):
+            p.grad = self._grads[off: off + n].view_as(p)
+            off += n
+        self._head_numel = sum(p.numel() for _, p in head)
+        self._total_numel = off
+        self._head_params = [p for _, p in head]
+        self._pending = 0
+        self._early = None
+        self._attached = model
+        for p in self._head_params:
+            p.register_post_accumulate_grad_hook(self._head_ready)
+
+    def _head_ready(self, _param) -> None:
+        if self._pending <= 0:
+            return
+        self._pending -= 1
+        if self._pending == 0 and self.world_size > 1 and self._head_numel:
+            # issued behind the kernels that produced these gradients; runs on the backend's own stream while the
+            # rest of the backward pass keeps the compute stream busy
+            self._early = dist.all_reduce(self._grads[: self._head_numel], op=dist.ReduceOp.SUM, group=self.group,
+                                          async_op=True)
+
+    def begin(self, model: torch.nn.Module) -> None:
+        """Call instead of ``optimizer.zero_grad()`` right before ``backward()``."""
+        if getattr(self, "_attached", None) is not model:
+            self.attach(model)
+        else:
+            for p in model.parameters():            # an optimizer.zero_grad(set_to_none=True) elsewhere drops the views
+                if p.requires_grad and p.grad is None:
+                    self.attach(model)
+                    break
+        self._grads.zero_()
+        self._pending = len(self._head_params)
+        self._early = None
+
+    def finish(self, extra: Optional[torch.Tensor] = None):
+        """After ``backward()``: sums what ``begin``'s hook has not already put on the wire; returns the summed ``extra``."""
+        n_extra = extra.numel() if extra is not None else 0
+        if n_extra > self._n_extra:
+            raise ValueError("GradAllReducer.finish: at most 8 extra scalars")
+        tail = self._grads[self._total_numel: self._total_numel + n_extra]
+        if n_extra:
+            tail.copy_(extra.reshape(-1))
+        if self.world_size > 1:
+            start = self._head_numel if self._early is not None else 0
+            late = dist.all_reduce(self._grads[start: self._total_numel + n_extra], op=dist.ReduceOp.SUM,
+                                   group=self.group, async_op=True)
+            if self._early is not None:
+                self._early.wait()
+            late.wait()
+            self._early = None
+        self._pending = 0
+        self.calls += 1
+        return tail.clone().view_as(extra) if n_extra else extra
+
     def allreduce(self, model: torch.nn.Module, extra: Optional[torch.Tensor] = None):
         """In-place sum of every ``p.grad`` over the ranks; returns the summed ``extra``."""
         grads: List[torch.Tensor] = [p.grad for p in model.parameters() if p.grad is not None]

@@ -36,19 +36,22 @@ def train(exp_name: str, *, env_factory: Optional[Callable[[int, int, int], obje
           n_envs: int = 6, env_size: int = 8, T: int = 64, B: int = 2, total_steps: int = 10_000_000,
           device: Optional[str] = None, lr: float = 2.5e-4, eps: float = 1e-5, seed: int = 0,
           reducer: Optional[GradAllReducer] = None, compact: bool = True, log: bool = False,
-          batched_inference: bool = True) -> List[list]:
+          batched_inference: bool = True, rank_seed: int = 0) -> List[list]:
     """Runs actors + learner until ``total_steps`` env-frames have been learned from
     (``step += n_envs*B*T`` per update, ``microbeast.py:230``).  Returns the loss rows that were
     also appended to ``<exp_name>Losses.csv``.
 
     ``env_factory(actor_id, n_envs, env_size)`` must return a vec-env with the surface
     ``env_packer.Env_Packer`` uses; the default is ``SyntheticVecEnv`` (no JVM here).
+    Data-parallel (``microbeast_b200.launch`` under torchrun): every rank calls this with the same ``seed`` (identical
+    model replicas), its own ``rank_seed`` (different environments and sampling streams) and a ``reducer``; every rank
+    then performs the same number of updates, which the gradient all-reduce inside ``PPO_learn`` requires.
     """
     if device is None:
         device = "cuda"
     dev = torch.device(device)
     if env_factory is None:
-        env_factory = lambda a_id, n, size: SyntheticVecEnv(n, size, seed=seed * 1000 + a_id)   # noqa: E731
+        env_factory = lambda a_id, n, size: SyntheticVecEnv(n, size, seed=seed * 1000 + a_id + 100003 * rank_seed)   # noqa: E731
     n_buffers = max(2 * n_actors, B)                                         # microbeast.py:120
 
     with open(exp_name + ".csv", "w") as f:                                  # microbeast.py:130-133
@@ -72,12 +75,12 @@ def train(exp_name: str, *, env_factory: Optional[Callable[[int, int, int], obje
     server = None
     if batched_inference:                 # one batched get_action for all actors (inference.py)
         from .inference import InferenceServer
-        server = InferenceServer(model, max_batch_envs=n_actors * n_envs, seed=seed, model_lock=model_lock).start()
+        server = InferenceServer(model, max_batch_envs=n_actors * n_envs, seed=seed + 15485863 * rank_seed, model_lock=model_lock).start()
     threads = []
     for i in range(n_actors):                                                # microbeast.py:179-191
         th = threading.Thread(target=act, daemon=True,
                               args=(model, n_envs, T, buffers, i, free_queue, full_queue, T, exp_name),
-                              kwargs=dict(envs=env_factory(i, n_envs, env_size), seed=seed * 7919 + i, server=server,
+                              kwargs=dict(envs=env_factory(i, n_envs, env_size), seed=seed * 7919 + i + 104729 * rank_seed, server=server,
                                           model_lock=model_lock))
         th.start()
         threads.append(th)

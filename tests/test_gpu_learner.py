@@ -1,4 +1,5 @@
 """The drop-in Agent.get_action / PPO_learn on the GPU against the oracle's CPU learner step."""
+import os
 import numpy as np
 import pytest
 import torch
@@ -510,3 +511,34 @@ def test_tensor_core_actor_is_as_accurate_as_cublas(preset, h):
     assert lg_t < 2e-6 and lg_t < 4 * lg_c + 1e-7, (lg_t, lg_c)
     assert lp_t < 1.0, (lp_t, lp_c)                       # 1e-5 even on these O(100..7000) logits
     assert en_t < 3 * en_c + 1.0, (en_t, en_c)            # the entropy is ill-conditioned there for cuBLAS too
+
+
+def test_torchrun_launcher_drives_train_and_keeps_the_loss_csv(tmp_path):
+    """``python -m torch.distributed.run ... -m microbeast_b200.launch``: one rank per visible GPU (two
+    when there are at least two), the reference's two CSV files from rank 0 (microbeast.py:130-139,233-239), the
+    same number of updates and bit-identical replicas on every rank."""
+    import csv
+    import subprocess
+    import sys
+    nproc = 2 if torch.cuda.device_count() >= 2 else 1
+    exp = str(tmp_path / "run")
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={nproc}",
+           "--master-addr", "127.0.0.1", "--master-port", str(29600 + (os.getpid() % 300)),
+           "-m", "microbeast_b200.launch", "--exp_name", exp, "--n_actors", "2", "--n_envs", "3", "--env_size", "8",
+           "--T", "8", "--B", "2", "--total_steps", str(8 * 3 * 2 * 3 * nproc)]
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    res = subprocess.run(cmd, cwd=root, capture_output=True, text=True, timeout=600)
+    assert res.returncode == 0, res.stdout[-2000:] + res.stderr[-4000:]
+    with open(exp + "Losses.csv") as f:
+        rows = list(csv.reader(f))
+    assert rows[0] == ["update", "pg_loss", "value_loss", "entropy_loss", "total_loss", "update time"]
+    assert len(rows) == 1 + 3 and all(len(r) == 6 for r in rows[1:])
+    assert all(np.isfinite(float(v)) for r in rows[1:] for v in r[1:5])
+    assert os.path.isfile(exp + ".csv")
+    if nproc == 2:
+        assert os.path.isfile(exp + ".rank1Losses.csv")
+        with open(exp + ".rank1Losses.csv") as f:
+            other = list(csv.reader(f))
+        # the logged losses are the global means: the same numbers on every rank
+        assert [r[1:5] for r in other[1:]] == [r[1:5] for r in rows[1:]]
+        assert "identical on every rank: True" in res.stdout

@@ -60,10 +60,32 @@ def _worker(rank, world, port, ret):
         assert red.world_size == world and red.rank == rank
         four = red.allreduce(agent, four)
         flat = torch.cat([p.grad.reshape(-1) for p in agent.parameters()])
+        # the overlapped path (gradients are views of the bucket, head slice reduced from a hook) gives the same sums
+        red2 = parallel.GradAllReducer()
+        agent2, _ = _make(4, rows, T, seed=11)
+        red2.begin(agent2)
+        out, _ = agent2.get_action(shard, learning=True)
+        from oracle.vtrace import vtrace_losses
+        r = hi - lo
+        rs = lambda x: x.reshape((r, T + 1) + tuple(x.shape[1:]))
+        lp, base, ent = rs(out["logprobs"]), rs(out["baseline"].flatten()), rs(out["entropy"])
+        res = vtrace_losses(rs(shard["logprobs"])[:, 1:], lp[:, :-1], base[:, :-1], base[:, -1],
+                            rs(shard["reward"])[:, 1:], rs(shard["done"])[:, 1:], ent[:, :-1])
+        four2 = torch.stack([res["pg_loss"], res["value_loss"], res["entropy_loss"], res["total_loss"]]) * (r / float(rows))
+        four2[3].backward()
+        early_fired = red2._early is not None
+        four2 = red2.finish(four2.detach())
+        flat2 = torch.cat([p.grad.reshape(-1) for p in agent2.parameters()])
+        views = all(p.grad.data_ptr() >= red2._grads.data_ptr() and
+                    p.grad.data_ptr() < red2._grads.data_ptr() + red2._grads.numel() * 4 for p in agent2.parameters())
         if rank == 0:
             ret["four"] = four.numpy()
             ret["grad"] = flat.numpy()
             ret["calls"] = red.calls
+            ret["four2"] = four2.numpy()
+            ret["grad2"] = flat2.numpy()
+            ret["early"] = early_fired
+            ret["views"] = views
     finally:
         dist.destroy_process_group()
 
@@ -74,6 +96,7 @@ def test_two_rank_gradient_sum_equals_full_batch():
         ret = mgr.dict()
         mp.spawn(_worker, args=(world, port, ret), nprocs=world, join=True)
         four, grad, calls = np.array(ret["four"]), np.array(ret["grad"]), ret["calls"]
+        four2, grad2, early, views = np.array(ret["four2"]), np.array(ret["grad2"]), ret["early"], ret["views"]
     torch.set_num_threads(1)
     rows, T = 4, 6
     agent, batch = _make(4, rows, T, seed=11)
@@ -83,6 +106,9 @@ def test_two_rank_gradient_sum_equals_full_batch():
     np.testing.assert_allclose(four, want_four, rtol=2e-6, atol=1e-7)
     scale = np.abs(want_grad).max()
     assert np.abs(grad - want_grad).max() <= 2e-6 * scale
+    assert early and views, "the head slice must go out from the hook, and gradients must stay views of the bucket"
+    np.testing.assert_allclose(four2, want_four, rtol=2e-6, atol=1e-7)
+    assert np.abs(grad2 - want_grad).max() <= 2e-6 * scale
 
 
 def test_single_process_reducer_is_a_no_op():
