@@ -495,8 +495,25 @@ def run_ours(args):
             "note": "fp32-accurate product as three TF32 tensor-core products of hi/lo-split operands; TF32 peak taken as "
                     "half the measured dense bf16 rate of MEASURED_PEAKS.json"})
 
+    roof_hbm = roof
+    if "actor_head_fwd" in kernels and "issued_tf32_tflops" in kernels["actor_head_fwd"] and \
+            (roof is None or kernels["actor_head_fwd"]["avg_ms"] > roof["avg_launch_ms"]):
+        kf = kernels["actor_head_fwd"]
+        # The dominant kernel of the path is now the fused actor Linear + policy head, which is bound by the tensor
+        # pipe.  Its arithmetic is DEFINED as three TF32 products per fp32 product: algorithmic flops
+        # per launch = 3 * 2 * frames * (80 * cells) * 256, against the TF32 dense peak = half the measured bf16 rate.
+        roof = {"kernel": "actor_head_fwd", "bound": "tensor", "achieved": kf["issued_tf32_tflops"],
+                "peak": kf["tf32_peak_tflops"], "unit": "TFLOP/s", "frac": kf["frac_of_tf32_peak_issued"], "traffic": None,
+                "peak_source": "MEASURED_PEAKS.json bf16_tflops / 2 (TF32 runs at half the bf16 rate)",
+                "alg_flops_per_launch": 3.0 * 2.0 * ops.launch_notes["actor_head_fwd"]["m"] *
+                                        (80 * ops.launch_notes["actor_head_fwd"]["cells"]) * ops.launch_notes["actor_head_fwd"]["k"],
+                "fp32_equivalent_tflops": kf["algorithmic_tflops_fp32"],
+                "frac_of_bf16_peak": kf["issued_tf32_tflops"] / (2 * kf["tf32_peak_tflops"]),
+                "avg_launch_ms": kf["avg_ms"], "kernel_share_of_step": kf["avg_ms"] / ms_step}
+
     # ---- e2e: host batch through the public call ---------------------------------------
     e2e = None
+    e2e_other = None
     if not args.no_e2e:
         from microbeast_b200 import buffers as mbuf
         wire = {k: v.cpu() for k, v in dev_batch.items()}
@@ -506,14 +523,41 @@ def run_ours(args):
         host = {k: torch.empty(v.shape, dtype=v.dtype, pin_memory=True).copy_(v) for k, v in wire.items()}
         h2d = sum(v.numel() * v.element_size() for v in host.values())
         e2e_steps = max(3, min(args.steps, 10))
-        ms_e2e, _, _, _ = timed(lambda: step(host, True), e2e_steps, 3)
+        # serial: PPO_learn(host batch) copies, then computes.  pipelined (the headline): learner.BatchPrefetcher stages
+        # batch k+1 on a side stream while step k runs -- every step still pays its own host->device copy and the
+        # device->host read of its four losses inside the timed region, they just overlap the previous step's kernels
+        ms_serial, _, _, _ = timed(lambda: step(host, True), max(3, e2e_steps // 2), 3)
+        from microbeast_b200.learner import BatchPrefetcher
+        pf = BatchPrefetcher(dev)
+        state = {"next": pf.submit(host)}
+
+        def e2e_step():
+            cur = state["next"]
+            state["next"] = pf.submit(host)
+            return step(cur, True)
+        ms_e2e, _, _, _ = timed(e2e_step, e2e_steps, 3)
+        torch.cuda.synchronize()
+        del state, pf
         e2e = {"value": frames / (ms_e2e * 1e-3), "unit": UNIT, "h2d_bytes_per_step": h2d * world,
                "d2h_bytes_per_step": 16 * world, "ms_per_step": ms_e2e, "steps": e2e_steps,
-               "call": "microbeast_b200.learner.PPO_learn(model, model, name, pinned_host_batch, adam, rows, T, 1)",
+               "call": "cur, nxt = nxt, BatchPrefetcher.submit(pinned_host_batch); PPO_learn(model, model, name, cur, adam, "
+                       "rows, T, 1)  (microbeast_b200.learner)",
+               "serial": {"value": frames / (ms_serial * 1e-3), "ms_per_step": ms_serial,
+                          "call": "PPO_learn(model, model, name, pinned_host_batch, adam, rows, T, 1): copy, then compute"},
                "wire_format": ("obs one int32 per cell (27 binary planes), action_mask bit-packed, action u8 -- widened "
                                "on the device by mb_unpack_obs / mb_unpack_rollout; reward/logprobs f32, done bool") if args.wire == "compact"
                else "obs u8, action_mask u8, action i64, reward/logprobs f32, done bool"}
         del host
+        # the other wire format, for the record: compact is an opt-in of create_buffers
+        other = {k: v.cpu() for k, v in dev_batch.items()}
+        other["obs"] = batch["obs"].cpu()
+        if args.wire != "compact":
+            other = mbuf.pack_batch(other)
+        host2 = {k: torch.empty(v.shape, dtype=v.dtype, pin_memory=True).copy_(v) for k, v in other.items()}
+        ms_o, _, _, _ = timed(lambda: step(host2, True), 3, 2)
+        e2e_other = {"wire": "plain" if args.wire == "compact" else "compact", "value": frames / (ms_o * 1e-3), "unit": UNIT,
+                     "ms_per_step": ms_o, "h2d_bytes_per_step": sum(v.numel() * v.element_size() for v in host2.values()) * world}
+        del host2, other
 
     # ---- informational only: the same step with PyTorch's TF32 convolutions / matmuls allowed ----
     # (the encoder is PyTorch's; `value` above keeps it in strict fp32 so that "dtype": "f32" holds)
@@ -554,6 +598,57 @@ def run_ours(args):
         except Exception as exc:        # report, do not hide: the headline above does not depend on it
             info = dict(info or {})
             info["graphed"] = {"error": f"{type(exc).__name__}: {exc}"[:300]}
+
+    info = dict(info or {})
+    if e2e_other is not None:
+        info["e2e_other_wire"] = e2e_other
+    if roof_hbm is not None and roof_hbm is not roof:
+        info["roofline_hbm"] = roof_hbm
+
+    # ---- acting mode: Agent.get_action (encoder + mb_head_sample) latency at small frame counts ------------------
+    if rank == 0 and not args.no_graph_info:
+        acting = {}
+        for n_act in (6, 60, 600):
+            env_out = dict(obs=batch["obs"][:n_act].float().view((1, 1, n_act) + tuple(batch["obs"].shape[1:])),
+                           action_mask=batch["action_mask"][:n_act].view(1, n_act, -1))
+            u = torch.rand((n_act, 7 * cells), device=dev)
+            with torch.no_grad():
+                for _ in range(5):
+                    model.get_action(env_out, uniforms=u)
+                torch.cuda.synchronize()
+                t0 = time.perf_counter()
+                for _ in range(20):
+                    out_a, _ = model.get_action(env_out, uniforms=u)
+                    out_a["action"].cpu()                    # an actor needs the actions on the host (microbeast.py:91)
+                wall = (time.perf_counter() - t0) / 20
+                ops.start_kernel_timing()
+                for _ in range(10):
+                    model.get_action(env_out, uniforms=u)
+                kt = ops.stop_kernel_timing()
+            acting[str(n_act)] = {"get_action_wall_us": wall * 1e6,
+                                  "head_sample_kernel_us": 1e3 * sum(kt.get("head_sample", [0])) / max(len(kt.get("head_sample", [1])), 1)}
+        info["acting_mode"] = {"frames": acting, "note": "Agent.get_action(learning=False) end to end on the host clock "
+                               "(encoder + actor Linear + mb_head_sample + action D2H) and the sampling kernel alone"}
+
+    # ---- configs[2] as written: 1024 rows in total, split over the ranks (strong scaling) ---------------------------
+    if args.workload == "c2" and not args.no_graph_info:
+        try:
+            rows3 = 1024 // world
+            b3 = synth.make_rollout_batch(h, w, T, rows3, seed=4321 + rank, device=dev, preset=args.preset,
+                                          obs_dtype=torch.uint8, full_keys=False)
+            with torch.no_grad():
+                o3, _ = model.get_action(b3, learning=True, policy_logits=False)
+                b3["logprobs"] = o3["logprobs"] + 0.3 * torch.randn_like(o3["logprobs"])
+                del o3
+            d3 = {k: b3[k] for k in LEARNER_KEYS}
+            ms3, _, _, _ = timed(lambda: PPO_learn(model, model, "bench", d3, opt, rows3, T, 1, reducer=reducer, sync=False),
+                                 max(3, min(args.steps, 5)), 3)
+            info["c3_strong"] = {"rows_total": 1024, "rows_per_gpu": rows3, "n_gpus": world, "ms_per_step": ms3,
+                                 "value": 1024 * T / (ms3 * 1e-3), "unit": UNIT,
+                                 "note": "BASELINE configs[2]: 16x16, T=80, B=1024 rows in total over the ranks, batch resident"}
+            del b3, d3
+        except Exception as exc:
+            info["c3_strong"] = {"error": f"{type(exc).__name__}: {exc}"[:300]}
 
     # ---- cpu baseline (rank 0, N=1) ------------------------------------------------------
     cpu = None

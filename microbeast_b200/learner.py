@@ -31,12 +31,15 @@ class _Stager:
     (0.7 GB at 16x16, T=80, 256 rows) overlaps the encoder forward of the same step.
     """
 
-    def __init__(self):
+    def __init__(self, slots: int = 1, obs_on_side_stream: bool = False):
         self.buffers = {}
         self.streams = {}
+        self.slots = max(int(slots), 1)
+        self.turn = 0
+        self.obs_on_side_stream = obs_on_side_stream
 
     def _buf(self, name, shape, dtype, device):
-        key = (name, tuple(shape), dtype, device)
+        key = (name, tuple(shape), dtype, device, self.turn % self.slots)
         buf = self.buffers.get(key)
         if buf is None:
             buf = self.buffers[key] = torch.empty(tuple(shape), dtype=dtype, device=device)
@@ -59,7 +62,7 @@ class _Stager:
                 out[k] = t
                 continue
             buf = self._buf(k, t.shape, t.dtype, device)
-            if k == "obs":
+            if k == "obs" and not self.obs_on_side_stream:
                 buf.copy_(t, non_blocking=True)
             else:
                 with torch.cuda.stream(side):
@@ -82,10 +85,38 @@ class _Stager:
                 out["action"] = act
         ready = torch.cuda.Event()
         ready.record(side)
+        self.turn += 1
         return out, ready
 
 
 _stager = _Stager()
+
+
+class BatchPrefetcher:
+    """Double-buffered host -> device staging: ``submit(host_batch)`` starts the copies (and the widening of the
+    compact wire format) of the NEXT batch on a side stream and returns at once; the dictionary it returns goes to
+    ``PPO_learn`` / ``learner_losses`` like any device batch (they wait for its ``"_ready"`` event).  Submitting batch
+    k+1 before calling ``PPO_learn`` on batch k hides the transfer behind step k -- what the reference's commented-out
+    ``.to(device)`` (``libs/utils.py:216``) would pay in full on every update, and what eight ranks sharing one host's
+    memory bandwidth otherwise all pay at the same moment.
+
+        pf = BatchPrefetcher(device); nxt = pf.submit(get_batch(...))
+        while training:
+            cur, nxt = nxt, pf.submit(get_batch(...))
+            PPO_learn(model, model, name, cur, optimizer, B, T, n_envs)
+    """
+
+    def __init__(self, device, slots: int = 2):
+        self.device = torch.device(device)
+        self._stager = _Stager(slots=slots, obs_on_side_stream=True)
+
+    def submit(self, batch: Dict[str, torch.Tensor], keys=LEARNER_KEYS) -> Dict[str, torch.Tensor]:
+        out, ready = self._stager.stage(batch, self.device, keys)
+        out = dict(out)
+        if ready is not None:
+            out["_ready"] = ready
+            out["_ready_all"] = True           # obs too came over the side stream: wait before the encoder
+        return out
 
 
 def batch_to_device(batch: Dict[str, torch.Tensor], device, keys=LEARNER_KEYS):
@@ -170,6 +201,10 @@ def PPO_learn(actor_model: nn.Module, learner_model, exp_name: str, batch, optim
         dev_batch, ready = batch_to_device(batch, device)
         if ready is not None:
             dev_batch["_ready"] = ready
+        elif "_ready" in batch:                 # staged ahead of time by a BatchPrefetcher
+            dev_batch["_ready"] = batch["_ready"]
+            if batch.get("_ready_all"):
+                torch.cuda.current_stream().wait_event(batch["_ready"])
         world = reducer.world_size if reducer is not None else 1
         keep = getattr(learner_model, "sparse_head", None)
         if sparse_head is not None:
