@@ -243,6 +243,24 @@ MB_API int mb_actor_head_fwd(const float* a_hi, const float* a_lo, const float* 
                              int32_t logits_alive_only, float* logp_out, float* ent_out, int64_t n_frames,
                              int32_t cells, int32_t k, int32_t* status, void* stream);
 
+/* Backward of actor Linear + policy head over the cells that can have a gradient (reference: loss.backward(),
+ * libs/utils.py:334, through model.py:167-214; a cell without a valid action has exactly zero gradient, quirk Q1).
+ * Everything runs on the device, nothing synchronises with the host: per cell the frames with a valid action are
+ * listed in ascending order, dlogits of those (frame, cell) pairs is formed from the pair's logits (`logits`
+ * [n_frames, 78*cells]: only the cells with a valid action are read, which is what mb_actor_head_fwd writes with
+ * logits_alive_only), its cell record and the frame's upstream gradients g_logp / g_ent [n_frames], and two fp32 FMA
+ * products give
+ *   d_hidden [n_frames, 256] = sum over the frame's alive cells of dlogits . W_cell      (zeroed, then vector atomics)
+ *   d_weight [78*cells, 256] = sum over the cell's alive frames of dlogits^T hidden_row  (zeroed, then vector atomics)
+ *   d_bias   [78*cells]      = sum of dlogits.
+ * hidden [n_frames, 256], weight [78*cells, 256], cell_meta from mb_pack_cells.  k must be 256, cells <= 1024.
+ * workspace: >= mb_cells_bwd_workspace_bytes(n_frames, cells) bytes (the lists, sized for the worst case), 16-byte
+ * aligned, contents irrelevant.  Atomic accumulation order varies from run to run (as torch's index_add_ does). */
+MB_API size_t mb_cells_bwd_workspace_bytes(int64_t n_frames, int32_t cells);
+MB_API int mb_cells_bwd(const float* hidden, const float* weight, const float* logits, const void* cell_meta,
+                        const float* g_logp, const float* g_ent, float* d_hidden, float* d_weight, float* d_bias,
+                        void* workspace, size_t workspace_bytes, int64_t n_frames, int32_t cells, int32_t k, void* stream);
+
 /* Backward of max_pool2d(kernel 3, stride 2, padding 1) (reference model.py:96) from the argmax
  * indices of the forward: dy, idx [planes, (h+1)/2, (w+1)/2] (idx = flat position in the h*w input
  * plane, as torch.nn.functional.max_pool2d(..., return_indices=True) returns it), dx [planes, h, w]. */

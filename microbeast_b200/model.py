@@ -171,6 +171,9 @@ TENSOR_CORE_ACTOR = True
 # learner mode: actor Linear and policy head as ONE tcgen05 kernel (mb_actor_head_fwd): the logits stay in tensor memory,
 # only the cells that have a valid action are written out (for the backward pass); off: mb_linear_tf32x3 + mb_head_eval_fwd
 FUSED_ACTOR_HEAD = True
+# backward of the actor head by mb_cells_bwd (device-side cell lists, no host sync) whenever the fused forward ran and
+# Agent.sparse_backward is not False; off: the round-1 torch cell-list path (nonzero + bmm + index_add_)
+CELL_KERNEL_BACKWARD = True
 
 
 def cell_list(action_mask: torch.Tensor, cells: int, auto: bool):
@@ -260,8 +263,10 @@ class _ActorHead(torch.autograd.Function):
             meta = ops.pack_cells(action_mask, action, cells)
             fused = ops.actor_head_fwd(hidden, ops.pack_actor_weight(weight, bias, cells), meta,
                                        want_logits=True if want_logits else "alive")
+        ctx.meta = None
         if fused is not None:
             logprobs, entropy, _cell_out, logits = fused
+            ctx.meta = meta
         else:
             logits = ops.linear_tf32x3(hidden, weight, bias) if TENSOR_CORE_ACTOR else None    # model.py:167
             if logits is None:
@@ -278,6 +283,10 @@ class _ActorHead(torch.autograd.Function):
         n, cells = hidden.shape[0], ctx.cells
         g_lp = torch.zeros(n, device=hidden.device) if g_lp is None else g_lp.contiguous()
         g_ent = torch.zeros(n, device=hidden.device) if g_ent is None else g_ent.contiguous()
+        if ctx.meta is not None and ctx.mode and CELL_KERNEL_BACKWARD and hidden.shape[1] == 256 and cells <= 1024:
+            # the device-side cell lists + the fp32 FMA products of csrc/cells.cu: no host synchronisation, capturable
+            g_hidden, g_weight, g_bias = ops.cells_bwd(hidden, weight, logits, ctx.meta, g_lp, g_ent)
+            return g_hidden, g_weight, g_bias, None, None, None, None, None
         # "auto": below ~1e6 (frame, cell) pairs the dense GEMMs cost less than the list's bookkeeping and its two
         # host synchronisations (8x8 maps are launch-bound, profiles/r01_bench_c1_n1.json)
         small = ctx.mode == "auto" and n * cells < _SPARSE_BACKWARD_MIN_PAIRS

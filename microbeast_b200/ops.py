@@ -442,6 +442,42 @@ def actor_head_fwd(hidden: torch.Tensor, packed_weight, cell_meta: torch.Tensor,
     return logp, ent, cell_out, logits
 
 
+_cells_ws: Dict[Tuple[int, int], torch.Tensor] = {}
+
+
+def cells_bwd(hidden: torch.Tensor, weight: torch.Tensor, logits: torch.Tensor, cell_meta: torch.Tensor,
+              g_logp: torch.Tensor, g_ent: torch.Tensor):
+    """``(d_hidden [N,256], d_weight [78C,256], d_bias [78C])`` of actor Linear + policy head over the cells with a valid
+    action, entirely on the device and without a host synchronisation (``mb_cells_bwd``).  ``logits`` needs valid
+    values only in those cells (``actor_head_fwd(..., want_logits="alive")``)."""
+    dev = _need_cuda(hidden=hidden, weight=weight, logits=logits, cell_meta=cell_meta, g_logp=g_logp, g_ent=g_ent)
+    hidden = _as(hidden, torch.float32, "hidden")
+    weight = _as(weight, torch.float32, "weight")
+    logits = _as(logits, torch.float32, "logits")
+    g_logp = _as(g_logp, torch.float32, "g_logp")
+    g_ent = _as(g_ent, torch.float32, "g_ent")
+    n, k = hidden.shape
+    cells = cell_meta.shape[0]
+    if k != 256 or tuple(weight.shape) != (cells * LOGITS_PER_CELL, k) or tuple(logits.shape) != (n, cells * LOGITS_PER_CELL) \
+            or tuple(cell_meta.shape) != (cells, n, 4) or g_logp.numel() != n or g_ent.numel() != n:
+        raise ValueError("cells_bwd: shape mismatch (hidden [N,256], weight [78C,256], logits [N,78C], cell_meta [C,N,4])")
+    need = int(lib.mb_cells_bwd_workspace_bytes(n, cells))
+    idx = dev.index if dev.index is not None else torch.cuda.current_device()
+    ws = _cells_ws.get((idx, 0))
+    if ws is None or ws.numel() < need:
+        if ws is not None:
+            _retired_workspaces.append(ws)          # a captured graph may still address it
+        ws = torch.empty(need, dtype=torch.uint8, device=dev)
+        _cells_ws[(idx, 0)] = ws
+    d_hidden = torch.empty_like(hidden)
+    d_weight = torch.empty_like(weight)
+    d_bias = torch.empty(cells * LOGITS_PER_CELL, dtype=torch.float32, device=dev)
+    with torch.cuda.device(dev), _Launch("cells_bwd", note={"n": n, "cells": cells}):
+        _check(lib.mb_cells_bwd(_ptr(hidden), _ptr(weight), _ptr(logits), _ptr(cell_meta), _ptr(g_logp), _ptr(g_ent),
+                                _ptr(d_hidden), _ptr(d_weight), _ptr(d_bias), _ptr(ws), ws.numel(), n, cells, k, _stream()))
+    return d_hidden, d_weight, d_bias
+
+
 def maxpool3s2_bwd(dy: torch.Tensor, idx: torch.Tensor, h: int, w: int) -> torch.Tensor:
     """``dx [n,c,h,w]`` of ``max_pool2d(x, 3, stride=2, padding=1)`` from ``dy`` and the forward's argmax
     indices (both ``[n,c,(h+1)//2,(w+1)//2]``)."""

@@ -90,3 +90,33 @@ def test_pack_cells_flags_bad_actions_and_packs_bits():
     ops.pack_cells(mask.cuda(), action.cuda(), cells)
     with pytest.raises(ValueError):
         ops.check_status(torch.device("cuda", 0))
+
+
+@pytest.mark.parametrize("n,cells,preset", [(300, 64, "dense"), (97, 16, "all_valid"), (2000, 256, "dense"), (33, 9, "one_valid"),
+                                            (64, 64, "all_masked"), (5, 4, "realistic")])
+def test_cells_backward_matches_autograd_of_the_oracle(n, cells, preset):
+    """mb_cells_bwd (device-side lists of the cells with a valid action + two fp32 products) against torch autograd
+    through the oracle head on the CPU: d hidden, d weight, d bias within 1e-5 (rms norm)."""
+    from microbeast_b200 import ops
+    from oracle.head import head_eval_fast
+    hidden, weight, bias, mask, action = _case(n, cells, 256, preset, seed=n * 3 + cells)
+    g = torch.Generator().manual_seed(n)
+    g_lp, g_en = torch.randn(n, generator=g), torch.randn(n, generator=g) * 0.1
+    h = hidden.clone().requires_grad_(True)
+    w = weight.clone().requires_grad_(True)
+    b = bias.clone().requires_grad_(True)
+    lp, en = head_eval_fast(torch.addmm(b, h, w.t()), mask, action)
+    ((lp * g_lp).sum() + (en * g_en).sum()).backward()
+    d = lambda t: t.cuda()
+    meta = ops.pack_cells(d(mask), d(action), cells)
+    _, _, _, logits = ops.actor_head_fwd(d(hidden), ops.pack_actor_weight(d(weight), d(bias), cells), meta, want_logits="alive")
+    dh, dw, db = ops.cells_bwd(d(hidden), d(weight), logits, meta, d(g_lp), d(g_en))
+    dh2, dw2, db2 = ops.cells_bwd(d(hidden), d(weight), logits, meta, d(g_lp), d(g_en))       # buffers re-zeroed, lists rebuilt
+    for name, got, again, want in (("d_hidden", dh, dh2, h.grad), ("d_weight", dw, dw2, w.grad), ("d_bias", db, db2, b.grad)):
+        if float(want.abs().max()) == 0.0:
+            assert not got.any() and not again.any(), name
+            continue
+        ok, worst = close_rms(got, want, 1e-5)
+        assert ok, f"{name}: {worst:.2f}x the 1e-5 bound"
+        ok, worst = close_rms(again, want, 1e-5)
+        assert ok, f"{name} (second call): {worst:.2f}x the 1e-5 bound"
