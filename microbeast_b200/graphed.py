@@ -36,8 +36,9 @@ class GraphedLearner:
     plain SGD works as is).  The first ``step`` runs ``warmup`` eager steps on its batch (cuDNN
     autotuning, lazy handles, optimiser-state allocation) and then puts the weights and the optimiser
     state back in place -- state tensors the warm-up created are reset to zeros -- before capturing.
-    The model's ``sparse_head`` must be False: the cell-list path sizes its tensors from the data
-    and synchronises, which a captured graph cannot do.
+    The model's ``sparse_head`` must be False: that (torch) cell-list path sizes its tensors from the data
+    and synchronises, which a captured graph cannot do.  The default backward of the actor head -- device-side cell
+    lists, ``mb_cells_bwd`` -- has no such limit and is captured as is.
     """
 
     def __init__(self, learner_model: nn.Module, optimizer: torch.optim.Optimizer, B: int, T: int, n_envs: int = 1, *,
@@ -94,9 +95,10 @@ class GraphedLearner:
 
     # ---- the step, as PPO_learn runs it ------------------------------------------------------
     def _forward_backward(self):
-        # the cell-list backward of the actor head sizes tensors from the data (host syncs): dense here
+        # "kernel": the device-side cell-list backward (mb_cells_bwd, no host sync) when the fused forward ran, else the
+        # dense kernels; never the torch cell-list path, which sizes tensors from the data and synchronises
         keep = getattr(self.model, "sparse_backward", False)
-        self.model.sparse_backward = False
+        self.model.sparse_backward = "kernel" if keep else False
         try:
             loss4, _ = learner_losses(self.model, self._device_batch(), self.rows, self.T, **self.kw)
             loss4[3].backward()                                                            # utils.py:334

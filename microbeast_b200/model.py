@@ -290,7 +290,8 @@ class _ActorHead(torch.autograd.Function):
         # "auto": below ~1e6 (frame, cell) pairs the dense GEMMs cost less than the list's bookkeeping and its two
         # host synchronisations (8x8 maps are launch-bound, profiles/r01_bench_c1_n1.json)
         small = ctx.mode == "auto" and n * cells < _SPARSE_BACKWARD_MIN_PAIRS
-        cl = cell_list(action_mask, cells, auto=(ctx.mode == "auto")) if (ctx.mode and not small) else None
+        use_list = ctx.mode and ctx.mode != "kernel" and not small          # "kernel" without the kernel path: dense
+        cl = cell_list(action_mask, cells, auto=(ctx.mode == "auto")) if use_list else None
         if cl is None:
             dlogits = ops.head_eval_bwd(logits, action_mask, action, g_lp, g_ent)
             return dlogits @ weight, dlogits.t() @ hidden, dlogits.sum(dim=0), None, None, None, None, None
