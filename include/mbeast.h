@@ -222,7 +222,9 @@ MB_API int mb_linear_tf32x3(const float* a_hi, const float* a_lo, const float* b
  * need not exist in memory).  Three steps:
  *   mb_pack_cells         mask [n_frames, 78*cells] u8 + action [n_frames, 7*cells] i64 -> cell_meta [cells][n_frames]
  *                         records of 16 B (78 mask bits, seven 6-bit action indices); out-of-range actions are clamped
- *                         and flagged in `status` (torch validate_args raises there, model.py:38).
+ *                         and flagged in `status` (torch validate_args raises there, model.py:38).  alive_bits (optional)
+ *                         [cells][ceil(n_frames/32)] u32: bit i of word w = frame 32w+i has a valid action in the cell
+ *                         (what mb_cells_bwd builds its lists from).
  *   mb_pack_actor_weight  weight [78*cells, k], bias [78*cells] -> TF32 hi / lo copies w_hi, w_lo [80*cells, k] with
  *                         every cell's 78 rows padded to 80, bias_p [80*cells].  Once per weight update.
  *   mb_actor_head_fwd     a_hi, a_lo [n_frames, k] = the TF32 hi / lo parts of `hidden` (mb_split_tf32); three TF32
@@ -234,8 +236,8 @@ MB_API int mb_linear_tf32x3(const float* a_hi, const float* a_lo, const float* b
  *                         logits_alive_only != 0 only cells that have a valid action are written (the rest of the
  *                         buffer is left untouched) -- all a backward pass needs, at a fraction of the traffic.
  * k % 32 == 0; every pointer 16-byte aligned. */
-MB_API int mb_pack_cells(const uint8_t* mask, const int64_t* action, void* cell_meta, int64_t n_frames, int32_t cells,
-                         int32_t* status, void* stream);
+MB_API int mb_pack_cells(const uint8_t* mask, const int64_t* action, void* cell_meta, void* alive_bits, int64_t n_frames,
+                         int32_t cells, int32_t* status, void* stream);
 MB_API int mb_pack_actor_weight(const float* weight, const float* bias, float* w_hi, float* w_lo, float* bias_p,
                                 int32_t cells, int32_t k, void* stream);
 MB_API int mb_actor_head_fwd(const float* a_hi, const float* a_lo, const float* w_hi, const float* w_lo,
@@ -253,12 +255,14 @@ MB_API int mb_actor_head_fwd(const float* a_hi, const float* a_lo, const float* 
  *   d_hidden [n_frames, 256] = sum over the frame's alive cells of dlogits . W_cell      (zeroed, then vector atomics)
  *   d_weight [78*cells, 256] = sum over the cell's alive frames of dlogits^T hidden_row  (zeroed, then vector atomics)
  *   d_bias   [78*cells]      = sum of dlogits.
- * hidden [n_frames, 256], weight [78*cells, 256], cell_meta from mb_pack_cells.  k must be 256, cells <= 1024.
+ * hidden [n_frames, 256], weight [78*cells, 256], cell_meta and alive_bits from mb_pack_cells.  k must be 256,
+ * cells <= 1024.
  * workspace: >= mb_cells_bwd_workspace_bytes(n_frames, cells) bytes (the lists, sized for the worst case), 16-byte
  * aligned, contents irrelevant.  Atomic accumulation order varies from run to run (as torch's index_add_ does). */
 MB_API size_t mb_cells_bwd_workspace_bytes(int64_t n_frames, int32_t cells);
 MB_API int mb_cells_bwd(const float* hidden, const float* weight, const float* logits, const void* cell_meta,
-                        const float* g_logp, const float* g_ent, float* d_hidden, float* d_weight, float* d_bias,
+                        const void* alive_bits, const float* g_logp, const float* g_ent, float* d_hidden, float* d_weight,
+                        float* d_bias,
                         void* workspace, size_t workspace_bytes, int64_t n_frames, int32_t cells, int32_t k, void* stream);
 
 /* Backward of max_pool2d(kernel 3, stride 2, padding 1) (reference model.py:96) from the argmax

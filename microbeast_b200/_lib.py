@@ -47,12 +47,12 @@ SIGNATURES = {
                                       ctypes.c_int32, ctypes.c_int32, _P]),
     "mb_split_tf32": (ctypes.c_int, [_P, _P, _P, ctypes.c_int64, _P]),
     "mb_linear_tf32x3": (ctypes.c_int, [_P, _P, _P, _P, _P, _P, ctypes.c_int64, ctypes.c_int64, ctypes.c_int32, _P, _P]),
-    "mb_pack_cells": (ctypes.c_int, [_P, _P, _P, ctypes.c_int64, ctypes.c_int32, _P, _P]),
+    "mb_pack_cells": (ctypes.c_int, [_P, _P, _P, _P, ctypes.c_int64, ctypes.c_int32, _P, _P]),
     "mb_pack_actor_weight": (ctypes.c_int, [_P, _P, _P, _P, _P, ctypes.c_int32, ctypes.c_int32, _P]),
     "mb_actor_head_fwd": (ctypes.c_int, [_P, _P, _P, _P, _P, _P, _P, _P, ctypes.c_int32, _P, _P, ctypes.c_int64,
                                          ctypes.c_int32, ctypes.c_int32, _P, _P]),
     "mb_cells_bwd_workspace_bytes": (ctypes.c_size_t, [ctypes.c_int64, ctypes.c_int32]),
-    "mb_cells_bwd": (ctypes.c_int, [_P, _P, _P, _P, _P, _P, _P, _P, _P, _P, ctypes.c_size_t, ctypes.c_int64, ctypes.c_int32,
+    "mb_cells_bwd": (ctypes.c_int, [_P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, ctypes.c_size_t, ctypes.c_int64, ctypes.c_int32,
                                     ctypes.c_int32, _P]),
     "mb_maxpool3s2_bwd": (ctypes.c_int, [_P, _P, _P, ctypes.c_int64, ctypes.c_int32, ctypes.c_int32, _P]),
     "mb_conv3x3_wgrad_blocks": (ctypes.c_int, [ctypes.c_int64, ctypes.c_int32, ctypes.c_int32, ctypes.c_int32,

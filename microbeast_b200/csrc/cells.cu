@@ -41,12 +41,13 @@ __device__ __forceinline__ int rec_action(const uint4& m, int k) {
 }
 
 // ---- lists -----------------------------------------------------------------------------------
-__global__ void __launch_bounds__(256) cell_count_kernel(const uint4* __restrict__ meta, int* __restrict__ counts, int n_frames) {
+// alive_bits [cells][words]: bit i of word w = frame 32*w + i has a valid action in the cell (written by mb_pack_cells)
+__global__ void __launch_bounds__(256) cell_count_kernel(const uint32_t* __restrict__ alive_bits, int* __restrict__ counts, int words) {
     __shared__ int part[8];
     const int c = blockIdx.x;
-    const uint4* row = meta + (long long)c * n_frames;
+    const uint32_t* row = alive_bits + (long long)c * words;
     int n = 0;
-    for (int f = threadIdx.x; f < n_frames; f += 256) n += rec_alive(__ldg(row + f)) ? 1 : 0;
+    for (int w = threadIdx.x; w < words; w += 256) n += __popc(__ldg(row + w));
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) n += __shfl_xor_sync(0xffffffffu, n, o);
     if ((threadIdx.x & 31) == 0) part[threadIdx.x >> 5] = n;
@@ -82,29 +83,39 @@ __global__ void __launch_bounds__(1024) cell_scan_kernel(const int* __restrict__
 }
 
 // per cell: alive frames in ascending order into entries[chunk_off[c] * 32 ...], tail of the last chunk = -1
-__global__ void __launch_bounds__(256) cell_fill_kernel(const uint4* __restrict__ meta, const int* __restrict__ chunk_off,
-                                                        int* __restrict__ entries, int n_frames) {
+__global__ void __launch_bounds__(256) cell_fill_kernel(const uint32_t* __restrict__ alive_bits, const int* __restrict__ chunk_off,
+                                                        int* __restrict__ entries, int words) {
     __shared__ int warp_tot[8];
     __shared__ int base_s;
     const int c = blockIdx.x;
-    const uint4* row = meta + (long long)c * n_frames;
+    const uint32_t* row = alive_bits + (long long)c * words;
     int* out = entries + (long long)chunk_off[c] * kChunk;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     if (threadIdx.x == 0) base_s = 0;
     __syncthreads();
-    for (int f0 = 0; f0 < n_frames; f0 += 256) {
-        const int f = f0 + threadIdx.x;
-        const bool alive = f < n_frames && rec_alive(__ldg(row + f));
-        const unsigned bal = __ballot_sync(0xffffffffu, alive);
-        if (lane == 0) warp_tot[warp] = __popc(bal);
+    for (int w0 = 0; w0 < words; w0 += 256) {
+        const int w = w0 + threadIdx.x;
+        uint32_t bits = w < words ? __ldg(row + w) : 0u;
+        const int n = __popc(bits);
+        int incl = n;                                       // inclusive prefix over the warp's 32 words
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const int v = __shfl_up_sync(0xffffffffu, incl, o);
+            if (lane >= o) incl += v;
+        }
+        if (lane == 31) warp_tot[warp] = incl;
         __syncthreads();
-        int before = base_s;
-        for (int w = 0; w < warp; ++w) before += warp_tot[w];
-        if (alive) out[before + __popc(bal & ((1u << lane) - 1u))] = f;
+        int pos = base_s + incl - n;
+        for (int k = 0; k < warp; ++k) pos += warp_tot[k];
+        while (bits) {                                      // the word's frames, ascending
+            const int i = __ffs(bits) - 1;
+            bits &= bits - 1;
+            out[pos++] = 32 * w + i;
+        }
         __syncthreads();
         if (threadIdx.x == 0) {
             int t = 0;
-            for (int w = 0; w < 8; ++w) t += warp_tot[w];
+            for (int k = 0; k < 8; ++k) t += warp_tot[k];
             base_s += t;
         }
         __syncthreads();
@@ -235,8 +246,10 @@ __global__ void __launch_bounds__(kGradThreads, 1) cell_grad_kernel(const float*
                  reinterpret_cast<float*>(st + kHBytes), reinterpret_cast<float*>(st + kHBytes + kDzBytes), lane);
     };
 
-    const int kt = lane;                 // this thread's 8 hidden columns: 8*kt .. 8*kt+7
-    float accW[10][8];                   // dW_c rows 10*warp .. 10*warp+9, columns of kt
+    // this thread's 8 hidden columns: 4*lane .. 4*lane+3 and 128 + 4*lane .. +3 (a warp's 128-bit loads and vector
+    // atomics then cover one contiguous 512-B run each: no bank conflicts, full sectors)
+    const int c0 = 4 * lane, c1 = kHid / 2 + 4 * lane;
+    float accW[10][8];                   // dW_c rows 10*warp .. 10*warp+9, this thread's 8 columns
     float accB[10];
 #pragma unroll
     for (int a = 0; a < 10; ++a) {
@@ -253,9 +266,9 @@ __global__ void __launch_bounds__(kGradThreads, 1) cell_grad_kernel(const float*
         for (int a = 0; a < 10; ++a) {
             const int j = 10 * warp + a;
             if (j < kLogitsPerCell) {
-                float* dst = d_weight + ((long long)cur_cell * kLogitsPerCell + j) * kHid + 8 * kt;
-                atomicAdd(reinterpret_cast<float4*>(dst), make_float4(accW[a][0], accW[a][1], accW[a][2], accW[a][3]));
-                atomicAdd(reinterpret_cast<float4*>(dst + 4), make_float4(accW[a][4], accW[a][5], accW[a][6], accW[a][7]));
+                float* dst = d_weight + ((long long)cur_cell * kLogitsPerCell + j) * kHid;
+                atomicAdd(reinterpret_cast<float4*>(dst + c0), make_float4(accW[a][0], accW[a][1], accW[a][2], accW[a][3]));
+                atomicAdd(reinterpret_cast<float4*>(dst + c1), make_float4(accW[a][4], accW[a][5], accW[a][6], accW[a][7]));
                 if (lane == 0) atomicAdd(d_bias + cur_cell * kLogitsPerCell + j, accB[a]);
             }
             accB[a] = 0.f;
@@ -300,11 +313,11 @@ __global__ void __launch_bounds__(kGradThreads, 1) cell_grad_kernel(const float*
             for (int a = 0; a < 4; ++a)
 #pragma unroll
                 for (int b = 0; b < 8; ++b) acc[a][b] = 0.f;
-#pragma unroll 2
+#pragma unroll 3
             for (int j = 0; j < kLogitsPerCell; ++j) {
                 const float4 d4 = *reinterpret_cast<const float4*>(DzT + j * kChunk + 4 * warp);
-                const float4 w0 = *reinterpret_cast<const float4*>(Wc + j * kHid + 8 * kt);
-                const float4 w1 = *reinterpret_cast<const float4*>(Wc + j * kHid + 8 * kt + 4);
+                const float4 w0 = *reinterpret_cast<const float4*>(Wc + j * kHid + c0);
+                const float4 w1 = *reinterpret_cast<const float4*>(Wc + j * kHid + c1);
                 const float d[4] = {d4.x, d4.y, d4.z, d4.w};
                 const float w[8] = {w0.x, w0.y, w0.z, w0.w, w1.x, w1.y, w1.z, w1.w};
 #pragma unroll
@@ -316,9 +329,9 @@ __global__ void __launch_bounds__(kGradThreads, 1) cell_grad_kernel(const float*
             for (int a = 0; a < 4; ++a) {
                 const int f = s_frame[s][4 * warp + a];
                 if (f >= 0) {
-                    float* dst = d_hidden + (long long)f * kHid + 8 * kt;
-                    atomicAdd(reinterpret_cast<float4*>(dst), make_float4(acc[a][0], acc[a][1], acc[a][2], acc[a][3]));
-                    atomicAdd(reinterpret_cast<float4*>(dst + 4), make_float4(acc[a][4], acc[a][5], acc[a][6], acc[a][7]));
+                    float* dst = d_hidden + (long long)f * kHid;
+                    atomicAdd(reinterpret_cast<float4*>(dst + c0), make_float4(acc[a][0], acc[a][1], acc[a][2], acc[a][3]));
+                    atomicAdd(reinterpret_cast<float4*>(dst + c1), make_float4(acc[a][4], acc[a][5], acc[a][6], acc[a][7]));
                 }
             }
         }
@@ -326,8 +339,8 @@ __global__ void __launch_bounds__(kGradThreads, 1) cell_grad_kernel(const float*
 #pragma unroll 2
         for (int e = 0; e < kChunk; ++e) {
             const float2* dp = reinterpret_cast<const float2*>(Dz + e * kPadJ + 10 * warp);
-            const float4 h0 = *reinterpret_cast<const float4*>(H + e * kHid + 8 * kt);
-            const float4 h1 = *reinterpret_cast<const float4*>(H + e * kHid + 8 * kt + 4);
+            const float4 h0 = *reinterpret_cast<const float4*>(H + e * kHid + c0);
+            const float4 h1 = *reinterpret_cast<const float4*>(H + e * kHid + c1);
             const float h[8] = {h0.x, h0.y, h0.z, h0.w, h1.x, h1.y, h1.z, h1.w};
             float d[10];
 #pragma unroll
@@ -371,7 +384,8 @@ extern "C" size_t mb_cells_bwd_workspace_bytes(int64_t n_frames, int32_t cells) 
 }
 
 extern "C" int mb_cells_bwd(const float* hidden, const float* weight, const float* logits, const void* cell_meta,
-                            const float* g_logp, const float* g_ent, float* d_hidden, float* d_weight, float* d_bias,
+                            const void* alive_bits, const float* g_logp, const float* g_ent, float* d_hidden, float* d_weight,
+                            float* d_bias,
                             void* workspace, size_t workspace_bytes, int64_t n_frames, int32_t cells, int32_t k, void* stream) {
     using namespace mb;
     if (n_frames < 0 || cells <= 0 || cells > 1024 || k != kHid || n_frames > 0x7fffffff) {
@@ -387,7 +401,7 @@ extern "C" int mb_cells_bwd(const float* hidden, const float* weight, const floa
     MB_CUDA(cudaMemsetAsync(d_bias, 0, size_t(cells) * kLogitsPerCell * sizeof(float), st));
     if (n_frames == 0) return MB_OK;
     MB_CUDA(cudaMemsetAsync(d_hidden, 0, size_t(n_frames) * kHid * sizeof(float), st));
-    if (!hidden || !weight || !logits || !cell_meta || !g_logp || !g_ent || !workspace) {
+    if (!hidden || !weight || !logits || !cell_meta || !alive_bits || !g_logp || !g_ent || !workspace) {
         set_error("mb_cells_bwd: null input pointer");
         return MB_ERR_INVALID;
     }
@@ -410,9 +424,11 @@ extern "C" int mb_cells_bwd(const float* hidden, const float* weight, const floa
     int* chunk_cell = header + 4;
     int* entries = chunk_cell + cap;
     const uint4* meta = reinterpret_cast<const uint4*>(cell_meta);
-    cell_count_kernel<<<cells, 256, 0, st>>>(meta, counts, int(n_frames));
+    const uint32_t* bits = reinterpret_cast<const uint32_t*>(alive_bits);
+    const int words = int((n_frames + 31) / 32);
+    cell_count_kernel<<<cells, 256, 0, st>>>(bits, counts, words);
     cell_scan_kernel<<<1, 1024, 0, st>>>(counts, chunk_off, chunk_cell, header, cells);
-    cell_fill_kernel<<<cells, 256, 0, st>>>(meta, chunk_off, entries, int(n_frames));
+    cell_fill_kernel<<<cells, 256, 0, st>>>(bits, chunk_off, entries, words);
     int dev = 0;
     MB_CUDA(cudaGetDevice(&dev));
     static bool attr_set[64] = {};

@@ -54,8 +54,8 @@ constexpr int kPackMaskPitch = 628, kPackActPitch = 456;
 
 __global__ void __launch_bounds__(kPackThreads) pack_cells_kernel(const uint8_t* __restrict__ mask,
                                                                   const int64_t* __restrict__ action,
-                                                                  uint4* __restrict__ meta, long long n_frames,
-                                                                  int cells, int* status) {
+                                                                  uint4* __restrict__ meta, uint32_t* __restrict__ alive_bits,
+                                                                  long long n_frames, int cells, int* status) {
     __shared__ __align__(16) uint8_t s_mask[kPackFrames * kPackMaskPitch];
     __shared__ __align__(16) uint8_t s_act[kPackFrames * kPackActPitch];
     const int cell_tiles = (cells + kPackCells - 1) / kPackCells;
@@ -103,11 +103,13 @@ __global__ void __launch_bounds__(kPackThreads) pack_cells_kernel(const uint8_t*
     }
     __syncthreads();
     const int fi = threadIdx.x & 31, ci = threadIdx.x >> 5;
-    if (fi >= nf || ci >= nc) return;
+    if (ci >= nc) return;                               // whole warps leave together (ci is the warp index)
+    const bool live = fi < nf;                          // lanes past the last frame only take part in the ballot
+    const int fr = live ? fi : 0;
     // 78 mask bytes -> 78 bits, four bytes at a time: the cell starts on an even byte of a 4-byte aligned row, so its
     // bytes are read as 21 aligned words shifted by 0 or 16 bits; per word, vcmpne4 gives 0xff per non-zero byte and
     // a multiply gathers one bit of each byte into a nibble
-    const uint32_t* mw = reinterpret_cast<const uint32_t*>(s_mask + fi * kPackMaskPitch + ((ci * kLogitsPerCell) & ~3));
+    const uint32_t* mw = reinterpret_cast<const uint32_t*>(s_mask + fr * kPackMaskPitch + ((ci * kLogitsPerCell) & ~3));
     const int sh = ((ci * kLogitsPerCell) & 2) * 8;
     uint32_t w[3] = {0u, 0u, 0u};
     uint32_t prev = mw[0];
@@ -121,7 +123,7 @@ __global__ void __launch_bounds__(kPackThreads) pack_cells_kernel(const uint8_t*
         w[(4 * i) >> 5] |= nib << ((4 * i) & 31);
     }
     w[2] &= 0x3fffu;
-    const long long* a = reinterpret_cast<const long long*>(s_act + fi * kPackActPitch + ci * kCompsPerCell * 8);
+    const long long* a = reinterpret_cast<const long long*>(s_act + fr * kPackActPitch + ci * kCompsPerCell * 8);
     constexpr int LEN[7] = {6, 4, 4, 4, 4, 7, 49};
     uint32_t act[7];
     bool bad = false;
@@ -131,13 +133,18 @@ __global__ void __launch_bounds__(kPackThreads) pack_cells_kernel(const uint8_t*
         bad = bad || v < 0 || v >= LEN[k];
         act[k] = uint32_t(v < 0 ? 0 : (v >= LEN[k] ? LEN[k] - 1 : v));       // clamped like csrc/head.cu; flagged below
     }
-    if (bad && status) atomicOr(status, kStatusBadAction);
+    if (bad && live && status) atomicOr(status, kStatusBadAction);
     uint4 r;
     r.x = w[0];
     r.y = w[1];
     r.z = w[2] | (act[0] << 14) | (act[1] << 20) | (act[2] << 26);
     r.w = act[3] | (act[4] << 6) | (act[5] << 12) | (act[6] << 18);
-    meta[(long long)(c0 + ci) * n_frames + f0 + fi] = r;
+    if (live) meta[(long long)(c0 + ci) * n_frames + f0 + fi] = r;
+    if (alive_bits) {
+        // one word per (cell, 32 frames): bit i = frame f0 + i has a valid action in this cell (the lists of mb_cells_bwd)
+        const unsigned bal = __ballot_sync(0xffffffffu, live && (w[0] | w[1] | w[2]) != 0u);
+        if (fi == 0) alive_bits[(long long)(c0 + ci) * ((n_frames + 31) / 32) + f0 / 32] = bal;
+    }
 }
 
 // W [78C, K] -> hi / lo [80C, K] (TF32 split as in gemm.cu: x = hi + lo up to 2^-22 |x|), bias -> [80C]
@@ -431,15 +438,15 @@ bool fu_map(FuEncodeFn enc, CUtensorMap* m, const float* base, long long rows, i
 
 }  // namespace
 
-int pack_cells(const uint8_t* mask, const int64_t* action, void* meta, long long n_frames, int cells, int* status,
-               cudaStream_t st) {
+int pack_cells(const uint8_t* mask, const int64_t* action, void* meta, void* alive_bits, long long n_frames, int cells,
+               int* status, cudaStream_t st) {
     const long long blocks = ((n_frames + kPackFrames - 1) / kPackFrames) * ((cells + kPackCells - 1) / kPackCells);
     if (blocks > 0x7fffffffLL) {
         set_error("mb_pack_cells: problem too large for one launch");
         return MB_ERR_INVALID;
     }
-    pack_cells_kernel<<<unsigned(blocks), kPackThreads, 0, st>>>(mask, action, reinterpret_cast<uint4*>(meta), n_frames, cells,
-                                                                 status);
+    pack_cells_kernel<<<unsigned(blocks), kPackThreads, 0, st>>>(mask, action, reinterpret_cast<uint4*>(meta),
+                                                                 reinterpret_cast<uint32_t*>(alive_bits), n_frames, cells, status);
     MB_CUDA(cudaGetLastError());
     return MB_OK;
 }
@@ -493,8 +500,8 @@ int actor_head_fwd(const float* a_hi, const float* a_lo, const float* wp_hi, con
 
 }  // namespace mb
 
-extern "C" int mb_pack_cells(const uint8_t* mask, const int64_t* action, void* cell_meta, int64_t n_frames, int32_t cells,
-                             int32_t* status, void* stream) {
+extern "C" int mb_pack_cells(const uint8_t* mask, const int64_t* action, void* cell_meta, void* alive_bits, int64_t n_frames,
+                             int32_t cells, int32_t* status, void* stream) {
     if (n_frames < 0 || cells <= 0) {
         mb::set_error("mb_pack_cells: n_frames=%lld cells=%d out of range", (long long)n_frames, cells);
         return MB_ERR_INVALID;
@@ -505,7 +512,7 @@ extern "C" int mb_pack_cells(const uint8_t* mask, const int64_t* action, void* c
         mb::set_error("mb_pack_cells: null or misaligned pointer (cell_meta 16 B, action 8 B)");
         return MB_ERR_INVALID;
     }
-    return mb::pack_cells(mask, action, cell_meta, n_frames, cells, status, static_cast<cudaStream_t>(stream));
+    return mb::pack_cells(mask, action, cell_meta, alive_bits, n_frames, cells, status, static_cast<cudaStream_t>(stream));
 }
 
 extern "C" int mb_pack_actor_weight(const float* weight, const float* bias, float* w_hi, float* w_lo, float* bias_p,

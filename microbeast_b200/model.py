@@ -267,6 +267,7 @@ class _ActorHead(torch.autograd.Function):
         if fused is not None:
             logprobs, entropy, _cell_out, logits = fused
             ctx.meta = meta
+            ctx.alive_bits = meta.alive_bits
         else:
             logits = ops.linear_tf32x3(hidden, weight, bias) if TENSOR_CORE_ACTOR else None    # model.py:167
             if logits is None:
@@ -285,7 +286,7 @@ class _ActorHead(torch.autograd.Function):
         g_ent = torch.zeros(n, device=hidden.device) if g_ent is None else g_ent.contiguous()
         if ctx.meta is not None and ctx.mode and CELL_KERNEL_BACKWARD and hidden.shape[1] == 256 and cells <= 1024:
             # the device-side cell lists + the fp32 FMA products of csrc/cells.cu: no host synchronisation, capturable
-            g_hidden, g_weight, g_bias = ops.cells_bwd(hidden, weight, logits, ctx.meta, g_lp, g_ent)
+            g_hidden, g_weight, g_bias = ops.cells_bwd(hidden, weight, logits, ctx.meta, g_lp, g_ent, ctx.alive_bits)
             return g_hidden, g_weight, g_bias, None, None, None, None, None
         # "auto": below ~1e6 (frame, cell) pairs the dense GEMMs cost less than the list's bookkeeping and its two
         # host synchronisations (8x8 maps are launch-bound, profiles/r01_bench_c1_n1.json)

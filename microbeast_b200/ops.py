@@ -391,8 +391,11 @@ def pack_cells(action_mask: torch.Tensor, action: torch.Tensor, cells: int) -> t
     if tuple(action_mask.shape) != (n, cells * LOGITS_PER_CELL) or tuple(action.shape) != (n, cells * COMPONENTS_PER_CELL):
         raise ValueError("pack_cells: action_mask must be [N, 78*cells] and action [N, 7*cells]")
     meta = torch.empty((cells, n, 4), dtype=torch.int32, device=dev)
+    alive = torch.empty((cells, (n + 31) // 32), dtype=torch.int32, device=dev)
     with torch.cuda.device(dev), _Launch("pack_cells", note={"cells": n * cells}):
-        _check(lib.mb_pack_cells(_ptr(action_mask), _ptr(action), _ptr(meta), n, cells, _ptr(status_word(dev)), _stream()))
+        _check(lib.mb_pack_cells(_ptr(action_mask), _ptr(action), _ptr(meta), _ptr(alive), n, cells,
+                                 _ptr(status_word(dev)), _stream()))
+    meta.alive_bits = alive          # [cells, ceil(N/32)]: bit i of word w = frame 32w+i has a valid action (mb_cells_bwd)
     return meta
 
 
@@ -446,7 +449,7 @@ _cells_ws: Dict[Tuple[int, int], torch.Tensor] = {}
 
 
 def cells_bwd(hidden: torch.Tensor, weight: torch.Tensor, logits: torch.Tensor, cell_meta: torch.Tensor,
-              g_logp: torch.Tensor, g_ent: torch.Tensor):
+              g_logp: torch.Tensor, g_ent: torch.Tensor, alive_bits: Optional[torch.Tensor] = None):
     """``(d_hidden [N,256], d_weight [78C,256], d_bias [78C])`` of actor Linear + policy head over the cells with a valid
     action, entirely on the device and without a host synchronisation (``mb_cells_bwd``).  ``logits`` needs valid
     values only in those cells (``actor_head_fwd(..., want_logits="alive")``)."""
@@ -458,6 +461,10 @@ def cells_bwd(hidden: torch.Tensor, weight: torch.Tensor, logits: torch.Tensor, 
     g_ent = _as(g_ent, torch.float32, "g_ent")
     n, k = hidden.shape
     cells = cell_meta.shape[0]
+    if alive_bits is None:
+        alive_bits = getattr(cell_meta, "alive_bits", None)
+    if alive_bits is None or tuple(alive_bits.shape) != (cells, (n + 31) // 32):
+        raise ValueError("cells_bwd: alive_bits [cells, ceil(N/32)] int32 is required (ops.pack_cells attaches it to cell_meta)")
     if k != 256 or tuple(weight.shape) != (cells * LOGITS_PER_CELL, k) or tuple(logits.shape) != (n, cells * LOGITS_PER_CELL) \
             or tuple(cell_meta.shape) != (cells, n, 4) or g_logp.numel() != n or g_ent.numel() != n:
         raise ValueError("cells_bwd: shape mismatch (hidden [N,256], weight [78C,256], logits [N,78C], cell_meta [C,N,4])")
@@ -473,7 +480,7 @@ def cells_bwd(hidden: torch.Tensor, weight: torch.Tensor, logits: torch.Tensor, 
     d_weight = torch.empty_like(weight)
     d_bias = torch.empty(cells * LOGITS_PER_CELL, dtype=torch.float32, device=dev)
     with torch.cuda.device(dev), _Launch("cells_bwd", note={"n": n, "cells": cells}):
-        _check(lib.mb_cells_bwd(_ptr(hidden), _ptr(weight), _ptr(logits), _ptr(cell_meta), _ptr(g_logp), _ptr(g_ent),
+        _check(lib.mb_cells_bwd(_ptr(hidden), _ptr(weight), _ptr(logits), _ptr(cell_meta), _ptr(alive_bits), _ptr(g_logp), _ptr(g_ent),
                                 _ptr(d_hidden), _ptr(d_weight), _ptr(d_bias), _ptr(ws), ws.numel(), n, cells, k, _stream()))
     return d_hidden, d_weight, d_bias
 
