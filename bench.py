@@ -510,6 +510,10 @@ def run_ours(args):
                 "fp32_equivalent_tflops": kf["algorithmic_tflops_fp32"],
                 "frac_of_bf16_peak": kf["issued_tf32_tflops"] / (2 * kf["tf32_peak_tflops"]),
                 "avg_launch_ms": kf["avg_ms"], "kernel_share_of_step": kf["avg_ms"] / ms_step}
+        try:        # DRAM bytes of one launch from the ncu --set full capture (profiles/): operands are L2-resident
+            roof["traffic"] = json.load(open(os.path.join(ROOT, "profiles", "traffic.json"))).get("actor_head_fwd", {}).get(args.workload)
+        except Exception:
+            pass
 
     # ---- e2e: host batch through the public call ---------------------------------------
     e2e = None
