@@ -68,31 +68,34 @@ __global__ void __launch_bounds__(kPackThreads) pack_cells_kernel(const uint8_t*
                      ((reinterpret_cast<uintptr_t>(mask) | reinterpret_cast<uintptr_t>(action)) & 15) == 0;
     if (vec) {
         // 39 + 28 sixteen-byte pieces per frame; rows are padded by 4 / 8 bytes, so the pieces are stored as words.
-        // All of a thread's loads are issued before the first store (9 x 16 B in flight per thread).
-        constexpr int kPer = (kPackFrames * 67 + kPackThreads - 1) / kPackThreads;
-        uint4 v[kPer];
+        // Warp w stages frames 4w .. 4w+3, its lanes the pieces lane, lane+32, lane+64 of each (no integer division);
+        // all of a thread's loads are issued before its first store (12 x 16 B in flight per thread).
+        const int wq = threadIdx.x >> 5, ln = threadIdx.x & 31;
+        uint4 v[12];
 #pragma unroll
-        for (int u = 0; u < kPer; ++u) {
-            const int i = threadIdx.x + u * kPackThreads;
-            if (i < nf * 67) {
-                const int fi = i / 67, r = i - fi * 67;
-                const bool is_m = r < 39;
-                const uint8_t* g = is_m ? mask + ((f0 + fi) * cells + c0) * kLogitsPerCell
-                                        : reinterpret_cast<const uint8_t*>(action + ((f0 + fi) * cells + c0) * kCompsPerCell);
-                v[u] = __ldg(reinterpret_cast<const uint4*>(g + 16 * (is_m ? r : r - 39)));
-            }
-        }
+        for (int j = 0; j < 4; ++j)
 #pragma unroll
-        for (int u = 0; u < kPer; ++u) {
-            const int i = threadIdx.x + u * kPackThreads;
-            if (i < nf * 67) {
-                const int fi = i / 67, r = i - fi * 67;
-                const bool is_m = r < 39;
-                uint32_t* d = reinterpret_cast<uint32_t*>((is_m ? s_mask + fi * kPackMaskPitch : s_act + fi * kPackActPitch) +
-                                                          16 * (is_m ? r : r - 39));
-                d[0] = v[u].x; d[1] = v[u].y; d[2] = v[u].z; d[3] = v[u].w;
+            for (int q = 0; q < 3; ++q) {
+                const int fi = 4 * wq + j, r = ln + 32 * q;
+                if (fi < nf && r < 67) {
+                    const bool is_m = r < 39;
+                    const uint8_t* g = is_m ? mask + ((f0 + fi) * cells + c0) * kLogitsPerCell
+                                            : reinterpret_cast<const uint8_t*>(action + ((f0 + fi) * cells + c0) * kCompsPerCell);
+                    v[3 * j + q] = __ldg(reinterpret_cast<const uint4*>(g + 16 * (is_m ? r : r - 39)));
+                }
             }
-        }
+#pragma unroll
+        for (int j = 0; j < 4; ++j)
+#pragma unroll
+            for (int q = 0; q < 3; ++q) {
+                const int fi = 4 * wq + j, r = ln + 32 * q;
+                if (fi < nf && r < 67) {
+                    const bool is_m = r < 39;
+                    uint32_t* d = reinterpret_cast<uint32_t*>((is_m ? s_mask + fi * kPackMaskPitch : s_act + fi * kPackActPitch) +
+                                                              16 * (is_m ? r : r - 39));
+                    d[0] = v[3 * j + q].x; d[1] = v[3 * j + q].y; d[2] = v[3 * j + q].z; d[3] = v[3 * j + q].w;
+                }
+            }
     } else {
         for (int fi = 0; fi < nf; ++fi) {
             const uint8_t* gm = mask + ((f0 + fi) * cells + c0) * kLogitsPerCell;
