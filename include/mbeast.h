@@ -207,6 +207,22 @@ MB_API int mb_conv3x3_fwd_supported(int32_t cin, int32_t cout, int32_t h, int32_
 MB_API int mb_conv3x3_fwd(const float* in, const float* wk, const float* bias, float* out, int64_t n_frames,
                           int32_t cin, int32_t cout, int32_t h, int32_t w, int32_t wmode, void* stream);
 
+/* The same two kernels with the element-wise neighbours of a residual block (reference model.py:67-73:
+ * relu -> conv0 -> relu -> conv1 -> + x, and its autograd) folded in, so that ReLU, the residual add and ReLU's
+ * backward cost no pass over the activations of their own:
+ *   relu_in != 0   the convolution reads max(in, 0) (forward: conv(relu(x)));
+ *   mask_src       [like out] or NULL: out is zeroed where mask_src <= 0 (backward: the data gradient through the
+ *                  ReLU that preceded the convolution, mask_src = that ReLU's input);
+ *   add_src        [like out] or NULL: added to out after the mask (forward: the skip connection; backward: the
+ *                  gradient that bypasses the block);
+ *   relu_x != 0    mb_conv3x3_wgrad_relu differentiates conv(relu(x)) with respect to the weights: x is rectified
+ *                  as it is read. */
+MB_API int mb_conv3x3_fwd_fused(const float* in, const float* wk, const float* bias, float* out, int64_t n_frames,
+                                int32_t cin, int32_t cout, int32_t h, int32_t w, int32_t wmode, int32_t relu_in,
+                                const float* mask_src, const float* add_src, void* stream);
+MB_API int mb_conv3x3_wgrad_relu(const float* x, const float* dy, float* partials, int32_t n_blocks, int64_t n_frames,
+                                 int32_t cin, int32_t cout, int32_t h, int32_t w, int32_t relu_x, void* stream);
+
 /* Actor Linear forward (reference model.py:136,167: logits = actor(hidden)) on the tcgen05 tensor cores at
  * fp32 accuracy: c[m,n] = a[m,k] * b[n,k]^T + bias[n] with both operands given as a TF32 "hi" part and a TF32
  * "lo" remainder (mb_split_tf32: x = hi + lo up to 2^-22 |x|) and three TF32 products accumulated in fp32:
@@ -270,6 +286,14 @@ MB_API int mb_cells_bwd(const float* hidden, const float* weight, const float* l
  * plane, as torch.nn.functional.max_pool2d(..., return_indices=True) returns it), dx [planes, h, w]. */
 MB_API int mb_maxpool3s2_bwd(const float* dy, const int64_t* idx, float* dx, int64_t planes, int32_t h, int32_t w,
                              void* stream);
+
+/* max_pool2d(kernel 3, stride 2, padding 1) forward (reference model.py:96) with a one-byte argmax: y, code
+ * [planes, (h+1)/2, (w+1)/2]; code = ky * 3 + kx of the winner inside its window, first maximum in row-major scan
+ * order (ATen's tie rule; NaN wins like there).  mb_maxpool3s2_bwd_code is the matching backward:
+ * dx [planes, h, w] = sum of dy over the windows whose winner the pixel is. */
+MB_API int mb_maxpool3s2_fwd(const float* x, float* y, uint8_t* code, int64_t planes, int32_t h, int32_t w, void* stream);
+MB_API int mb_maxpool3s2_bwd_code(const float* dy, const uint8_t* code, float* dx, int64_t planes, int32_t h, int32_t w,
+                                  void* stream);
 
 /* Tuning knobs for benchmarking (not part of the reference surface).  Keys:
  *   "head_ctas_per_sm" (0 = as many as fit), "head_grid" (0 = auto), "head_variant" (tile /

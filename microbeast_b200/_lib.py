@@ -45,6 +45,10 @@ SIGNATURES = {
     "mb_conv3x3_fwd_supported": (ctypes.c_int, [ctypes.c_int32, ctypes.c_int32, ctypes.c_int32, ctypes.c_int32]),
     "mb_conv3x3_fwd": (ctypes.c_int, [_P, _P, _P, _P, ctypes.c_int64, ctypes.c_int32, ctypes.c_int32, ctypes.c_int32,
                                       ctypes.c_int32, ctypes.c_int32, _P]),
+    "mb_conv3x3_fwd_fused": (ctypes.c_int, [_P, _P, _P, _P, ctypes.c_int64, ctypes.c_int32, ctypes.c_int32, ctypes.c_int32,
+                                            ctypes.c_int32, ctypes.c_int32, ctypes.c_int32, _P, _P, _P]),
+    "mb_conv3x3_wgrad_relu": (ctypes.c_int, [_P, _P, _P, ctypes.c_int32, ctypes.c_int64, ctypes.c_int32, ctypes.c_int32,
+                                             ctypes.c_int32, ctypes.c_int32, ctypes.c_int32, _P]),
     "mb_split_tf32": (ctypes.c_int, [_P, _P, _P, ctypes.c_int64, _P]),
     "mb_linear_tf32x3": (ctypes.c_int, [_P, _P, _P, _P, _P, _P, ctypes.c_int64, ctypes.c_int64, ctypes.c_int32, _P, _P]),
     "mb_pack_cells": (ctypes.c_int, [_P, _P, _P, _P, ctypes.c_int64, ctypes.c_int32, _P, _P]),
@@ -55,6 +59,8 @@ SIGNATURES = {
     "mb_cells_bwd": (ctypes.c_int, [_P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, ctypes.c_size_t, ctypes.c_int64, ctypes.c_int32,
                                     ctypes.c_int32, _P]),
     "mb_maxpool3s2_bwd": (ctypes.c_int, [_P, _P, _P, ctypes.c_int64, ctypes.c_int32, ctypes.c_int32, _P]),
+    "mb_maxpool3s2_fwd": (ctypes.c_int, [_P, _P, _P, ctypes.c_int64, ctypes.c_int32, ctypes.c_int32, _P]),
+    "mb_maxpool3s2_bwd_code": (ctypes.c_int, [_P, _P, _P, ctypes.c_int64, ctypes.c_int32, ctypes.c_int32, _P]),
     "mb_conv3x3_wgrad_blocks": (ctypes.c_int, [ctypes.c_int64, ctypes.c_int32, ctypes.c_int32, ctypes.c_int32,
                                                ctypes.c_int32]),
     "mb_conv3x3_wgrad": (ctypes.c_int, [_P, _P, _P, ctypes.c_int32, ctypes.c_int64, ctypes.c_int32, ctypes.c_int32,

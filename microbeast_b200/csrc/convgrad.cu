@@ -120,12 +120,22 @@ __device__ __forceinline__ void row_fma(float (&acc)[kWgTM][9], const float (&up
 }
 
 // All rows of one frame for this thread's (4 output channels, 1 input channel).
+template <int W>
+__device__ __forceinline__ void relu_row(float (&r)[W]) {
+#pragma unroll
+    for (int i = 0; i < W; ++i) r[i] = fmaxf(r[i], 0.0f);
+}
+
 template <class C>
-__device__ __forceinline__ void frame_fma(float (&acc)[kWgTM][9], const float* xplane, const float* ybase) {
+__device__ __forceinline__ void frame_fma(float (&acc)[kWgTM][9], const float* xplane, const float* ybase, bool relu_x) {
     constexpr int W = C::W, H = C::H;
     float up[W], mid[W], dn[W];
     load_row<W>(mid, xplane);
     load_row<W>(dn, xplane + W);
+    if (relu_x) {
+        relu_row<W>(mid);
+        relu_row<W>(dn);
+    }
     row_fma<W, false, true>(acc, mid, mid, dn, ybase, C::PLANE);                 // y = 0: no row above
     if constexpr (H > 2) {
         // small maps unroll completely; at 16x16 the 14 interior rows would be 8 k FMAs of straight-line
@@ -138,6 +148,7 @@ __device__ __forceinline__ void frame_fma(float (&acc)[kWgTM][9], const float* x
                 mid[i] = dn[i];
             }
             load_row<W>(dn, xplane + (y + 1) * W);
+            if (relu_x) relu_row<W>(dn);
             row_fma<W, true, true>(acc, up, mid, dn, ybase + y * W, C::PLANE);
         }
     }
@@ -152,7 +163,8 @@ __device__ __forceinline__ void frame_fma(float (&acc)[kWgTM][9], const float* x
 template <class C>
 __global__ void __launch_bounds__(kWgThreads) conv3x3_wgrad_kernel(const float* __restrict__ x,
                                                                     const float* __restrict__ dy,
-                                                                    float* __restrict__ partials, long long n_frames) {
+                                                                    float* __restrict__ partials, long long n_frames,
+                                                                    int relu_x) {
     extern __shared__ __align__(16) float wg_smem[];
     const int tid = threadIdx.x;
     const int g = tid / C::P;                       // frame group
@@ -204,7 +216,7 @@ __global__ void __launch_bounds__(kWgThreads) conv3x3_wgrad_kernel(const float* 
 #pragma unroll 1
         for (int j = 0; j < C::FG; ++j) {
             const float* fr = base + (g * C::FG + j) * C::FRAME;
-            frame_fma<C>(acc, fr + ci_eff * C::PLANE, fr + (C::CIN + cog * kWgTM) * C::PLANE);
+            frame_fma<C>(acc, fr + ci_eff * C::PLANE, fr + (C::CIN + cog * kWgTM) * C::PLANE, relu_x != 0);
         }
         // bias gradient = sum of dY over frames and pixels: thread (b_co, b_sl) adds its share of the staged dY
         // planes of channel b_co (a handful of float4 per chunk next to thousands of FMAs)
@@ -264,7 +276,8 @@ int wg_grid(int dev, long long n_frames, int* grid) {
 }
 
 template <class C>
-int wg_launch(const float* x, const float* dy, float* partials, int n_blocks, long long n_frames, cudaStream_t st) {
+int wg_launch(const float* x, const float* dy, float* partials, int n_blocks, long long n_frames, int relu_x,
+              cudaStream_t st) {
     int dev = 0, grid = 0;
     MB_CUDA(cudaGetDevice(&dev));
     const int rc = wg_grid<C>(dev, n_frames, &grid);
@@ -273,7 +286,7 @@ int wg_launch(const float* x, const float* dy, float* partials, int n_blocks, lo
         set_error("mb_conv3x3_wgrad: n_blocks=%d, but mb_conv3x3_wgrad_blocks gives %d for this shape", n_blocks, grid);
         return MB_ERR_INVALID;
     }
-    conv3x3_wgrad_kernel<C><<<grid, kWgThreads, C::SMEM, st>>>(x, dy, partials, n_frames);
+    conv3x3_wgrad_kernel<C><<<grid, kWgThreads, C::SMEM, st>>>(x, dy, partials, n_frames, relu_x);
     MB_CUDA(cudaGetLastError());
     return MB_OK;
 }
@@ -306,11 +319,11 @@ int conv3x3_wgrad_blocks(long long n_frames, int cin, int cout, int h, int w, in
 }
 
 int conv3x3_wgrad(const float* x, const float* dy, float* partials, int n_blocks, long long n_frames, int cin,
-                  int cout, int h, int w, cudaStream_t st) {
+                  int cout, int h, int w, int relu_x, cudaStream_t st) {
     if (h == w) {
 #define X(CI, CO, HH, CIS, GG, FG)              \
     if (cin == CI && cout == CO && h == HH)     \
-        return wg_launch<WgCfg<CI, CO, HH, CIS, GG, FG>>(x, dy, partials, n_blocks, n_frames, st);
+        return wg_launch<WgCfg<CI, CO, HH, CIS, GG, FG>>(x, dy, partials, n_blocks, n_frames, relu_x, st);
         MB_WG_SHAPES(X)
 #undef X
     }
@@ -390,7 +403,7 @@ __device__ __forceinline__ void fwd_fma(float (&acc)[kWgTM][XW], const float (&w
 // staged plane of channel 0 of frame t.
 template <class C, int X0>
 __device__ __forceinline__ void fwd_rows(float (&acc)[C::FPT][C::RPT][kWgTM][C::XW], const float* const (&rowp)[C::FPT],
-                                         const float* wcog) {
+                                         const float* wcog, bool relu_in) {
     constexpr int W = C::W;
 #pragma unroll 2
     for (int ci = 0; ci < C::CIN; ++ci) {
@@ -411,6 +424,10 @@ __device__ __forceinline__ void fwd_rows(float (&acc)[C::FPT][C::RPT][kWgTM][C::
                 float r0[W], r1[W];
                 load_row<W>(r0, pr);
                 load_row<W>(r1, pr + W);
+                if (relu_in) {
+                    relu_row<W>(r0);
+                    relu_row<W>(r1);
+                }
                 fwd_fma<W, C::XW, X0, false, true>(acc[t][0], wt, r0, r0, r1);
                 fwd_fma<W, C::XW, X0, true, false>(acc[t][1], wt, r0, r1, r1);
             } else {                                       // halo rows make -W / +W valid for every row
@@ -418,6 +435,11 @@ __device__ __forceinline__ void fwd_rows(float (&acc)[C::FPT][C::RPT][kWgTM][C::
                 load_row<W>(mid, pr);
                 load_row<W>(up, pr - W);
                 load_row<W>(dn, pr + W);
+                if (relu_in) {                             // halo rows are zero: relu leaves them zero
+                    relu_row<W>(mid);
+                    relu_row<W>(up);
+                    relu_row<W>(dn);
+                }
                 fwd_fma<W, C::XW, X0, true, true>(acc[t][0], wt, up, mid, dn);
             }
         }
@@ -427,7 +449,9 @@ __device__ __forceinline__ void fwd_rows(float (&acc)[C::FPT][C::RPT][kWgTM][C::
 template <class C>
 __global__ void __launch_bounds__(kWgThreads) conv3x3_fwd_kernel(const float* __restrict__ in, const float* __restrict__ wk,
                                                                   const float* __restrict__ bias, float* __restrict__ out,
-                                                                  long long n_frames, int wmode) {
+                                                                  long long n_frames, int wmode, int relu_in,
+                                                                  const float* __restrict__ mask_src,
+                                                                  const float* __restrict__ add_src) {
     extern __shared__ __align__(16) float fw_smem[];
     float* wsm = fw_smem;                              // [CIN][COUT][9]
     float* bsm = wsm + C::WK;                          // [COUT]
@@ -500,9 +524,9 @@ __global__ void __launch_bounds__(kWgThreads) conv3x3_fwd_kernel(const float* __
                         for (int x = 0; x < C::XW; ++x) acc[t][rr][m][x] = bsm[cog * kWgTM + m];
             }
             if (C::SEG == 1 || seg == 0) {             // uniform per warp
-                fwd_rows<C, 0>(acc, rowp, wcog);
+                fwd_rows<C, 0>(acc, rowp, wcog, relu_in != 0);
             } else {
-                fwd_rows<C, (C::SEG > 1 ? 8 : 0)>(acc, rowp, wcog);
+                fwd_rows<C, (C::SEG > 1 ? 8 : 0)>(acc, rowp, wcog, relu_in != 0);
             }
 #pragma unroll
             for (int t = 0; t < C::FPT; ++t) {
@@ -512,8 +536,18 @@ __global__ void __launch_bounds__(kWgThreads) conv3x3_fwd_kernel(const float* __
                     for (int rr = 0; rr < C::RPT; ++rr)
 #pragma unroll
                         for (int m = 0; m < kWgTM; ++m) {
-                            float* o = out + ((f * C::COUT + cog * kWgTM + m) * C::H + yy * C::RPT + rr) * C::W +
-                                       seg * C::XW;
+                            const long long oi = ((f * C::COUT + cog * kWgTM + m) * C::H + yy * C::RPT + rr) * C::W + seg * C::XW;
+                            float* o = out + oi;
+                            // fused element-wise tails: ReLU backward (zero where the reference's pre-activation was
+                            // not positive) and / or a residual add, at the positions this thread writes
+                            if (mask_src) {
+#pragma unroll
+                                for (int x = 0; x < C::XW; ++x) acc[t][rr][m][x] = __ldg(mask_src + oi + x) > 0.0f ? acc[t][rr][m][x] : 0.0f;
+                            }
+                            if (add_src) {
+#pragma unroll
+                                for (int x = 0; x < C::XW; ++x) acc[t][rr][m][x] += __ldg(add_src + oi + x);
+                            }
                             if constexpr (C::XW == 2) {
                                 *reinterpret_cast<float2*>(o) = make_float2(acc[t][rr][m][0], acc[t][rr][m][1]);
                             } else {
@@ -534,7 +568,7 @@ __global__ void __launch_bounds__(kWgThreads) conv3x3_fwd_kernel(const float* __
 
 template <class C>
 int fw_launch(const float* in, const float* wk, const float* bias, float* out, long long n_frames, int wmode,
-              cudaStream_t st) {
+              int relu_in, const float* mask_src, const float* add_src, cudaStream_t st) {
     int dev = 0;
     MB_CUDA(cudaGetDevice(&dev));
     static int occ[64] = {};
@@ -548,7 +582,7 @@ int fw_launch(const float* in, const float* wk, const float* bias, float* out, l
     const long long chunks = (n_frames + C::CH - 1) / C::CH;
     const long long cap = (long long)sm_count(dev) * o;
     const int grid = int(chunks < cap ? (chunks > 0 ? chunks : 1) : cap);
-    conv3x3_fwd_kernel<C><<<grid, kWgThreads, C::SMEM, st>>>(in, wk, bias, out, n_frames, wmode);
+    conv3x3_fwd_kernel<C><<<grid, kWgThreads, C::SMEM, st>>>(in, wk, bias, out, n_frames, wmode, relu_in, mask_src, add_src);
     MB_CUDA(cudaGetLastError());
     return MB_OK;
 }
@@ -570,10 +604,11 @@ int conv3x3_fwd_supported(int cin, int cout, int h, int w) {
 }
 
 int conv3x3_fwd(const float* in, const float* wk, const float* bias, float* out, long long n_frames, int cin, int cout,
-                int h, int w, int wmode, cudaStream_t st) {
+                int h, int w, int wmode, int relu_in, const float* mask_src, const float* add_src, cudaStream_t st) {
     if (h == w) {
-#define X(CI, CO, HH, FG, FPT) \
-    if (cin == CI && cout == CO && h == HH) return fw_launch<FwCfg<CI, CO, HH, FG, FPT>>(in, wk, bias, out, n_frames, wmode, st);
+#define X(CI, CO, HH, FG, FPT)                  \
+    if (cin == CI && cout == CO && h == HH)     \
+        return fw_launch<FwCfg<CI, CO, HH, FG, FPT>>(in, wk, bias, out, n_frames, wmode, relu_in, mask_src, add_src, st);
         MB_FW_SHAPES(X)
 #undef X
     }
@@ -648,6 +683,194 @@ __global__ void __launch_bounds__(256) maxpool3s2_bwd_vec_kernel(const float* __
     }
 }
 
+// ---------------------------------------------------------------------------------------------
+// max_pool2d(kernel 3, stride 2, padding 1) forward with a ONE-BYTE argmax (reference model.py:96).  ATen's
+// max_pool_forward_nchw writes an int64 index per output (8 B next to the 4-B value) and took 0.45 ms of the step;
+// here the winner is stored as its position inside the 3x3 window, code = ky * 3 + kx, first maximum in row-major
+// scan order (ATen's tie rule), and the backward below reads that byte.
+// ---------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) maxpool3s2_fwd_kernel(const float* __restrict__ x, float* __restrict__ y,
+                                                             uint8_t* __restrict__ code, long long planes, int h, int w,
+                                                             int oh, int ow) {
+    const long long total = planes * oh * ow;
+    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+        const long long pl = i / (oh * ow);
+        const int o = int(i - pl * (oh * ow));
+        const int oy = o / ow, ox = o - oy * ow;
+        const float* p = x + pl * (h * w);
+        float best = -INFINITY;
+        int bc = 0;
+        bool first = true;
+#pragma unroll
+        for (int ky = 0; ky < 3; ++ky) {
+            const int yy = 2 * oy - 1 + ky;
+            if (yy < 0 || yy >= h) continue;
+#pragma unroll
+            for (int kx = 0; kx < 3; ++kx) {
+                const int xx = 2 * ox - 1 + kx;
+                if (xx < 0 || xx >= w) continue;
+                const float v = __ldg(p + yy * w + xx);
+                if (first || v > best || v != v) {          // ATen: (val > maxval) || isnan(val)
+                    best = v;
+                    bc = ky * 3 + kx;
+                    first = false;
+                }
+            }
+        }
+        y[i] = best;
+        code[i] = uint8_t(bc);
+    }
+}
+
+// gather-form backward from the one-byte codes: an input pixel looks at the <= 4 windows that cover it
+__global__ void __launch_bounds__(256) maxpool3s2_bwd_code_kernel(const float* __restrict__ dy, const uint8_t* __restrict__ code,
+                                                                  float* __restrict__ dx, long long planes, int h, int w,
+                                                                  int oh, int ow) {
+    const long long total = planes * h * w;
+    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+        const long long pl = i / (h * w);
+        const int pix = int(i - pl * (h * w));
+        const int y = pix / w, x = pix - y * w;
+        const int oy0 = y >> 1, oy1 = min((y + 1) >> 1, oh - 1);
+        const int ox0 = x >> 1, ox1 = min((x + 1) >> 1, ow - 1);
+        const float* g = dy + pl * (oh * ow);
+        const uint8_t* cd = code + pl * (oh * ow);
+        float s = 0.0f;
+        for (int oy = oy0; oy <= oy1; ++oy)
+            for (int ox = ox0; ox <= ox1; ++ox) {
+                const int c = __ldg(cd + oy * ow + ox);
+                const int wy = 2 * oy - 1 + c / 3, wx = 2 * ox - 1 + c % 3;
+                if (wy == y && wx == x) s += __ldg(g + oy * ow + ox);
+            }
+        dx[i] = s;
+    }
+}
+
+// Two neighbouring outputs of a row per thread (w % 4 == 0): per input row one 16-byte load (columns 2*ox .. 2*ox+3) and
+// the column to their left; float2 / two-byte stores.  LW / LH = log2 of the map size: index split by shifts.
+template <int LW, int LH>
+__global__ void __launch_bounds__(256) maxpool3s2_fwd_vec_kernel(const float* __restrict__ x, float* __restrict__ y,
+                                                                 uint8_t* __restrict__ code, long long planes) {
+    constexpr int W = 1 << LW, H = 1 << LH, OW = W / 2, OH = H / 2, PW = OW / 2;
+    const long long total = planes * (OH * PW);
+    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+        const long long pl = i / (OH * PW);
+        const int r = int(i - pl * (OH * PW));
+        const int oy = r / PW, ox = (r - oy * PW) * 2;
+        const float* p = x + pl * (H * W);
+        float best[2] = {-INFINITY, -INFINITY};
+        int bc[2] = {0, 0};
+        bool first[2] = {true, true};
+#pragma unroll
+        for (int ky = 0; ky < 3; ++ky) {
+            const int yy = 2 * oy - 1 + ky;
+            if (yy < 0 || yy >= H) continue;
+            const float4 v4 = __ldg(reinterpret_cast<const float4*>(p + yy * W + 2 * ox));
+            const float left = ox > 0 ? __ldg(p + yy * W + 2 * ox - 1) : 0.0f;
+            const float right = (2 * ox + 4 < W) ? __ldg(p + yy * W + 2 * ox + 4) : 0.0f;
+            (void)right;
+            // output ox: columns 2ox-1, 2ox, 2ox+1 = left, v4.x, v4.y;  output ox+1: columns 2ox+1, 2ox+2, 2ox+3 = v4.y, v4.z, v4.w
+            const float c0[3] = {left, v4.x, v4.y};
+            const float c1[3] = {v4.y, v4.z, v4.w};
+#pragma unroll
+            for (int kx = 0; kx < 3; ++kx) {
+                if (!(kx == 0 && ox == 0)) {                 // column -1 does not exist
+                    const float v = c0[kx];
+                    if (first[0] || v > best[0] || v != v) { best[0] = v; bc[0] = ky * 3 + kx; first[0] = false; }
+                }
+                {
+                    const float v = c1[kx];
+                    if (first[1] || v > best[1] || v != v) { best[1] = v; bc[1] = ky * 3 + kx; first[1] = false; }
+                }
+            }
+        }
+        const long long o = pl * (OH * OW) + oy * OW + ox;
+        *reinterpret_cast<float2*>(y + o) = make_float2(best[0], best[1]);
+        *reinterpret_cast<uchar2*>(code + o) = make_uchar2((unsigned char)bc[0], (unsigned char)bc[1]);
+    }
+}
+
+// The gather of maxpool3s2_bwd_vec_kernel with one-byte window codes instead of int64 positions.
+template <int LW, int LH>
+__global__ void __launch_bounds__(256) maxpool3s2_bwd_code_vec_kernel(const float* __restrict__ dy, const uint8_t* __restrict__ code,
+                                                                      float* __restrict__ dx, long long planes) {
+    constexpr int W = 1 << LW, H = 1 << LH, OW = W / 2, OH = H / 2, QW = W / 4;
+    const long long total = planes * (H * QW);
+    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+        const long long pl = i / (H * QW);
+        const int r = int(i - pl * (H * QW));
+        const int y = r / QW, x0 = (r - y * QW) * 4;
+        const int oy0 = y >> 1, oy1 = min((y + 1) >> 1, OH - 1);
+        const int oxa = x0 >> 1;
+        const float* g = dy + pl * (OH * OW);
+        const uint8_t* cd = code + pl * (OH * OW);
+        float o[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+        for (int k = 0; k < 2; ++k) {
+            const int oy = k == 0 ? oy0 : oy1;
+            if (k == 1 && oy1 == oy0) break;
+#pragma unroll
+            for (int j = 0; j < 3; ++j) {
+                const int ox = oxa + j;
+                if (ox >= OW) break;
+                const int c = __ldg(cd + oy * OW + ox);
+                const int ky = (c * 11) >> 5, kx = c - 3 * ky;              // c / 3, c % 3 for c in 0..8
+                const bool row = (2 * oy - 1 + ky) == y;
+                const int d = (2 * ox - 1 + kx) - x0;                       // which of my four pixels, if any
+                const float v = __ldg(g + oy * OW + ox);
+#pragma unroll
+                for (int e = 0; e < 4; ++e) o[e] += (row && d == e) ? v : 0.0f;
+            }
+        }
+        *reinterpret_cast<float4*>(dx + pl * (H * W) + y * W + x0) = make_float4(o[0], o[1], o[2], o[3]);
+    }
+}
+
+int maxpool3s2_fwd(const float* x, float* y, uint8_t* code, long long planes, int h, int w, cudaStream_t st) {
+    int dev = 0;
+    MB_CUDA(cudaGetDevice(&dev));
+    const int oh = (h + 1) / 2, ow = (w + 1) / 2;
+    if (h == w && (h == 4 || h == 8 || h == 16 || h == 32) && (reinterpret_cast<uintptr_t>(x) & 15) == 0 &&
+        (reinterpret_cast<uintptr_t>(y) & 7) == 0 && (reinterpret_cast<uintptr_t>(code) & 1) == 0) {
+        const long long tot2 = planes * oh * (ow / 2);
+        const long long want2 = (tot2 + 255) / 256, cap2 = (long long)sm_count(dev) * 16;
+        const int grid = int(want2 < cap2 ? want2 : cap2);
+        if (h == 4) maxpool3s2_fwd_vec_kernel<2, 2><<<grid, 256, 0, st>>>(x, y, code, planes);
+        if (h == 8) maxpool3s2_fwd_vec_kernel<3, 3><<<grid, 256, 0, st>>>(x, y, code, planes);
+        if (h == 16) maxpool3s2_fwd_vec_kernel<4, 4><<<grid, 256, 0, st>>>(x, y, code, planes);
+        if (h == 32) maxpool3s2_fwd_vec_kernel<5, 5><<<grid, 256, 0, st>>>(x, y, code, planes);
+        MB_CUDA(cudaGetLastError());
+        return MB_OK;
+    }
+    const long long total = planes * oh * ow;
+    const long long want = (total + 255) / 256, cap = (long long)sm_count(dev) * 16;
+    maxpool3s2_fwd_kernel<<<int(want < cap ? want : cap), 256, 0, st>>>(x, y, code, planes, h, w, oh, ow);
+    MB_CUDA(cudaGetLastError());
+    return MB_OK;
+}
+
+int maxpool3s2_bwd_code(const float* dy, const uint8_t* code, float* dx, long long planes, int h, int w, cudaStream_t st) {
+    int dev = 0;
+    MB_CUDA(cudaGetDevice(&dev));
+    const int oh = (h + 1) / 2, ow = (w + 1) / 2;
+    if (h == w && (h == 4 || h == 8 || h == 16 || h == 32) && (reinterpret_cast<uintptr_t>(dx) & 15) == 0) {
+        const long long tot4 = planes * h * (w / 4);
+        const long long want4 = (tot4 + 255) / 256, cap4 = (long long)sm_count(dev) * 16;
+        const int grid = int(want4 < cap4 ? want4 : cap4);
+        if (h == 4) maxpool3s2_bwd_code_vec_kernel<2, 2><<<grid, 256, 0, st>>>(dy, code, dx, planes);
+        if (h == 8) maxpool3s2_bwd_code_vec_kernel<3, 3><<<grid, 256, 0, st>>>(dy, code, dx, planes);
+        if (h == 16) maxpool3s2_bwd_code_vec_kernel<4, 4><<<grid, 256, 0, st>>>(dy, code, dx, planes);
+        if (h == 32) maxpool3s2_bwd_code_vec_kernel<5, 5><<<grid, 256, 0, st>>>(dy, code, dx, planes);
+        MB_CUDA(cudaGetLastError());
+        return MB_OK;
+    }
+    const long long total = planes * h * w;
+    const long long want = (total + 255) / 256, cap = (long long)sm_count(dev) * 16;
+    maxpool3s2_bwd_code_kernel<<<int(want < cap ? want : cap), 256, 0, st>>>(dy, code, dx, planes, h, w, oh, ow);
+    MB_CUDA(cudaGetLastError());
+    return MB_OK;
+}
+
 int maxpool3s2_bwd(const float* dy, const long long* idx, float* dx, long long planes, int h, int w, cudaStream_t st) {
     int dev = 0;
     MB_CUDA(cudaGetDevice(&dev));
@@ -692,7 +915,24 @@ extern "C" int mb_conv3x3_fwd(const float* in, const float* wk, const float* bia
         mb::set_error("mb_conv3x3_fwd: in and out must be 16-byte aligned");
         return MB_ERR_INVALID;
     }
-    return mb::conv3x3_fwd(in, wk, bias, out, n_frames, cin, cout, h, w, wmode, static_cast<cudaStream_t>(stream));
+    return mb::conv3x3_fwd(in, wk, bias, out, n_frames, cin, cout, h, w, wmode, 0, nullptr, nullptr,
+                           static_cast<cudaStream_t>(stream));
+}
+
+extern "C" int mb_conv3x3_fwd_fused(const float* in, const float* wk, const float* bias, float* out, int64_t n_frames,
+                                    int32_t cin, int32_t cout, int32_t h, int32_t w, int32_t wmode, int32_t relu_in,
+                                    const float* mask_src, const float* add_src, void* stream) {
+    if (n_frames < 0 || wmode < 0 || wmode > 2) {
+        mb::set_error("mb_conv3x3_fwd_fused: n_frames=%lld wmode=%d out of range", (long long)n_frames, wmode);
+        return MB_ERR_INVALID;
+    }
+    if (n_frames == 0) return MB_OK;
+    if (!in || !wk || !out || ((reinterpret_cast<uintptr_t>(in) | reinterpret_cast<uintptr_t>(out)) & 15)) {
+        mb::set_error("mb_conv3x3_fwd_fused: null pointer, or in / out not 16-byte aligned");
+        return MB_ERR_INVALID;
+    }
+    return mb::conv3x3_fwd(in, wk, bias, out, n_frames, cin, cout, h, w, wmode, relu_in, mask_src, add_src,
+                           static_cast<cudaStream_t>(stream));
 }
 
 extern "C" int mb_maxpool3s2_bwd(const float* dy, const int64_t* idx, float* dx, int64_t planes, int32_t h, int32_t w,
@@ -735,5 +975,43 @@ extern "C" int mb_conv3x3_wgrad(const float* x, const float* dy, float* partials
         mb::set_error("mb_conv3x3_wgrad: x and dy must be 16-byte aligned");
         return MB_ERR_INVALID;
     }
-    return mb::conv3x3_wgrad(x, dy, partials, n_blocks, n_frames, cin, cout, h, w, static_cast<cudaStream_t>(stream));
+    return mb::conv3x3_wgrad(x, dy, partials, n_blocks, n_frames, cin, cout, h, w, 0, static_cast<cudaStream_t>(stream));
+}
+
+extern "C" int mb_conv3x3_wgrad_relu(const float* x, const float* dy, float* partials, int32_t n_blocks, int64_t n_frames,
+                                     int32_t cin, int32_t cout, int32_t h, int32_t w, int32_t relu_x, void* stream) {
+    if (n_frames < 0 || n_blocks <= 0 || !x || !dy || !partials ||
+        ((reinterpret_cast<uintptr_t>(x) | reinterpret_cast<uintptr_t>(dy)) & 15)) {
+        mb::set_error("mb_conv3x3_wgrad_relu: bad arguments (null / misaligned pointer, n_frames=%lld, n_blocks=%d)",
+                      (long long)n_frames, n_blocks);
+        return MB_ERR_INVALID;
+    }
+    return mb::conv3x3_wgrad(x, dy, partials, n_blocks, n_frames, cin, cout, h, w, relu_x, static_cast<cudaStream_t>(stream));
+}
+
+extern "C" int mb_maxpool3s2_fwd(const float* x, float* y, uint8_t* code, int64_t planes, int32_t h, int32_t w, void* stream) {
+    if (planes < 0 || h <= 0 || w <= 0) {
+        mb::set_error("mb_maxpool3s2_fwd: planes=%lld %dx%d out of range", (long long)planes, h, w);
+        return MB_ERR_INVALID;
+    }
+    if (planes == 0) return MB_OK;
+    if (!x || !y || !code) {
+        mb::set_error("mb_maxpool3s2_fwd: null pointer");
+        return MB_ERR_INVALID;
+    }
+    return mb::maxpool3s2_fwd(x, y, code, planes, h, w, static_cast<cudaStream_t>(stream));
+}
+
+extern "C" int mb_maxpool3s2_bwd_code(const float* dy, const uint8_t* code, float* dx, int64_t planes, int32_t h, int32_t w,
+                                      void* stream) {
+    if (planes < 0 || h <= 0 || w <= 0) {
+        mb::set_error("mb_maxpool3s2_bwd_code: planes=%lld %dx%d out of range", (long long)planes, h, w);
+        return MB_ERR_INVALID;
+    }
+    if (planes == 0) return MB_OK;
+    if (!dy || !code || !dx) {
+        mb::set_error("mb_maxpool3s2_bwd_code: null pointer");
+        return MB_ERR_INVALID;
+    }
+    return mb::maxpool3s2_bwd_code(dy, code, dx, planes, h, w, static_cast<cudaStream_t>(stream));
 }

@@ -134,14 +134,22 @@ class _MaxPool3s2(torch.autograd.Function):
 
     @staticmethod
     def forward(ctx, x):
+        ctx.hw = (x.shape[2], x.shape[3])
+        if FAST_MAXPOOL_FORWARD:
+            y, code = ops.maxpool3s2_fwd(x.contiguous())          # one-byte argmax instead of ATen's int64 index
+            ctx.save_for_backward(code)
+            ctx.coded = True
+            return y
         y, idx = F.max_pool2d(x, kernel_size=3, stride=2, padding=1, return_indices=True)
         ctx.save_for_backward(idx)
-        ctx.hw = (x.shape[2], x.shape[3])
+        ctx.coded = False
         return y
 
     @staticmethod
     def backward(ctx, g):
         (idx,) = ctx.saved_tensors
+        if ctx.coded:
+            return ops.maxpool3s2_bwd_code(g.contiguous(), idx, *ctx.hw)
         return ops.maxpool3s2_bwd(g, idx, *ctx.hw)
 
 
@@ -159,12 +167,17 @@ def conv3x3(conv: nn.Conv2d, x: torch.Tensor) -> torch.Tensor:
 
 
 FAST_CONV_BACKWARD = True
+# max-pool forward by mb_maxpool3s2_fwd (value + one-byte argmax) instead of ATen's kernel with int64 indices
+FAST_MAXPOOL_FORWARD = True
 # weight gradients of the 3x3 convolutions by mb_conv3x3_wgrad (fp32 FMA, deterministic) instead of cuDNN's
 # wgrad kernels, which were a third of the learner step (profiles/r01_encoder_layers.txt)
 FAST_CONV_WGRAD = True
 # forward convolutions and their data gradients by mb_conv3x3_fwd (fp32 FMA, register tiled) instead of cuDNN's
 # implicit-GEMM / winograd kernels
 FAST_CONV_FORWARD = True
+# a whole residual block (relu-conv-relu-conv + skip, model.py:67-73) as one autograd node whose element-wise steps are
+# folded into the convolution kernels (no ReLU / add / ReLU-backward passes over the activations)
+FUSED_RES_BLOCK = True
 # actor Linear forward (learner mode) by mb_linear_tf32x3: tcgen05 tensor cores, three TF32 products of hi/lo-split
 # operands accumulated in fp32 (error 5.5e-7 of max|logit|; cuBLAS fp32: 5.0e-7) instead of a SIMT SGEMM
 TENSOR_CORE_ACTOR = True
@@ -311,6 +324,44 @@ class _ActorHead(torch.autograd.Function):
         return g_hidden, g_weight, g_bias, None, None, None, None, None
 
 
+class _ResBlock(torch.autograd.Function):
+    """``conv1(relu(conv0(relu(x)))) + x`` (reference ``model.py:67-73``) in four kernel launches forward + backward
+    pairs, with every element-wise step folded into a convolution kernel (``mb_conv3x3_fwd_fused`` /
+    ``mb_conv3x3_wgrad_relu``): the ReLUs are applied as the convolutions read their input, the skip connection is
+    added in conv1's epilogue, and in the backward the ReLU masks and the bypassing gradient are applied in the
+    epilogues of the data-gradient convolutions.  Same fp32 arithmetic as the unfused composition (the element-wise
+    steps are exact); only ``x`` and ``conv0``'s output are kept for the backward (no ReLU outputs)."""
+
+    @staticmethod
+    def forward(ctx, x, w0, b0, w1, b1):
+        y0 = ops.conv3x3_fwd(x, w0, b0, wmode=1, relu_in=True)
+        out = ops.conv3x3_fwd(y0, w1, b1, wmode=1, relu_in=True, add_src=x)
+        ctx.save_for_backward(x, y0, w0, w1)
+        return out
+
+    @staticmethod
+    def backward(ctx, g):
+        x, y0, w0, w1 = ctx.saved_tensors
+        g = g.contiguous()
+        gw1, gb1 = ops.conv3x3_wgrad(y0, g, relu_x=True)
+        g0 = ops.conv3x3_fwd(g, w1, None, wmode=2, mask_src=y0)                  # through conv1, then relu'(y0)
+        gw0, gb0 = ops.conv3x3_wgrad(x, g0, relu_x=True)
+        gx = ops.conv3x3_fwd(g0, w0, None, wmode=2, mask_src=x, add_src=g)       # through conv0, relu'(x), + skip
+        return gx, gw0, gb0, gw1, gb1
+
+
+def _res_block_fusable(x: torch.Tensor, channels: int) -> bool:
+    if not (FUSED_RES_BLOCK and FAST_CONV_BACKWARD and FAST_CONV_FORWARD and FAST_CONV_WGRAD):
+        return False
+    if not (x.is_cuda and x.dtype == torch.float32 and x.dim() == 4 and torch.is_grad_enabled() and x.is_contiguous()):
+        return False
+    n, c, h, w = x.shape
+    if c != channels or h != w or n == 0 or x.data_ptr() & 15:
+        return False
+    from ._lib import lib
+    return bool(lib.mb_conv3x3_fwd_supported(c, c, h, w)) and lib.mb_conv3x3_wgrad_blocks(n, c, c, h, w) > 0
+
+
 class Residual_Block(nn.Module):
     """relu-conv-relu-conv + skip -- reference ``model.py:56-73``."""
 
@@ -321,6 +372,8 @@ class Residual_Block(nn.Module):
         self.conv1 = nn.Conv2d(channels, channels, kernel_size=3, padding=1)
 
     def forward(self, x):
+        if _res_block_fusable(x, self.channels):
+            return _ResBlock.apply(x, self.conv0.weight, self.conv0.bias, self.conv1.weight, self.conv1.bias)
         y = conv3x3(self.conv0, F.relu(x))
         y = conv3x3(self.conv1, F.relu(y))
         return y + x

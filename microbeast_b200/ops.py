@@ -296,10 +296,11 @@ def active_cells(action_mask: torch.Tensor, cells: int) -> torch.Tensor:
     return out.view(torch.bool)
 
 
-def conv3x3_wgrad(x: torch.Tensor, dy: torch.Tensor):
+def conv3x3_wgrad(x: torch.Tensor, dy: torch.Tensor, relu_x: bool = False):
     """``(dW [cout, cin, 3, 3], dbias [cout])`` of a 3x3 / stride 1 / pad 1 convolution from its input
     ``x [n,cin,h,w]`` and output gradient ``dy [n,cout,h,w]`` (fp32, NCHW contiguous), or ``None``
-    when the shape is not one ``csrc/convgrad.cu`` instantiates (the caller then uses cuDNN)."""
+    when the shape is not one ``csrc/convgrad.cu`` instantiates (the caller then uses cuDNN).  ``relu_x``: the
+    convolution was applied to ``relu(x)`` (``x`` is rectified as the kernel reads it)."""
     dev = _need_cuda(x=x, dy=dy)
     if x.dtype != torch.float32 or dy.dtype != torch.float32 or x.dim() != 4 or dy.dim() != 4:
         return None
@@ -318,16 +319,20 @@ def conv3x3_wgrad(x: torch.Tensor, dy: torch.Tensor):
             return None
         partials = torch.empty((blocks, cout * cin * 9 + cout), dtype=torch.float32, device=dev)
         with _Launch(f"conv3x3_wgrad_{cin}x{cout}x{h}", note={"n": n, "cin": cin, "cout": cout, "h": h}):
-            _check(lib.mb_conv3x3_wgrad(_ptr(x), _ptr(dy), _ptr(partials), blocks, n, cin, cout, h, w, _stream()))
+            _check(lib.mb_conv3x3_wgrad_relu(_ptr(x), _ptr(dy), _ptr(partials), blocks, n, cin, cout, h, w,
+                                             1 if relu_x else 0, _stream()))
     total = partials.sum(dim=0)
     return total[: cout * cin * 9].view(cout, cin, 3, 3), total[cout * cin * 9:]
 
 
-def conv3x3_fwd(x: torch.Tensor, wk: torch.Tensor, bias: Optional[torch.Tensor], wmode: int = 0) -> Optional[torch.Tensor]:
+def conv3x3_fwd(x: torch.Tensor, wk: torch.Tensor, bias: Optional[torch.Tensor], wmode: int = 0, relu_in: bool = False,
+                mask_src: Optional[torch.Tensor] = None, add_src: Optional[torch.Tensor] = None) -> Optional[torch.Tensor]:
     """``out [n,cout,h,w]`` of a 3x3 / stride 1 / pad 1 convolution of ``x [n,cin,h,w]`` (``mb_conv3x3_fwd``), or
     ``None`` for a shape that is not covered.  ``wmode`` 0: ``wk [cin, cout, 9]``; 1: ``wk`` is a torch Conv2d
     weight ``[cout, cin, 3, 3]`` (forward); 2: ``x`` is an output gradient and ``wk`` the torch weight
-    ``[cin, cout, 3, 3]`` of the convolution it came from -- the result is that convolution's input gradient."""
+    ``[cin, cout, 3, 3]`` of the convolution it came from -- the result is that convolution's input gradient.
+    Fused element-wise neighbours (``mb_conv3x3_fwd_fused``): ``relu_in`` convolves ``relu(x)``; ``mask_src`` (shaped like
+    the output) zeroes the output where ``mask_src <= 0``; ``add_src`` (shaped like the output) is added last."""
     dev = _need_cuda(x=x, wk=wk, bias=bias)
     if x.dtype != torch.float32 or x.dim() != 4 or wk.dim() not in (3, 4):
         return None
@@ -343,8 +348,12 @@ def conv3x3_fwd(x: torch.Tensor, wk: torch.Tensor, bias: Optional[torch.Tensor],
     if x.data_ptr() & 15:
         return None
     out = torch.empty((n, cout, h, w), dtype=torch.float32, device=dev)
+    for name, t in (("mask_src", mask_src), ("add_src", add_src)):
+        if t is not None and (tuple(t.shape) != tuple(out.shape) or t.dtype != torch.float32 or not t.is_contiguous() or not t.is_cuda):
+            raise ValueError(f"conv3x3_fwd: `{name}` must be a contiguous float32 CUDA tensor shaped like the output")
     with torch.cuda.device(dev), _Launch(f"conv3x3_fwd_{cin}x{cout}x{h}", note={"n": n, "cin": cin, "cout": cout, "h": h}):
-        _check(lib.mb_conv3x3_fwd(_ptr(x), _ptr(wk), _ptr(bias), _ptr(out), n, cin, cout, h, w, int(wmode), _stream()))
+        _check(lib.mb_conv3x3_fwd_fused(_ptr(x), _ptr(wk), _ptr(bias), _ptr(out), n, cin, cout, h, w, int(wmode),
+                                        1 if relu_in else 0, _ptr(mask_src), _ptr(add_src), _stream()))
     return out
 
 
@@ -497,6 +506,33 @@ def maxpool3s2_bwd(dy: torch.Tensor, idx: torch.Tensor, h: int, w: int) -> torch
     dx = torch.empty((n, c, h, w), dtype=torch.float32, device=dev)
     with torch.cuda.device(dev), _Launch("maxpool3s2_bwd"):
         _check(lib.mb_maxpool3s2_bwd(_ptr(dy), _ptr(idx), _ptr(dx), n * c, h, w, _stream()))
+    return dx
+
+
+def maxpool3s2_fwd(x: torch.Tensor):
+    """``(y, code)`` of ``max_pool2d(x, 3, stride=2, padding=1)``: ``code`` uint8 = position of the winner inside its 3x3
+    window (``ky * 3 + kx``, ATen's first-maximum tie rule) -- ``mb_maxpool3s2_fwd``."""
+    dev = _need_cuda(x=x)
+    x = _as(x, torch.float32, "x")
+    n, c, h, w = x.shape
+    y = torch.empty((n, c, (h + 1) // 2, (w + 1) // 2), dtype=torch.float32, device=dev)
+    code = torch.empty(y.shape, dtype=torch.uint8, device=dev)
+    with torch.cuda.device(dev), _Launch("maxpool3s2_fwd"):
+        _check(lib.mb_maxpool3s2_fwd(_ptr(x), _ptr(y), _ptr(code), n * c, h, w, _stream()))
+    return y, code
+
+
+def maxpool3s2_bwd_code(dy: torch.Tensor, code: torch.Tensor, h: int, w: int) -> torch.Tensor:
+    """Backward of :func:`maxpool3s2_fwd` from its one-byte codes (``mb_maxpool3s2_bwd_code``)."""
+    dev = _need_cuda(dy=dy, code=code)
+    dy = _as(dy, torch.float32, "dy")
+    code = _as(code, torch.uint8, "code")
+    if dy.dim() != 4 or dy.shape != code.shape or tuple(dy.shape[2:]) != ((h + 1) // 2, (w + 1) // 2):
+        raise ValueError("maxpool3s2_bwd_code: dy / code must be [n, c, (h+1)//2, (w+1)//2]")
+    n, c = dy.shape[:2]
+    dx = torch.empty((n, c, h, w), dtype=torch.float32, device=dev)
+    with torch.cuda.device(dev), _Launch("maxpool3s2_bwd"):
+        _check(lib.mb_maxpool3s2_bwd_code(_ptr(dy), _ptr(code), _ptr(dx), n * c, h, w, _stream()))
     return dx
 
 

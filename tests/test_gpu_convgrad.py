@@ -200,3 +200,55 @@ def test_encoder_with_and_without_fast_forward():
         for k in res[True][1]:
             ok, worst = close_rms(res[True][1][k], res[False][1][k], 3e-4)
             assert ok, (h, k, worst)
+
+
+@pytest.mark.parametrize("c,h,n", [(16, 8, 67), (32, 4, 300), (32, 2, 129), (16, 4, 5)])
+def test_fused_residual_block_matches_the_unfused_composition(c, h, n):
+    """model._ResBlock (ReLU, skip add and ReLU backward folded into the convolution kernels) against float64 autograd
+    of relu-conv-relu-conv + x (reference model.py:67-73): output, input gradient and all four parameter gradients."""
+    from microbeast_b200 import model as mmodel
+    g = torch.Generator(device="cuda").manual_seed(c + h + n)
+    blk = mmodel.Residual_Block(c).cuda()
+    x = torch.randn(n, c, h, h, device="cuda", generator=g, requires_grad=True)
+    gout = torch.randn(n, c, h, h, device="cuda", generator=g)
+    assert mmodel._res_block_fusable(x, c)
+    out = blk(x)
+    out.backward(gout)
+    got = [out.detach(), x.grad] + [p.grad for p in blk.parameters()]
+    ref = mmodel.Residual_Block(c).cuda().double()
+    ref.load_state_dict(blk.state_dict())
+    x64 = x.detach().double().requires_grad_(True)
+    mmodel.FUSED_RES_BLOCK = False
+    try:
+        y = F.conv2d(F.relu(F.conv2d(F.relu(x64), ref.conv0.weight, ref.conv0.bias, padding=1)), ref.conv1.weight, ref.conv1.bias,
+                     padding=1) + x64
+    finally:
+        mmodel.FUSED_RES_BLOCK = True
+    y.backward(gout.double())
+    want = [y.detach(), x64.grad] + [p.grad for p in ref.parameters()]
+    for name, a, b in zip(("out", "dx", "dW0", "db0", "dW1", "db1"), got, want):
+        ok, worst = close_rms(a.double(), b, 1e-5)
+        assert ok, f"{name}: {worst:.2f}x the 1e-5 bound"
+
+
+@pytest.mark.parametrize("n,c,h", [(1, 1, 2), (3, 5, 4), (7, 16, 8), (5, 16, 16), (2, 3, 7), (4, 2, 1), (1000, 32, 4)])
+def test_maxpool_forward_with_byte_codes_matches_aten(n, c, h):
+    """mb_maxpool3s2_fwd / mb_maxpool3s2_bwd_code == ATen's max_pool2d and its backward, bit for bit, ties included
+    (first maximum in row-major scan order)."""
+    from microbeast_b200 import ops
+    g = torch.Generator(device="cuda").manual_seed(n + c + h)
+    for ties in (True, False):
+        x = torch.randint(0, 4, (n, c, h, h), device="cuda", generator=g).float() if ties else \
+            torch.randn(n, c, h, h, device="cuda", generator=g)
+        x.requires_grad_(True)
+        want, idx = F.max_pool2d(x, 3, 2, 1, return_indices=True)
+        y, code = ops.maxpool3s2_fwd(x.detach())
+        assert torch.equal(y, want)
+        oh = (h + 1) // 2
+        oy = torch.arange(oh, device="cuda").view(1, 1, oh, 1)
+        ox = torch.arange(oh, device="cuda").view(1, 1, 1, oh)
+        pix = (2 * oy - 1 + code.long() // 3) * h + (2 * ox - 1 + code.long() % 3)
+        assert torch.equal(pix, idx)
+        dy = torch.randn(want.shape, device="cuda", generator=g)
+        (gx,) = torch.autograd.grad(want, x, dy)
+        assert torch.allclose(ops.maxpool3s2_bwd_code(dy, code, h, h), gx, rtol=0, atol=1e-6)
