@@ -207,6 +207,14 @@ MB_API int mb_conv3x3_fwd_supported(int32_t cin, int32_t cout, int32_t h, int32_
 MB_API int mb_conv3x3_fwd(const float* in, const float* wk, const float* bias, float* out, int64_t n_frames,
                           int32_t cin, int32_t cout, int32_t h, int32_t w, int32_t wmode, void* stream);
 
+/* The encoder's FIRST convolution (reference model.py:88,121: Conv2d(27, 16, 3, padding=1) on the 27 binary feature
+ * planes, model.py:156-160) straight from bit-packed observations: obs_bits [n_frames, h*w] i32, bit c = plane c (the
+ * rollout store's wire format, see mb_unpack_obs); weight [16, 27, 3, 3] (torch layout), bias [16] or NULL;
+ * out [n_frames, 16, h, w] f32.  out = bias + the sum of the weight columns of the set bits under each tap (any bit
+ * pattern; fp32 additions only).  planes must be 27, cout 16, h == w in {8, 16}; other shapes: MB_ERR_UNSUPPORTED. */
+MB_API int mb_conv1_bits_fwd(const int32_t* obs_bits, const float* weight, const float* bias, float* out, int64_t n_frames,
+                             int32_t planes, int32_t cout, int32_t h, int32_t w, void* stream);
+
 /* The same two kernels with the element-wise neighbours of a residual block (reference model.py:67-73:
  * relu -> conv0 -> relu -> conv1 -> + x, and its autograd) folded in, so that ReLU, the residual add and ReLU's
  * backward cost no pass over the activations of their own:

@@ -13,6 +13,7 @@ UNITS="abi head vtrace unpack convgrad gemm"
 [ -f "$HERE/cells.cu" ] && UNITS="$UNITS cells"
 [ -f "$HERE/fused.cu" ] && UNITS="$UNITS fused"
 [ -f "$HERE/sampler.cu" ] && UNITS="$UNITS sampler"
+[ -f "$HERE/convbits.cu" ] && UNITS="$UNITS convbits"
 [ -f "$HERE/convtc.cu" ] && UNITS="$UNITS convtc"
 pids=""
 for u in $UNITS; do

@@ -128,6 +128,42 @@ class _Conv3x3(torch.autograd.Function):
         return gx, gw, gb
 
 
+class _Conv1Bits(torch.autograd.Function):
+    """The encoder's first convolution (reference ``model.py:88,121``) evaluated straight from bit-packed observations
+    (``mb_conv1_bits_fwd``: sums of weight columns over the set bits, no ``[N, 27, h, w]`` fp32 tensor in the forward
+    pass).  The weight gradient needs the planes as numbers: they are expanded once, in the backward
+    (``mb_unpack_obs``), for ``mb_conv3x3_wgrad``.  Observations carry no gradient."""
+
+    @staticmethod
+    def forward(ctx, obs_bits, weight, bias):
+        ctx.save_for_backward(obs_bits)
+        ctx.planes = weight.shape[1]
+        return ops.conv1_bits_fwd(obs_bits, weight, bias)
+
+    @staticmethod
+    def backward(ctx, g):
+        (obs_bits,) = ctx.saved_tensors
+        x = ops.unpack_obs(obs_bits, planes=ctx.planes)
+        g = g.contiguous()
+        both = ops.conv3x3_wgrad(x, g)
+        if both is None:
+            _, gw, gb = torch.ops.aten.convolution_backward(
+                g, x, torch.empty((g.shape[1], ctx.planes, 3, 3), device=g.device), [g.shape[1]], [1, 1], [1, 1], [1, 1], False,
+                [0, 0], 1, [False, True, True])
+            return None, gw, gb
+        return None, both[0], both[1]
+
+
+def conv1_from_bits(conv: nn.Conv2d, obs_bits: torch.Tensor):
+    """``conv(planes(obs_bits))`` through :class:`_Conv1Bits`, or ``None`` when that kernel does not cover the shape."""
+    if not (FAST_CONV1_BITS and obs_bits.is_cuda and obs_bits.dtype == torch.int32 and obs_bits.dim() == 3):
+        return None
+    n, h, w = obs_bits.shape
+    if tuple(conv.weight.shape) != (16, 27, 3, 3) or h != w or h not in (8, 16) or n == 0:
+        return None
+    return _Conv1Bits.apply(obs_bits, conv.weight, conv.bias)
+
+
 class _MaxPool3s2(torch.autograd.Function):
     """``max_pool2d(x, 3, stride=2, padding=1)`` (reference model.py:96) with the backward as a gather over
     the saved argmax indices (``mb_maxpool3s2_bwd``) instead of ATen's ``max_pool_backward_nchw``."""
@@ -167,6 +203,8 @@ def conv3x3(conv: nn.Conv2d, x: torch.Tensor) -> torch.Tensor:
 
 
 FAST_CONV_BACKWARD = True
+# first convolution straight from the bit-packed observations of the compact rollout store (mb_conv1_bits_fwd)
+FAST_CONV1_BITS = True
 # max-pool forward by mb_maxpool3s2_fwd (value + one-byte argmax) instead of ATen's kernel with int64 indices
 FAST_MAXPOOL_FORWARD = True
 # weight gradients of the 3x3 convolutions by mb_conv3x3_wgrad (fp32 FMA, deterministic) instead of cuDNN's
@@ -395,7 +433,13 @@ class ConvSequence(nn.Module):
         return (self._out_channels, (h + 1) // 2, (w + 1) // 2)
 
     def forward(self, x):
-        x = maxpool3s2(conv3x3(self.conv, x))
+        if x.dtype == torch.int32:          # bit-packed observations [N, h, w] (first stage only): see Agent._obs
+            y = conv1_from_bits(self.conv, x)
+            if y is None:
+                y = conv3x3(self.conv, ops.unpack_obs(x, planes=self.conv.weight.shape[1]))
+        else:
+            y = conv3x3(self.conv, x)
+        x = maxpool3s2(y)
         return self.res_block1(self.res_block0(x))
 
 
@@ -437,7 +481,9 @@ class Agent(nn.Module):
 
     def _obs(self, input_dict, learning):
         obs = input_dict["obs"] if learning else input_dict["obs"][0, 0, ...]     # model.py:156-160
-        if obs.dtype == torch.int32:     # bit-packed planes from the compact rollout store: [N,h,w] -> NCHW fp32
+        if obs.dtype == torch.int32:     # bit-packed planes from the compact rollout store: [N,h,w]
+            if FAST_CONV1_BITS and obs.is_cuda:
+                return obs               # the first ConvSequence convolves the bits directly (or expands them itself)
             return ops.unpack_obs(obs, planes=self.obs_planes)
         if obs.dtype != torch.float32:
             obs = obs.float()            # uint8 wire format of the B200 rollout store

@@ -357,6 +357,25 @@ def conv3x3_fwd(x: torch.Tensor, wk: torch.Tensor, bias: Optional[torch.Tensor],
     return out
 
 
+def conv1_bits_fwd(obs_bits: torch.Tensor, weight: torch.Tensor, bias: Optional[torch.Tensor]) -> Optional[torch.Tensor]:
+    """The encoder's first convolution from bit-packed observations (``mb_conv1_bits_fwd``): ``obs_bits [N,h,w]`` int32,
+    ``weight [16,27,3,3]`` -> ``[N,16,h,w]`` fp32; ``None`` when the shape is not covered."""
+    dev = _need_cuda(obs_bits=obs_bits, weight=weight, bias=bias)
+    if obs_bits.dtype != torch.int32 or obs_bits.dim() != 3 or tuple(weight.shape) != (16, 27, 3, 3):
+        return None
+    n, h, w = obs_bits.shape
+    if h != w or h not in (8, 16) or n == 0:
+        return None
+    obs_bits = obs_bits.contiguous()
+    weight = _as(weight, torch.float32, "weight")
+    if bias is not None:
+        bias = _as(bias, torch.float32, "bias")
+    out = torch.empty((n, 16, h, w), dtype=torch.float32, device=dev)
+    with torch.cuda.device(dev), _Launch(f"conv1_bits_fwd_{h}", note={"n": n, "h": h}):
+        _check(lib.mb_conv1_bits_fwd(_ptr(obs_bits), _ptr(weight), _ptr(bias), _ptr(out), n, 27, 16, h, w, _stream()))
+    return out
+
+
 def split_tf32(x: torch.Tensor) -> Tuple[torch.Tensor, torch.Tensor]:
     """``(hi, lo)``: ``hi`` = ``x`` rounded to TF32, ``lo`` = the remainder rounded to TF32 (``x = hi + lo`` up
     to 2^-22 |x|) -- the operand form ``linear_tf32x3`` takes."""

@@ -252,3 +252,33 @@ def test_maxpool_forward_with_byte_codes_matches_aten(n, c, h):
         dy = torch.randn(want.shape, device="cuda", generator=g)
         (gx,) = torch.autograd.grad(want, x, dy)
         assert torch.allclose(ops.maxpool3s2_bwd_code(dy, code, h, h), gx, rtol=0, atol=1e-6)
+
+
+@pytest.mark.parametrize("h,n", [(16, 37), (8, 130), (8, 3), (16, 1)])
+def test_first_convolution_from_bits(h, n):
+    """mb_conv1_bits_fwd on bit-packed observations == conv2d on the expanded planes (float64), for one-hot groups and
+    for arbitrary bit patterns; its autograd node gives the weight / bias gradients of the dense convolution."""
+    from microbeast_b200 import model as mmodel, ops, synth
+    g = torch.Generator().manual_seed(h + n)
+    conv = torch.nn.Conv2d(27, 16, 3, padding=1).cuda()
+    for pattern in ("one_hot", "random"):
+        if pattern == "one_hot":
+            planes = synth.make_obs(n, h, h, gen=g).permute(0, 3, 1, 2).contiguous()
+        else:
+            planes = (torch.rand(n, 27, h, h, generator=g) < 0.3).float()
+        shifts = torch.arange(27, dtype=torch.int64).view(1, 27, 1, 1)
+        bits = (planes.long() << shifts).sum(1).to(torch.int32).cuda()
+        want = F.conv2d(planes.double().cuda(), conv.weight.double(), conv.bias.double(), padding=1)
+        got = ops.conv1_bits_fwd(bits, conv.weight, conv.bias)
+        ok, worst = close_rms(got.double(), want, 1e-5)
+        assert ok, (pattern, worst)
+    conv.zero_grad()
+    y = mmodel.conv1_from_bits(conv, bits)
+    gout = torch.randn(y.shape, generator=torch.Generator(device="cuda").manual_seed(1), device="cuda")
+    y.backward(gout)
+    ref = torch.nn.Conv2d(27, 16, 3, padding=1).cuda().double()
+    ref.load_state_dict(conv.state_dict())
+    ref(planes.double().cuda()).backward(gout.double())
+    for name, a, b in (("dW", conv.weight.grad, ref.weight.grad), ("db", conv.bias.grad, ref.bias.grad)):
+        ok, worst = close_rms(a.double(), b, 1e-5)
+        assert ok, (name, worst)

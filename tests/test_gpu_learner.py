@@ -202,9 +202,13 @@ def test_ppo_learn_accepts_the_compact_wire_format():
     a = PPO_learn(mine, mine, "plain", batch, torch.optim.SGD(mine.parameters(), lr=0.0), 3, 10, 2)
     ga = [p.grad.clone() for p in mine.parameters()]
     b = PPO_learn(mine, mine, "compact", mbuf.pack_batch(batch), torch.optim.SGD(mine.parameters(), lr=0.0), 3, 10, 2)
-    assert a == b                     # forward path is deterministic: identical losses
-    for x, p in zip(ga, mine.parameters()):          # cuDNN weight gradients are not run-to-run deterministic
-        ok, worst = close_rms(p.grad, x, 1e-4)
+    # the compact format's first convolution adds weight columns over the set observation bits (mb_conv1_bits_fwd), the
+    # plain one multiplies by 0.0 / 1.0 planes: same mathematics, another fp32 summation order
+    np.testing.assert_allclose(a, b, rtol=2e-5, atol=1e-7)
+    # two fp32 orderings of the first convolution, amplified by the N(0, 0.15^2) fixture weights of this test
+    # (measured 3.3e-4 of a gradient's rms); atomics in the cell-list backward add run-to-run noise at 1e-6
+    for x, p in zip(ga, mine.parameters()):
+        ok, worst = close_rms(p.grad, x, 1e-3)
         assert ok, worst
 
 
@@ -247,12 +251,20 @@ def test_packed_observations_feed_the_encoder_unchanged():
     mine, _ = _pair(8, 8, seed=13)
     batch = synth.make_rollout_batch(8, 8, 4, 2, seed=9, full_keys=False)
     dev = {k: v.cuda() for k, v in batch.items()}
+    from microbeast_b200 import model as mmodel
     with torch.no_grad():
         a, _ = mine.get_action(dev, learning=True)
         dev["obs"] = mbuf.pack_obs(batch["obs"]).cuda()
-        b, _ = mine.get_action(dev, learning=True)
+        b, _ = mine.get_action(dev, learning=True)          # first convolution straight from the bits
+        mmodel.FAST_CONV1_BITS = False
+        try:
+            c, _ = mine.get_action(dev, learning=True)      # bits expanded to planes first: the float path's arithmetic
+        finally:
+            mmodel.FAST_CONV1_BITS = True
     for k in ("policy_logits", "logprobs", "entropy", "baseline"):
-        assert torch.equal(a[k], b[k]), k
+        assert torch.equal(a[k], c[k]), k
+        ok, worst = close_rms(b[k], a[k], 1e-4)             # sums of weight columns vs multiplications by 0 / 1, N(0, 0.15^2) weights
+        assert ok, (k, worst)
 
 
 def test_train_driver_runs_actors_and_learner(tmp_path):
