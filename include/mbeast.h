@@ -224,12 +224,16 @@ MB_API int mb_conv1_bits_fwd(const int32_t* obs_bits, const float* weight, const
  *   add_src        [like out] or NULL: added to out after the mask (forward: the skip connection; backward: the
  *                  gradient that bypasses the block);
  *   relu_x != 0    mb_conv3x3_wgrad_relu differentiates conv(relu(x)) with respect to the weights: x is rectified
- *                  as it is read. */
+ *                  as it is read;
+ *   accumulate_out [cout*cin*9 + cout] or NULL: every CTA adds its share to this (caller-zeroed) result with atomics
+ *                  instead of writing a slot of `partials` (which may then be NULL): no summation pass afterwards, but
+ *                  the order of the fp32 additions varies from run to run. */
 MB_API int mb_conv3x3_fwd_fused(const float* in, const float* wk, const float* bias, float* out, int64_t n_frames,
                                 int32_t cin, int32_t cout, int32_t h, int32_t w, int32_t wmode, int32_t relu_in,
                                 const float* mask_src, const float* add_src, void* stream);
 MB_API int mb_conv3x3_wgrad_relu(const float* x, const float* dy, float* partials, int32_t n_blocks, int64_t n_frames,
-                                 int32_t cin, int32_t cout, int32_t h, int32_t w, int32_t relu_x, void* stream);
+                                 int32_t cin, int32_t cout, int32_t h, int32_t w, int32_t relu_x, float* accumulate_out,
+                                 void* stream);
 
 /* Actor Linear forward (reference model.py:136,167: logits = actor(hidden)) on the tcgen05 tensor cores at
  * fp32 accuracy: c[m,n] = a[m,k] * b[n,k]^T + bias[n] with both operands given as a TF32 "hi" part and a TF32

@@ -48,7 +48,7 @@ SIGNATURES = {
     "mb_conv3x3_fwd_fused": (ctypes.c_int, [_P, _P, _P, _P, ctypes.c_int64, ctypes.c_int32, ctypes.c_int32, ctypes.c_int32,
                                             ctypes.c_int32, ctypes.c_int32, ctypes.c_int32, _P, _P, _P]),
     "mb_conv3x3_wgrad_relu": (ctypes.c_int, [_P, _P, _P, ctypes.c_int32, ctypes.c_int64, ctypes.c_int32, ctypes.c_int32,
-                                             ctypes.c_int32, ctypes.c_int32, ctypes.c_int32, _P]),
+                                             ctypes.c_int32, ctypes.c_int32, ctypes.c_int32, _P, _P]),
     "mb_conv1_bits_fwd": (ctypes.c_int, [_P, _P, _P, _P, ctypes.c_int64, ctypes.c_int32, ctypes.c_int32, ctypes.c_int32,
                                          ctypes.c_int32, _P]),
     "mb_split_tf32": (ctypes.c_int, [_P, _P, _P, ctypes.c_int64, _P]),

@@ -164,7 +164,7 @@ template <class C>
 __global__ void __launch_bounds__(kWgThreads) conv3x3_wgrad_kernel(const float* __restrict__ x,
                                                                     const float* __restrict__ dy,
                                                                     float* __restrict__ partials, long long n_frames,
-                                                                    int relu_x) {
+                                                                    int relu_x, float* __restrict__ atomic_out) {
     extern __shared__ __align__(16) float wg_smem[];
     const int tid = threadIdx.x;
     const int g = tid / C::P;                       // frame group
@@ -241,12 +241,15 @@ __global__ void __launch_bounds__(kWgThreads) conv3x3_wgrad_kernel(const float* 
     float* bred = red + kWgThreads * (kWgTM * 9);
     bred[tid] = bsum;
     __syncthreads();
-    float* out = partials + (long long)blockIdx.x * C::SLOT;
+    // atomic_out: add this CTA's share straight into the [OUT + COUT] result (zeroed by the caller) instead of writing a
+    // slot for a later fixed-order sum: one pass less per convolution, at the price of a run-to-run summation order
+    float* out = atomic_out ? atomic_out : partials + (long long)blockIdx.x * C::SLOT;
     if (tid < C::COUT) {
         float s = 0.0f;
 #pragma unroll
         for (int k = 0; k < C::BSL; ++k) s += bred[k * C::COUT + tid];
-        out[C::OUT + tid] = s;
+        if (atomic_out) atomicAdd(out + C::OUT + tid, s);
+        else out[C::OUT + tid] = s;
     }
     for (int e = tid; e < C::OUT; e += kWgThreads) {
         const int co = e / (C::CIN * 9), rem = e % (C::CIN * 9);
@@ -255,7 +258,8 @@ __global__ void __launch_bounds__(kWgThreads) conv3x3_wgrad_kernel(const float* 
 #pragma unroll
         for (int gg = 0; gg < C::G; ++gg)
             s += red[((gg * C::COG + co / kWgTM) * C::CIS + ci2) * (kWgTM * 9) + (co % kWgTM) * 9 + tap];
-        out[e] = s;
+        if (atomic_out) atomicAdd(out + e, s);
+        else out[e] = s;
     }
 }
 
@@ -277,7 +281,7 @@ int wg_grid(int dev, long long n_frames, int* grid) {
 
 template <class C>
 int wg_launch(const float* x, const float* dy, float* partials, int n_blocks, long long n_frames, int relu_x,
-              cudaStream_t st) {
+              float* atomic_out, cudaStream_t st) {
     int dev = 0, grid = 0;
     MB_CUDA(cudaGetDevice(&dev));
     const int rc = wg_grid<C>(dev, n_frames, &grid);
@@ -286,7 +290,7 @@ int wg_launch(const float* x, const float* dy, float* partials, int n_blocks, lo
         set_error("mb_conv3x3_wgrad: n_blocks=%d, but mb_conv3x3_wgrad_blocks gives %d for this shape", n_blocks, grid);
         return MB_ERR_INVALID;
     }
-    conv3x3_wgrad_kernel<C><<<grid, kWgThreads, C::SMEM, st>>>(x, dy, partials, n_frames, relu_x);
+    conv3x3_wgrad_kernel<C><<<grid, kWgThreads, C::SMEM, st>>>(x, dy, partials, n_frames, relu_x, atomic_out);
     MB_CUDA(cudaGetLastError());
     return MB_OK;
 }
@@ -319,11 +323,11 @@ int conv3x3_wgrad_blocks(long long n_frames, int cin, int cout, int h, int w, in
 }
 
 int conv3x3_wgrad(const float* x, const float* dy, float* partials, int n_blocks, long long n_frames, int cin,
-                  int cout, int h, int w, int relu_x, cudaStream_t st) {
+                  int cout, int h, int w, int relu_x, float* atomic_out, cudaStream_t st) {
     if (h == w) {
 #define X(CI, CO, HH, CIS, GG, FG)              \
     if (cin == CI && cout == CO && h == HH)     \
-        return wg_launch<WgCfg<CI, CO, HH, CIS, GG, FG>>(x, dy, partials, n_blocks, n_frames, relu_x, st);
+        return wg_launch<WgCfg<CI, CO, HH, CIS, GG, FG>>(x, dy, partials, n_blocks, n_frames, relu_x, atomic_out, st);
         MB_WG_SHAPES(X)
 #undef X
     }
@@ -975,18 +979,20 @@ extern "C" int mb_conv3x3_wgrad(const float* x, const float* dy, float* partials
         mb::set_error("mb_conv3x3_wgrad: x and dy must be 16-byte aligned");
         return MB_ERR_INVALID;
     }
-    return mb::conv3x3_wgrad(x, dy, partials, n_blocks, n_frames, cin, cout, h, w, 0, static_cast<cudaStream_t>(stream));
+    return mb::conv3x3_wgrad(x, dy, partials, n_blocks, n_frames, cin, cout, h, w, 0, nullptr, static_cast<cudaStream_t>(stream));
 }
 
 extern "C" int mb_conv3x3_wgrad_relu(const float* x, const float* dy, float* partials, int32_t n_blocks, int64_t n_frames,
-                                     int32_t cin, int32_t cout, int32_t h, int32_t w, int32_t relu_x, void* stream) {
-    if (n_frames < 0 || n_blocks <= 0 || !x || !dy || !partials ||
+                                     int32_t cin, int32_t cout, int32_t h, int32_t w, int32_t relu_x, float* accumulate_out,
+                                     void* stream) {
+    if (n_frames < 0 || n_blocks <= 0 || !x || !dy || (!partials && !accumulate_out) ||
         ((reinterpret_cast<uintptr_t>(x) | reinterpret_cast<uintptr_t>(dy)) & 15)) {
         mb::set_error("mb_conv3x3_wgrad_relu: bad arguments (null / misaligned pointer, n_frames=%lld, n_blocks=%d)",
                       (long long)n_frames, n_blocks);
         return MB_ERR_INVALID;
     }
-    return mb::conv3x3_wgrad(x, dy, partials, n_blocks, n_frames, cin, cout, h, w, relu_x, static_cast<cudaStream_t>(stream));
+    return mb::conv3x3_wgrad(x, dy, partials, n_blocks, n_frames, cin, cout, h, w, relu_x, accumulate_out,
+                             static_cast<cudaStream_t>(stream));
 }
 
 extern "C" int mb_maxpool3s2_fwd(const float* x, float* y, uint8_t* code, int64_t planes, int32_t h, int32_t w, void* stream) {

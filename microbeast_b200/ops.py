@@ -317,11 +317,17 @@ def conv3x3_wgrad(x: torch.Tensor, dy: torch.Tensor, relu_x: bool = False):
         x, dy = x.contiguous(), dy.contiguous()
         if (x.data_ptr() | dy.data_ptr()) & 15:
             return None
-        partials = torch.empty((blocks, cout * cin * 9 + cout), dtype=torch.float32, device=dev)
-        with _Launch(f"conv3x3_wgrad_{cin}x{cout}x{h}", note={"n": n, "cin": cin, "cout": cout, "h": h}):
-            _check(lib.mb_conv3x3_wgrad_relu(_ptr(x), _ptr(dy), _ptr(partials), blocks, n, cin, cout, h, w,
-                                             1 if relu_x else 0, _stream()))
-    total = partials.sum(dim=0)
+        if DETERMINISTIC_WGRAD:
+            partials = torch.empty((blocks, cout * cin * 9 + cout), dtype=torch.float32, device=dev)
+            with _Launch(f"conv3x3_wgrad_{cin}x{cout}x{h}", note={"n": n, "cin": cin, "cout": cout, "h": h}):
+                _check(lib.mb_conv3x3_wgrad_relu(_ptr(x), _ptr(dy), _ptr(partials), blocks, n, cin, cout, h, w,
+                                                 1 if relu_x else 0, None, _stream()))
+            total = partials.sum(dim=0)           # fixed order: deterministic
+        else:
+            total = torch.zeros(cout * cin * 9 + cout, dtype=torch.float32, device=dev)
+            with _Launch(f"conv3x3_wgrad_{cin}x{cout}x{h}", note={"n": n, "cin": cin, "cout": cout, "h": h}):
+                _check(lib.mb_conv3x3_wgrad_relu(_ptr(x), _ptr(dy), None, blocks, n, cin, cout, h, w,
+                                                 1 if relu_x else 0, _ptr(total), _stream()))
     return total[: cout * cin * 9].view(cout, cin, 3, 3), total[cout * cin * 9:]
 
 
@@ -474,6 +480,10 @@ def actor_head_fwd(hidden: torch.Tensor, packed_weight, cell_meta: torch.Tensor,
 
 
 _cells_ws: Dict[Tuple[int, int], torch.Tensor] = {}
+# True: every CTA of mb_conv3x3_wgrad writes a partial result and torch sums them in a fixed order (one more pass per
+# convolution); False: the CTAs add into the result with atomics (the cell-list backward of the actor head uses atomics
+# anyway, so a learner step is not bit-reproducible from run to run either way)
+DETERMINISTIC_WGRAD = False
 
 
 def cells_bwd(hidden: torch.Tensor, weight: torch.Tensor, logits: torch.Tensor, cell_meta: torch.Tensor,

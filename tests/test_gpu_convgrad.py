@@ -39,8 +39,17 @@ def test_wgrad_matches_autograd(cin, cout, h, n):
     assert ok, worst
     ok, worst = close_rms(gb.double(), dy.double().sum(dim=(0, 2, 3)), 2e-5)
     assert ok, ("bias gradient", worst)
-    again, gb2 = ops.conv3x3_wgrad(x, dy)
-    assert torch.equal(got, again) and torch.equal(gb, gb2), "the kernel and its fixed-order partial sum are deterministic"
+    # default: CTAs add into the result with atomics (order varies from run to run); DETERMINISTIC_WGRAD: slots + a
+    # fixed-order sum, bit-reproducible
+    ops.DETERMINISTIC_WGRAD = True
+    try:
+        det, gbd = ops.conv3x3_wgrad(x, dy)
+        again, gb2 = ops.conv3x3_wgrad(x, dy)
+    finally:
+        ops.DETERMINISTIC_WGRAD = False
+    assert torch.equal(det, again) and torch.equal(gbd, gb2), "the kernel and its fixed-order partial sum are deterministic"
+    ok, worst = close_rms(det.double(), ref64, 2e-5)
+    assert ok, worst
 
 
 def test_wgrad_one_hot_taps():
