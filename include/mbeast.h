@@ -215,6 +215,14 @@ MB_API int mb_conv3x3_fwd(const float* in, const float* wk, const float* bias, f
 MB_API int mb_conv1_bits_fwd(const int32_t* obs_bits, const float* weight, const float* bias, float* out, int64_t n_frames,
                              int32_t planes, int32_t cout, int32_t h, int32_t w, void* stream);
 
+/* Its weight and bias gradients (what autograd of model.py:88 gives for a 0/1 input), again from the bits:
+ * dy [n_frames, 16, h, w] f32 (16-byte aligned); accumulate_out [16*27*9 + 16] f32, ZEROED by the caller (or holding a
+ * running total): the kernel ADDS dW [16][27][3][3] and then db [16] into it with atomics.  Each (plane, frame) costs
+ * work in proportion to its set cells -- or its unset ones when more than half are set -- so the expanded planes are
+ * never formed in the backward pass either.  Same shape limits as mb_conv1_bits_fwd. */
+MB_API int mb_conv1_bits_wgrad(const int32_t* obs_bits, const float* dy, float* accumulate_out, int64_t n_frames,
+                               int32_t planes, int32_t cout, int32_t h, int32_t w, void* stream);
+
 /* The same two kernels with the element-wise neighbours of a residual block (reference model.py:67-73:
  * relu -> conv0 -> relu -> conv1 -> + x, and its autograd) folded in, so that ReLU, the residual add and ReLU's
  * backward cost no pass over the activations of their own:

@@ -51,6 +51,8 @@ SIGNATURES = {
                                              ctypes.c_int32, ctypes.c_int32, ctypes.c_int32, _P, _P]),
     "mb_conv1_bits_fwd": (ctypes.c_int, [_P, _P, _P, _P, ctypes.c_int64, ctypes.c_int32, ctypes.c_int32, ctypes.c_int32,
                                          ctypes.c_int32, _P]),
+    "mb_conv1_bits_wgrad": (ctypes.c_int, [_P, _P, _P, ctypes.c_int64, ctypes.c_int32, ctypes.c_int32, ctypes.c_int32,
+                                           ctypes.c_int32, _P]),
     "mb_split_tf32": (ctypes.c_int, [_P, _P, _P, ctypes.c_int64, _P]),
     "mb_linear_tf32x3": (ctypes.c_int, [_P, _P, _P, _P, _P, _P, ctypes.c_int64, ctypes.c_int64, ctypes.c_int32, _P, _P]),
     "mb_pack_cells": (ctypes.c_int, [_P, _P, _P, _P, ctypes.c_int64, ctypes.c_int32, _P, _P]),

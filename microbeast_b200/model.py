@@ -131,8 +131,8 @@ class _Conv3x3(torch.autograd.Function):
 class _Conv1Bits(torch.autograd.Function):
     """The encoder's first convolution (reference ``model.py:88,121``) evaluated straight from bit-packed observations
     (``mb_conv1_bits_fwd``: sums of weight columns over the set bits, no ``[N, 27, h, w]`` fp32 tensor in the forward
-    pass).  The weight gradient needs the planes as numbers: they are expanded once, in the backward
-    (``mb_unpack_obs``), for ``mb_conv3x3_wgrad``.  Observations carry no gradient."""
+    pass); the weight and bias gradients come from the bits as well (``mb_conv1_bits_wgrad``).  Observations carry no
+    gradient."""
 
     @staticmethod
     def forward(ctx, obs_bits, weight, bias):
@@ -143,14 +143,10 @@ class _Conv1Bits(torch.autograd.Function):
     @staticmethod
     def backward(ctx, g):
         (obs_bits,) = ctx.saved_tensors
-        x = ops.unpack_obs(obs_bits, planes=ctx.planes)
         g = g.contiguous()
-        both = ops.conv3x3_wgrad(x, g)
-        if both is None:
-            _, gw, gb = torch.ops.aten.convolution_backward(
-                g, x, torch.empty((g.shape[1], ctx.planes, 3, 3), device=g.device), [g.shape[1]], [1, 1], [1, 1], [1, 1], False,
-                [0, 0], 1, [False, True, True])
-            return None, gw, gb
+        both = ops.conv1_bits_wgrad(obs_bits, g) if FAST_CONV1_BITS_WGRAD else None
+        if both is None:                                   # the planes as numbers, for the dense weight-gradient kernel
+            both = ops.conv3x3_wgrad(ops.unpack_obs(obs_bits, planes=ctx.planes), g)
         return None, both[0], both[1]
 
 
@@ -205,6 +201,8 @@ def conv3x3(conv: nn.Conv2d, x: torch.Tensor) -> torch.Tensor:
 FAST_CONV_BACKWARD = True
 # first convolution straight from the bit-packed observations of the compact rollout store (mb_conv1_bits_fwd)
 FAST_CONV1_BITS = True
+# ... and its weight gradient too (mb_conv1_bits_wgrad); False: mb_unpack_obs + mb_conv3x3_wgrad in the backward
+FAST_CONV1_BITS_WGRAD = True
 # max-pool forward by mb_maxpool3s2_fwd (value + one-byte argmax) instead of ATen's kernel with int64 indices
 FAST_MAXPOOL_FORWARD = True
 # weight gradients of the 3x3 convolutions by mb_conv3x3_wgrad (fp32 FMA, deterministic) instead of cuDNN's

@@ -382,6 +382,23 @@ def conv1_bits_fwd(obs_bits: torch.Tensor, weight: torch.Tensor, bias: Optional[
     return out
 
 
+def conv1_bits_wgrad(obs_bits: torch.Tensor, dy: torch.Tensor) -> Optional[Tuple[torch.Tensor, torch.Tensor]]:
+    """``(dW [16,27,3,3], db [16])`` of that first convolution from the bits (``mb_conv1_bits_wgrad``: work in
+    proportion to the set -- or, for mostly-set planes, the unset -- cells); ``None`` when the shape is not covered."""
+    dev = _need_cuda(obs_bits=obs_bits, dy=dy)
+    if obs_bits.dtype != torch.int32 or obs_bits.dim() != 3 or dy.dim() != 4 or dy.shape[1] != 16:
+        return None
+    n, h, w = obs_bits.shape
+    if h != w or h not in (8, 16) or n == 0 or tuple(dy.shape) != (n, 16, h, w):
+        return None
+    obs_bits = obs_bits.contiguous()
+    dy = _as(dy, torch.float32, "dy")
+    total = torch.zeros(16 * 27 * 9 + 16, dtype=torch.float32, device=dev)
+    with torch.cuda.device(dev), _Launch(f"conv1_bits_wgrad_{h}", note={"n": n, "h": h}):
+        _check(lib.mb_conv1_bits_wgrad(_ptr(obs_bits), _ptr(dy), _ptr(total), n, 27, 16, h, w, _stream()))
+    return total[:16 * 27 * 9].view(16, 27, 3, 3), total[16 * 27 * 9:]
+
+
 def split_tf32(x: torch.Tensor) -> Tuple[torch.Tensor, torch.Tensor]:
     """``(hi, lo)``: ``hi`` = ``x`` rounded to TF32, ``lo`` = the remainder rounded to TF32 (``x = hi + lo`` up
     to 2^-22 |x|) -- the operand form ``linear_tf32x3`` takes."""

@@ -18,6 +18,9 @@ opt = torch.optim.Adam(model.parameters(), lr=2.5e-4, eps=1e-5, fused=True)
 batch = synth.make_rollout_batch(h, w, T, rows, seed=1, device=dev, obs_dtype=torch.uint8, full_keys=False)
 batch["logprobs"] = -torch.rand(batch["reward"].shape, device=dev) * 30
 b = {k: batch[k] for k in LEARNER_KEYS}
+if "--plain-obs" not in sys.argv:        # the resident batch of bench.py: observations as one int32 per cell
+    shifts = torch.arange(27, device=dev, dtype=torch.int32)
+    b["obs"] = (batch["obs"].to(torch.int32) << shifts).sum(-1, dtype=torch.int32)
 for _ in range(4):
     PPO_learn(model, model, "p", b, opt, rows, T, 1, sync=False)
 torch.cuda.synchronize()
@@ -25,4 +28,4 @@ with profile(activities=[ProfilerActivity.CUDA, ProfilerActivity.CPU]) as prof:
     for _ in range(3):
         PPO_learn(model, model, "p", b, opt, rows, T, 1, sync=False)
     torch.cuda.synchronize()
-print(prof.key_averages().table(sort_by="cuda_time_total", row_limit=28, max_name_column_width=70))
+print(prof.key_averages().table(sort_by="cuda_time_total", row_limit=45, max_name_column_width=70))

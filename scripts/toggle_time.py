@@ -35,4 +35,6 @@ for combo in itertools.product([True, False], repeat=len(names)):
     kt = ops.stop_kernel_timing()
     conv = sum(sum(v) for k, v in kt.items() if k.startswith("conv3x3")) / 3
     pool = sum(sum(v) for k, v in kt.items() if k.startswith("maxpool")) / 3
+    bits = {k: round(sum(v) / 3, 3) for k, v in kt.items() if k.startswith("conv1_bits") or k.startswith("unpack")}
+    print(bits)
     print(dict(zip(names, combo)), "step %.3f ms" % (s.elapsed_time(e) / 10), "conv kernels %.3f ms" % conv, "pool kernels %.3f" % pool, flush=True)

@@ -270,24 +270,35 @@ def test_first_convolution_from_bits(h, n):
     from microbeast_b200 import model as mmodel, ops, synth
     g = torch.Generator().manual_seed(h + n)
     conv = torch.nn.Conv2d(27, 16, 3, padding=1).cuda()
-    for pattern in ("one_hot", "random"):
+    for pattern in ("one_hot", "random", "full", "empty"):
         if pattern == "one_hot":
             planes = synth.make_obs(n, h, h, gen=g).permute(0, 3, 1, 2).contiguous()
-        else:
+        elif pattern == "random":
             planes = (torch.rand(n, 27, h, h, generator=g) < 0.3).float()
+        else:
+            planes = torch.full((n, 27, h, h), 1.0 if pattern == "full" else 0.0)
         shifts = torch.arange(27, dtype=torch.int64).view(1, 27, 1, 1)
         bits = (planes.long() << shifts).sum(1).to(torch.int32).cuda()
         want = F.conv2d(planes.double().cuda(), conv.weight.double(), conv.bias.double(), padding=1)
         got = ops.conv1_bits_fwd(bits, conv.weight, conv.bias)
         ok, worst = close_rms(got.double(), want, 1e-5)
         assert ok, (pattern, worst)
-    conv.zero_grad()
-    y = mmodel.conv1_from_bits(conv, bits)
-    gout = torch.randn(y.shape, generator=torch.Generator(device="cuda").manual_seed(1), device="cuda")
-    y.backward(gout)
-    ref = torch.nn.Conv2d(27, 16, 3, padding=1).cuda().double()
-    ref.load_state_dict(conv.state_dict())
-    ref(planes.double().cuda()).backward(gout.double())
-    for name, a, b in (("dW", conv.weight.grad, ref.weight.grad), ("db", conv.bias.grad, ref.bias.grad)):
-        ok, worst = close_rms(a.double(), b, 1e-5)
-        assert ok, (name, worst)
+        # weight / bias gradients: from the bits (set cells, or unset cells against the rectangle sums for planes that
+        # are mostly set -- "one_hot" and "full" take that branch) and, with the switch off, from the expanded planes
+        gout = torch.randn(want.shape, generator=torch.Generator(device="cuda").manual_seed(1), device="cuda")
+        ref = torch.nn.Conv2d(27, 16, 3, padding=1).cuda().double()
+        ref.load_state_dict(conv.state_dict())
+        ref(planes.double().cuda()).backward(gout.double())
+        for from_bits in (True, False):
+            conv.zero_grad()
+            old = mmodel.FAST_CONV1_BITS_WGRAD
+            mmodel.FAST_CONV1_BITS_WGRAD = from_bits
+            before = ops.launch_counts.get(f"conv1_bits_wgrad_{h}", 0)
+            try:
+                mmodel.conv1_from_bits(conv, bits).backward(gout)
+            finally:
+                mmodel.FAST_CONV1_BITS_WGRAD = old
+            assert (ops.launch_counts.get(f"conv1_bits_wgrad_{h}", 0) - before == 1) == from_bits
+            for name, a, b in (("dW", conv.weight.grad, ref.weight.grad), ("db", conv.bias.grad, ref.bias.grad)):
+                err = (a.double() - b).abs().max() / b.abs().max().clamp_min(1.0)
+                assert err < 2e-6, (pattern, from_bits, name, float(err))
