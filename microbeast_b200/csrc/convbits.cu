@@ -4,13 +4,17 @@
 // (model.py:156-160).  gym-microRTS observations are 27 binary feature planes; the rollout store ships them as one
 // int32 per cell (bit c = plane c, csrc/unpack.cu).  A 3x3 convolution over 0/1 inputs is a sum of weight columns:
 //     out[n, co, y, x] = bias[co] + sum over the 9 taps, over the SET bits c of cell (y+ky-1, x+kx-1): W[co, c, ky, kx]
-// -- 5 set bits per cell for one-hot planes, i.e. 45 additions of a 16-vector per output pixel instead of 243 FMAs of
-// one (and no [N, 27, h, w] fp32 tensor has to be written and read back for the forward pass).  Any bit pattern is
-// handled (the loop runs over the set bits, whatever their number); out-of-image taps see the zero halo.
+// -- and no [N, 27, h, w] fp32 tensor has to be written and read back.  The kernel is bound by the shared-memory
+// reads of those 16-float columns (64 bytes into registers per column and pixel), so it counts EXCEPTIONS instead of
+// set bits: gym-microRTS leaves a cell empty by setting plane 0 of each of its five one-hot groups (planes 0, 5, 10,
+// 13, 21), which is what ~90 % of the cells look like.  Per pixel it starts from bias + the sum of those five columns
+// over the taps inside the image (nine precomputed border classes), then adds the column of every plane a cell has
+// beyond that pattern and subtracts the column of every pattern plane the cell lacks: ~1 column per cell instead of 5.
+// Any bit pattern is handled exactly the same way (the pattern is only where the counting starts; fp32 additions,
+// another summation order); out-of-image taps carry the pattern in the halo, i.e. no exception.
 //
 // One thread per output pixel, 16 accumulators (the 16 output channels).  The weights sit in shared memory as
-// [tap][plane][16] rows padded to 80 bytes, so that lanes whose cells differ read different bank groups while the
-// common case -- neighbouring cells with the same planes set -- is a broadcast.
+// [tap][plane][16] rows padded to 80 bytes.
 #include "common.cuh"
 
 #include "../../include/mbeast.h"
@@ -23,6 +27,7 @@ namespace {
 
 constexpr int kBitsCout = 16, kBitsCin = 27;
 constexpr int kRowPitch = 20;                       // floats per [tap][plane] row: 16 + 4 padding
+constexpr unsigned kEmptyCell = (1u << 0) | (1u << 5) | (1u << 10) | (1u << 13) | (1u << 21);   // plane 0 of each one-hot group
 
 template <int H>
 __global__ void __launch_bounds__(256) conv1_bits_fwd_kernel(const int* __restrict__ obs_bits, const float* __restrict__ weight,
@@ -32,40 +37,59 @@ __global__ void __launch_bounds__(256) conv1_bits_fwd_kernel(const int* __restri
     constexpr int FPC = 256 / HW > 0 ? 256 / HW : 1;                  // frames per CTA pass (8x8: 4, 16x16: 1)
     constexpr int TP = W + 2;                                          // tile pitch with halo
     __shared__ __align__(16) float wt[9 * kBitsCin * kRowPitch];
-    __shared__ float bs[kBitsCout];
+    __shared__ __align__(16) float start[9][kBitsCout];               // bias + empty-cell columns of the taps inside, per border class
     __shared__ int tile[FPC][(H + 2) * TP];
     // torch layout [cout][cin][3][3] -> [tap][cin][cout]
     for (int i = threadIdx.x; i < 9 * kBitsCin * kBitsCout; i += 256) {
         const int co = i % kBitsCout, ci = (i / kBitsCout) % kBitsCin, tap = i / (kBitsCout * kBitsCin);
         wt[(tap * kBitsCin + ci) * kRowPitch + co] = weight[(co * kBitsCin + ci) * 9 + tap];
     }
-    if (threadIdx.x < kBitsCout) bs[threadIdx.x] = bias ? bias[threadIdx.x] : 0.0f;
-    for (int i = threadIdx.x; i < FPC * (H + 2) * TP; i += 256) (&tile[0][0])[i] = 0;      // the halo stays zero
+    for (int i = threadIdx.x; i < FPC * (H + 2) * TP; i += 256) (&tile[0][0])[i] = int(kEmptyCell);   // halo: no exception
+    __syncthreads();
+    if (threadIdx.x < 9 * kBitsCout) {
+        const int co = threadIdx.x % kBitsCout, cls = threadIdx.x / kBitsCout, cy = cls / 3, cx = cls % 3;   // 0 first, 1 inner, 2 last
+        float v = bias ? bias[co] : 0.0f;
+        for (int tap = 0; tap < 9; ++tap) {
+            const int ky = tap / 3, kx = tap % 3;
+            if ((cy == 0 && ky == 0) || (cy == 2 && ky == 2) || (cx == 0 && kx == 0) || (cx == 2 && kx == 2)) continue;
+            for (int ci = 0; ci < kBitsCin; ++ci)
+                if ((kEmptyCell >> ci) & 1u) v += wt[(tap * kBitsCin + ci) * kRowPitch + co];
+        }
+        start[cls][co] = v;
+    }
     __syncthreads();
     const int slot = threadIdx.x / HW, pix = threadIdx.x % HW;
     const int y = pix / W, x = pix % W;
+    const int cls = (y == 0 ? 0 : y == H - 1 ? 2 : 1) * 3 + (x == 0 ? 0 : x == W - 1 ? 2 : 1);
     const long long n_pass = (n_frames + FPC - 1) / FPC;
     for (long long pass = blockIdx.x; pass < n_pass; pass += gridDim.x) {
         const long long f = pass * FPC + slot;
         const bool live = slot < FPC && f < n_frames;
-        if (slot < FPC) tile[slot][(y + 1) * TP + x + 1] = live ? __ldg(obs_bits + f * HW + pix) : 0;
+        if (slot < FPC) tile[slot][(y + 1) * TP + x + 1] = live ? __ldg(obs_bits + f * HW + pix) : int(kEmptyCell);
         __syncthreads();
         if (live) {
             float acc[kBitsCout];
 #pragma unroll
-            for (int c = 0; c < kBitsCout; ++c) acc[c] = bs[c];
+            for (int q = 0; q < 4; ++q) {
+                const float4 v = reinterpret_cast<const float4*>(start[cls])[q];
+                acc[4 * q] = v.x, acc[4 * q + 1] = v.y, acc[4 * q + 2] = v.z, acc[4 * q + 3] = v.w;
+            }
 #pragma unroll
             for (int tap = 0; tap < 9; ++tap) {
-                unsigned word = unsigned(tile[slot][(y + tap / 3) * TP + x + tap % 3]) & ((1u << kBitsCin) - 1u);
+                unsigned word = (unsigned(tile[slot][(y + tap / 3) * TP + x + tap % 3]) ^ kEmptyCell) & ((1u << kBitsCin) - 1u);
                 const float* base = wt + tap * kBitsCin * kRowPitch;
-                while (word) {
+                while (word) {                                 // planes where this cell departs from the empty pattern
                     const int ci = __ffs(word) - 1;
                     word &= word - 1;
+                    const float sign = ((kEmptyCell >> ci) & 1u) ? -1.0f : 1.0f;      // a pattern plane it lacks / an extra plane
                     const float4* r = reinterpret_cast<const float4*>(base + ci * kRowPitch);
 #pragma unroll
                     for (int q = 0; q < 4; ++q) {
                         const float4 v = r[q];
-                        acc[4 * q] += v.x; acc[4 * q + 1] += v.y; acc[4 * q + 2] += v.z; acc[4 * q + 3] += v.w;
+                        acc[4 * q] = fmaf(sign, v.x, acc[4 * q]);
+                        acc[4 * q + 1] = fmaf(sign, v.y, acc[4 * q + 1]);
+                        acc[4 * q + 2] = fmaf(sign, v.z, acc[4 * q + 2]);
+                        acc[4 * q + 3] = fmaf(sign, v.w, acc[4 * q + 3]);
                     }
                 }
             }
