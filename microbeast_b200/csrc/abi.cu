@@ -44,6 +44,7 @@ int head_eval_cells_bwd(const float*, const uint8_t*, const int64_t*, const floa
 void head_set_tuning(int ctas_per_sm, int grid_override, int variant);
 void vtrace_set_tuning(int force_generic, int variant, int l2_promo);
 void gemm_set_tuning(int group_m, int stream_store);
+void conv_set_tuning(int tensor_cores);
 void vtrace_static_poison(int on);
 void vtrace_set_debug(int v);
 size_t vtrace_workspace_bytes(long long rows);
@@ -111,6 +112,7 @@ int mb_set_tuning(const char* key, int32_t value) {
     else if (!strcmp(key, "vtrace_debug")) mb::vtrace_set_debug(value);
     else if (!strcmp(key, "gemm_group_m")) gemm_group_m = value;
     else if (!strcmp(key, "gemm_stream_store")) gemm_stream_store = value;
+    else if (!strcmp(key, "conv_tc")) mb::conv_set_tuning(value);
     else {
         mb::set_error("mb_set_tuning: unknown key '%s'", key);
         return MB_ERR_INVALID;

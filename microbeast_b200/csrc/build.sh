@@ -9,18 +9,17 @@ OBJ="$HERE/build"
 NVCC="${NVCC:-/usr/local/cuda/bin/nvcc}"
 FLAGS="-gencode arch=compute_100a,code=sm_100a -O3 -lineinfo -std=c++17 -Xcompiler -fPIC -Xcompiler -fvisibility=hidden ${MB_NVCC_EXTRA}"
 mkdir -p "$OBJ"
-UNITS="abi head vtrace unpack convgrad gemm"
+UNITS="abi head vtrace unpack convgrad convtc gemm"
 [ -f "$HERE/cells.cu" ] && UNITS="$UNITS cells"
 [ -f "$HERE/fused.cu" ] && UNITS="$UNITS fused"
 [ -f "$HERE/sampler.cu" ] && UNITS="$UNITS sampler"
 [ -f "$HERE/convbits.cu" ] && UNITS="$UNITS convbits"
-[ -f "$HERE/convtc.cu" ] && UNITS="$UNITS convtc"
 pids=""
 for u in $UNITS; do
     src="$HERE/$u.cu"
     obj="$OBJ/$u.o"
     if [ -n "$MB_REBUILD" ] || [ -n "$MB_NVCC_EXTRA" ] || [ ! -f "$obj" ] || [ "$src" -nt "$obj" ] || \
-       [ "$HERE/common.cuh" -nt "$obj" ] || [ "$HERE/../../include/mbeast.h" -nt "$obj" ] || [ "$0" -nt "$obj" ]; then
+       [ "$HERE/common.cuh" -nt "$obj" ] || [ "$HERE/tc.cuh" -nt "$obj" ] || [ "$HERE/../../include/mbeast.h" -nt "$obj" ] || [ "$0" -nt "$obj" ]; then
         rm -f "$obj"
         ( "$NVCC" $FLAGS -c -o "$obj" "$src" 2>&1 | sed "s/^/[$u] /" ; ) &
         pids="$pids $!"

@@ -607,8 +607,17 @@ int conv3x3_fwd_supported(int cin, int cout, int h, int w) {
     return 0;
 }
 
+// csrc/convtc.cu: the same convolution on the tensor cores, for the 16- / 32-channel maps of 8x8 and smaller
+int conv3x3_tc_supported(int cin, int cout, int h, int w);
+int conv3x3_tc(const float* in, const float* wk, const float* bias, float* out, long long n_frames, int cin, int cout, int h,
+               int w, int wmode, int relu_in, const float* mask_src, const float* add_src, cudaStream_t st);
+static int g_conv_tc = 1;                      // mb_set_tuning("conv_tc", 0): keep every shape on the fp32 FMA kernel below
+void conv_set_tuning(int tensor_cores) { g_conv_tc = tensor_cores; }
+
 int conv3x3_fwd(const float* in, const float* wk, const float* bias, float* out, long long n_frames, int cin, int cout,
                 int h, int w, int wmode, int relu_in, const float* mask_src, const float* add_src, cudaStream_t st) {
+    if (g_conv_tc && conv3x3_tc_supported(cin, cout, h, w))
+        return conv3x3_tc(in, wk, bias, out, n_frames, cin, cout, h, w, wmode, relu_in, mask_src, add_src, st);
     if (h == w) {
 #define X(CI, CO, HH, FG, FPT)                  \
     if (cin == CI && cout == CO && h == HH)     \

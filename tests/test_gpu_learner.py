@@ -196,19 +196,24 @@ def test_unpack_rollout_kernel(cells, n):
 def test_ppo_learn_accepts_the_compact_wire_format():
     from microbeast_b200 import buffers as mbuf, synth
     from microbeast_b200.learner import PPO_learn
-    mine, _ = _pair(8, 8, seed=21)
+    from microbeast_b200.model import Agent
+    from oracle import NVEC_CELL
+    torch.manual_seed(21)
+    # torch's default initialisation: the N(0, 0.15^2) golden fixture weights amplify a flipped max-pool near-tie into a
+    # 1e-3 gradient change (tests/test_gpu_parity.py documents one), which is not what this test is about
+    mine = Agent((8, 8, 27), list(NVEC_CELL) * 64, 64).cuda()
     batch = synth.make_rollout_batch(8, 8, 10, 6, seed=8, full_keys=False)
     batch["logprobs"] = -torch.rand(batch["reward"].shape) * 30
     a = PPO_learn(mine, mine, "plain", batch, torch.optim.SGD(mine.parameters(), lr=0.0), 3, 10, 2)
     ga = [p.grad.clone() for p in mine.parameters()]
     b = PPO_learn(mine, mine, "compact", mbuf.pack_batch(batch), torch.optim.SGD(mine.parameters(), lr=0.0), 3, 10, 2)
-    # the compact format's first convolution adds weight columns over the set observation bits (mb_conv1_bits_fwd), the
-    # plain one multiplies by 0.0 / 1.0 planes: same mathematics, another fp32 summation order
+    # the compact format's first convolution adds / subtracts weight columns over the observation bits
+    # (mb_conv1_bits_fwd, and mb_conv1_bits_wgrad in the backward), the plain one multiplies by 0.0 / 1.0 planes: same
+    # mathematics, another fp32 summation order
     np.testing.assert_allclose(a, b, rtol=2e-5, atol=1e-7)
-    # two fp32 orderings of the first convolution, amplified by the N(0, 0.15^2) fixture weights of this test
-    # (measured 3.3e-4 of a gradient's rms); atomics in the cell-list backward add run-to-run noise at 1e-6
+    # atomics in the cell-list backward and in the weight gradients add run-to-run noise at 1e-6 of a gradient's rms
     for x, p in zip(ga, mine.parameters()):
-        ok, worst = close_rms(p.grad, x, 1e-3)
+        ok, worst = close_rms(p.grad, x, 2e-4)
         assert ok, worst
 
 
