@@ -49,7 +49,6 @@ constexpr int kTcJobN = 144;                     // 9 taps x 16 output channels 
 constexpr int kTcSlotCols = 160;                 // TMEM columns from one accumulator slot to the next
 constexpr int kTcSlots = 3;
 constexpr int kTcStages = 2;
-constexpr int kTcRawBytes = 48 * 1024;          // ring of raw input tiles in flight (cp.async)
 constexpr int kTcTileA = kTcM * 128;             // bytes of an A operand half: 128 rows x 32 fp32
 constexpr int kTcXchPitch = 17;                  // floats per pixel in the warp-boundary exchange (16 + 1: no bank conflicts)
 constexpr int kTcXchWarp = 2 * 8 * kTcXchPitch;    // floats a warp publishes: its last row's z0 and its first row's z2
@@ -64,9 +63,10 @@ struct TcCfg {
     static constexpr int KSTEPS = CIN / 8;
     static constexpr int BBYTES = JOBS * kTcJobB;                  // one half (hi or lo) of the weights
     static constexpr int LOADS = 32 * CIN / kTcStagers;            // float4 pieces per staging thread and tile
-    static constexpr int RAW_SLOTS = kTcRawBytes / (kTcM * CIN * 4);   // 3 (cin 32) or 6 (cin 16) tiles
+    static constexpr int RAW_SLOTS = CIN == 32 ? 3 : 6;               // raw input tiles in the cp.async ring
+    static constexpr int RAW_BYTES = RAW_SLOTS * (kTcM * CIN + kTcM) * 4;  // frames padded by HW floats each: + 128 floats per tile
     static constexpr int AHEAD = RAW_SLOTS - 1;                       // tiles whose loads are in flight
-    static constexpr int SMEM = 1024 + 2 * BBYTES + kTcStages * 2 * kTcTileA + kTcXchBytes + kTcRawBytes;
+    static constexpr int SMEM = 1024 + 2 * BBYTES + kTcStages * 2 * kTcTileA + kTcXchBytes + RAW_BYTES;
     static_assert(kTcM % HW == 0 && HW >= 4 && (CIN == 16 || CIN == 32) && (COUT == 16 || COUT == 32), "shape");
 };
 
@@ -95,7 +95,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) conv3x3_tc_kernel(const float* 
                                                                     const float* __restrict__ bias, float* __restrict__ out,
                                                                     long long n_frames, int wmode, int relu_in,
                                                                     const float* __restrict__ mask_src,
-                                                                    const float* __restrict__ add_src) {
+                                                                    const float* __restrict__ add_src, int debug) {
     constexpr int CIN = C::CIN, COUT = C::COUT, H = C::H, W = C::W, HW = C::HW;
     extern __shared__ uint8_t tc_smem_raw[];
     __shared__ __align__(8) uint64_t a_full[kTcStages], a_empty[kTcStages], acc_full[kTcSlots], acc_empty[kTcSlots];
@@ -124,15 +124,26 @@ __global__ void __launch_bounds__(kTcThreads, 1) conv3x3_tc_kernel(const float* 
     // weights -> B rows n = (job * 9 + tap) * 16 + c, K-major (k = input channel), split; wmode as mb_conv3x3_fwd:
     // 0 = [cin][cout][9], 1 = a torch Conv2d weight [cout][cin][3][3], 2 = the torch weight [cin][cout][3][3] of the
     // convolution whose data gradient this is, taps flipped
-    for (int i = tid; i < 9 * COUT * CIN; i += kTcThreads) {
-        const int ci = i % CIN, n = i / CIN;
+    // (all the loads first: one round trip to L2 instead of one per element)
+    constexpr int kWPer = (9 * COUT * CIN + kTcThreads - 1) / kTcThreads;
+    float wreg[kWPer];
+#pragma unroll
+    for (int r = 0; r < kWPer; ++r) {
+        const int i = tid + r * kTcThreads, ci = i % CIN, n = i / CIN;
         const int c16 = n % 16, tap = (n / 16) % 9, co = (n / kTcJobN) * 16 + c16;
-        const float v = wmode == 0 ? wk[(ci * COUT + co) * 9 + tap]
-                      : wmode == 1 ? wk[(co * CIN + ci) * 9 + tap] : wk[(ci * COUT + co) * 9 + (8 - tap)];
-        float hi, lo;
-        split_tf32_pair(v, hi, lo);
-        *reinterpret_cast<float*>(b_hi + sw128_off(n, ci)) = hi;
-        *reinterpret_cast<float*>(b_lo + sw128_off(n, ci)) = lo;
+        wreg[r] = 0.0f;
+        if (i < 9 * COUT * CIN)
+            wreg[r] = __ldg(wk + (wmode == 0 ? (ci * COUT + co) * 9 + tap : wmode == 1 ? (co * CIN + ci) * 9 + tap : (ci * COUT + co) * 9 + (8 - tap)));
+    }
+#pragma unroll
+    for (int r = 0; r < kWPer; ++r) {
+        const int i = tid + r * kTcThreads, ci = i % CIN, n = i / CIN;
+        if (i < 9 * COUT * CIN) {
+            float hi, lo;
+            split_tf32_pair(wreg[r], hi, lo);
+            *reinterpret_cast<float*>(b_hi + sw128_off(n, ci)) = hi;
+            *reinterpret_cast<float*>(b_lo + sw128_off(n, ci)) = lo;
+        }
     }
     if (tid < COUT) s_bias[tid] = bias ? bias[tid] : 0.0f;
     fence_proxy_async_smem();                                // the MMAs read these generic-proxy writes
@@ -144,16 +155,19 @@ __global__ void __launch_bounds__(kTcThreads, 1) conv3x3_tc_kernel(const float* 
 
     if (warp >= 12 && warp < 16) {
         // ===================== staging: NCHW floats -> swizzled K-major TF32 halves =====================
+        // thread = pixel of the tile.  The raw ring holds tiles as they lie in memory ([frame][channel][pixel]), each
+        // frame followed by HW floats of padding so that the frames a warp straddles (4x4, 2x2 maps) fall on other banks.
         const int t = tid - 384;
-        float4* raw = reinterpret_cast<float4*>(raw_base);                        // [RAW_SLOTS][32 * CIN]: a thread reads back its own pieces
+        constexpr int kFrameF = CIN * HW + HW;                                    // floats per frame in the ring
         auto issue = [&](long long tile, int slot) {
-            const long long f0 = tile * C::FPT;
+            const float* src = in + tile * (long long)(kTcM * CIN);
+            float* dst = reinterpret_cast<float*>(raw_base) + slot * (C::FPT * kFrameF);
 #pragma unroll
             for (int r = 0; r < C::LOADS; ++r) {
-                const int j = t + kTcStagers * r, ci = j % CIN, g = j / CIN;             // g: which 4 pixels of the tile
-                const int fr = g / (HW / 4), q = g % (HW / 4);
-                const bool valid = f0 + fr < n_frames;                            // frames past the end read as zeros
-                tc_cp_async16(raw + slot * (32 * CIN) + j, valid ? in + ((f0 + fr) * CIN + ci) * HW + 4 * q : in, valid);
+                const int i = t + kTcStagers * r;                                 // 16-byte piece of the tile, in memory order
+                const int fr = i / (CIN * HW / 4), rem = i % (CIN * HW / 4);
+                const bool valid = tile * C::FPT + fr < n_frames;                 // frames past the end read as zeros
+                tc_cp_async16(dst + fr * kFrameF + 4 * rem, valid ? src + 4 * i : in, valid);
             }
         };
 #pragma unroll
@@ -162,31 +176,37 @@ __global__ void __launch_bounds__(kTcThreads, 1) conv3x3_tc_kernel(const float* 
             if (tile < n_tiles) issue(tile, d);
             asm volatile("cp.async.commit_group;" ::: "memory");
         }
+        const int sfr = t / HW, spix = t % HW, r7 = t & 7;
+        const uint32_t row_off = uint32_t((t >> 3) * 1024 + r7 * 128);
         uint32_t it = 0;
         for (long long tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, ++it) {
             const int s = it % kTcStages;
+            asm volatile("cp.async.wait_group %0;" ::"n"(C::AHEAD - 1) : "memory");       // my pieces of this tile have landed
+            asm volatile("bar.sync 4, 128;" ::: "memory");   // ... everyone's have, and everyone is done with the previous tile's slot
             const long long ahead = tile + (long long)C::AHEAD * gridDim.x;
-            if (ahead < n_tiles) issue(ahead, (it + C::AHEAD) % C::RAW_SLOTS);    // the slot read one iteration ago
+            if (ahead < n_tiles) issue(ahead, (it + C::AHEAD) % C::RAW_SLOTS);
             asm volatile("cp.async.commit_group;" ::: "memory");
-            asm volatile("cp.async.wait_group %0;" ::"n"(C::AHEAD) : "memory");   // this tile's pieces have landed
             mbar_wait(&a_empty[s], ((it / kTcStages) & 1) ^ 1, nullptr);          // passes at once the first time round
-            uint8_t* ah = a_base + s * 2 * kTcTileA;
-            uint8_t* al = ah + kTcTileA;
-            const float4* mine = raw + (it % C::RAW_SLOTS) * (32 * CIN);
+            if (debug & 2) {                                                      // timing experiment: no conversion
+                mbar_arrive(&a_full[s]);
+                continue;
+            }
+            uint8_t* ah = a_base + s * 2 * kTcTileA + row_off;
+            const float* px = reinterpret_cast<const float*>(raw_base) + (it % C::RAW_SLOTS) * (C::FPT * kFrameF) + sfr * kFrameF + spix;
 #pragma unroll
-            for (int r = 0; r < C::LOADS; ++r) {
-                const int j = t + kTcStagers * r, ci = j % CIN, g = j / CIN;
-                const float4 v = mine[j];
-                float e[4] = {v.x, v.y, v.z, v.w};
+            for (int cg = 0; cg < CIN / 4; ++cg) {
+                uint32_t hi[4], lo[4];
 #pragma unroll
                 for (int k = 0; k < 4; ++k) {
-                    const float xv = relu_in ? fmaxf(e[k], 0.0f) : e[k];
-                    float hi, lo;
-                    split_tf32_pair(xv, hi, lo);
-                    const uint32_t off = sw128_off(4 * g + k, ci);
-                    *reinterpret_cast<float*>(ah + off) = hi;
-                    *reinterpret_cast<float*>(al + off) = lo;
+                    float xv = px[(4 * cg + k) * HW];
+                    if (relu_in) xv = fmaxf(xv, 0.0f);
+                    // nearest TF32 (ties away from zero, as cvt.rna.tf32.f32), twice: x = hi + lo up to 2^-22 |x|
+                    hi[k] = (__float_as_uint(xv) + 0x1000u) & 0xffffe000u;
+                    lo[k] = (__float_as_uint(xv - __uint_as_float(hi[k])) + 0x1000u) & 0xffffe000u;
                 }
+                const uint32_t off = uint32_t((cg ^ r7) << 4);                   // the 128-byte swizzle: 16-byte chunk ^ row-in-atom
+                *reinterpret_cast<uint4*>(ah + off) = make_uint4(hi[0], hi[1], hi[2], hi[3]);
+                *reinterpret_cast<uint4*>(ah + kTcTileA + off) = make_uint4(lo[0], lo[1], lo[2], lo[3]);
             }
             fence_proxy_async_smem();
             mbar_arrive(&a_full[s]);
@@ -210,6 +230,10 @@ __global__ void __launch_bounds__(kTcThreads, 1) conv3x3_tc_kernel(const float* 
                     const uint32_t d = tmem_base + uint32_t(slot * kTcSlotCols);
                     const uint64_t bh = make_kmajor_sw128_desc(smem_u32(b_hi + h * kTcJobB));
                     const uint64_t bl = make_kmajor_sw128_desc(smem_u32(b_lo + h * kTcJobB));
+                    if (debug & 4) {                         // timing experiment: no MMAs
+                        tc_commit(&acc_full[slot]);
+                        continue;
+                    }
                     // the two small cross terms first, the hi * hi bulk last (see the header)
 #pragma unroll
                     for (int k = 0; k < C::KSTEPS; ++k) mma_tf32(d, a_lo + uint64_t(k * 2), bh + uint64_t(k * 2), idesc, k != 0);
@@ -242,19 +266,36 @@ __global__ void __launch_bounds__(kTcThreads, 1) conv3x3_tc_kernel(const float* 
                 if (int(job % kTcSlots) != group) continue;
                 mbar_wait(&acc_full[group], mine & 1, nullptr);
                 tc_fence_after();
+                if (debug & 1) {                             // timing experiment: no epilogue work
+                    tc_fence_before();
+                    __syncwarp();
+                    if (lane == 0) mbar_arrive(&acc_empty[group]);
+                    ++mine;
+                    continue;
+                }
                 float acc[16], z0[16], z2[16];
+                // 12 units of (tap row ky, 4 channels): the TMEM reads of unit u + 1 are in flight while unit u is shifted
+                uint32_t ybuf[2][12];
+                auto unit_issue = [&](int u, uint32_t (&dst)[12]) {
+                    const uint32_t col = taddr + uint32_t((u / 4) * 48 + (u % 4) * 4);          // tap (ky, 0), channels 4 * (u % 4) ..
+                    tmem_ld4x3_issue(col, col + 16u, col + 32u, dst);
+                };
+                unit_issue(0, ybuf[0]);
 #pragma unroll
-                for (int ky = 0; ky < 3; ++ky) {
-                    float ya[16], yb[16], yc[16];            // taps (ky, 0), (ky, 1), (ky, 2) of this pixel
-                    tmem_ld48(taddr + uint32_t(ky * 48), ya, yb, yc);
+                for (int u = 0; u < 12; ++u) {
+                    uint32_t (&cur)[12] = ybuf[u & 1];
+                    tmem_ld_wait12(cur);
+                    if (u + 1 < 12) unit_issue(u + 1, ybuf[(u + 1) & 1]);
+                    const int ky = u / 4, c0 = (u % 4) * 4;
 #pragma unroll
-                    for (int c = 0; c < 16; ++c) {
+                    for (int i = 0; i < 4; ++i) {
                         // Z[q][ky] = Y[q-1][ky,0] + Y[q][ky,1] + Y[q+1][ky,2] within the pixel row
-                        const float l = __shfl_up_sync(0xffffffffu, ya[c], 1), r = __shfl_down_sync(0xffffffffu, yc[c], 1);
-                        const float z = fmaf(mxl, l, fmaf(mxr, r, yb[c]));
-                        if (ky == 0) z0[c] = z;
-                        if (ky == 1) acc[c] = z;
-                        if (ky == 2) z2[c] = z;
+                        const float l = __shfl_up_sync(0xffffffffu, __uint_as_float(cur[i]), 1);
+                        const float r = __shfl_down_sync(0xffffffffu, __uint_as_float(cur[8 + i]), 1);
+                        const float z = fmaf(mxl, l, fmaf(mxr, r, __uint_as_float(cur[4 + i])));
+                        if (ky == 0) z0[c0 + i] = z;
+                        if (ky == 1) acc[c0 + i] = z;
+                        if (ky == 2) z2[c0 + i] = z;
                     }
                 }
                 tc_fence_before();
@@ -313,6 +354,8 @@ __global__ void __launch_bounds__(kTcThreads, 1) conv3x3_tc_kernel(const float* 
     if (warp == 16) tmem_dealloc(tmem_base, 512);
 }
 
+int g_tc_debug = 0;          // mb_set_tuning("conv_tc_debug", bits): timing experiments that skip a role's work (wrong results)
+
 template <class C>
 int tc_launch(const float* in, const float* wk, const float* bias, float* out, long long n_frames, int wmode, int relu_in,
               const float* mask_src, const float* add_src, cudaStream_t st) {
@@ -326,7 +369,7 @@ int tc_launch(const float* in, const float* wk, const float* bias, float* out, l
     }
     const long long tiles = (n_frames + C::FPT - 1) / C::FPT, cap = sm_count(dev);
     conv3x3_tc_kernel<C><<<int(tiles < cap ? tiles : cap), kTcThreads, C::SMEM, st>>>(in, wk, bias, out, n_frames, wmode, relu_in,
-                                                                                    mask_src, add_src);
+                                                                                    mask_src, add_src, g_tc_debug);
     MB_CUDA(cudaGetLastError());
     return MB_OK;
 }
@@ -336,6 +379,8 @@ int tc_launch(const float* in, const float* wk, const float* bias, float* out, l
     X(16, 16, 8) X(16, 16, 4) X(16, 32, 8) X(16, 32, 4) X(32, 16, 8) X(32, 16, 4) X(32, 32, 8) X(32, 32, 4) X(32, 32, 2)
 
 }  // namespace
+
+void conv_tc_set_debug(int bits) { g_tc_debug = bits; }
 
 int conv3x3_tc_supported(int cin, int cout, int h, int w) {
     if (h != w) return 0;

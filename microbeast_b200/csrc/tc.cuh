@@ -106,6 +106,27 @@ __device__ __forceinline__ void tmem_ld48(uint32_t taddr, float (&a)[16], float 
     }
 }
 
+// Split-phase TMEM reads for software pipelining: tmem_ld4x3_issue starts three 4-column loads (columns col0.., col1..,
+// col2.. of this thread's lane) into r[0..11] and returns; tmem_ld_wait12 waits for every load this thread has issued
+// and ties r[] to the wait, so that no use of r[] can be scheduled before it.
+__device__ __forceinline__ void tmem_ld4x3_issue(uint32_t t0, uint32_t t1, uint32_t t2, uint32_t (&r)[12]) {
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x4.b32 {%0, %1, %2, %3}, [%12];\n\t"
+        "tcgen05.ld.sync.aligned.32x32b.x4.b32 {%4, %5, %6, %7}, [%13];\n\t"
+        "tcgen05.ld.sync.aligned.32x32b.x4.b32 {%8, %9, %10, %11}, [%14];"
+        : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
+          "=r"(r[9]), "=r"(r[10]), "=r"(r[11])
+        : "r"(t0), "r"(t1), "r"(t2)
+        : "memory");
+}
+__device__ __forceinline__ void tmem_ld_wait12(uint32_t (&r)[12]) {
+    asm volatile("tcgen05.wait::ld.sync.aligned;"
+                 : "+r"(r[0]), "+r"(r[1]), "+r"(r[2]), "+r"(r[3]), "+r"(r[4]), "+r"(r[5]), "+r"(r[6]), "+r"(r[7]), "+r"(r[8]),
+                   "+r"(r[9]), "+r"(r[10]), "+r"(r[11])
+                 :
+                 : "memory");
+}
+
 // Instruction descriptor of tcgen05.mma.kind::tf32 for an M x N tile: [4,6) D format 1 = F32; [7,10) A format
 // 2 = TF32; [10,13) B format 2 = TF32; bits 15 / 16 = 0: A and B are K-major; [17,23) N >> 3; [24,29) M >> 4.
 __host__ __device__ constexpr uint32_t tf32_idesc(int m, int n) {

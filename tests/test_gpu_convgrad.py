@@ -302,3 +302,38 @@ def test_first_convolution_from_bits(h, n):
             for name, a, b in (("dW", conv.weight.grad, ref.weight.grad), ("db", conv.bias.grad, ref.bias.grad)):
                 err = (a.double() - b).abs().max() / b.abs().max().clamp_min(1.0)
                 assert err < 2e-6, (pattern, from_bits, name, float(err))
+
+
+@pytest.mark.parametrize("cin,cout,h", [(16, 16, 8), (16, 16, 4), (16, 32, 8), (16, 32, 4), (32, 16, 8), (32, 16, 4),
+                                         (32, 32, 8), (32, 32, 4), (32, 32, 2)])
+def test_tensor_core_convolution_against_float64(cin, cout, h):
+    """csrc/convtc.cu (tcgen05, one M128 x N144 product per pixel tile against all nine taps + shift-and-add epilogue)
+    for every shape it covers: forward with a torch weight, the data-gradient form with ReLU on the input, the ReLU
+    mask and the residual add folded in, frame counts that leave the last 128-pixel tile ragged -- against float64
+    conv2d / conv_transpose2d.  Measured on B200: 2.3e-7 of max |out| (the fp32 FMA kernel: 6.8e-7); bound 2e-6."""
+    from microbeast_b200 import ops, set_tuning
+    g = torch.Generator(device="cuda").manual_seed(cin * 100 + cout + h)
+    rnd = lambda *shape: torch.randn(shape, generator=g, device="cuda")
+    frames_per_tile = 128 // (h * h)
+    for n in (1, frames_per_tile + 1, 5 * frames_per_tile - 1, 301):
+        x, wt, b = rnd(n, cin, h, h), rnd(cout, cin, 3, 3) * 0.2, rnd(cout)
+        want = F.conv2d(x.double(), wt.double(), b.double(), padding=1)
+        before = dict(ops.launch_counts)
+        got = ops.conv3x3_fwd(x, wt, b, wmode=1)
+        assert float((got.double() - want).abs().max() / want.abs().max()) < 2e-6, ("forward", n)
+        # [cin][cout][9] weight layout (wmode 0)
+        got0 = ops.conv3x3_fwd(x, wt.permute(1, 0, 2, 3).reshape(cin, cout, 9).contiguous(), b, wmode=0)
+        assert torch.equal(got0, got), ("wmode 0", n)
+        wt2 = rnd(cin, cout, 3, 3) * 0.2                  # weight of a convolution cout -> cin whose input gradient this is
+        msk, add = rnd(n, cout, h, h), rnd(n, cout, h, h)
+        want2 = F.conv_transpose2d(torch.relu(x).double(), wt2.double(), padding=1)
+        want2 = torch.where(msk > 0, want2, torch.zeros_like(want2)) + add.double()
+        got2 = ops.conv3x3_fwd(x, wt2, None, wmode=2, relu_in=True, mask_src=msk, add_src=add)
+        assert float((got2.double() - want2).abs().max() / want2.abs().max()) < 2e-6, ("data gradient + tails", n)
+        # the fp32 FMA kernel behind the same entry point (mb_set_tuning("conv_tc", 0)) agrees to fp32 rounding
+        set_tuning("conv_tc", 0)
+        try:
+            old = ops.conv3x3_fwd(x, wt, b, wmode=1)
+        finally:
+            set_tuning("conv_tc", 1)
+        assert float((old - got).abs().max() / want.abs().max()) < 2e-6, ("FMA kernel", n)
