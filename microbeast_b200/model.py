@@ -325,6 +325,9 @@ class _ActorHead(torch.autograd.Function):
         ctx.save_for_backward(hidden, weight, logits, action_mask, action)
         ctx.cells, ctx.mode = cells, mode
         ctx.mark_non_differentiable(logits)
+        # undefined output gradients arrive as None: autograd would otherwise zero-fill an [N, 78C] fp32 gradient for
+        # `logits` before every backward (1.66 GB, 0.22 ms of the config-2 step)
+        ctx.set_materialize_grads(False)
         return logits, logprobs, entropy
 
     @staticmethod
