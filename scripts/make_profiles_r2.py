@@ -57,7 +57,12 @@ keep = [k for k in keep if k in idx]
 N, C = 20736, 256
 alg = {"pack_cells": ("pack_cells", "byte", (78 + 56 + 16) * N * C), "actor_head_fwd": ("actor_head_fwd", "flop (3 x TF32)", 3 * 2.0 * N * 80 * C * 256),
        "cell_grad": ("cells_bwd", "flop (fp32 FMA x2)", None), "head_kernel": ("head_sample", "byte", 474 * C * N + 8 * N),
-       "vtrace": ("vtrace_loss", "byte", 37 * 65536 * 512 + 4 * 65536)}
+       "vtrace": ("vtrace_loss", "byte", 37 * 65536 * 512 + 4 * 65536),
+       # tensor-core convolutions: issued TF32 flops = 3 passes x 2 x pixels x 9 taps x cin x cout
+       "TcCfg<32, 32, 4>": ("conv3x3_tc_32x32x4", "flop (3 x TF32)", 3 * 2.0 * N * 16 * 9 * 32 * 32),
+       "TcCfg<16, 16, 8>": ("conv3x3_tc_16x16x8", "flop (3 x TF32)", 3 * 2.0 * N * 64 * 9 * 16 * 16),
+       # first convolution from bits: bytes = one int32 per cell in, 16 fp32 per cell out (fwd); the reverse + 7 KB (wgrad)
+       "conv1_bits_fwd": ("conv1_bits_fwd", "byte", N * 256 * (4 + 64)), "conv1_bits_wgrad": ("conv1_bits_wgrad", "byte", N * 256 * (4 + 64))}
 traffic = json.load(open(os.path.join(P, "traffic.json")))
 with open(os.path.join(P, "r02_ncu_kernels.csv"), "w") as f:
     w = csv.writer(f)
@@ -84,8 +89,8 @@ with open(os.path.join(P, "r02_ncu_kernels.csv"), "w") as f:
 json.dump(traffic, open(os.path.join(P, "traffic.json"), "w"), indent=1)
 open(os.path.join(P, "r02_ncu_stalls.md"), "w").write(
     "# ncu --set full, source page summary (r02)\n\nCommand: `ncu --set full --clock-control none --import-source on "
-    "-k regex:'pack_cells_kernel|actor_head_fwd_kernel|cell_grad_kernel|head_kernel|vtrace_tma' -s 5 -c 5 python "
-    "scripts/profile_r2.py 2` (config 2 shapes: 20 736 frames x 256 cells; T=512 x R=65 536 for V-trace; one launch each, "
+    "-k regex:'pack_cells_kernel|actor_head_fwd_kernel|cell_grad_kernel|head_kernel|vtrace_tma|conv3x3_tc_kernel|conv1_bits' -s 9 -c 9 python "
+    "scripts/profile_r2.py 2` (config 2 shapes: 20 736 frames x 256 cells; T=512 x R=65 536 for V-trace; 20 736 frames for the convolutions; one launch each, "
     "cold cache).\n\n" + "\n".join(stall_summary(src)))
 
 rows = [r for r in csv.reader(open(os.path.join(G, "launches_r2.csv"))) if len(r) > 10]
