@@ -2,7 +2,7 @@
 """Benchmark of the learner hot path (BASELINE.json metric: learner env-frames/s).
 
     python bench.py --gpus 1 --steps 20 --warmup 5                 # our arm, one JSON line
-    python bench.py --impl reference --steps 3 --warmup 1          # reference CPU arm (oracle port)
+    python bench.py --impl reference --steps 3 --warmup 1          # reference CPU arm (the staged reference itself)
     torchrun --nnodes=1 --nproc-per-node N ... bench.py --gpus N   # data-parallel, weak scaling
     python bench.py --sweep vtrace | --sweep head                  # kernel-only tables (profiles/)
 
@@ -13,13 +13,19 @@ per rank (N=4 is config 3's global batch of 1024 rows).  frames/step = rows*T as
 reference counts them (microbeast.py:230).
 
 value   = whole-job frames/s with the batch already resident in HBM.
-e2e     = the same step through the public call PPO_learn(...) with the batch in pinned HOST
-          memory: host->device copies of that step's inputs and the device->host read of the
-          four losses are inside the timed region.
-roofline= the dominant kernel of ours (head_eval_bwd, 758 B/cell), timed live with CUDA events
-          on the launching stream inside the timed region, against MEASURED_PEAKS.json.
-cpu_baseline = the oracle port of the reference's CPU path (oracle/learner.py) timed on the
-          host cores on a bounded sample of the same workload (rank 0, N=1 only).
+e2e     = the same step through the public calls BatchPrefetcher.submit(...) + PPO_learn(...) with the batch in
+          pinned HOST memory: host->device copies of that step's inputs (staged one step ahead on a side stream)
+          and the device->host read of the four losses are inside the timed region.
+parity  = the gate run before timing: one lr = 0 step on a 32-row sample of the benchmarked workload, GPU fp32 and
+          CPU fp32 (the reference's arithmetic) both against a float64 evaluation (oracle/parity.py); the bench exits 3
+          instead of printing a number when the GPU is further off than max(1e-5, 4 x the CPU's error).
+roofline= the dominant kernel of ours -- the fused actor Linear + policy head (csrc/fused.cu), a tensor-pipe kernel:
+          issued TF32 TFLOP/s, timed live with CUDA events on the launching stream inside the timed region, against
+          half the measured bf16 rate of MEASURED_PEAKS.json; the dominant HBM-bound kernel sits under
+          info.roofline_hbm.
+cpu_baseline = the reference's own PPO_learn + Agent (byte copies staged into oracle/_ref by oracle/stage_ref.py;
+          the oracle port when they are missing) timed on the host cores on a bounded sample of the same workload
+          (rank 0, N=1 only).  --impl reference runs only that arm and never imports the package.
 """
 from __future__ import annotations
 

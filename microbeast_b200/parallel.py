@@ -87,10 +87,21 @@ class GradAllReducer:
         for p in self._head_params:
             p.register_post_accumulate_grad_hook(self._head_ready)
 
+    def _mark(self, name: str) -> None:
+        """With ``self.marks = {}`` set by a caller (scripts/dp_timeline.py), records a CUDA event on the compute stream
+        at the named point of the step; ``None`` (the default) costs nothing."""
+        marks = getattr(self, "marks", None)
+        if marks is not None:
+            ev = torch.cuda.Event(enable_timing=True)
+            ev.record()
+            marks[name] = ev
+
     def _head_ready(self, _param) -> None:
         if self._pending <= 0:
             return
         self._pending -= 1
+        if self._pending == 0:
+            self._mark("head_grads_ready")
         if self._pending == 0 and self.world_size > 1 and self._head_numel:
             # issued behind the kernels that produced these gradients; runs on the backend's own stream while the
             # rest of the backward pass keeps the compute stream busy
@@ -106,6 +117,7 @@ class GradAllReducer:
                 if p.requires_grad and p.grad is None:
                     self.attach(model)
                     break
+        self._mark("begin")
         self._grads.zero_()
         self._pending = len(self._head_params)
         self._early = None
@@ -116,6 +128,7 @@ class GradAllReducer:
         if n_extra > self._n_extra:
             raise ValueError("GradAllReducer.finish: at most 8 extra scalars")
         tail = self._grads[self._total_numel: self._total_numel + n_extra]
+        self._mark("backward_done")
         if n_extra:
             tail.copy_(extra.reshape(-1))
         if self.world_size > 1:
@@ -126,6 +139,7 @@ class GradAllReducer:
                 self._early.wait()
             late.wait()
             self._early = None
+        self._mark("gradients_summed")
         self._pending = 0
         self.calls += 1
         return tail.clone().view_as(extra) if n_extra else extra
