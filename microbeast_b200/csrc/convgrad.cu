@@ -25,6 +25,8 @@
 //   * persistent CTAs walk the frame chunks; every CTA writes its partial dW -- and the bias gradient,
 //     summed from the dY planes it staged anyway -- to its own slot of a [grid, COUT*CIN*9 + COUT]
 //     buffer, and the caller adds the slots up (fixed order: deterministic).
+#include <atomic>
+
 #include "common.cuh"
 
 #include "../../include/mbeast.h"
@@ -611,7 +613,7 @@ int conv3x3_fwd_supported(int cin, int cout, int h, int w) {
 int conv3x3_tc_supported(int cin, int cout, int h, int w);
 int conv3x3_tc(const float* in, const float* wk, const float* bias, float* out, long long n_frames, int cin, int cout, int h,
                int w, int wmode, int relu_in, const float* mask_src, const float* add_src, cudaStream_t st);
-static int g_conv_tc = 1;                      // mb_set_tuning("conv_tc", 0): keep every shape on the fp32 FMA kernel below
+static std::atomic<int> g_conv_tc{1};                       // mb_set_tuning("conv_tc", 0): keep every shape on the fp32 FMA kernel below
 void conv_set_tuning(int tensor_cores) { g_conv_tc = tensor_cores; }
 
 int conv3x3_fwd(const float* in, const float* wk, const float* bias, float* out, long long n_frames, int cin, int cout,

@@ -30,6 +30,8 @@
 //              shuffles as the 144 columns are read (8x8 maps: the two frame rows that meet at a warp boundary go
 //              through shared memory), then bias / ReLU-mask / residual add and coalesced NCHW stores.
 // The weights (both halves, all taps) stay in shared memory for the CTA's lifetime.
+#include <atomic>
+
 #include "common.cuh"
 #include "tc.cuh"
 
@@ -354,7 +356,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) conv3x3_tc_kernel(const float* 
     if (warp == 16) tmem_dealloc(tmem_base, 512);
 }
 
-int g_tc_debug = 0;          // mb_set_tuning("conv_tc_debug", bits): timing experiments that skip a role's work (wrong results)
+std::atomic<int> g_tc_debug{0};          // mb_set_tuning("conv_tc_debug", bits): timing experiments that skip a role's work (wrong results)
 
 template <class C>
 int tc_launch(const float* in, const float* wk, const float* bias, float* out, long long n_frames, int wmode, int relu_in,

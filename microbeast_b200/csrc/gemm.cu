@@ -22,6 +22,8 @@
 //   warps 2-9:        epilogue -- tcgen05.ld both accumulators (a warp reads its own 32-lane quadrant, a
 //                     thread 128 columns of one output row), sum them in registers, release the
 //                     accumulators, then add the bias and store while warp 1 already runs the next tile.
+#include <atomic>
+
 #include "common.cuh"
 #include "tc.cuh"
 
@@ -240,20 +242,50 @@ EncodeTiledFn gemm_encode_fn() {
     return fn;
 }
 
-// [rows, K] fp32 row-major -> boxes of box_rows x 32 floats (128 B), 128-byte swizzle, zero fill past the edges
+// [rows, K] fp32 row-major -> boxes of box_rows x 32 floats (128 B), 128-byte swizzle, zero fill past the edges.
+// The learner calls with the same buffers every step, so encoded maps are kept in a small direct-mapped cache keyed
+// by (pointer, rows, K, box rows); a map describes addresses and shapes only, never contents.
+struct GemmMapKey {
+    const void* base;
+    long long rows;
+    int K, box_rows;
+    bool operator==(const GemmMapKey& o) const { return base == o.base && rows == o.rows && K == o.K && box_rows == o.box_rows; }
+};
+struct GemmMapSlot {
+    GemmMapKey key;
+    CUtensorMap map;
+    bool valid;
+};
+GemmMapSlot g_gemm_maps[64];
+std::mutex g_gemm_map_mutex;
+
 bool gemm_map(EncodeTiledFn enc, CUtensorMap* m, const float* base, long long rows, int K, int box_rows) {
+    const GemmMapKey key{base, rows, K, box_rows};
+    size_t h = (reinterpret_cast<uintptr_t>(base) >> 8) ^ (size_t(rows) * 0x9E3779B97F4A7C15ull) ^ (size_t(box_rows) << 5) ^ size_t(K);
+    GemmMapSlot& slot = g_gemm_maps[(h ^ (h >> 23)) & 63];
+    std::lock_guard<std::mutex> lock(g_gemm_map_mutex);
+    if (slot.valid && slot.key == key) {
+        *m = slot.map;
+        return true;
+    }
     const cuuint64_t gdim[2] = {cuuint64_t(K), cuuint64_t(rows)};
     const cuuint64_t gstride[1] = {cuuint64_t(K) * 4u};
     const cuuint32_t box[2] = {cuuint32_t(kGemmBK), cuuint32_t(box_rows)};
     const cuuint32_t estr[2] = {1, 1};
-    return enc(m, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<float*>(base), gdim, gstride, box, estr,
-               CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
-               CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+    if (enc(m, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<float*>(base), gdim, gstride, box, estr,
+            CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+            CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) != CUDA_SUCCESS)
+        return false;
+    slot.key = key;
+    slot.map = *m;
+    slot.valid = true;
+    return true;
 }
 
 }  // namespace
 
-static int g_gemm_group_m = 0, g_gemm_stream_store = 0;
+// process-wide experiment knobs (mb_set_tuning): atomics, because autograd launches backward kernels from its own threads
+static std::atomic<int> g_gemm_group_m{0}, g_gemm_stream_store{0};
 void gemm_set_tuning(int group_m, int stream_store) {
     g_gemm_group_m = group_m;
     g_gemm_stream_store = stream_store;

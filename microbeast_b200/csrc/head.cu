@@ -18,6 +18,8 @@
 //
 // Roofline: HBM-bound.  Algorithmic bytes per cell: eval fwd 446, eval bwd 758, sample 474
 // (+8 / +8 / +4..8 per frame) -- SURVEY.md section 8(d).
+#include <atomic>
+
 #include "common.cuh"
 
 #include <math.h>
@@ -667,9 +669,9 @@ __global__ void __launch_bounds__(HeadCfg<TC, MODE>::kThreads) head_kernel(const
 // ---------------------------------------------------------------------------------------------
 // Host launchers
 // ---------------------------------------------------------------------------------------------
-static int g_head_ctas_per_sm = 0;      // 0 = as many as fit (occupancy query)
-static int g_head_grid_override = 0;
-static int g_head_variant = -1;         // tile / pipeline shape, see dispatch_head; -1 = per-mode default
+static std::atomic<int> g_head_ctas_per_sm{0};      // 0 = as many as fit (occupancy query)
+static std::atomic<int> g_head_grid_override{0};
+static std::atomic<int> g_head_variant{-1};         // tile / pipeline shape, see dispatch_head; -1 = per-mode default
 void head_set_tuning(int ctas_per_sm, int grid_override, int variant) {
     g_head_ctas_per_sm = ctas_per_sm;
     g_head_grid_override = grid_override;
@@ -693,9 +695,10 @@ static int launch_head(HeadParams p, cudaStream_t stream) {
         occ[dev] = n > 0 ? n : 1;
     }
     p.tiles_per_frame = (p.cells + TC - 1) / TC;
-    const int per_sm = (g_head_ctas_per_sm > 0 && g_head_ctas_per_sm < occ[dev]) ? g_head_ctas_per_sm : occ[dev];
+    const int want_per_sm = g_head_ctas_per_sm.load(), want_grid = g_head_grid_override.load();
+    const int per_sm = (want_per_sm > 0 && want_per_sm < occ[dev]) ? want_per_sm : occ[dev];
     long long grid = (long long)sm_count(dev) * per_sm;
-    if (g_head_grid_override > 0) grid = g_head_grid_override;
+    if (want_grid > 0) grid = want_grid;
     if (grid > p.n_frames) grid = p.n_frames;
     head_kernel<TC, MODE, NSTAGE><<<dim3((unsigned)grid), dim3(Cfg::kThreads), smem, stream>>>(p);
     MB_CUDA(cudaGetLastError());

@@ -21,6 +21,8 @@
 //
 // Roofline: HBM-bound, 29 B per [r,t] element forward (+8 B with the two gradient outputs).
 // Shapes below ~1e7 elements are launch/latency bound and L2 resident.
+#include <atomic>
+
 #include "common.cuh"
 
 #include <cuda.h>
@@ -613,7 +615,7 @@ static EncodeTiledFn get_encode_fn() {
     return fn;
 }
 
-static int g_vt_l2_promo = 256;      // bytes: 0 (none), 64, 128, 256
+static std::atomic<int> g_vt_l2_promo{256};      // bytes: 0 (none), 64, 128, 256
 
 static bool encode_map_2d(EncodeTiledFn enc, CUtensorMap* m, const void* base, bool is_u8, long long rows, int T,
                           long long stride_elems, int tile_steps, int box_rows) {
@@ -674,10 +676,10 @@ static bool make_map_2d(EncodeTiledFn enc, CUtensorMap* m, const void* base, boo
     return true;
 }
 
-static int g_vt_debug = 0;
+static std::atomic<int> g_vt_debug{0};
 void vtrace_set_debug(int v) { g_vt_debug = v; }
-static int g_vt_force_generic = 0;
-static int g_vt_variant = -1;        // -1 = by grid size; see the switch in vtrace_loss_launch
+static std::atomic<int> g_vt_force_generic{0};
+static std::atomic<int> g_vt_variant{-1};        // -1 = by grid size; see the switch in vtrace_loss_launch
 void vtrace_set_tuning(int force_generic, int variant, int l2_promo) {
     g_vt_force_generic = force_generic;
     g_vt_variant = variant;
@@ -881,7 +883,7 @@ constexpr size_t kVtStaticScratchBytes = 64 * 1024;
 
 static __device__ __align__(256) unsigned char g_vt_static_scratch[kVtStaticScratchBytes];
 
-static int g_vt_static_poison = 0;    // test hook, see mb_set_tuning("vtrace_static_poison")
+static std::atomic<int> g_vt_static_poison{0};    // test hook, see mb_set_tuning("vtrace_static_poison")
 
 static int vt_static_scratch(void** out, cudaStream_t stream) {
     static std::mutex mu;
