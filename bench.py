@@ -403,6 +403,11 @@ def run_ours(args):
             dist.barrier()
         torch.cuda.synchronize()
 
+    # kernels that can be the dominant one of the step: only these carry live CUDA-event pairs inside the timed region
+    # (an event pair around each of the step's ~120 launches costs 0.3 ms per step; the rest of the `kernels` table
+    # comes from a separate, untimed pass)
+    LIVE = ("actor_head_fwd", "pack_cells", "cells_bwd", "head_eval_fwd", "head_eval_bwd", "vtrace_loss")
+
     def timed(fn, steps, warmup, sample_clocks=False, kernel_timing=False):
         sampler = ClockSampler(local) if sample_clocks else None
         if sampler:
@@ -414,7 +419,7 @@ def run_ours(args):
             sampler.mark_begin()
         launches0 = ops.total_launches()
         if kernel_timing:
-            ops.start_kernel_timing()
+            ops.start_kernel_timing(only=LIVE if kernel_timing == "live" else None)
         t0, t1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         t0.record()
         for _ in range(steps):
@@ -434,9 +439,14 @@ def run_ours(args):
 
     # ---- value: batch resident in HBM -------------------------------------------------
     ms_step, launches, ktimes, clocks = timed(lambda: step(dev_batch, False), args.steps, max(args.warmup, 3),
-                                              sample_clocks=True, kernel_timing=True)
+                                              sample_clocks=True, kernel_timing="live")
     frames = rows * T * world
     value = frames / (ms_step * 1e-3)
+    # every other kernel of the step, for the `kernels` table: three more steps, outside the timed region
+    _, _, kt_all, _ = timed(lambda: step(dev_batch, False), 3, 1, kernel_timing=True)
+    live_names = set(ktimes)
+    for name, ts in kt_all.items():
+        ktimes.setdefault(name, ts)
 
     # ---- roofline of the dominant kernel (live CUDA events from the timed region) -------
     peak, peak_src = hbm_peak()
@@ -461,7 +471,8 @@ def run_ours(args):
         avg = sum(ts) / len(ts)
         gbs = alg[name] / (avg * 1e-3) / 1e9 if name in alg else None
         kernels[name] = {"launches": len(ts), "avg_ms": avg, "alg_bytes": alg.get(name),
-                         "gbs": gbs, "frac_of_peak": (gbs / peak if gbs else None)}
+                         "gbs": gbs, "frac_of_peak": (gbs / peak if gbs else None),
+                         "timed": "live, inside the timed region" if name in live_names else "separate pass after it"}
         if name.startswith("conv3x3_wgrad") and name in ops.launch_notes:
             nt = ops.launch_notes[name]
             flops = 2.0 * nt["n"] * nt["cout"] * nt["cin"] * (3 * nt["h"] - 2) ** 2      # taps inside the image only
@@ -542,16 +553,38 @@ def run_ours(args):
         state = {"next": pf.submit(host)}
 
         def e2e_step():
-            cur = state["next"]
+            # launch step k, stage batch k+1 behind it (its copies overlap step k's kernels; the slot it overwrites was
+            # released by step k-1), then read step k's four losses on the host
+            out = step(state["next"], False)
             state["next"] = pf.submit(host)
-            return step(cur, True)
+            return out.tolist()
         ms_e2e, _, _, _ = timed(e2e_step, e2e_steps, 3)
+        torch.cuda.synchronize()
+
+        def e2e_step_deferred():
+            # for the record, not the headline: the same loop with step k's losses read while step k+1 runs, so the
+            # device queue never drains (a logger that is one update late); every step still pays its H2D and its D2H
+            out = step(state["next"], False)
+            slot = state["turn"] = (state.get("turn", 0) + 1) % 2
+            pinned4[slot].copy_(out, non_blocking=True)       # D2H of this step's four losses, stream-ordered after it
+            ev = torch.cuda.Event()
+            ev.record()
+            state["next"] = pf.submit(host)
+            prev, state["pending"] = state.get("pending"), (pinned4[slot], ev)
+            if prev is None:
+                return None
+            prev[1].synchronize()                             # waits for step k-1 only; step k keeps the device busy
+            return prev[0].tolist()
+        pinned4 = [torch.empty(4, dtype=torch.float32, pin_memory=True) for _ in range(2)]
+        ms_def, _, _, _ = timed(e2e_step_deferred, e2e_steps, 3)
         torch.cuda.synchronize()
         del state, pf
         e2e = {"value": frames / (ms_e2e * 1e-3), "unit": UNIT, "h2d_bytes_per_step": h2d * world,
                "d2h_bytes_per_step": 16 * world, "ms_per_step": ms_e2e, "steps": e2e_steps,
-               "call": "cur, nxt = nxt, BatchPrefetcher.submit(pinned_host_batch); PPO_learn(model, model, name, cur, adam, "
-                       "rows, T, 1)  (microbeast_b200.learner)",
+               "call": "out = PPO_learn(model, model, name, cur, adam, rows, T, 1, sync=False); cur = "
+                       "BatchPrefetcher.submit(pinned_host_batch); losses = out.tolist()  (microbeast_b200.learner)",
+               "deferred_read": {"value": frames / (ms_def * 1e-3), "ms_per_step": ms_def,
+                                 "note": "losses of step k read on the host while step k+1 runs; not the headline"},
                "serial": {"value": frames / (ms_serial * 1e-3), "ms_per_step": ms_serial,
                           "call": "PPO_learn(model, model, name, pinned_host_batch, adam, rows, T, 1): copy, then compute"},
                "wire_format": ("obs one int32 per cell (27 binary planes), action_mask bit-packed, action u8 -- widened "

@@ -31,12 +31,13 @@ class _Stager:
     (0.7 GB at 16x16, T=80, 256 rows) overlaps the encoder forward of the same step.
     """
 
-    def __init__(self, slots: int = 1, obs_on_side_stream: bool = False):
+    def __init__(self, slots: int = 1, obs_on_side_stream: bool = False, prepack_cells: bool = False):
         self.buffers = {}
         self.streams = {}
         self.slots = max(int(slots), 1)
         self.turn = 0
         self.obs_on_side_stream = obs_on_side_stream
+        self.prepack_cells = prepack_cells      # also build the fused actor head's cell records on the side stream
 
     def _buf(self, name, shape, dtype, device):
         key = (name, tuple(shape), dtype, device, self.turn % self.slots)
@@ -45,7 +46,9 @@ class _Stager:
             buf = self.buffers[key] = torch.empty(tuple(shape), dtype=dtype, device=device)
         return buf
 
-    def stage(self, batch, device, keys):
+    def stage(self, batch, device, keys, slot_free=None):
+        """``slot_free``: a recorded CUDA event after which the staging buffers of this turn's slot are no longer read
+        (``BatchPrefetcher``); without it the side stream waits for everything enqueued on the compute stream so far."""
         compact = "action_mask_bits" in batch        # wire format of buffers.pack_batch / compact store
         keys = [("action_mask_bits" if (k == "action_mask" and compact) else k) for k in keys]
         if all(batch[k].is_cuda for k in keys) and not compact and batch["action"].dtype == torch.int64:
@@ -55,7 +58,10 @@ class _Stager:
             side = self.streams[device] = torch.cuda.Stream(device=device)
         main = torch.cuda.current_stream(device)
         out = {}
-        side.wait_stream(main)                  # the staging buffers may still be read by the last step
+        if slot_free is not None:
+            side.wait_event(slot_free)          # the step that read this slot's buffers last has finished
+        else:
+            side.wait_stream(main)              # the staging buffers may still be read by the last step
         for k in keys:
             t = batch[k]
             if t.is_cuda:
@@ -83,6 +89,15 @@ class _Stager:
                 out["action_mask"] = mask
             if a8 is not None:
                 out["action"] = act
+        if self.prepack_cells and out["action"].dtype == torch.int64 and out["action_mask"].dim() == 2:
+            # the operand form of mb_actor_head_fwd (16-byte (cell, frame) records + alive bitmap): 0.17 ms at config 2
+            # that the step no longer spends on its own stream (model.Agent.get_action picks "_cell_meta" up)
+            n = out["action"].shape[0]
+            cells = out["action"].shape[1] // 7
+            with torch.cuda.stream(side):
+                out["_cell_meta"] = ops.pack_cells(out["action_mask"], out["action"], cells,
+                                                   out=self._buf("cell_meta", (cells, n, 4), torch.int32, device),
+                                                   out_alive=self._buf("cell_alive", (cells, (n + 31) // 32), torch.int32, device))
         ready = torch.cuda.Event()
         ready.record(side)
         self.turn += 1
@@ -108,14 +123,31 @@ class BatchPrefetcher:
 
     def __init__(self, device, slots: int = 2):
         self.device = torch.device(device)
-        self._stager = _Stager(slots=slots, obs_on_side_stream=True)
+        self._stager = _Stager(slots=slots, obs_on_side_stream=True, prepack_cells=True)
+        self._last = {}                        # slot -> the dictionary staged into it last
 
     def submit(self, batch: Dict[str, torch.Tensor], keys=LEARNER_KEYS) -> Dict[str, torch.Tensor]:
-        out, ready = self._stager.stage(batch, self.device, keys)
+        """May be called while the step on the previous batch is still being enqueued or running:
+
+            out = PPO_learn(model, model, name, cur, optimizer, B, T, n_envs, sync=False)    # launches step k
+            nxt = pf.submit(get_batch(...))                                                  # batch k+1 behind it
+            losses = out.tolist()                                                            # step k's four losses
+
+        ``PPO_learn`` records ``"_release"`` once it no longer reads a staged batch; a slot is overwritten only after
+        the release of the batch staged into it before (two slots: batch k+1 waits for step k-1, not for step k)."""
+        slot = self._stager.turn % self._stager.slots
+        prev = self._last.get(slot)
+        free = prev["_release"] if (prev is not None and prev.get("_released")) else None
+        # (a batch that was staged but never went through PPO_learn has no release: stage() then waits for the whole
+        # compute stream, as it does without a prefetcher)
+        out, ready = self._stager.stage(batch, self.device, keys, slot_free=free)
         out = dict(out)
         if ready is not None:
             out["_ready"] = ready
             out["_ready_all"] = True           # obs too came over the side stream: wait before the encoder
+            out["_release"] = torch.cuda.Event()
+            out["_released"] = False
+            self._last[slot] = out
         return out
 
 
@@ -203,6 +235,8 @@ def PPO_learn(actor_model: nn.Module, learner_model, exp_name: str, batch, optim
             dev_batch["_ready"] = ready
         elif "_ready" in batch:                 # staged ahead of time by a BatchPrefetcher
             dev_batch["_ready"] = batch["_ready"]
+            if "_cell_meta" in batch:           # the fused actor head's cell records, packed on the prefetcher's stream
+                dev_batch["_cell_meta"] = batch["_cell_meta"]
             if batch.get("_ready_all"):
                 torch.cuda.current_stream().wait_event(batch["_ready"])
         world = reducer.world_size if reducer is not None else 1
@@ -227,6 +261,9 @@ def PPO_learn(actor_model: nn.Module, learner_model, exp_name: str, batch, optim
             loss4[3].backward()                                                            # utils.py:334
             losses = loss4.detach()
         optimizer.step()                                                                   # utils.py:335
+        if batch.get("_release") is not None:   # staged by a BatchPrefetcher: its buffers are free from here on
+            batch["_release"].record(torch.cuda.current_stream())
+            batch["_released"] = True
         if actor_model is not learner_model:
             actor_model.load_state_dict(learner_model.state_dict())                        # utils.py:337
         if not sync:

@@ -304,12 +304,13 @@ class _ActorHead(torch.autograd.Function):
     list is sized from the data)."""
 
     @staticmethod
-    def forward(ctx, hidden, weight, bias, action_mask, action, cells, mode, want_logits=True):
+    def forward(ctx, hidden, weight, bias, action_mask, action, cells, mode, want_logits=True, meta=None):
         fused = None
         if TENSOR_CORE_ACTOR and FUSED_ACTOR_HEAD and hidden.shape[1] % 32 == 0 and hidden.shape[0] > 0:
             # model.py:167-214 in one kernel; ``logits`` then holds the cells with a valid action only (enough for
             # the backward: every other cell has exactly zero gradient) unless the caller wants policy_logits
-            meta = ops.pack_cells(action_mask, action, cells)
+            if meta is None or tuple(meta.shape) != (cells, hidden.shape[0], 4) or not hasattr(meta, "alive_bits"):
+                meta = ops.pack_cells(action_mask, action, cells)      # else: packed ahead by learner.BatchPrefetcher
             fused = ops.actor_head_fwd(hidden, ops.pack_actor_weight(weight, bias, cells), meta,
                                        want_logits=True if want_logits else "alive")
         ctx.meta = None
@@ -339,7 +340,7 @@ class _ActorHead(torch.autograd.Function):
         if ctx.meta is not None and ctx.mode and CELL_KERNEL_BACKWARD and hidden.shape[1] == 256 and cells <= 1024:
             # the device-side cell lists + the fp32 FMA products of csrc/cells.cu: no host synchronisation, capturable
             g_hidden, g_weight, g_bias = ops.cells_bwd(hidden, weight, logits, ctx.meta, g_lp, g_ent, ctx.alive_bits)
-            return g_hidden, g_weight, g_bias, None, None, None, None, None
+            return g_hidden, g_weight, g_bias, None, None, None, None, None, None
         # "auto": below ~1e6 (frame, cell) pairs the dense GEMMs cost less than the list's bookkeeping and its two
         # host synchronisations (8x8 maps are launch-bound, profiles/r01_bench_c1_n1.json)
         small = ctx.mode == "auto" and n * cells < _SPARSE_BACKWARD_MIN_PAIRS
@@ -347,7 +348,7 @@ class _ActorHead(torch.autograd.Function):
         cl = cell_list(action_mask, cells, auto=(ctx.mode == "auto")) if use_list else None
         if cl is None:
             dlogits = ops.head_eval_bwd(logits, action_mask, action, g_lp, g_ent)
-            return dlogits @ weight, dlogits.t() @ hidden, dlogits.sum(dim=0), None, None, None, None, None
+            return dlogits @ weight, dlogits.t() @ hidden, dlogits.sum(dim=0), None, None, None, None, None, None
         fidx, cidx = cl
         lmax, width = fidx.shape[1], hidden.shape[1]
         safe, mask_c, act_c = gather_cells(fidx, cidx, n, action_mask, action, cells)
@@ -360,7 +361,7 @@ class _ActorHead(torch.autograd.Function):
         g_bias = dl.sum(dim=1).reshape(-1)
         g_hid = torch.bmm(dl, weight.view(cells, LOGITS_PER_CELL, width))                   # [C, lmax, 256]
         g_hidden = hidden.new_zeros((n + _PAD_ROWS, width)).index_add_(0, flat, g_hid.reshape(-1, width))[:n]
-        return g_hidden, g_weight, g_bias, None, None, None, None, None
+        return g_hidden, g_weight, g_bias, None, None, None, None, None, None
 
 
 class _ResBlock(torch.autograd.Function):
@@ -570,6 +571,7 @@ class Agent(nn.Module):
                 return (dict(action=action, policy_logits=None, logprobs=sparse[0], baseline=baseline,
                              entropy=sparse[1]), ())
         logits, logprobs, entropy = _ActorHead.apply(hidden, self.actor.weight, self.actor.bias, action_mask,
-                                                     action, self.cells, self.sparse_backward, bool(policy_logits))
+                                                     action, self.cells, self.sparse_backward, bool(policy_logits),
+                                                     input_dict.get("_cell_meta"))
         return (dict(action=action, policy_logits=logits if policy_logits else None, logprobs=logprobs,
                      baseline=baseline, entropy=entropy), ())

@@ -29,10 +29,15 @@ _retired_workspaces: list = []
 _timing = None      # list of (name, start_event, end_event) while kernel timing is on
 
 
-def start_kernel_timing() -> None:
-    """Record a CUDA-event pair around every kernel launch (on the launching stream)."""
-    global _timing
+_timing_only = None
+
+
+def start_kernel_timing(only=None) -> None:
+    """Record a CUDA-event pair around every kernel launch (on the launching stream); ``only``: an iterable of launch
+    names to restrict it to (an event pair costs ~3 us of stream time, which adds up over the ~120 launches of a step)."""
+    global _timing, _timing_only
     _timing = []
+    _timing_only = set(only) if only is not None else None
 
 
 def stop_kernel_timing() -> Dict[str, list]:
@@ -58,7 +63,8 @@ class _Launch:
             launch_notes[name] = note        # problem size of the latest launch under this name (bench.py reads it)
 
     def __enter__(self):
-        if _timing is not None:
+        self.timed = _timing is not None and (_timing_only is None or self.name in _timing_only)
+        if self.timed:
             self.start = torch.cuda.Event(enable_timing=True)
             self.start.record()
         return self
@@ -66,7 +72,7 @@ class _Launch:
     def __exit__(self, exc_type, exc, tb):
         if exc_type is None:
             launch_counts[self.name] = launch_counts.get(self.name, 0) + 1
-            if _timing is not None:
+            if self.timed and _timing is not None:
                 end = torch.cuda.Event(enable_timing=True)
                 end.record()
                 _timing.append((self.name, self.start, end))
@@ -432,17 +438,23 @@ def linear_tf32x3(x: torch.Tensor, weight: torch.Tensor, bias: Optional[torch.Te
     return out
 
 
-def pack_cells(action_mask: torch.Tensor, action: torch.Tensor, cells: int) -> torch.Tensor:
+def pack_cells(action_mask: torch.Tensor, action: torch.Tensor, cells: int, out: Optional[torch.Tensor] = None,
+               out_alive: Optional[torch.Tensor] = None) -> torch.Tensor:
     """``cell_meta [cells, N, 4]`` int32: one 16-byte record per (cell, frame) -- 78 mask bits and the seven action
-    indices as 6-bit fields -- the operand form of the fused actor-head kernels (``mb_pack_cells``)."""
+    indices as 6-bit fields -- the operand form of the fused actor-head kernels (``mb_pack_cells``).  ``out`` /
+    ``out_alive`` (``[cells, N, 4]`` / ``[cells, ceil(N/32)]`` int32) let a caller keep the records in buffers of its
+    own (``learner.BatchPrefetcher`` packs the next batch on its side stream)."""
     dev = _need_cuda(action_mask=action_mask, action=action)
     action_mask = _mask_u8(action_mask)
     action = _as(action, torch.int64, "action")
     n = action_mask.shape[0]
     if tuple(action_mask.shape) != (n, cells * LOGITS_PER_CELL) or tuple(action.shape) != (n, cells * COMPONENTS_PER_CELL):
         raise ValueError("pack_cells: action_mask must be [N, 78*cells] and action [N, 7*cells]")
-    meta = torch.empty((cells, n, 4), dtype=torch.int32, device=dev)
-    alive = torch.empty((cells, (n + 31) // 32), dtype=torch.int32, device=dev)
+    meta = out if out is not None else torch.empty((cells, n, 4), dtype=torch.int32, device=dev)
+    alive = out_alive if out_alive is not None else torch.empty((cells, (n + 31) // 32), dtype=torch.int32, device=dev)
+    if tuple(meta.shape) != (cells, n, 4) or tuple(alive.shape) != (cells, (n + 31) // 32) or meta.dtype != torch.int32 or \
+            alive.dtype != torch.int32 or not (meta.is_contiguous() and alive.is_contiguous()) or meta.device != dev or alive.device != dev:
+        raise ValueError("pack_cells: `out` must be a contiguous int32 [cells, N, 4] and `out_alive` [cells, ceil(N/32)] on the inputs' device")
     with torch.cuda.device(dev), _Launch("pack_cells", note={"cells": n * cells}):
         _check(lib.mb_pack_cells(_ptr(action_mask), _ptr(action), _ptr(meta), _ptr(alive), n, cells,
                                  _ptr(status_word(dev)), _stream()))

@@ -560,3 +560,28 @@ def test_torchrun_launcher_drives_train_and_keeps_the_loss_csv(tmp_path):
         # the logged losses are the global means: the same numbers on every rank
         assert [r[1:5] for r in other[1:]] == [r[1:5] for r in rows[1:]]
         assert "identical on every rank: True" in res.stdout
+
+
+def test_prefetcher_packs_the_cell_records_ahead():
+    """learner.BatchPrefetcher builds the fused actor head's (cell, frame) records on its side stream; PPO_learn then
+    launches no pack_cells of its own and returns the same losses and gradients as with a plain host batch."""
+    from microbeast_b200 import buffers as mbuf, ops, synth
+    from microbeast_b200.learner import BatchPrefetcher, PPO_learn
+    from microbeast_b200.model import Agent
+    from oracle import NVEC_CELL
+    torch.manual_seed(5)
+    mine = Agent((8, 8, 27), list(NVEC_CELL) * 64, 64).cuda()
+    batch = synth.make_rollout_batch(8, 8, 10, 6, seed=3, full_keys=False)
+    batch["logprobs"] = -torch.rand(batch["reward"].shape) * 30
+    opt = torch.optim.SGD(mine.parameters(), lr=0.0)
+    a = PPO_learn(mine, mine, "plain", mbuf.pack_batch(batch), opt, 3, 10, 2)
+    ga = [p.grad.clone() for p in mine.parameters()]
+    staged = BatchPrefetcher("cuda").submit(mbuf.pack_batch(batch))
+    assert "_cell_meta" in staged and hasattr(staged["_cell_meta"], "alive_bits")
+    before = ops.launch_counts.get("pack_cells", 0)
+    b = PPO_learn(mine, mine, "staged", staged, opt, 3, 10, 2)
+    assert ops.launch_counts.get("pack_cells", 0) == before          # the records came with the batch
+    np.testing.assert_allclose(a, b, rtol=1e-6, atol=1e-8)
+    for x, p in zip(ga, mine.parameters()):
+        ok, worst = close_rms(p.grad, x, 1e-5)                        # atomics in the backward: run-to-run noise at 1e-6
+        assert ok, worst
