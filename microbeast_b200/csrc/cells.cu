@@ -32,7 +32,6 @@ constexpr int kChunk = 32;                 // list entries per chunk
 constexpr int kPadJ = 80;                  // logits per cell, padded
 constexpr int kHid = 256;                  // width of `hidden` (model.py:130)
 
-__device__ __forceinline__ bool rec_alive(const uint4& m) { return (m.x | m.y | (m.z & 0x3fffu)) != 0u; }
 __device__ __forceinline__ bool rec_bit(const uint4& m, int i) {
     return i < 32 ? ((m.x >> i) & 1u) : i < 64 ? ((m.y >> (i - 32)) & 1u) : ((m.z >> (i - 64)) & 1u);
 }

@@ -9,7 +9,8 @@
 // set bits: gym-microRTS leaves a cell empty by setting plane 0 of each of its five one-hot groups (planes 0, 5, 10,
 // 13, 21), which is what ~90 % of the cells look like.  Per pixel it starts from bias + the sum of those five columns
 // over the taps inside the image (nine precomputed border classes), then adds the column of every plane a cell has
-// beyond that pattern and subtracts the column of every pattern plane the cell lacks: ~1 column per cell instead of 5.
+// beyond that pattern and subtracts the column of every pattern plane the cell lacks; for a one-hot group the two
+// are one precomputed "swap" column W[p] - W[default] (see the table below): ~0.5 columns per cell instead of 5.
 // Any bit pattern is handled exactly the same way (the pattern is only where the counting starts; fp32 additions,
 // another summation order); out-of-image taps carry the pattern in the halo, i.e. no exception.
 //
@@ -27,7 +28,35 @@ namespace {
 
 constexpr int kBitsCout = 16, kBitsCin = 27;
 constexpr int kRowPitch = 20;                       // floats per [tap][plane] row: 16 + 4 padding
-constexpr unsigned kEmptyCell = (1u << 0) | (1u << 5) | (1u << 10) | (1u << 13) | (1u << 21);   // plane 0 of each one-hot group
+
+// Virtual columns of the table a pixel adds up (all with sign +):
+//   [0, 27)   "swap" columns  W[p] - W[d(g)]  : group g of cell holds exactly the one plane p != its default d(g)
+//   [27, 54)  plain columns   W[p]            : a non-default plane of a group that is not one-hot
+//   [54, 59)  "drop" columns  -W[d(g)]        : a group that is not one-hot and lacks its default plane
+// A one-hot cell (every real observation) costs ONE column per group that departs from the default, half of the
+// set-minus / plus pairs of a plain exception count; any other bit pattern is still summed exactly.
+constexpr int kGroups = 5;
+// first plane of each group (= its default, empty-cell plane) and the group sizes: hp, resources, owner, unit type,
+// action (model.py:156-160 / gym-microRTS observation layout)
+__host__ __device__ constexpr int group_base(int g) { return g == 0 ? 0 : g == 1 ? 5 : g == 2 ? 10 : g == 3 ? 13 : 21; }
+__host__ __device__ constexpr int group_len(int g) { return g == 0 ? 5 : g == 1 ? 5 : g == 2 ? 3 : g == 3 ? 8 : 6; }
+constexpr int kVirtCols = 2 * kBitsCin + kGroups;              // 59
+
+__device__ __forceinline__ unsigned long long virt_mask(unsigned word) {
+    unsigned long long v = 0ull;
+#pragma unroll
+    for (int g = 0; g < kGroups; ++g) {
+        const unsigned bits = (word >> group_base(g)) & ((1u << group_len(g)) - 1u);
+        if (bits == 1u) continue;                              // the default plane alone: nothing to add
+        if (__popc(bits) == 1) {
+            v |= (unsigned long long)bits << group_base(g);    // swap column of the one plane that is set
+        } else {
+            v |= (unsigned long long)(bits & ~1u) << (kBitsCin + group_base(g));       // plain columns of the other planes
+            if (!(bits & 1u)) v |= 1ull << (2 * kBitsCin + g);                         // and the default plane is missing
+        }
+    }
+    return v;
+}
 
 template <int H>
 __global__ void __launch_bounds__(256) conv1_bits_fwd_kernel(const int* __restrict__ obs_bits, const float* __restrict__ weight,
@@ -36,24 +65,33 @@ __global__ void __launch_bounds__(256) conv1_bits_fwd_kernel(const int* __restri
     constexpr int W = H, HW = H * W;
     constexpr int FPC = 256 / HW > 0 ? 256 / HW : 1;                  // frames per CTA pass (8x8: 4, 16x16: 1)
     constexpr int TP = W + 2;                                          // tile pitch with halo
-    __shared__ __align__(16) float wt[9 * kBitsCin * kRowPitch];
+    __shared__ __align__(16) float wt[9 * kVirtCols * kRowPitch];     // [tap][virtual column][16 + 4]
     __shared__ __align__(16) float start[9][kBitsCout];               // bias + empty-cell columns of the taps inside, per border class
-    __shared__ int tile[FPC][(H + 2) * TP];
-    // torch layout [cout][cin][3][3] -> [tap][cin][cout]
-    for (int i = threadIdx.x; i < 9 * kBitsCin * kBitsCout; i += 256) {
-        const int co = i % kBitsCout, ci = (i / kBitsCout) % kBitsCin, tap = i / (kBitsCout * kBitsCin);
-        wt[(tap * kBitsCin + ci) * kRowPitch + co] = weight[(co * kBitsCin + ci) * 9 + tap];
+    __shared__ unsigned long long tile[FPC][(H + 2) * TP];             // per cell: which virtual columns it contributes
+    // torch layout [cout][cin][3][3] -> the virtual column table
+    for (int i = threadIdx.x; i < 9 * kVirtCols * kBitsCout; i += 256) {
+        const int co = i % kBitsCout, vc = (i / kBitsCout) % kVirtCols, tap = i / (kBitsCout * kVirtCols);
+        auto wv = [&](int ci) { return weight[(co * kBitsCin + ci) * 9 + tap]; };
+        float v;
+        if (vc < 2 * kBitsCin) {
+            const int p = vc % kBitsCin;
+            int g = 0;
+#pragma unroll
+            for (int q = 1; q < kGroups; ++q) g += (p >= group_base(q)) ? 1 : 0;
+            v = vc < kBitsCin ? wv(p) - wv(group_base(g)) : wv(p);
+        } else {
+            v = -wv(group_base(vc - 2 * kBitsCin));
+        }
+        wt[(tap * kVirtCols + vc) * kRowPitch + co] = v;
     }
-    for (int i = threadIdx.x; i < FPC * (H + 2) * TP; i += 256) (&tile[0][0])[i] = int(kEmptyCell);   // halo: no exception
-    __syncthreads();
+    for (int i = threadIdx.x; i < FPC * (H + 2) * TP; i += 256) (&tile[0][0])[i] = 0ull;       // halo: empty cells, no column
     if (threadIdx.x < 9 * kBitsCout) {
         const int co = threadIdx.x % kBitsCout, cls = threadIdx.x / kBitsCout, cy = cls / 3, cx = cls % 3;   // 0 first, 1 inner, 2 last
         float v = bias ? bias[co] : 0.0f;
         for (int tap = 0; tap < 9; ++tap) {
             const int ky = tap / 3, kx = tap % 3;
             if ((cy == 0 && ky == 0) || (cy == 2 && ky == 2) || (cx == 0 && kx == 0) || (cx == 2 && kx == 2)) continue;
-            for (int ci = 0; ci < kBitsCin; ++ci)
-                if ((kEmptyCell >> ci) & 1u) v += wt[(tap * kBitsCin + ci) * kRowPitch + co];
+            for (int g = 0; g < kGroups; ++g) v += weight[(co * kBitsCin + group_base(g)) * 9 + tap];
         }
         start[cls][co] = v;
     }
@@ -65,7 +103,8 @@ __global__ void __launch_bounds__(256) conv1_bits_fwd_kernel(const int* __restri
     for (long long pass = blockIdx.x; pass < n_pass; pass += gridDim.x) {
         const long long f = pass * FPC + slot;
         const bool live = slot < FPC && f < n_frames;
-        if (slot < FPC) tile[slot][(y + 1) * TP + x + 1] = live ? __ldg(obs_bits + f * HW + pix) : int(kEmptyCell);
+        if (slot < FPC)
+            tile[slot][(y + 1) * TP + x + 1] = live ? virt_mask(unsigned(__ldg(obs_bits + f * HW + pix)) & ((1u << kBitsCin) - 1u)) : 0ull;
         __syncthreads();
         if (live) {
             float acc[kBitsCout];
@@ -76,20 +115,19 @@ __global__ void __launch_bounds__(256) conv1_bits_fwd_kernel(const int* __restri
             }
 #pragma unroll
             for (int tap = 0; tap < 9; ++tap) {
-                unsigned word = (unsigned(tile[slot][(y + tap / 3) * TP + x + tap % 3]) ^ kEmptyCell) & ((1u << kBitsCin) - 1u);
-                const float* base = wt + tap * kBitsCin * kRowPitch;
-                while (word) {                                 // planes where this cell departs from the empty pattern
-                    const int ci = __ffs(word) - 1;
-                    word &= word - 1;
-                    const float sign = ((kEmptyCell >> ci) & 1u) ? -1.0f : 1.0f;      // a pattern plane it lacks / an extra plane
-                    const float4* r = reinterpret_cast<const float4*>(base + ci * kRowPitch);
+                const unsigned long long vm = tile[slot][(y + tap / 3) * TP + x + tap % 3];
+                const float* base = wt + tap * kVirtCols * kRowPitch;
+                unsigned lo = unsigned(vm), hi = unsigned(vm >> 32);
+                while (lo | hi) {                              // one trip per departing group of a one-hot cell
+                    const bool in_lo = lo != 0u;
+                    const unsigned w32 = in_lo ? lo : hi;
+                    const int vc = __ffs(w32) - 1 + (in_lo ? 0 : 32);
+                    if (in_lo) lo &= lo - 1; else hi &= hi - 1;
+                    const float4* r = reinterpret_cast<const float4*>(base + vc * kRowPitch);
 #pragma unroll
                     for (int q = 0; q < 4; ++q) {
                         const float4 v = r[q];
-                        acc[4 * q] = fmaf(sign, v.x, acc[4 * q]);
-                        acc[4 * q + 1] = fmaf(sign, v.y, acc[4 * q + 1]);
-                        acc[4 * q + 2] = fmaf(sign, v.z, acc[4 * q + 2]);
-                        acc[4 * q + 3] = fmaf(sign, v.w, acc[4 * q + 3]);
+                        acc[4 * q] += v.x; acc[4 * q + 1] += v.y; acc[4 * q + 2] += v.z; acc[4 * q + 3] += v.w;
                     }
                 }
             }
