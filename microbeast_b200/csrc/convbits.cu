@@ -201,7 +201,7 @@ struct BwCfg {
 };
 
 template <int H>
-__global__ void __launch_bounds__(BwCfg<H>::THREADS) conv1_bits_wgrad_kernel(const int* __restrict__ obs_bits, const float* __restrict__ dy,
+__global__ void __launch_bounds__(BwCfg<H>::THREADS, 3) conv1_bits_wgrad_kernel(const int* __restrict__ obs_bits, const float* __restrict__ dy,
                                                                                float* __restrict__ total, long long n_frames) {
     using C = BwCfg<H>;
     constexpr int W = C::W, HW = C::HW, PW = C::PW, CP = C::CP;
