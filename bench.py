@@ -394,8 +394,8 @@ def run_ours(args):
                   "parity": parity, "config": workload_config(args)}, args)
             raise SystemExit(3)
 
-    def step(b, sync):
-        return PPO_learn(model, model, "bench", b, opt, rows, T, 1, reducer=reducer, sync=sync)
+    def step(b, sync, prefetch=None):
+        return PPO_learn(model, model, "bench", b, opt, rows, T, 1, reducer=reducer, sync=sync, prefetch=prefetch)
 
     def barrier():
         torch.cuda.synchronize()
@@ -553,23 +553,21 @@ def run_ours(args):
         state = {"next": pf.submit(host)}
 
         def e2e_step():
-            # launch step k, stage batch k+1 behind it (its copies overlap step k's kernels; the slot it overwrites was
-            # released by step k-1), then read step k's four losses on the host
-            out = step(state["next"], False)
-            state["next"] = pf.submit(host)
-            return out.tolist()
+            # step k through the drop-in call; batch k+1 is submitted from inside it, once step k's forward pass is
+            # enqueued (its copies overlap step k's backward; the slot it overwrites was released by step k-1)
+            cur = state["next"]
+            return step(cur, True, prefetch=lambda: state.__setitem__("next", pf.submit(host)))
         ms_e2e, _, _, _ = timed(e2e_step, e2e_steps, 3)
         torch.cuda.synchronize()
 
         def e2e_step_deferred():
             # for the record, not the headline: the same loop with step k's losses read while step k+1 runs, so the
             # device queue never drains (a logger that is one update late); every step still pays its H2D and its D2H
-            out = step(state["next"], False)
+            out = step(state["next"], False, prefetch=lambda: state.__setitem__("next", pf.submit(host)))
             slot = state["turn"] = (state.get("turn", 0) + 1) % 2
             pinned4[slot].copy_(out, non_blocking=True)       # D2H of this step's four losses, stream-ordered after it
             ev = torch.cuda.Event()
             ev.record()
-            state["next"] = pf.submit(host)
             prev, state["pending"] = state.get("pending"), (pinned4[slot], ev)
             if prev is None:
                 return None
@@ -581,8 +579,8 @@ def run_ours(args):
         del state, pf
         e2e = {"value": frames / (ms_e2e * 1e-3), "unit": UNIT, "h2d_bytes_per_step": h2d * world,
                "d2h_bytes_per_step": 16 * world, "ms_per_step": ms_e2e, "steps": e2e_steps,
-               "call": "out = PPO_learn(model, model, name, cur, adam, rows, T, 1, sync=False); cur = "
-                       "BatchPrefetcher.submit(pinned_host_batch); losses = out.tolist()  (microbeast_b200.learner)",
+               "call": "losses = PPO_learn(model, model, name, cur, adam, rows, T, 1, prefetch=lambda: nxt.append("
+                       "BatchPrefetcher.submit(pinned_host_batch)))  (microbeast_b200.learner)",
                "deferred_read": {"value": frames / (ms_def * 1e-3), "ms_per_step": ms_def,
                                  "note": "losses of step k read on the host while step k+1 runs; not the headline"},
                "serial": {"value": frames / (ms_serial * 1e-3), "ms_per_step": ms_serial,

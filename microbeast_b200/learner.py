@@ -127,11 +127,13 @@ class BatchPrefetcher:
         self._last = {}                        # slot -> the dictionary staged into it last
 
     def submit(self, batch: Dict[str, torch.Tensor], keys=LEARNER_KEYS) -> Dict[str, torch.Tensor]:
-        """May be called while the step on the previous batch is still being enqueued or running:
+        """May be called while the step on the previous batch is still being enqueued or running -- best from inside it:
 
-            out = PPO_learn(model, model, name, cur, optimizer, B, T, n_envs, sync=False)    # launches step k
-            nxt = pf.submit(get_batch(...))                                                  # batch k+1 behind it
-            losses = out.tolist()                                                            # step k's four losses
+            nxt = [pf.submit(get_batch(...))]
+            while training:
+                cur = nxt.pop()
+                PPO_learn(model, model, name, cur, optimizer, B, T, n_envs,
+                          prefetch=lambda: nxt.append(pf.submit(get_batch(...))))     # runs after step k's forward is enqueued
 
         ``PPO_learn`` records ``"_release"`` once it no longer reads a staged batch; a slot is overwritten only after
         the release of the batch staged into it before (two slots: batch k+1 waits for step k-1, not for step k)."""
@@ -213,7 +215,7 @@ def learner_losses(learner_model: nn.Module, batch: Dict[str, torch.Tensor], row
 def PPO_learn(actor_model: nn.Module, learner_model, exp_name: str, batch, optimizer, B: int, T: int,
               n_envs: int, lock=threading.Lock(), *, gamma=0.99, rho_bar=1.0, c_bar=1.0, pg_rho_bar=1.0,
               entropy_coef=0.01, reducer: Optional[GradAllReducer] = None, time_major: bool = False,
-              sync: bool = True, sparse_head=None):
+              sync: bool = True, sparse_head=None, prefetch=None):
     """Performs a learning (optimization) step -- reference ``libs/utils.py:223-342``.
 
     ``batch``: flat ``[N, ...]`` tensors, ``N = B*n_envs*(T+1)``, on the host (copied to the
@@ -224,6 +226,9 @@ def PPO_learn(actor_model: nn.Module, learner_model, exp_name: str, batch, optim
     returned losses are then the global ones.  ``sparse_head`` (False / True / "auto") overrides
     ``learner_model.sparse_head`` for this step: evaluate the actor head only on cells with a valid
     action (same losses and gradients; costs two host syncs inside the step).
+    ``prefetch``: a callable run once the forward pass and the losses are enqueued, before the backward pass -- the
+    place to ``BatchPrefetcher.submit`` the NEXT batch: the device then has a forward pass of work queued (the host
+    time of the submit is hidden) and the copy has the whole backward pass to overlap with.
     """
     if not isinstance(lock, type(threading.Lock())):
         lock = threading.Lock()      # reference quirk Q15: microbeast.py:251 passes exp_name here
@@ -250,6 +255,8 @@ def PPO_learn(actor_model: nn.Module, learner_model, exp_name: str, batch, optim
         finally:
             if sparse_head is not None:
                 learner_model.sparse_head = keep
+        if prefetch is not None:
+            prefetch()
         if reducer is not None and reducer.world_size > 1:
             # gradients live in the reducer's flat bucket: zeroed there, the head's slice goes on the wire as soon as
             # the actor-head backward has run and overlaps the encoder's backward (parallel.GradAllReducer)

@@ -1,0 +1,7 @@
+#!/bin/bash
+# end-of-round refresh: full GPU suite (with the parity numbers written out), bench line, ncu passes
+mkdir -p gpurun_out
+rm -f gpurun_out/parity.jsonl
+MB_PARITY_OUT=gpurun_out/parity.jsonl python -m pytest tests -x -q -m gpu 2>&1 | tail -3
+python bench.py --steps 20 --warmup 5 > gpurun_out/bench_n1.json 2> gpurun_out/bench_n1.err; echo "bench exit $?"
+bash scripts/gpu_profile_r2.sh 2>&1 | tail -3
