@@ -354,7 +354,11 @@ def run_ours(args):
         raise SystemExit("bench.py: no CUDA device; the product path has no CPU fallback")
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
+    bound_cores = None
     if world > 1:
+        # one process per GPU, on the host cores (and, by first touch, the pinned memory) of the GPU's own socket
+        from microbeast_b200.parallel import bind_to_gpu_numa
+        bound_cores = bind_to_gpu_numa(local)
         dist.init_process_group("nccl", device_id=dev)
     torch.backends.cudnn.allow_tf32 = False          # dtype f32 means f32: no TF32 anywhere
     torch.backends.cuda.matmul.allow_tf32 = False
@@ -552,18 +556,27 @@ def run_ours(args):
         pf = BatchPrefetcher(dev)
         state = {"next": pf.submit(host)}
 
+        def submit_next():
+            state["next"] = pf.submit(host)
+            return state["next"]
+
         def e2e_step():
-            # step k through the drop-in call; batch k+1 is submitted from inside it, once step k's forward pass is
-            # enqueued (its copies overlap step k's backward; the slot it overwrites was released by step k-1)
-            cur = state["next"]
-            return step(cur, True, prefetch=lambda: state.__setitem__("next", pf.submit(host)))
+            # step k is enqueued, batch k+1 submitted behind it (its copies overlap step k's kernels; the slot it
+            # overwrites was released by step k-1), then step k's four losses are read on the host
+            # measured (scripts/e2e_placement.py, N = 1 / 8): submitting once the whole step is enqueued 6.86 / 8.62 ms,
+            # from PPO_learn's prefetch hook after the forward pass 7.01 / 8.85, before the step 7.69 / 11.0 -- right
+            # after a loss read the forward pass is host-bound, so the submit's host time is cheapest at the end
+            out = step(state["next"], False)
+            submit_next()
+            return out.tolist()
         ms_e2e, _, _, _ = timed(e2e_step, e2e_steps, 3)
         torch.cuda.synchronize()
 
         def e2e_step_deferred():
             # for the record, not the headline: the same loop with step k's losses read while step k+1 runs, so the
             # device queue never drains (a logger that is one update late); every step still pays its H2D and its D2H
-            out = step(state["next"], False, prefetch=lambda: state.__setitem__("next", pf.submit(host)))
+            out = step(state["next"], False)
+            submit_next()
             slot = state["turn"] = (state.get("turn", 0) + 1) % 2
             pinned4[slot].copy_(out, non_blocking=True)       # D2H of this step's four losses, stream-ordered after it
             ev = torch.cuda.Event()
@@ -579,8 +592,8 @@ def run_ours(args):
         del state, pf
         e2e = {"value": frames / (ms_e2e * 1e-3), "unit": UNIT, "h2d_bytes_per_step": h2d * world,
                "d2h_bytes_per_step": 16 * world, "ms_per_step": ms_e2e, "steps": e2e_steps,
-               "call": "losses = PPO_learn(model, model, name, cur, adam, rows, T, 1, prefetch=lambda: nxt.append("
-                       "BatchPrefetcher.submit(pinned_host_batch)))  (microbeast_b200.learner)",
+               "call": "out = PPO_learn(model, model, name, cur, adam, rows, T, 1, sync=False); cur = "
+                       "BatchPrefetcher.submit(pinned_host_batch); losses = out.tolist()  (microbeast_b200.learner)",
                "deferred_read": {"value": frames / (ms_def * 1e-3), "ms_per_step": ms_def,
                                  "note": "losses of step k read on the host while step k+1 runs; not the headline"},
                "serial": {"value": frames / (ms_serial * 1e-3), "ms_per_step": ms_serial,
@@ -641,6 +654,10 @@ def run_ours(args):
             info["graphed"] = {"error": f"{type(exc).__name__}: {exc}"[:300]}
 
     info = dict(info or {})
+    if world > 1:
+        info["host_binding"] = {"cores_per_rank": len(bound_cores) if bound_cores else None,
+                                "note": "each rank restricted to the host cores NVML lists next to its GPU "
+                                        "(parallel.bind_to_gpu_numa); None = NVML / sched_setaffinity unavailable"}
     if e2e_other is not None:
         info["e2e_other_wire"] = e2e_other
     if roof_hbm is not None and roof_hbm is not roof:

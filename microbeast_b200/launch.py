@@ -53,6 +53,8 @@ def main(argv=None) -> int:
     torch.cuda.set_device(local)
     device = torch.device("cuda", local)
     if distributed:
+        from .parallel import bind_to_gpu_numa
+        bind_to_gpu_numa(local)                 # host cores (and first-touch pinned memory) of the GPU's own socket
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         dist.init_process_group(args.backend, device_id=device if args.backend == "nccl" else None)
     reducer = GradAllReducer() if distributed else None

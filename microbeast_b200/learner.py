@@ -39,15 +39,19 @@ class _Stager:
         self.obs_on_side_stream = obs_on_side_stream
         self.prepack_cells = prepack_cells      # also build the fused actor head's cell records on the side stream
 
-    def _buf(self, name, shape, dtype, device):
-        key = (name, tuple(shape), dtype, device, self.turn % self.slots)
+    def _buf(self, name, shape, dtype, device, slot=None):
+        key = (name, tuple(shape), dtype, device, (self.turn % self.slots) if slot is None else slot)
         buf = self.buffers.get(key)
         if buf is None:
             buf = self.buffers[key] = torch.empty(tuple(shape), dtype=dtype, device=device)
         return buf
 
-    def stage(self, batch, device, keys, slot_free=None):
-        """``slot_free``: a recorded CUDA event after which the staging buffers of this turn's slot are no longer read
+    def stage(self, batch, device, keys, slot_free=None, defer=False):
+        """Host -> device copies on the side stream, then the device-side widening of the compact wire format (and, for
+        a prefetcher, the fused head's cell records).  Returns ``(out, ready_event)``; with ``defer=True`` the widening
+        is left to the caller: ``(out, copied_event, finish)`` where ``finish()`` enqueues it (same side stream, after
+        the copies), updates ``out`` in place and returns the ready event.
+        ``slot_free``: a recorded CUDA event after which the staging buffers of this turn's slot are no longer read
         (``BatchPrefetcher``); without it the side stream waits for everything enqueued on the compute stream so far."""
         compact = "action_mask_bits" in batch        # wire format of buffers.pack_batch / compact store
         keys = [("action_mask_bits" if (k == "action_mask" and compact) else k) for k in keys]
@@ -57,6 +61,8 @@ class _Stager:
         if side is None:
             side = self.streams[device] = torch.cuda.Stream(device=device)
         main = torch.cuda.current_stream(device)
+        slot = self.turn % self.slots
+        self.turn += 1
         out = {}
         if slot_free is not None:
             side.wait_event(slot_free)          # the step that read this slot's buffers last has finished
@@ -67,41 +73,49 @@ class _Stager:
             if t.is_cuda:
                 out[k] = t
                 continue
-            buf = self._buf(k, t.shape, t.dtype, device)
+            buf = self._buf(k, t.shape, t.dtype, device, slot)
             if k == "obs" and not self.obs_on_side_stream:
                 buf.copy_(t, non_blocking=True)
             else:
                 with torch.cuda.stream(side):
                     buf.copy_(t, non_blocking=True)
             out[k] = buf
-        if compact or out["action"].dtype == torch.uint8:
-            # widen bit-packed masks / uint8 actions on the side stream, still off the critical path
-            n = out["action"].shape[0]
-            cells = out["action"].shape[1] // 7
-            bits = out.pop("action_mask_bits", None)
-            a8 = out["action"] if out["action"].dtype == torch.uint8 else None
-            with torch.cuda.stream(side):
-                mask, act = ops.unpack_rollout(
-                    bits, a8, cells,
-                    self._buf("wide_mask", (n, cells * 78), torch.uint8, device) if bits is not None else None,
-                    self._buf("wide_action", (n, cells * 7), torch.int64, device) if a8 is not None else None)
-            if bits is not None:
-                out["action_mask"] = mask
-            if a8 is not None:
-                out["action"] = act
-        if self.prepack_cells and out["action"].dtype == torch.int64 and out["action_mask"].dim() == 2:
-            # the operand form of mb_actor_head_fwd (16-byte (cell, frame) records + alive bitmap): 0.17 ms at config 2
-            # that the step no longer spends on its own stream (model.Agent.get_action picks "_cell_meta" up)
-            n = out["action"].shape[0]
-            cells = out["action"].shape[1] // 7
-            with torch.cuda.stream(side):
-                out["_cell_meta"] = ops.pack_cells(out["action_mask"], out["action"], cells,
-                                                   out=self._buf("cell_meta", (cells, n, 4), torch.int32, device),
-                                                   out_alive=self._buf("cell_alive", (cells, (n + 31) // 32), torch.int32, device))
-        ready = torch.cuda.Event()
-        ready.record(side)
-        self.turn += 1
-        return out, ready
+
+        def finish():
+            if compact or out["action"].dtype == torch.uint8:
+                # widen bit-packed masks / uint8 actions on the side stream, still off the critical path
+                n = out["action"].shape[0]
+                cells = out["action"].shape[1] // 7
+                bits = out.pop("action_mask_bits", None)
+                a8 = out["action"] if out["action"].dtype == torch.uint8 else None
+                with torch.cuda.stream(side):
+                    mask, act = ops.unpack_rollout(
+                        bits, a8, cells,
+                        self._buf("wide_mask", (n, cells * 78), torch.uint8, device, slot) if bits is not None else None,
+                        self._buf("wide_action", (n, cells * 7), torch.int64, device, slot) if a8 is not None else None)
+                if bits is not None:
+                    out["action_mask"] = mask
+                if a8 is not None:
+                    out["action"] = act
+            if self.prepack_cells and out["action"].dtype == torch.int64 and out["action_mask"].dim() == 2:
+                # the operand form of mb_actor_head_fwd (16-byte (cell, frame) records + alive bitmap): 0.17 ms at config
+                # 2 that the step no longer spends on its own stream (model.Agent.get_action picks "_cell_meta" up)
+                n = out["action"].shape[0]
+                cells = out["action"].shape[1] // 7
+                with torch.cuda.stream(side):
+                    out["_cell_meta"] = ops.pack_cells(
+                        out["action_mask"], out["action"], cells,
+                        out=self._buf("cell_meta", (cells, n, 4), torch.int32, device, slot),
+                        out_alive=self._buf("cell_alive", (cells, (n + 31) // 32), torch.int32, device, slot))
+            ready = torch.cuda.Event()
+            ready.record(side)
+            return ready
+
+        if defer:
+            copied = torch.cuda.Event()
+            copied.record(side)
+            return out, copied, finish
+        return out, finish()
 
 
 _stager = _Stager()
@@ -142,11 +156,20 @@ class BatchPrefetcher:
         free = prev["_release"] if (prev is not None and prev.get("_released")) else None
         # (a batch that was staged but never went through PPO_learn has no release: stage() then waits for the whole
         # compute stream, as it does without a prefetcher)
-        out, ready = self._stager.stage(batch, self.device, keys, slot_free=free)
-        out = dict(out)
-        if ready is not None:
-            out["_ready"] = ready
-            out["_ready_all"] = True           # obs too came over the side stream: wait before the encoder
+        staged = self._stager.stage(batch, self.device, keys, slot_free=free, defer=True)
+        out = dict(staged[0])
+        if len(staged) == 3:
+            _, copied, finish = staged
+            live = staged[0]                   # finish() updates this dictionary in place
+
+            def _finish():                     # the device-side widening + cell records, enqueued when the consumer says so
+                ready = finish()
+                out.update(live)
+                out.pop("action_mask_bits", None)
+                out["_ready"] = ready
+            out["_ready_copy"] = copied        # obs too came over the side stream: wait for the copies before the encoder
+            out["_ready_all"] = True
+            out["_finish"] = _finish
             out["_release"] = torch.cuda.Event()
             out["_released"] = False
             self._last[slot] = out
@@ -176,6 +199,8 @@ def learner_losses(learner_model: nn.Module, batch: Dict[str, torch.Tensor], row
     ``(t, b, e)`` order (quirk Q7); ``True`` treats the flat batch as what it is, ``[T+1, rows]``,
     so that a row really is one trajectory, and runs the time-major V-trace kernel on it in place.
     """
+    if "_finish" in batch:                   # a BatchPrefetcher batch whose device-side widening is still to be enqueued
+        batch.pop("_finish")()
     kw = {}
     if getattr(learner_model, "skips_policy_logits", False):
         kw["policy_logits"] = False          # never read below (utils.py:237-329): the fused kernel need not store them
@@ -227,14 +252,17 @@ def PPO_learn(actor_model: nn.Module, learner_model, exp_name: str, batch, optim
     ``learner_model.sparse_head`` for this step: evaluate the actor head only on cells with a valid
     action (same losses and gradients; costs two host syncs inside the step).
     ``prefetch``: a callable run once the forward pass and the losses are enqueued, before the backward pass -- the
-    place to ``BatchPrefetcher.submit`` the NEXT batch: the device then has a forward pass of work queued (the host
-    time of the submit is hidden) and the copy has the whole backward pass to overlap with.
+    place to ``BatchPrefetcher.submit`` the NEXT batch (return what ``submit`` returned): the device then has a forward
+    pass of work queued (the host time of the submit is hidden) and the copy has the whole backward pass to overlap
+    with; the batch's device-side widening is enqueued at the end of this step.
     """
     if not isinstance(lock, type(threading.Lock())):
         lock = threading.Lock()      # reference quirk Q15: microbeast.py:251 passes exp_name here
     device = next(learner_model.parameters()).device
     rows = B * n_envs
     with lock:
+        if isinstance(batch, dict) and "_finish" in batch:      # staged by a BatchPrefetcher, widening not yet enqueued
+            batch.pop("_finish")()
         dev_batch, ready = batch_to_device(batch, device)
         if ready is not None:
             dev_batch["_ready"] = ready
@@ -243,7 +271,7 @@ def PPO_learn(actor_model: nn.Module, learner_model, exp_name: str, batch, optim
             if "_cell_meta" in batch:           # the fused actor head's cell records, packed on the prefetcher's stream
                 dev_batch["_cell_meta"] = batch["_cell_meta"]
             if batch.get("_ready_all"):
-                torch.cuda.current_stream().wait_event(batch["_ready"])
+                torch.cuda.current_stream().wait_event(batch.get("_ready_copy", batch["_ready"]))
         world = reducer.world_size if reducer is not None else 1
         keep = getattr(learner_model, "sparse_head", None)
         if sparse_head is not None:
@@ -255,8 +283,7 @@ def PPO_learn(actor_model: nn.Module, learner_model, exp_name: str, batch, optim
         finally:
             if sparse_head is not None:
                 learner_model.sparse_head = keep
-        if prefetch is not None:
-            prefetch()
+        staged_next = prefetch() if prefetch is not None else None
         if reducer is not None and reducer.world_size > 1:
             # gradients live in the reducer's flat bucket: zeroed there, the head's slice goes on the wire as soon as
             # the actor-head backward has run and overlaps the encoder's backward (parallel.GradAllReducer)
@@ -271,6 +298,11 @@ def PPO_learn(actor_model: nn.Module, learner_model, exp_name: str, batch, optim
         if batch.get("_release") is not None:   # staged by a BatchPrefetcher: its buffers are free from here on
             batch["_release"].record(torch.cuda.current_stream())
             batch["_released"] = True
+        if isinstance(staged_next, dict) and "_finish" in staged_next:
+            # the next batch's copies have been running since `prefetch`; its device-side widening is enqueued only now,
+            # behind this step's kernels in host order, so that it shares the GPU with the encoder's backward pass
+            # rather than with the two persistent actor-head kernels
+            staged_next.pop("_finish")()
         if actor_model is not learner_model:
             actor_model.load_state_dict(learner_model.state_dict())                        # utils.py:337
         if not sync:

@@ -15,6 +15,28 @@ import torch
 import torch.distributed as dist
 
 
+def bind_to_gpu_numa(device_index: int) -> Optional[List[int]]:
+    """Restrict this process to the host cores next to GPU ``device_index`` (NVML's ideal CPU affinity).  With one
+    process per GPU on a two-socket host this keeps the launching thread, NCCL's proxy thread and -- by first touch --
+    the pinned staging buffers allocated afterwards on the GPU's own socket, so that eight ranks do not pull their
+    host->device copies across the socket interconnect.  Returns the core list, or ``None`` when NVML or
+    ``sched_setaffinity`` is unavailable (nothing is changed then)."""
+    try:
+        import os
+        import pynvml
+        pynvml.nvmlInit()
+        handle = pynvml.nvmlDeviceGetHandleByIndex(device_index)
+        words = pynvml.nvmlDeviceGetCpuAffinity(handle, (os.cpu_count() + 63) // 64)
+        cores = [64 * i + b for i, w in enumerate(words) for b in range(64) if (int(w) >> b) & 1]
+        allowed = sorted(set(cores) & set(os.sched_getaffinity(0)))
+        if not allowed:
+            return None
+        os.sched_setaffinity(0, allowed)
+        return allowed
+    except Exception:
+        return None
+
+
 def shard_rows(total_rows: int, rank: int, world_size: int) -> Tuple[int, int]:
     """``[start, stop)`` of this rank's rows; whole rows stay on one rank (a V-trace
     recurrence never crosses ranks).  Equal shards when ``world_size`` divides

@@ -50,8 +50,10 @@ def before():
 
 
 def hook():
-    return PPO_learn(model, model, "p", state["next"], opt, rows, T, 1, reducer=red,
-                     prefetch=lambda: state.__setitem__("next", pf.submit(host)))
+    def sub():
+        state["next"] = pf.submit(host)
+        return state["next"]
+    return PPO_learn(model, model, "p", state["next"], opt, rows, T, 1, reducer=red, prefetch=sub)
 
 
 def after():

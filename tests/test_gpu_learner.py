@@ -576,12 +576,24 @@ def test_prefetcher_packs_the_cell_records_ahead():
     opt = torch.optim.SGD(mine.parameters(), lr=0.0)
     a = PPO_learn(mine, mine, "plain", mbuf.pack_batch(batch), opt, 3, 10, 2)
     ga = [p.grad.clone() for p in mine.parameters()]
-    staged = BatchPrefetcher("cuda").submit(mbuf.pack_batch(batch))
-    assert "_cell_meta" in staged and hasattr(staged["_cell_meta"], "alive_bits")
-    before = ops.launch_counts.get("pack_cells", 0)
-    b = PPO_learn(mine, mine, "staged", staged, opt, 3, 10, 2)
-    assert ops.launch_counts.get("pack_cells", 0) == before          # the records came with the batch
+    pf = BatchPrefetcher("cuda")
+    staged = pf.submit(mbuf.pack_batch(batch))
+    assert "_finish" in staged and "action_mask_bits" in staged      # copies under way, widening left to the consumer
+    nxt = []
+    b = PPO_learn(mine, mine, "staged", staged, opt, 3, 10, 2,
+                  prefetch=lambda: nxt.append(pf.submit(mbuf.pack_batch(batch))) or nxt[-1])
+    assert "_cell_meta" in staged and hasattr(staged["_cell_meta"], "alive_bits") and "_finish" not in staged
     np.testing.assert_allclose(a, b, rtol=1e-6, atol=1e-8)
     for x, p in zip(ga, mine.parameters()):
         ok, worst = close_rms(p.grad, x, 1e-5)                        # atomics in the backward: run-to-run noise at 1e-6
         assert ok, worst
+    # the batch submitted from inside that step: widened at the step's end, records packed on the side stream, so the
+    # next step launches no pack_cells of its own; two more rounds exercise the slot release / reuse
+    assert "_finish" not in nxt[-1] and "_cell_meta" in nxt[-1]
+    for _ in range(3):
+        before = ops.launch_counts.get("pack_cells", 0)
+        cur = nxt.pop()
+        c = PPO_learn(mine, mine, "staged", cur, opt, 3, 10, 2,
+                      prefetch=lambda: nxt.append(pf.submit(mbuf.pack_batch(batch))) or nxt[-1])
+        assert ops.launch_counts.get("pack_cells", 0) == before + 1      # exactly the one of the batch submitted inside
+        np.testing.assert_allclose(a, c, rtol=1e-6, atol=1e-8)
