@@ -662,6 +662,27 @@ def run_ours(args):
         info["e2e_other_wire"] = e2e_other
     if roof_hbm is not None and roof_hbm is not roof:
         info["roofline_hbm"] = roof_hbm
+    if rank == 0 and not args.no_e2e:
+        # what the compact store costs the ACTOR side: the slot write of one env step of the
+        # reference's 6 envs per actor (microbeast.py:73-100) packs the mask to bits and the observation planes to one
+        # int32 per cell on the host; no other number in this line contains that cost
+        from microbeast_b200 import buffers as mbuf
+        g6 = torch.Generator().manual_seed(0)
+        m6 = (torch.rand(6, 78 * cells, generator=g6) < 0.06).to(torch.uint8)
+        o6 = (torch.rand(6, h, w, 27, generator=g6) < 0.2).to(torch.uint8)
+        for fn, arg in ((mbuf.pack_mask, m6), (mbuf.pack_obs, o6)):
+            for _ in range(20):
+                fn(arg)
+        t0 = time.perf_counter()
+        for _ in range(200):
+            mbuf.pack_mask(m6)
+        t1 = time.perf_counter()
+        for _ in range(200):
+            mbuf.pack_obs(o6)
+        t2 = time.perf_counter()
+        info["host_packing"] = {"mask_us_per_slot_write": (t1 - t0) / 200 * 1e6, "obs_us_per_slot_write": (t2 - t1) / 200 * 1e6,
+                                "envs_per_write": 6, "note": "numpy packing an actor pays per env step with "
+                                "create_buffers(compact=True); one host thread, outside every timed region above"}
 
     # ---- acting mode: Agent.get_action (encoder + mb_head_sample) latency at small frame counts ------------------
     if rank == 0 and not args.no_graph_info:

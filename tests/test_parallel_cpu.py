@@ -120,3 +120,17 @@ def test_single_process_reducer_is_a_no_op():
     extra = torch.tensor([1.0, 2.0])
     assert red.world_size == 1 and red.allreduce(lin, extra) is extra
     assert torch.equal(lin.weight.grad, before)
+
+
+def test_bind_to_gpu_numa_is_harmless_without_nvml():
+    """parallel.bind_to_gpu_numa returns the bound core list, or None (and changes nothing) where NVML or
+    sched_setaffinity is unavailable -- as in this CPU-only container."""
+    import os
+    from microbeast_b200.parallel import bind_to_gpu_numa
+    before = os.sched_getaffinity(0) if hasattr(os, "sched_getaffinity") else None
+    cores = bind_to_gpu_numa(0)
+    assert cores is None or (isinstance(cores, list) and set(cores) <= set(before))
+    if cores is None and before is not None:
+        assert os.sched_getaffinity(0) == before
+    if before is not None:
+        os.sched_setaffinity(0, before)
