@@ -368,12 +368,23 @@ __global__ void __launch_bounds__(kFuThreads, 1) actor_head_fwd_kernel(const __g
 }
 
 // per frame: the C cell results in cell order -> logp, ent
-__global__ void __launch_bounds__(256) frame_sum_kernel(const float2* __restrict__ cell_out, float* __restrict__ logp,
+__global__ void __launch_bounds__(64) frame_sum_kernel(const float2* __restrict__ cell_out, float* __restrict__ logp,
                                                         float* __restrict__ ent, long long M, int cells) {
     const long long f = blockIdx.x * (long long)blockDim.x + threadIdx.x;
     if (f >= M) return;
     float lp = 0.f, en = 0.f;
-    for (int c = 0; c < cells; ++c) {
+    int c = 0;
+    for (; c + 16 <= cells; c += 16) {                 // 16 loads in flight, added in cell order
+        float2 v[16];
+#pragma unroll
+        for (int i = 0; i < 16; ++i) v[i] = __ldg(cell_out + (long long)(c + i) * M + f);
+#pragma unroll
+        for (int i = 0; i < 16; ++i) {
+            lp += v[i].x;
+            en += v[i].y;
+        }
+    }
+    for (; c < cells; ++c) {
         const float2 v = __ldg(cell_out + (long long)c * M + f);
         lp += v.x;
         en += v.y;
@@ -495,7 +506,7 @@ int actor_head_fwd(const float* a_hi, const float* a_lo, const float* wp_hi, con
                                                             int(M), cells, K, status);
     MB_CUDA(cudaGetLastError());
     if (logp && ent) {
-        frame_sum_kernel<<<unsigned((M + 255) / 256), 256, 0, st>>>(reinterpret_cast<const float2*>(cell_out), logp, ent, M, cells);
+        frame_sum_kernel<<<unsigned((M + 63) / 64), 64, 0, st>>>(reinterpret_cast<const float2*>(cell_out), logp, ent, M, cells);
         MB_CUDA(cudaGetLastError());
     }
     return MB_OK;
