@@ -281,6 +281,20 @@ MB_API int mb_actor_head_fwd(const float* a_hi, const float* a_lo, const float* 
                              int32_t logits_alive_only, float* logp_out, float* ent_out, int64_t n_frames,
                              int32_t cells, int32_t k, int32_t* status, void* stream);
 
+/* The same forward over the (frame, cell) pairs that have a valid action only: log-prob and entropy of every other pair
+ * are exactly 0 (quirk Q1) and the learner never reads policy_logits (libs/utils.py:237-329), so their 78 logits are
+ * not formed at all -- 6 % of the work at microRTS densities.  alive_bits [cells][ceil(n_frames / 32)] as written by
+ * mb_pack_cells; workspace of mb_actor_head_list_workspace_bytes(n_frames, cells) bytes (device memory, 16-byte
+ * aligned: the cell-ordered lists are built in it on the device, no host synchronisation); cell_out is zeroed by the
+ * call and filled for the live pairs; logits_out [n_frames, 78 * cells] or NULL receives the logits of the live cells
+ * (what mb_cells_bwd needs), other cells are left untouched.  Logits, cell_out, logp_out, ent_out are bit-identical
+ * to mb_actor_head_fwd's.  cells <= 1024, k % 32 == 0. */
+MB_API size_t mb_actor_head_list_workspace_bytes(int64_t n_frames, int32_t cells);
+MB_API int mb_actor_head_list_fwd(const float* a_hi, const float* a_lo, const float* w_hi, const float* w_lo,
+                                  const float* bias_p, const void* cell_meta, const void* alive_bits, float* cell_out,
+                                  float* logits_out, float* logp_out, float* ent_out, void* workspace, size_t workspace_bytes,
+                                  int64_t n_frames, int32_t cells, int32_t k, int32_t* status, void* stream);
+
 /* Backward of actor Linear + policy head over the cells that can have a gradient (reference: loss.backward(),
  * libs/utils.py:334, through model.py:167-214; a cell without a valid action has exactly zero gradient, quirk Q1).
  * Everything runs on the device, nothing synchronises with the host: per cell the frames with a valid action are

@@ -59,6 +59,9 @@ SIGNATURES = {
     "mb_pack_actor_weight": (ctypes.c_int, [_P, _P, _P, _P, _P, ctypes.c_int32, ctypes.c_int32, _P]),
     "mb_actor_head_fwd": (ctypes.c_int, [_P, _P, _P, _P, _P, _P, _P, _P, ctypes.c_int32, _P, _P, ctypes.c_int64,
                                          ctypes.c_int32, ctypes.c_int32, _P, _P]),
+    "mb_actor_head_list_workspace_bytes": (ctypes.c_size_t, [ctypes.c_int64, ctypes.c_int32]),
+    "mb_actor_head_list_fwd": (ctypes.c_int, [_P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, ctypes.c_size_t, ctypes.c_int64,
+                                              ctypes.c_int32, ctypes.c_int32, _P, _P]),
     "mb_cells_bwd_workspace_bytes": (ctypes.c_size_t, [ctypes.c_int64, ctypes.c_int32]),
     "mb_cells_bwd": (ctypes.c_int, [_P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, ctypes.c_size_t, ctypes.c_int64, ctypes.c_int32,
                                     ctypes.c_int32, _P]),

@@ -46,6 +46,7 @@ void vtrace_set_tuning(int force_generic, int variant, int l2_promo);
 void gemm_set_tuning(int group_m, int stream_store);
 void conv_set_tuning(int tensor_cores);
 void conv_tc_set_debug(int bits);
+void head_list_set_debug(int bits);
 void vtrace_static_poison(int on);
 void vtrace_set_debug(int v);
 size_t vtrace_workspace_bytes(long long rows);
@@ -115,6 +116,7 @@ int mb_set_tuning(const char* key, int32_t value) {
     else if (!strcmp(key, "gemm_stream_store")) gemm_stream_store = value;
     else if (!strcmp(key, "conv_tc")) mb::conv_set_tuning(value);
     else if (!strcmp(key, "conv_tc_debug")) mb::conv_tc_set_debug(value);
+    else if (!strcmp(key, "head_list_debug")) mb::head_list_set_debug(value);
     else {
         mb::set_error("mb_set_tuning: unknown key '%s'", key);
         return MB_ERR_INVALID;

@@ -60,13 +60,14 @@ __global__ void __launch_bounds__(256) cell_count_kernel(const uint32_t* __restr
 
 // one block: chunk offsets per cell, the cell of every chunk, header = {n_chunks, n_entries_alive}
 __global__ void __launch_bounds__(1024) cell_scan_kernel(const int* __restrict__ counts, int* __restrict__ chunk_off,
-                                                         int* __restrict__ chunk_cell, int* __restrict__ header, int cells) {
+                                                         int* __restrict__ chunk_cell, int* __restrict__ header, int cells,
+                                                         int chunk) {
     __shared__ int s_off[1025];
     if (threadIdx.x == 0) {
         int run = 0, alive = 0;
         for (int c = 0; c < cells; ++c) {            // cells <= 1024: a serial scan of a few hundred adds
             s_off[c] = run;
-            run += (counts[c] + kChunk - 1) / kChunk;
+            run += (counts[c] + chunk - 1) / chunk;
             alive += counts[c];
         }
         s_off[cells] = run;
@@ -83,12 +84,12 @@ __global__ void __launch_bounds__(1024) cell_scan_kernel(const int* __restrict__
 
 // per cell: alive frames in ascending order into entries[chunk_off[c] * 32 ...], tail of the last chunk = -1
 __global__ void __launch_bounds__(256) cell_fill_kernel(const uint32_t* __restrict__ alive_bits, const int* __restrict__ chunk_off,
-                                                        int* __restrict__ entries, int words) {
+                                                        int* __restrict__ entries, int words, int chunk) {
     __shared__ int warp_tot[8];
     __shared__ int base_s;
     const int c = blockIdx.x;
     const uint32_t* row = alive_bits + (long long)c * words;
-    int* out = entries + (long long)chunk_off[c] * kChunk;
+    int* out = entries + (long long)chunk_off[c] * chunk;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     if (threadIdx.x == 0) base_s = 0;
     __syncthreads();
@@ -120,7 +121,7 @@ __global__ void __launch_bounds__(256) cell_fill_kernel(const uint32_t* __restri
         __syncthreads();
     }
     const int total = base_s;
-    const int padded = (total + kChunk - 1) / kChunk * kChunk;
+    const int padded = (total + chunk - 1) / chunk * chunk;
     for (int i = total + threadIdx.x; i < padded; i += 256) out[i] = -1;
 }
 
@@ -377,6 +378,35 @@ static size_t cells_ws_ints(long long n_frames, int cells) {
 
 }  // namespace mb
 
+namespace mb {
+// Cell-ordered lists of the frames with a valid action, `chunk` entries per chunk (padding = -1), for other kernels of
+// the library (csrc/fused.cu: the list form of the actor head's forward).  Layout in `ws` (ints): counts [cells],
+// chunk_off [cells + 1], header [4] = {n_chunks, n_alive, ..}, chunk_cell [cap], entries [cap * chunk] with
+// cap = n_frames * cells / chunk + cells.
+size_t cell_lists_ws_ints(long long n_frames, int cells, int chunk) {
+    const size_t cap = size_t(n_frames) * cells / chunk + cells;
+    return size_t(cells) + cells + 1 + 4 + cap + cap * chunk;
+}
+int build_cell_lists(const uint32_t* alive_bits, int* ws, long long n_frames, int cells, int chunk, cudaStream_t st,
+                     int** chunk_cell_out, int** header_out, int** entries_out) {
+    const size_t cap = size_t(n_frames) * cells / chunk + cells;
+    int* counts = ws;
+    int* chunk_off = counts + cells;
+    int* header = chunk_off + cells + 1;
+    int* chunk_cell = header + 4;
+    int* entries = chunk_cell + cap;
+    const int words = int((n_frames + 31) / 32);
+    cell_count_kernel<<<cells, 256, 0, st>>>(alive_bits, counts, words);
+    cell_scan_kernel<<<1, 1024, 0, st>>>(counts, chunk_off, chunk_cell, header, cells, chunk);
+    cell_fill_kernel<<<cells, 256, 0, st>>>(alive_bits, chunk_off, entries, words, chunk);
+    MB_CUDA(cudaGetLastError());
+    *chunk_cell_out = chunk_cell;
+    *header_out = header;
+    *entries_out = entries;
+    return MB_OK;
+}
+}  // namespace mb
+
 extern "C" size_t mb_cells_bwd_workspace_bytes(int64_t n_frames, int32_t cells) {
     if (n_frames <= 0 || cells <= 0) return 0;
     return (mb::cells_ws_ints(n_frames, cells) * sizeof(int) + 255) & ~size_t(255);
@@ -426,8 +456,8 @@ extern "C" int mb_cells_bwd(const float* hidden, const float* weight, const floa
     const uint32_t* bits = reinterpret_cast<const uint32_t*>(alive_bits);
     const int words = int((n_frames + 31) / 32);
     cell_count_kernel<<<cells, 256, 0, st>>>(bits, counts, words);
-    cell_scan_kernel<<<1, 1024, 0, st>>>(counts, chunk_off, chunk_cell, header, cells);
-    cell_fill_kernel<<<cells, 256, 0, st>>>(bits, chunk_off, entries, words);
+    cell_scan_kernel<<<1, 1024, 0, st>>>(counts, chunk_off, chunk_cell, header, cells, kChunk);
+    cell_fill_kernel<<<cells, 256, 0, st>>>(bits, chunk_off, entries, words, kChunk);
     int dev = 0;
     MB_CUDA(cudaGetDevice(&dev));
     static bool attr_set[64] = {};

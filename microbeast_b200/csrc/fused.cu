@@ -19,6 +19,8 @@
 //                      columns out of TMEM, bias, mask, the seven segment soft-maxes, log-prob of the taken
 //                      actions and entropy -> cell_out [C][N] float2.
 //   frame_sum          per frame, the C cell results added in cell order (deterministic) -> logp, ent [N].
+#include <atomic>
+
 #include "common.cuh"
 #include "tc.cuh"
 
@@ -367,6 +369,223 @@ __global__ void __launch_bounds__(kFuThreads, 1) actor_head_fwd_kernel(const __g
     if (warp == 1) tmem_dealloc(tmem_base, kFuTmemCols);
 }
 
+// ---- the same forward over the LIVE (frame, cell) pairs only -------------------------------------------------
+// The learner never reads the logits (libs/utils.py:237-329) and a cell without a valid action contributes exactly 0 to
+// log-prob and entropy (quirk Q1), so only the pairs with a valid action -- 6 % at microRTS densities -- need their 78
+// logits at all.  Tiles are 128 entries of ONE cell out of the cell-ordered lists of csrc/cells.cu (build_cell_lists,
+// chunk = 128): M = 128 gathered rows of `hidden`, N = 80 (that cell's padded weight rows), K = 256.
+//   warps 8-11  gather: thread = entry; the row's hi / lo halves arrive by 16-byte cp.async straight into the K-major,
+//               128-byte-swizzled operand stage (the halves are pre-split in global memory, so no conversion), three
+//               k-blocks deep (a fourth stage changes nothing); thread 0 also issues the two TMA boxes of the cell's weight rows;
+//   warp 12     one lane issues the MMAs (same three products, same accumulator split and order as the dense kernel:
+//               the logits are bit-identical);
+//   warps 0-7   two epilogue groups over two TMEM slots: bias, the head of csrc/head.cu on the row's 80 columns,
+//               `cell_out` scattered to [cell][frame] (pre-zeroed: dead pairs stay exactly 0), logits of the live
+//               cells on request (all the backward pass needs).
+constexpr int kLfM = 128, kLfStages = 3, kLfThreads = 32 * 13;
+constexpr int kLfTileA = kLfM * kFuBK * 4;           // 16 KB
+constexpr int kLfTileB = kCellPad * kFuBK * 4;       // 10 KB = ten swizzle atoms
+constexpr int kLfStage = 2 * kLfTileA + 2 * kLfTileB;
+constexpr int kLfSmem = kLfStages * kLfStage + 1024;
+constexpr uint32_t kLfIdesc = tf32_idesc(kLfM, kCellPad);
+static_assert(kLfTileB % 1024 == 0, "swizzle atoms are 1024 B");
+
+struct LfMaps {
+    CUtensorMap b_hi, b_lo;
+};
+
+__device__ __forceinline__ void lf_cp_async16(void* dst_smem, const void* src, bool valid) {
+    const uint32_t bytes = valid ? 16u : 0u;         // 0 source bytes: the destination is zero-filled
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(smem_u32(dst_smem)), "l"(src), "r"(bytes) : "memory");
+}
+
+__global__ void __launch_bounds__(kLfThreads, 1) actor_head_list_fwd_kernel(const __grid_constant__ LfMaps maps,
+                                                                            const float* __restrict__ a_hi, const float* __restrict__ a_lo,
+                                                                            const float* __restrict__ bias_p,
+                                                                            const uint4* __restrict__ meta,
+                                                                            const int* __restrict__ entries,
+                                                                            const int* __restrict__ chunk_cell,
+                                                                            const int* __restrict__ header,
+                                                                            float2* __restrict__ cell_out,
+                                                                            float* __restrict__ logits_out, int M, int cells, int K,
+                                                                            int* status, int debug) {
+    extern __shared__ uint8_t lf_smem_raw[];
+    __shared__ __align__(8) uint64_t full_bar[kLfStages], empty_bar[kLfStages], acc_full[2], acc_empty[2];
+    __shared__ uint32_t tmem_slot;
+    uint8_t* smem = lf_smem_raw + ((1024u - (smem_u32(lf_smem_raw) & 1023u)) & 1023u);
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < kLfStages; ++s) {
+            mbar_init(&full_bar[s], 129);            // 128 gathering threads + the expect_tx arrival of the weight boxes
+            mbar_init(&empty_bar[s], 1);
+        }
+        for (int s = 0; s < 2; ++s) {
+            mbar_init(&acc_full[s], 1);
+            mbar_init(&acc_empty[s], 4);
+        }
+        fence_mbar_init();
+        tma_prefetch_desc(&maps.b_hi);
+        tma_prefetch_desc(&maps.b_lo);
+    }
+    if (warp == 12) tmem_alloc(&tmem_slot, 512);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = tmem_slot;
+    const int n_tiles = __ldg(header);               // chunks of 128 entries, each of one cell
+    const int kblocks = K / kFuBK;
+
+    if (warp >= 8 && warp < 12) {
+        // ===================== gather =====================
+        // eight lanes fetch the eight 16-byte pieces of one row's 128-byte k-block, so a warp instruction is four
+        // whole-line requests instead of 32 half-used sectors (16-byte pieces from 32 different rows left the kernel
+        // bound by L2 request rate: 0.34 ms against 0.22 ms); a thread serves rows t/8 + 16 i, i < 8
+        const int t = threadIdx.x - 256;
+        const int c8 = t & 7, r0 = t >> 3;
+        uint32_t issued = 0, arrived = 0;
+        for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+            const int cell = __ldg(chunk_cell + tile);
+            const float* rh[8];
+            const float* rl[8];
+            bool valid[8];
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+                const int f = __ldg(entries + (long long)tile * kLfM + r0 + 16 * i);       // -1: padding of the cell's last chunk
+                valid[i] = f >= 0;
+                rh[i] = a_hi + (long long)(valid[i] ? f : 0) * K + 4 * c8;
+                rl[i] = a_lo + (long long)(valid[i] ? f : 0) * K + 4 * c8;
+            }
+            for (int kb = 0; kb < kblocks; ++kb) {
+                const int s = issued % kLfStages;
+                mbar_wait(&empty_bar[s], ((issued / kLfStages) & 1) ^ 1, status);
+                uint8_t* st = smem + s * kLfStage;
+                if (t == 0) {
+                    mbar_arrive_expect_tx(&full_bar[s], uint32_t(2 * kLfTileB));
+                    tma_load_2d(st + 2 * kLfTileA, &maps.b_hi, kb * kFuBK, cell * kCellPad, &full_bar[s]);
+                    tma_load_2d(st + 2 * kLfTileA + kLfTileB, &maps.b_lo, kb * kFuBK, cell * kCellPad, &full_bar[s]);
+                }
+#pragma unroll
+                for (int i = 0; i < 8; ++i) {
+                    const int r = r0 + 16 * i;
+                    const uint32_t off = uint32_t(r * 128) + ((uint32_t(c8) ^ uint32_t(r & 7)) << 4);
+                    if (debug & 2) continue;                 // timing experiment: no gather
+                    lf_cp_async16(st + off, rh[i] + kb * kFuBK, valid[i]);
+                    lf_cp_async16(st + kLfTileA + off, rl[i] + kb * kFuBK, valid[i]);
+                }
+                asm volatile("cp.async.commit_group;" ::: "memory");
+                ++issued;
+                if (issued >= uint32_t(kLfStages)) {          // all but the last kLfStages - 1 groups have landed
+                    asm volatile("cp.async.wait_group %0;" ::"n"(kLfStages - 1) : "memory");
+                    fence_proxy_async_smem();
+                    while (arrived + (kLfStages - 1) < issued) {
+                        mbar_arrive(&full_bar[arrived % kLfStages]);
+                        ++arrived;
+                    }
+                }
+            }
+        }
+        asm volatile("cp.async.wait_group 0;" ::: "memory");
+        fence_proxy_async_smem();
+        while (arrived < issued) {
+            mbar_arrive(&full_bar[arrived % kLfStages]);
+            ++arrived;
+        }
+    } else if (warp == 12) {
+        // ===================== MMA issuer =====================
+        if (lane == 0) {
+            uint32_t it = 0, job = 0;
+            for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, ++job) {
+                const uint32_t slot = job & 1u;
+                mbar_wait(&acc_empty[slot], ((job >> 1) & 1u) ^ 1u, status);
+                tc_fence_after();
+                const uint32_t d_main = tmem_base + slot * 256u, d_lo = d_main + 128u;
+                for (int kb = 0; kb < kblocks; ++kb, ++it) {
+                    const int s = it % kLfStages;
+                    mbar_wait(&full_bar[s], (it / kLfStages) & 1, status);
+                    tc_fence_after();
+                    const uint32_t st = smem_u32(smem + s * kLfStage);
+                    const uint64_t ah = make_kmajor_sw128_desc(st), al = make_kmajor_sw128_desc(st + kLfTileA);
+                    const uint64_t bh = make_kmajor_sw128_desc(st + 2 * kLfTileA);
+                    const uint64_t bl = make_kmajor_sw128_desc(st + 2 * kLfTileA + kLfTileB);
+#pragma unroll
+                    for (int k = 0; k < kFuBK / 8; ++k) {
+                        const uint64_t adv = uint64_t((k * 8 * 4) >> 4);
+                        if (debug & 4) continue;             // timing experiment: no MMAs
+                        mma_tf32(d_main, ah + adv, bh + adv, kLfIdesc, (kb | k) != 0);
+                        mma_tf32(d_lo, al + adv, bh + adv, kLfIdesc, (kb | k) != 0);
+                        mma_tf32(d_lo, ah + adv, bl + adv, kLfIdesc, 1);
+                    }
+                    tc_commit(&empty_bar[s]);
+                }
+                tc_commit(&acc_full[slot]);
+            }
+        }
+    } else {
+        // ===================== epilogue: one thread per list entry =====================
+        const int group = warp >> 2, q = warp & 3;
+        uint32_t job = 0;
+        for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, ++job) {
+            if (int(job & 1u) != group) continue;
+            const uint32_t slot = job & 1u;
+            mbar_wait(&acc_full[slot], (job >> 1) & 1u, status);
+            tc_fence_after();
+            const uint32_t taddr = tmem_base + (uint32_t(q * 32) << 16) + slot * 256u;
+            if (debug & 1) {                                 // timing experiment: no epilogue work
+                tc_fence_before();
+                __syncwarp();
+                if (lane == 0) mbar_arrive(&acc_empty[slot]);
+                continue;
+            }
+            float z[kCellPad];
+#pragma unroll
+            for (int c = 0; c < kCellPad / 16; ++c) {
+                float v[16], w[16];
+                tmem_ld16(taddr + uint32_t(c * 16), v);
+                tmem_ld16(taddr + 128u + uint32_t(c * 16), w);
+#pragma unroll
+                for (int i = 0; i < 16; ++i) z[c * 16 + i] = v[i] + w[i];
+            }
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&acc_empty[slot]);
+            const int f = __ldg(entries + (long long)tile * kLfM + q * 32 + lane);
+            if (f >= 0) {
+                const int cell = __ldg(chunk_cell + tile);
+                const float4* bp = reinterpret_cast<const float4*>(bias_p + cell * kCellPad);
+#pragma unroll
+                for (int i = 0; i < kCellPad / 4; ++i) {
+                    const float4 b = __ldg(bp + i);
+                    z[4 * i] += b.x; z[4 * i + 1] += b.y; z[4 * i + 2] += b.z; z[4 * i + 3] += b.w;
+                }
+                const uint4 mt = __ldg(meta + (long long)cell * M + f);
+                if (logits_out) {
+                    // a cell's 78 logits are 312 contiguous bytes starting on an 8-byte boundary: 16-byte stores wherever
+                    // the alignment allows (19 + one 8-byte store instead of 39 8-byte stores)
+                    float* o = logits_out + ((long long)f * cells + cell) * kLogitsPerCell;
+                    if ((reinterpret_cast<uintptr_t>(o) & 15) == 0) {
+#pragma unroll
+                        for (int i = 0; i < 19; ++i)
+                            reinterpret_cast<float4*>(o)[i] = make_float4(z[4 * i], z[4 * i + 1], z[4 * i + 2], z[4 * i + 3]);
+                        *reinterpret_cast<float2*>(o + 76) = make_float2(z[76], z[77]);
+                    } else {
+                        *reinterpret_cast<float2*>(o) = make_float2(z[0], z[1]);
+#pragma unroll
+                        for (int i = 0; i < 19; ++i)
+                            reinterpret_cast<float4*>(o + 2)[i] = make_float4(z[4 * i + 2], z[4 * i + 3], z[4 * i + 4], z[4 * i + 5]);
+                    }
+                }
+                float lp = 0.f, en = 0.f;
+                cell_forward(z, mt, lp, en);
+                cell_out[(long long)cell * M + f] = make_float2(lp, en);
+            }
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    if (warp == 12) tmem_dealloc(tmem_base, 512);
+}
+
 // per frame: the C cell results in cell order -> logp, ent
 __global__ void __launch_bounds__(64) frame_sum_kernel(const float2* __restrict__ cell_out, float* __restrict__ logp,
                                                         float* __restrict__ ent, long long M, int cells) {
@@ -512,7 +731,90 @@ int actor_head_fwd(const float* a_hi, const float* a_lo, const float* wp_hi, con
     return MB_OK;
 }
 
+// csrc/cells.cu
+size_t cell_lists_ws_ints(long long n_frames, int cells, int chunk);
+int build_cell_lists(const uint32_t* alive_bits, int* ws, long long n_frames, int cells, int chunk, cudaStream_t st,
+                     int** chunk_cell_out, int** header_out, int** entries_out);
+
+std::atomic<int> g_lf_debug{0};      // mb_set_tuning("head_list_debug", bits): skip a role's work (timing experiments, wrong results)
+void head_list_set_debug(int bits) { g_lf_debug = bits; }
+
+int actor_head_list_fwd(const float* a_hi, const float* a_lo, const float* wp_hi, const float* wp_lo, const float* bias_p,
+                        const void* meta, const void* alive_bits, float* cell_out, float* logits_out, float* logp, float* ent,
+                        void* workspace, size_t workspace_bytes, long long M, int cells, int K, int* status, cudaStream_t st) {
+    FuEncodeFn enc = fu_encode_fn();
+    if (!enc) {
+        set_error("mb_actor_head_list_fwd: cuTensorMapEncodeTiled is not available from this driver");
+        return MB_ERR_UNSUPPORTED;
+    }
+    if (workspace_bytes < cell_lists_ws_ints(M, cells, kLfM) * sizeof(int)) {
+        set_error("mb_actor_head_list_fwd: workspace smaller than mb_actor_head_list_workspace_bytes(n_frames, cells)");
+        return MB_ERR_INVALID;
+    }
+    LfMaps maps;
+    const long long wrows = (long long)cells * kCellPad;
+    if (!fu_map(enc, &maps.b_hi, wp_hi, wrows, K, kCellPad) || !fu_map(enc, &maps.b_lo, wp_lo, wrows, K, kCellPad)) {
+        set_error("mb_actor_head_list_fwd: cuTensorMapEncodeTiled rejected cells=%d K=%d", cells, K);
+        return MB_ERR_INVALID;
+    }
+    int *chunk_cell = nullptr, *header = nullptr, *entries = nullptr;
+    const int rc = build_cell_lists(reinterpret_cast<const uint32_t*>(alive_bits), reinterpret_cast<int*>(workspace), M, cells, kLfM,
+                                    st, &chunk_cell, &header, &entries);
+    if (rc != MB_OK) return rc;
+    MB_CUDA(cudaMemsetAsync(cell_out, 0, size_t(cells) * size_t(M) * sizeof(float2), st));      // dead pairs: exactly 0 (Q1)
+    int dev = 0;
+    MB_CUDA(cudaGetDevice(&dev));
+    static bool attr_set[64] = {};
+    bool& done = attr_set[(dev >= 0 && dev < 64) ? dev : 0];
+    if (!done) {
+        MB_CUDA(cudaFuncSetAttribute(actor_head_list_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kLfSmem));
+        done = true;
+    }
+    actor_head_list_fwd_kernel<<<sm_count(dev), kLfThreads, kLfSmem, st>>>(maps, a_hi, a_lo, bias_p, reinterpret_cast<const uint4*>(meta),
+                                                                          entries, chunk_cell, header,
+                                                                          reinterpret_cast<float2*>(cell_out), logits_out, int(M), cells,
+                                                                          K, status, g_lf_debug.load());
+    MB_CUDA(cudaGetLastError());
+    if (logp && ent) {
+        frame_sum_kernel<<<unsigned((M + 63) / 64), 64, 0, st>>>(reinterpret_cast<const float2*>(cell_out), logp, ent, M, cells);
+        MB_CUDA(cudaGetLastError());
+    }
+    return MB_OK;
+}
+
 }  // namespace mb
+
+extern "C" size_t mb_actor_head_list_workspace_bytes(int64_t n_frames, int32_t cells) {
+    if (n_frames <= 0 || cells <= 0) return 0;
+    return (mb::cell_lists_ws_ints(n_frames, cells, mb::kLfM) * sizeof(int) + 255) & ~size_t(255);
+}
+
+extern "C" int mb_actor_head_list_fwd(const float* a_hi, const float* a_lo, const float* w_hi, const float* w_lo,
+                                      const float* bias_p, const void* cell_meta, const void* alive_bits, float* cell_out,
+                                      float* logits_out, float* logp_out, float* ent_out, void* workspace, size_t workspace_bytes,
+                                      int64_t n_frames, int32_t cells, int32_t k, int32_t* status, void* stream) {
+    if (n_frames < 0 || cells <= 0 || cells > 1024 || k <= 0 || k % 32 != 0 || n_frames > 0x7fffffff) {
+        mb::set_error("mb_actor_head_list_fwd: n_frames=%lld cells=%d k=%d: need 0 < cells <= 1024 and k %% 32 == 0", (long long)n_frames,
+                      cells, k);
+        return MB_ERR_INVALID;
+    }
+    if (n_frames == 0) return MB_OK;
+    if (!a_hi || !a_lo || !w_hi || !w_lo || !bias_p || !cell_meta || !alive_bits || !cell_out || !workspace ||
+        ((logp_out == nullptr) != (ent_out == nullptr))) {
+        mb::set_error("mb_actor_head_list_fwd: null pointer (logp_out / ent_out: both or neither)");
+        return MB_ERR_INVALID;
+    }
+    const uintptr_t all = reinterpret_cast<uintptr_t>(a_hi) | reinterpret_cast<uintptr_t>(a_lo) | reinterpret_cast<uintptr_t>(w_hi) |
+                          reinterpret_cast<uintptr_t>(w_lo) | reinterpret_cast<uintptr_t>(bias_p) |
+                          reinterpret_cast<uintptr_t>(cell_meta) | reinterpret_cast<uintptr_t>(cell_out) |
+                          reinterpret_cast<uintptr_t>(logits_out) | reinterpret_cast<uintptr_t>(workspace);
+    if (all & 15) {
+        mb::set_error("mb_actor_head_list_fwd: operands must be 16-byte aligned");
+        return MB_ERR_INVALID;
+    }
+    return mb::actor_head_list_fwd(a_hi, a_lo, w_hi, w_lo, bias_p, cell_meta, alive_bits, cell_out, logits_out, logp_out, ent_out,
+                                   workspace, workspace_bytes, n_frames, cells, k, status, static_cast<cudaStream_t>(stream));
+}
 
 extern "C" int mb_pack_cells(const uint8_t* mask, const int64_t* action, void* cell_meta, void* alive_bits, int64_t n_frames,
                              int32_t cells, int32_t* status, void* stream) {

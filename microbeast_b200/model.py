@@ -219,6 +219,8 @@ FUSED_RES_BLOCK = True
 TENSOR_CORE_ACTOR = True
 # learner mode: actor Linear and policy head as ONE tcgen05 kernel (mb_actor_head_fwd): the logits stay in tensor memory,
 # only the cells that have a valid action are written out (for the backward pass); off: mb_linear_tf32x3 + mb_head_eval_fwd
+# ... over the pairs with a valid action only when policy_logits is not asked for (mb_actor_head_list_fwd)
+LIST_ACTOR_HEAD = True
 FUSED_ACTOR_HEAD = True
 # backward of the actor head by mb_cells_bwd (device-side cell lists, no host sync) whenever the fused forward ran and
 # Agent.sparse_backward is not False; off: the round-1 torch cell-list path (nonzero + bmm + index_add_)
@@ -311,8 +313,12 @@ class _ActorHead(torch.autograd.Function):
             # the backward: every other cell has exactly zero gradient) unless the caller wants policy_logits
             if meta is None or tuple(meta.shape) != (cells, hidden.shape[0], 4) or not hasattr(meta, "alive_bits"):
                 meta = ops.pack_cells(action_mask, action, cells)      # else: packed ahead by learner.BatchPrefetcher
-            fused = ops.actor_head_fwd(hidden, ops.pack_actor_weight(weight, bias, cells), meta,
-                                       want_logits=True if want_logits else "alive")
+            packed = ops.pack_actor_weight(weight, bias, cells)
+            if LIST_ACTOR_HEAD and not want_logits:
+                # nobody reads policy_logits: form the logits of the (frame, cell) pairs with a valid action only
+                fused = ops.actor_head_list_fwd(hidden, packed, meta, want_logits="alive")
+            if fused is None:
+                fused = ops.actor_head_fwd(hidden, packed, meta, want_logits=True if want_logits else "alive")
         ctx.meta = None
         if fused is not None:
             logprobs, entropy, _cell_out, logits = fused

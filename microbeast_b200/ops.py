@@ -509,6 +509,40 @@ def actor_head_fwd(hidden: torch.Tensor, packed_weight, cell_meta: torch.Tensor,
 
 
 _cells_ws: Dict[Tuple[int, int], torch.Tensor] = {}
+
+
+def actor_head_list_fwd(hidden: torch.Tensor, packed_weight, cell_meta: torch.Tensor, want_logits=False):
+    """:func:`actor_head_fwd` over the (frame, cell) pairs that have a valid action only (``mb_actor_head_list_fwd``):
+    cell-ordered lists built on the device, 128 gathered rows of ``hidden`` per tile against one cell's weight rows.
+    Same outputs, bit for bit; ``want_logits``: False or ``"alive"`` (logits of the live cells into an otherwise
+    uninitialised ``[N, 78*cells]`` buffer).  ``None`` when the shape is not covered."""
+    dev = _need_cuda(hidden=hidden, cell_meta=cell_meta)
+    w_hi, w_lo, bias_p = packed_weight
+    hidden = _as(hidden, torch.float32, "hidden")
+    n, k = hidden.shape
+    cells = cell_meta.shape[0]
+    alive_bits = getattr(cell_meta, "alive_bits", None)
+    if k % 32 or w_hi.shape != (cells * 80, k) or tuple(cell_meta.shape) != (cells, n, 4) or n == 0 or cells > 1024 or \
+            alive_bits is None or want_logits is True:
+        return None
+    a_hi, a_lo = split_tf32(hidden)
+    need = int(lib.mb_actor_head_list_workspace_bytes(n, cells))
+    idx = dev.index if dev.index is not None else torch.cuda.current_device()
+    ws = _cells_ws.get((idx, 1))
+    if ws is None or ws.numel() < need:
+        if ws is not None:
+            _retired_workspaces.append(ws)          # a captured graph may still address it
+        ws = torch.empty(need, dtype=torch.uint8, device=dev)
+        _cells_ws[(idx, 1)] = ws
+    cell_out = torch.empty((cells, n, 2), dtype=torch.float32, device=dev)
+    logp = torch.empty(n, dtype=torch.float32, device=dev)
+    ent = torch.empty(n, dtype=torch.float32, device=dev)
+    logits = torch.empty((n, cells * LOGITS_PER_CELL), dtype=torch.float32, device=dev) if want_logits else None
+    with torch.cuda.device(dev), _Launch("actor_head_list_fwd", note={"m": n, "cells": cells, "k": k}):
+        _check(lib.mb_actor_head_list_fwd(_ptr(a_hi), _ptr(a_lo), _ptr(w_hi), _ptr(w_lo), _ptr(bias_p), _ptr(cell_meta),
+                                          _ptr(alive_bits), _ptr(cell_out), _ptr(logits), _ptr(logp), _ptr(ent), _ptr(ws),
+                                          ws.numel(), n, cells, k, _ptr(status_word(dev)), _stream()))
+    return logp, ent, cell_out, logits
 # True: every CTA of mb_conv3x3_wgrad writes a partial result and torch sums them in a fixed order (one more pass per
 # convolution); False: the CTAs add into the result with atomics (the cell-list backward of the actor head uses atomics
 # anyway, so a learner step is not bit-reproducible from run to run either way)

@@ -120,3 +120,25 @@ def test_cells_backward_matches_autograd_of_the_oracle(n, cells, preset):
         assert ok, f"{name}: {worst:.2f}x the 1e-5 bound"
         ok, worst = close_rms(again, want, 1e-5)
         assert ok, f"{name} (second call): {worst:.2f}x the 1e-5 bound"
+
+
+@pytest.mark.parametrize("n,cells,preset", [(300, 16, "dense"), (257, 64, "realistic"), (64, 256, "dense"), (1, 4, "all_valid"),
+                                            (130, 9, "all_masked"), (1000, 64, "one_valid")])
+def test_list_forward_equals_the_dense_fused_forward(n, cells, preset):
+    """mb_actor_head_list_fwd (only the (frame, cell) pairs with a valid action go through the tensor cores, gathered
+    from device-built lists) == mb_actor_head_fwd bit for bit: per-frame sums, per-cell results, and the logits of
+    every live cell; dead pairs are exactly zero."""
+    from microbeast_b200 import ops
+    hidden, weight, bias, mask, action = _case(n, cells, 256, preset, seed=n + cells)
+    d = lambda t: t.cuda()
+    meta = ops.pack_cells(d(mask), d(action), cells)
+    packed = ops.pack_actor_weight(d(weight), d(bias), cells)
+    lp0, en0, co0, lg0 = ops.actor_head_fwd(d(hidden), packed, meta, want_logits="alive")
+    for _ in range(2):                                   # twice: the workspace and the lists are rebuilt per call
+        got = ops.actor_head_list_fwd(d(hidden), packed, meta, want_logits="alive")
+        assert got is not None
+        lp1, en1, co1, lg1 = got
+        assert torch.equal(co1, co0) and torch.equal(lp1, lp0) and torch.equal(en1, en0)
+        alive = (mask.view(n, cells, 78) != 0).any(dim=2).cuda()
+        assert torch.equal(lg1.view(n, cells, 78)[alive], lg0.view(n, cells, 78)[alive])
+        assert not co1.permute(1, 0, 2)[~alive].any()

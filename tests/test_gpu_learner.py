@@ -460,7 +460,7 @@ def test_graphed_learner_matches_eager_steps(wire, opt_name):
         # become lr-sized weight differences, so its trajectories are compared loosely and only through the losses
         np.testing.assert_allclose(four_g, four_e, rtol=2e-4 if opt_name == "sgd" else 5e-3, atol=1e-6,
                                    err_msg=f"step {i}")
-    assert gl.launches_per_step.get("actor_head_fwd") == 1 and gl.launches_per_step.get("vtrace_loss") == 1
+    assert gl.launches_per_step.get("actor_head_list_fwd") == 1 and gl.launches_per_step.get("vtrace_loss") == 1
     assert gl.launches_per_step.get("cells_bwd") == 1           # the device-side cell-list backward is captured as is
     if opt_name == "sgd":
         for (name, pe), pg in zip(eager.named_parameters(), graphed.parameters()):
