@@ -19,10 +19,11 @@ e2e     = the same step through the public calls BatchPrefetcher.submit(...) + P
 parity  = the gate run before timing: one lr = 0 step on a 32-row sample of the benchmarked workload, GPU fp32 and
           CPU fp32 (the reference's arithmetic) both against a float64 evaluation (oracle/parity.py); the bench exits 3
           instead of printing a number when the GPU is further off than max(1e-5, 4 x the CPU's error).
-roofline= the dominant kernel of ours -- the fused actor Linear + policy head (csrc/fused.cu), a tensor-pipe kernel:
-          issued TF32 TFLOP/s, timed live with CUDA events on the launching stream inside the timed region, against
-          half the measured bf16 rate of MEASURED_PEAKS.json; the dominant HBM-bound kernel sits under
-          info.roofline_hbm.
+roofline= the dominant kernel of ours -- the actor head's backward over the (frame, cell) pairs with a valid action
+          (csrc/cells.cu), an fp32 FMA-pipe kernel: useful TFLOP/s, timed live with CUDA events on the launching stream
+          inside the timed region, against 148 SMs x 128 FMA lanes x the sampled SM clock; the dominant tensor-pipe
+          kernel (the fused actor Linear + policy head, dense and list form) sits under info.roofline_tensor, the
+          dominant HBM-bound one under info.roofline_hbm.
 cpu_baseline = the reference's own PPO_learn + Agent (byte copies staged into oracle/_ref by oracle/stage_ref.py;
           the oracle port when they are missing) timed on the host cores on a bounded sample of the same workload
           (rank 0, N=1 only).  --impl reference runs only that arm and never imports the package.
@@ -410,7 +411,7 @@ def run_ours(args):
     # kernels that can be the dominant one of the step: only these carry live CUDA-event pairs inside the timed region
     # (an event pair around each of the step's ~120 launches costs 0.3 ms per step; the rest of the `kernels` table
     # comes from a separate, untimed pass)
-    LIVE = ("actor_head_fwd", "pack_cells", "cells_bwd", "head_eval_fwd", "head_eval_bwd", "vtrace_loss")
+    LIVE = ("actor_head_fwd", "actor_head_list_fwd", "pack_cells", "cells_bwd", "head_eval_fwd", "head_eval_bwd", "vtrace_loss")
 
     def timed(fn, steps, warmup, sample_clocks=False, kernel_timing=False):
         sampler = ClockSampler(local) if sample_clocks else None
@@ -517,6 +518,43 @@ def run_ours(args):
                     "half the measured dense bf16 rate of MEASURED_PEAKS.json"})
 
     roof_hbm = roof
+    try:
+        bf16_peak = float(json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))["bf16_tflops"])
+    except Exception:
+        bf16_peak = 1646.0
+    roof_tensor = None
+    if "cells_bwd" in kernels or "actor_head_list_fwd" in kernels:
+        # the (frame, cell) pairs with a valid action: the units of the two list kernels of the actor head
+        alive = (dev_batch["action_mask"].view(n, cells, 78) != 0).any(dim=2)
+        pairs = int(alive.sum().item())
+        tiles = int(((alive.sum(dim=0) + 127) // 128).sum().item())
+        if "actor_head_list_fwd" in kernels:
+            kf = kernels["actor_head_list_fwd"]
+            issued = 3.0 * 2.0 * tiles * 128 * 80 * 256            # three TF32 products, 128-entry tiles of one cell, N = 80
+            kf.update({"bound": "tensor", "live_pairs": pairs, "tiles": tiles, "issued_tf32_tflops": issued / (kf["avg_ms"] * 1e-3) / 1e12,
+                       "frac_of_tf32_peak_issued": issued / (kf["avg_ms"] * 1e-3) / 1e12 / (bf16_peak / 2),
+                       "note": "the call's time includes building the cell lists, zeroing cell_out and the per-frame sums; "
+                               "the dense kernel it replaces (actor_head_fwd, info.roofline_tensor) issues 16x the flops"})
+        if "cells_bwd" in kernels:
+            kb = kernels["cells_bwd"]
+            useful = 2.0 * 2.0 * pairs * 78 * 256                  # d hidden and d weight: two [78 x 256] products per live pair
+            kb.update({"bound": "fma", "live_pairs": pairs, "useful_flops": useful, "tflops": useful / (kb["avg_ms"] * 1e-3) / 1e12,
+                       "fp32_peak_tflops": fp32_peak, "frac_of_fp32_peak": useful / (kb["avg_ms"] * 1e-3) / 1e12 / fp32_peak})
+            if roof is None or kb["avg_ms"] > roof["avg_launch_ms"]:
+                # The dominant kernel of the step: the actor head's backward over the live pairs, two fp32 FMA products per
+                # pair.  It is bound by the fp32 FMA pipe -- neither of the contract's "hbm" | "tensor" --
+                # so the peak is 148 SMs x 128 FMA lanes x 2 x the SM clock sampled during the timed region.
+                roof = {"kernel": "cells_bwd", "bound": "fma", "achieved": kb["tflops"], "peak": fp32_peak, "unit": "TFLOP/s",
+                        "frac": kb["frac_of_fp32_peak"], "traffic": None,
+                        "peak_source": "148 SMs x 128 fp32 FMA lanes x 2 flop x sampled SM clock (nvidia-smi, timed region)",
+                        "alg_flops_per_launch": useful, "live_pairs": pairs, "avg_launch_ms": kb["avg_ms"],
+                        "kernel_share_of_step": kb["avg_ms"] / ms_step,
+                        "note": "fp32 FMA-pipe bound (ncu: FMA pipe 48 % active, profiles/r02_ncu_kernels.csv); the dominant "
+                                "tensor-pipe and HBM-bound kernels are under info.roofline_tensor / info.roofline_hbm"}
+                try:
+                    roof["traffic"] = json.load(open(os.path.join(ROOT, "profiles", "traffic.json"))).get("cells_bwd", {}).get(args.workload)
+                except Exception:
+                    pass
     if "actor_head_fwd" in kernels and "issued_tf32_tflops" in kernels["actor_head_fwd"] and \
             (roof is None or kernels["actor_head_fwd"]["avg_ms"] > roof["avg_launch_ms"]):
         kf = kernels["actor_head_fwd"]
@@ -654,6 +692,31 @@ def run_ours(args):
             info["graphed"] = {"error": f"{type(exc).__name__}: {exc}"[:300]}
 
     info = dict(info or {})
+    if "actor_head_list_fwd" in kernels and "actor_head_fwd" not in kernels:
+        # the dense fused actor head (what Agent.get_action(policy_logits=True) runs): timed in a pass of its own
+        from microbeast_b200 import model as mmodel
+        mmodel.LIST_ACTOR_HEAD = False
+        try:
+            for _ in range(2):
+                step(dev_batch, False)
+            ops.start_kernel_timing(only=("actor_head_fwd",))
+            for _ in range(3):
+                step(dev_batch, False)
+            ts = ops.stop_kernel_timing().get("actor_head_fwd", [])
+        finally:
+            mmodel.LIST_ACTOR_HEAD = True
+        if ts:
+            sec = sum(ts) / len(ts) * 1e-3
+            issued = 3.0 * 2.0 * n * (80 * cells) * 256
+            info["roofline_tensor"] = {"kernel": "actor_head_fwd", "bound": "tensor", "achieved": issued / sec / 1e12,
+                                       "peak": bf16_peak / 2, "unit": "TFLOP/s", "frac": issued / sec / 1e12 / (bf16_peak / 2),
+                                       "avg_launch_ms": sec * 1e3, "alg_flops_per_launch": issued,
+                                       "peak_source": "MEASURED_PEAKS.json bf16_tflops / 2 (TF32 runs at half the bf16 rate)",
+                                       "note": "dense fused actor Linear + policy head over every (frame, cell) pair; the learner "
+                                               "step runs the list form instead (kernels.actor_head_list_fwd), which issues "
+                                               "1/16 of these flops; timed in a separate pass with model.LIST_ACTOR_HEAD = False",
+                                       "list_form": {k: kernels["actor_head_list_fwd"].get(k) for k in
+                                                     ("avg_ms", "issued_tf32_tflops", "frac_of_tf32_peak_issued", "tiles", "live_pairs")}}
     if world > 1:
         info["host_binding"] = {"cores_per_rank": len(bound_cores) if bound_cores else None,
                                 "note": "each rank restricted to the host cores NVML lists next to its GPU "

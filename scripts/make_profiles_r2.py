@@ -56,6 +56,8 @@ keep = ["Kernel Name", "launch__grid_size", "launch__block_size", "launch__regis
 keep = [k for k in keep if k in idx]
 N, C = 20736, 256
 alg = {"pack_cells": ("pack_cells", "byte", (78 + 56 + 16) * N * C), "actor_head_fwd": ("actor_head_fwd", "flop (3 x TF32)", 3 * 2.0 * N * 80 * C * 256),
+       # list form: ~6 % of the pairs are live at the "dense" preset; issued flops = 128-entry tiles x N 80 x K 256 x 3 passes
+       "actor_head_list_fwd": ("actor_head_list_fwd", "flop (3 x TF32, live pairs only)", None),
        "cell_grad": ("cells_bwd", "flop (fp32 FMA x2)", None), "head_kernel": ("head_sample", "byte", 474 * C * N + 8 * N),
        "vtrace": ("vtrace_loss", "byte", 37 * 65536 * 512 + 4 * 65536),
        # tensor-core convolutions: issued TF32 flops = 3 passes x 2 x pixels x 9 taps x cin x cout
@@ -89,7 +91,7 @@ with open(os.path.join(P, "r02_ncu_kernels.csv"), "w") as f:
 json.dump(traffic, open(os.path.join(P, "traffic.json"), "w"), indent=1)
 open(os.path.join(P, "r02_ncu_stalls.md"), "w").write(
     "# ncu --set full, source page summary (r02)\n\nCommand: `ncu --set full --clock-control none --import-source on "
-    "-k regex:'pack_cells_kernel|actor_head_fwd_kernel|cell_grad_kernel|head_kernel|vtrace_tma|conv3x3_tc_kernel|conv1_bits' -s 9 -c 9 python "
+    "-k regex:'pack_cells_kernel|actor_head_fwd_kernel|actor_head_list_fwd_kernel|cell_grad_kernel|head_kernel|vtrace_tma|conv3x3_tc_kernel|conv1_bits' -s 10 -c 10 python "
     "scripts/profile_r2.py 2` (config 2 shapes: 20 736 frames x 256 cells; T=512 x R=65 536 for V-trace; 20 736 frames for the convolutions; one launch each, "
     "cold cache).\n\n" + "\n".join(stall_summary(src)))
 

@@ -28,6 +28,7 @@ for _ in range(reps):
     flush.zero_(); meta = ops.pack_cells(mask, action, cells)
     packed = ops.pack_actor_weight(weight, bias, cells)
     flush.zero_(); _, _, _, logits = ops.actor_head_fwd(hidden, packed, meta, want_logits="alive")
+    flush.zero_(); ops.actor_head_list_fwd(hidden, packed, meta, want_logits="alive")
     flush.zero_(); ops.cells_bwd(hidden, weight, logits, meta, gl, ge)
     flush.zero_(); ops.head_sample(logits_dense, mask, u)
     flush.zero_(); ops.conv3x3_fwd(x32, w32, b32, wmode=1)
