@@ -103,8 +103,12 @@ for r in rows[1:]:
         data.append((r[ix["Kernel Name"]], float(r[ix["Metric Value"]].replace(",", ""))))
     except Exception:
         pass
-f = [i for i, d in enumerate(data) if "actor_head_fwd_kernel" in d[0]]
-span = data[f[-2]:f[-1]]
+# one default step = from one launch of the list-form actor head to the next (the dense head only runs in bench.py's
+# separate info.roofline_tensor pass at the end)
+f = [i for i, d in enumerate(data) if "actor_head_list_fwd_kernel" in d[0]]
+if len(f) < 3:
+    f = [i for i, d in enumerate(data) if "actor_head_fwd_kernel" in d[0]]
+span = data[f[2]:f[3]] if len(f) > 3 else data[f[-2]:f[-1]]
 tot = sum(d[1] for d in span)
 agg = collections.defaultdict(lambda: [0, 0.0])
 for n, t in span:
