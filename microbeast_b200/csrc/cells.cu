@@ -63,12 +63,15 @@ __global__ void __launch_bounds__(1024) cell_scan_kernel(const int* __restrict__
                                                          int* __restrict__ chunk_cell, int* __restrict__ header, int cells,
                                                          int chunk) {
     __shared__ int s_off[1025];
+    __shared__ int s_cnt[1024];
+    for (int c = threadIdx.x; c < cells; c += blockDim.x) s_cnt[c] = counts[c];      // one round trip, not one per cell
+    __syncthreads();
     if (threadIdx.x == 0) {
         int run = 0, alive = 0;
         for (int c = 0; c < cells; ++c) {            // cells <= 1024: a serial scan of a few hundred adds
             s_off[c] = run;
-            run += (counts[c] + chunk - 1) / chunk;
-            alive += counts[c];
+            run += (s_cnt[c] + chunk - 1) / chunk;
+            alive += s_cnt[c];
         }
         s_off[cells] = run;
         header[0] = run;
