@@ -21,8 +21,9 @@
 //
 // CTA = 17 warps, persistent over tiles (one CTA per SM):
 //   warps 12-15 stage A: the tile's NCHW floats arrive by cp.async, 2 (cin 32) or 5 (cin 16) tiles ahead -- one tile in
-//              flight per SM is 8-16 KB, which latency holds to ~1.7 TB/s; then optional ReLU, split, and both halves
-//              stored K-major with the 128-byte swizzle the MMA descriptors expect (a lane = a channel: conflict-free);
+//              flight per SM is 8-16 KB, which latency holds to ~1.7 TB/s; then a thread per pixel applies the optional
+//              ReLU, splits, and stores four channels per 16-byte store into the K-major, 128-byte-swizzled operand
+//              tiles the MMA descriptors expect (conflict-free: eight consecutive pixels hit the eight chunk slots);
 //   warp 16    one lane issues the MMAs: per 16-channel output group ("job") 3 passes x cin/8 k-steps of
 //              M128 x N144 x K8 into one of three TMEM accumulator slots, then commits;
 //   warps 0-11 three epilogue groups, one per accumulator slot (the epilogue is a long dependent chain per thread, so
