@@ -25,7 +25,15 @@ def bind_to_gpu_numa(device_index: int) -> Optional[List[int]]:
         import os
         import pynvml
         pynvml.nvmlInit()
-        handle = pynvml.nvmlDeviceGetHandleByIndex(device_index)
+        handle = None
+        try:        # CUDA ordinals follow CUDA_VISIBLE_DEVICES, NVML indices do not: identify the GPU by its PCI address
+            props = torch.cuda.get_device_properties(device_index)
+            bus_id = "%08x:%02x:%02x.0" % (props.pci_domain_id, props.pci_bus_id, props.pci_device_id)
+            handle = pynvml.nvmlDeviceGetHandleByPciBusId(bus_id.encode())
+        except Exception:
+            handle = None
+        if handle is None:
+            handle = pynvml.nvmlDeviceGetHandleByIndex(device_index)
         words = pynvml.nvmlDeviceGetCpuAffinity(handle, (os.cpu_count() + 63) // 64)
         cores = [64 * i + b for i, w in enumerate(words) for b in range(64) if (int(w) >> b) & 1]
         allowed = sorted(set(cores) & set(os.sched_getaffinity(0)))
